@@ -1,0 +1,172 @@
+/* spgx — C ABI of the B200-native SPG solver hot path (VBD sweep, XPBD projection, shared element evaluators).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++ or torch types.  The reference
+ * (alexrodag/spg @ 75122ce) has no FFI of its own; every entry point below names the reference C++
+ * interface it stands in for (paths relative to the reference root).  The C++ facade in
+ * include/spgx/spgx.hpp re-creates the reference's class surface (ParticleGroup, the energy classes'
+ * addStencil / preparePrecomputations, solver::VBD / solver::XPBD with step / addObject / setDt / ...)
+ * on top of these calls.
+ *
+ * Conventions: every function returning int returns 0 on success and a non-zero status otherwise;
+ * spgx_last_error() then returns the message a std::runtime_error in the reference would carry (the
+ * facade re-throws it).  Nothing throws across this boundary.  All host arrays are caller-owned and
+ * copied during the call; all device memory is owned by the library behind the opaque handles.
+ * Vertex data is fp64, 3 doubles per vertex (x, y, z); indices are int32.
+ * There is no CPU fallback: without a CUDA device every compute call fails with SPGX_ERR_CUDA.
+ */
+#ifndef SPGX_H
+#define SPGX_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPGX_OK 0
+#define SPGX_ERR_INVALID 1 /* std::runtime_error in the reference (validation) */
+#define SPGX_ERR_CUDA 2    /* CUDA runtime / driver failure, or no device */
+#define SPGX_ERR_STATE 3   /* call order violation (e.g. step before finalize) */
+#define SPGX_ERR_COMM 4    /* NCCL failure */
+
+/* Energy kinds (one per reference energy class on the hot path). Model parameters per stencil:
+ *  SPRING            spg/source/sim/energy/springEnergy.cpp:33            {restLength, stiffness}
+ *  SPRING_CONTINUUM  .../springContinuumEnergy.cpp:19                     {restLength, stiffness}
+ *  DISCRETE_BENDING  .../discreteBendingEnergy.cpp:33                     {restTheta, stiffness}
+ *  QUADRATIC_BENDING .../quadraticBendingEnergy.cpp:32                    {restTheta (must be 0), stiffness}
+ *  MEMBRANE_STVK     .../membraneStvkEnergy.cpp:31                        {young, poisson}
+ *  MEMBRANE_CHOI     .../membraneChoiEnergy.cpp:31                        {kWeft, kWarp, kBias}
+ *  MEMBRANE_BW       .../membraneBaraffWitkinEnergy.cpp:29                {kWeft, kWarp, kBias}
+ *  TET_STVK          .../stvkEnergy.cpp:68                                {young, poisson}
+ *  TET_SNH           .../stableNeoHookeanEnergy.cpp:64                    {young, poisson}
+ *  ANCHOR            .../springAnchorEnergy.cpp:29                        {anchor.x, anchor.y, anchor.z, stiffness}
+ */
+enum spgx_kind {
+    SPGX_SPRING = 0,
+    SPGX_SPRING_CONTINUUM = 1,
+    SPGX_DISCRETE_BENDING = 2,
+    SPGX_QUADRATIC_BENDING = 3,
+    SPGX_MEMBRANE_STVK = 4,
+    SPGX_MEMBRANE_CHOI = 5,
+    SPGX_MEMBRANE_BW = 6,
+    SPGX_TET_STVK = 7,
+    SPGX_TET_SNH = 8,
+    SPGX_ANCHOR = 9,
+    SPGX_KIND_COUNT = 10
+};
+
+enum spgx_solver_kind {
+    SPGX_VBD = 0,        /* spg/source/sim/solver/vbd.cpp:12-195 */
+    SPGX_XPBD = 1,       /* spg/source/sim/solver/xpbd.cpp:16-131, useParallelGaussSeidel = true */
+    SPGX_XPBD_SERIAL = 2 /* same with useParallelGaussSeidel = false (xpbd.cpp:96-102): stencils in index order */
+};
+
+typedef struct spgx_ctx spgx_ctx;     /* one CUDA device + stream (+ optional NCCL communicator) */
+typedef struct spgx_group spgx_group; /* a solver's copy of one ParticleGroup with its energies */
+
+typedef struct spgx_timings {
+    /* the four phases the reference prints under Verbosity::Performance (vbd.cpp:184-194, xpbd.cpp:125-130), ms */
+    double inertial_ms;
+    double solve_ms; /* "Coordinate block descent" / "Projection" */
+    double update_ms;
+    double total_ms;
+    int64_t kernel_launches; /* kernels launched by the last step call */
+} spgx_timings;
+
+/* ---- library ------------------------------------------------------------------------------- */
+const char *spgx_last_error(void); /* thread-local message of the last failed call */
+const char *spgx_version(void);
+int spgx_kind_stencil_size(int kind);     /* StencilBlockEnergy<S, C>::stencilSize(), energy.h:100 */
+int spgx_kind_num_constraints(int kind);  /* TnConstraints of the reference class */
+int spgx_kind_num_model_params(int kind); /* doubles per stencil expected by spgx_group_add_energy */
+int spgx_kind_num_record_params(int kind);/* doubles per stencil of the precomputed record (tests) */
+
+/* ---- pure host functions (no device needed) ------------------------------------------------- */
+/* coloring::colorVertices, spg/source/utils/graphColoring.cpp:72-84 (bit-exact, linear time).
+ * sets: nSets flat stencil arrays (entries[s], nEntries[s], stencilSizes[s]); colors: nVerts ints out. */
+int spgx_color_vertices(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                        const int32_t *stencilSizes, int32_t *colors);
+/* coloring::colorStencils, graphColoring.cpp:51-70. colors: nEntries / stencilSize ints out. */
+int spgx_color_stencils(const int32_t *entries, int64_t nEntries, int stencilSize, int32_t *colors);
+/* addStencil + preparePrecomputations of one energy kind on rest positions x0: writes
+ * nStencils * spgx_kind_num_record_params(kind) doubles. Same validation as the reference. */
+int spgx_prepare_energy(int kind, int nStencils, const int32_t *stencils, const double *modelParams,
+                        int nVerts, const double *x0, double *records);
+
+/* ---- context ------------------------------------------------------------------------------- */
+int spgx_ctx_create(int device, spgx_ctx **out);
+void spgx_ctx_destroy(spgx_ctx *ctx);
+int spgx_ctx_sync(spgx_ctx *ctx);
+
+/* page-lock / unlock a caller-owned host buffer so spgx_upload / spgx_download run at full PCIe rate */
+int spgx_host_register(void *ptr, uint64_t bytes);
+int spgx_host_unregister(void *ptr);
+
+/* ---- particle group (BaseSolver::addObject copies the group: baseSolver.cpp:10-14) ----------- */
+/* ParticleGroup::addParticle for nVerts particles (particleGroup.cpp:74-82): x current, x0 rest
+ * positions, mass (inverse mass w = mass == 0 ? 0 : 1/mass). Velocities start at zero. */
+int spgx_group_create(spgx_ctx *ctx, int nVerts, const double *x, const double *x0, const double *mass,
+                      spgx_group **out);
+void spgx_group_destroy(spgx_group *grp);
+/* energy->addStencil(...) for every stencil, pGroup.addEnergy(energy), energy->preparePrecomputations(pGroup).
+ * Energies are processed in the order they were added (vbd.cpp:128, xpbd.cpp:84). */
+int spgx_group_add_energy(spgx_group *grp, int kind, int nStencils, const int32_t *stencils,
+                          const double *modelParams, int *energyId);
+/* SpringAnchorEnergy::updateAnchor (springAnchorEnergy.h:13) and friends: overwrite `count` doubles of
+ * the precomputed record of one stencil starting at `offset`. Takes effect at the next step. */
+int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int offset, const double *values,
+                              int count);
+int spgx_energy_get_records(spgx_group *grp, int energyId, double *records);
+/* VBD::computeParallelVertexGroups + computeStencilInfoPerVertex (vbd.cpp:203-268) or
+ * XPBD::computeParallelStencilGroups (xpbd.cpp:133-160), then upload. Must be called once before stepping;
+ * calling it again re-does the precomputation (requirePrecomputationUpdate). */
+int spgx_group_finalize(spgx_group *grp, int solverKind);
+
+/* structure queries for the bit-exactness gates */
+int spgx_group_num_colors(spgx_group *grp, int energyId /* ignored for VBD */);
+int spgx_get_vertex_colors(spgx_group *grp, int32_t *colors /* nVerts */);
+/* VBD incidence table in the reference's order (vbd.cpp:231-268): for vertex v and energy e the entries
+ * [rowptr[v * nE + e], rowptr[v * nE + e + 1]) of (stencilIdx, localIdx) pairs. Pass entries == NULL to size. */
+int spgx_get_vertex_incidence(spgx_group *grp, int64_t *rowptr, int32_t *entries, int64_t *nEntries);
+int spgx_get_stencil_colors(spgx_group *grp, int energyId, int32_t *colors /* nStencils */);
+
+/* ---- state --------------------------------------------------------------------------------- */
+/* particleGroups()[i].positions() / velocities(): device -> host (either pointer may be NULL) */
+int spgx_download(spgx_group *grp, double *x, double *v);
+/* host -> device (callers may overwrite positions / velocities between steps, solverCompare.cpp:1388) */
+int spgx_upload(spgx_group *grp, const double *x, const double *v);
+/* ParticleGroup::reset (particleGroup.cpp:97-103): x <- xInitial, v <- 0 */
+int spgx_reset(spgx_group *grp);
+/* ParticleGroup::scaleMasses (particleGroup.cpp:105-113) */
+int spgx_scale_masses(spgx_group *grp, double factor);
+
+/* ---- solvers ------------------------------------------------------------------------------- */
+/* VBD::step (vbd.cpp:12-195): nFrames calls of step(), each `nsubsteps` substeps of dt/nsubsteps with
+ * `iterations` coloured sweeps. gravity: 3 doubles. Asynchronous on the context stream unless `sync`. */
+int spgx_vbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, const double *gravity, int nFrames,
+                  int sync);
+/* XPBD::step (xpbd.cpp:16-131). iterations == 1 is the reference ("small steps": one projection pass per
+ * substep, simplified numerator, energy.h:142-145); iterations > 1 keeps per-constraint lambda on device,
+ * reset every substep. */
+int spgx_xpbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, const double *gravity, int nFrames,
+                   int sync);
+int spgx_last_timings(spgx_group *grp, spgx_timings *out);
+/* 0: plain launches; 1 (default): the launch sequence of one step() is captured in a CUDA graph and replayed */
+int spgx_set_graph_mode(spgx_group *grp, int enabled);
+
+/* ---- per-element evaluators (tests; reference: energy.h:240-258, :117-153, :289) -------------- */
+/* accumulateVertexForce + accumulateVertexHessian of (stencil, local) on the CURRENT device positions:
+ * force3 = -dE/dx_v, hess9 = d2E/dx_v2 row-major. */
+int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, double *force3,
+                                   double *hess9);
+/* constraintsAndGradient: C (nC) and gradient (3S x nC row-major) on the current device positions */
+int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C, double *grad);
+
+/* ---- algorithmic byte model ---------------------------------- */
+/* bytes one VBD iteration (all colours) / one XPBD substep must move under the gather model */
+int spgx_model_bytes(spgx_group *grp, double *bytesPerIteration, double *bytesLowerBound);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPGX_H */

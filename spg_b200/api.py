@@ -1,0 +1,345 @@
+"""ctypes binding of include/spgx.h plus small Python classes mirroring the reference's solver surface
+(BaseSolver: addObject / setDt / setNumSubsteps / setGravity / step / reset, spg/include/spg/sim/solver/baseSolver.h:14-41;
+VBD::setIterations is the knob the reference leaves as a TODO at vbd.h:33).
+
+No arithmetic happens here. The library is loaded eagerly and a missing library is an ImportError: there is no
+CPU fallback for the product path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from . import scenes as _scenes
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libspgx.so"
+if not _LIB_PATH.exists():
+    raise ImportError(f"{_LIB_PATH} is missing: build it with `python -m spg_b200.build` "
+                      "(__graft_entry__.build()). There is no CPU fallback.")
+lib = C.CDLL(str(_LIB_PATH))
+
+SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL = 0, 1, 2
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+_lp = C.POINTER(C.c_int64)
+
+
+class Timings(C.Structure):
+    _fields_ = [("inertial_ms", C.c_double), ("solve_ms", C.c_double), ("update_ms", C.c_double),
+                ("total_ms", C.c_double), ("kernel_launches", C.c_int64)]
+
+
+# every symbol include/spgx.h declares, with its signature (tests/test_abi.py checks the list against the header)
+SIGNATURES = {
+    "spgx_last_error": (C.c_char_p, []),
+    "spgx_version": (C.c_char_p, []),
+    "spgx_kind_stencil_size": (C.c_int, [C.c_int]),
+    "spgx_kind_num_constraints": (C.c_int, [C.c_int]),
+    "spgx_kind_num_model_params": (C.c_int, [C.c_int]),
+    "spgx_kind_num_record_params": (C.c_int, [C.c_int]),
+    "spgx_color_vertices": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip]),
+    "spgx_color_stencils": (C.c_int, [_ip, C.c_int64, C.c_int, _ip]),
+    "spgx_prepare_energy": (C.c_int, [C.c_int, C.c_int, _ip, _dp, C.c_int, _dp, _dp]),
+    "spgx_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
+    "spgx_ctx_destroy": (None, [C.c_void_p]),
+    "spgx_ctx_sync": (C.c_int, [C.c_void_p]),
+    "spgx_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "spgx_host_unregister": (C.c_int, [C.c_void_p]),
+    "spgx_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
+    "spgx_group_destroy": (None, [C.c_void_p]),
+    "spgx_group_add_energy": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip, _dp, C.POINTER(C.c_int)]),
+    "spgx_energy_update_record": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, C.c_int]),
+    "spgx_energy_get_records": (C.c_int, [C.c_void_p, C.c_int, _dp]),
+    "spgx_group_finalize": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_group_num_colors": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_get_vertex_colors": (C.c_int, [C.c_void_p, _ip]),
+    "spgx_get_vertex_incidence": (C.c_int, [C.c_void_p, _lp, _ip, _lp]),
+    "spgx_get_stencil_colors": (C.c_int, [C.c_void_p, C.c_int, _ip]),
+    "spgx_download": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_upload": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_reset": (C.c_int, [C.c_void_p]),
+    "spgx_scale_masses": (C.c_int, [C.c_void_p, C.c_double]),
+    "spgx_vbd_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_int, _dp, C.c_int, C.c_int]),
+    "spgx_xpbd_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_int, _dp, C.c_int, C.c_int]),
+    "spgx_last_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
+    "spgx_set_graph_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_eval_vertex_force_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]),
+    "spgx_eval_constraints": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
+    "spgx_model_bytes": (C.c_int, [C.c_void_p, _dp, _dp]),
+}
+for _name, (_res, _args) in SIGNATURES.items():
+    _fn = getattr(lib, _name)
+    _fn.restype = _res
+    _fn.argtypes = _args
+
+
+class SpgxError(RuntimeError):
+    """What the C++ facade re-throws as std::runtime_error."""
+
+    def __init__(self, status: int, message: str):
+        super().__init__(message)
+        self.status = status
+
+
+def check(status: int) -> None:
+    if status != 0:
+        raise SpgxError(status, lib.spgx_last_error().decode())
+
+
+def _d(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _i(a):
+    return a.ctypes.data_as(_ip)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+# ---- pure host functions ---------------------------------------------------------------------------
+def color_vertices(n_verts: int, stencil_sets) -> np.ndarray:
+    """coloring::colorVertices (graphColoring.cpp:72-84). stencil_sets: list of [n, S] int arrays."""
+    sets = [_i32(s) for s in stencil_sets]
+    ptrs = (_ip * len(sets))(*[_i(s) for s in sets])
+    n_entries = np.array([s.size for s in sets], dtype=np.int64)
+    sizes = np.array([s.shape[1] for s in sets], dtype=np.int32)
+    colors = np.empty(n_verts, dtype=np.int32)
+    check(lib.spgx_color_vertices(n_verts, len(sets), ptrs, n_entries.ctypes.data_as(_lp), _i(sizes), _i(colors)))
+    return colors
+
+
+def color_stencils(stencils) -> np.ndarray:
+    """coloring::colorStencils (graphColoring.cpp:51-70). stencils: [n, S] int array."""
+    s = _i32(stencils)
+    colors = np.empty(s.shape[0], dtype=np.int32)
+    check(lib.spgx_color_stencils(_i(s), s.size, s.shape[1], _i(colors)))
+    return colors
+
+
+def prepare_energy(kind: int, stencils, params, x0) -> np.ndarray:
+    s, p, x0 = _i32(stencils), _f64(params), _f64(x0)
+    rec = np.empty((s.shape[0], lib.spgx_kind_num_record_params(kind)), dtype=np.float64)
+    check(lib.spgx_prepare_energy(kind, s.shape[0], _i(s), _d(p), x0.shape[0], _d(x0), _d(rec)))
+    return rec
+
+
+def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
+    """A page-locked numpy array (cudaHostRegister) for the end-to-end upload / download path."""
+    a = np.empty(shape, dtype=dtype)
+    check(lib.spgx_host_register(a.ctypes.data_as(C.c_void_p), a.nbytes))
+    return a
+
+
+# ---- device objects ----------------------------------------------------------------------------------
+class Context:
+    def __init__(self, device: int = 0):
+        self.handle = C.c_void_p()
+        check(lib.spgx_ctx_create(device, C.byref(self.handle)))
+        self.device = device
+
+    def sync(self):
+        check(lib.spgx_ctx_sync(self.handle))
+
+    def close(self):
+        if self.handle:
+            lib.spgx_ctx_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Group:
+    """A solver's device-resident copy of one ParticleGroup (BaseSolver::addObject, baseSolver.cpp:10-14)."""
+
+    def __init__(self, ctx: Context, x, x0, mass):
+        self.ctx = ctx
+        x, x0, mass = _f64(x), _f64(x0), _f64(mass)
+        self.n = int(mass.shape[0])
+        self.handle = C.c_void_p()
+        self.kinds = []
+        self.n_stencils = []
+        check(lib.spgx_group_create(ctx.handle, self.n, _d(x), _d(x0), _d(mass), C.byref(self.handle)))
+
+    @classmethod
+    def from_scene(cls, ctx: Context, scene: "_scenes.Scene") -> "Group":
+        g = cls(ctx, scene.x, scene.x0, scene.mass)
+        for e in scene.energies:
+            g.add_energy(e.kind, e.stencils, e.params)
+        return g
+
+    def add_energy(self, kind: int, stencils, params) -> int:
+        s, p = _i32(stencils), _f64(params)
+        eid = C.c_int(-1)
+        n = s.size // _scenes.STENCIL_SIZE[kind]
+        check(lib.spgx_group_add_energy(self.handle, kind, n, _i(s), _d(p), C.byref(eid)))
+        self.kinds.append(kind)
+        self.n_stencils.append(n)
+        return eid.value
+
+    def finalize(self, solver_kind: int):
+        check(lib.spgx_group_finalize(self.handle, solver_kind))
+
+    def records(self, eid: int) -> np.ndarray:
+        rec = np.empty((self.n_stencils[eid], lib.spgx_kind_num_record_params(self.kinds[eid])), dtype=np.float64)
+        check(lib.spgx_energy_get_records(self.handle, eid, _d(rec)))
+        return rec
+
+    def update_record(self, eid: int, stencil: int, offset: int, values):
+        v = _f64(values)
+        check(lib.spgx_energy_update_record(self.handle, eid, stencil, offset, _d(v), v.size))
+
+    def num_colors(self, eid: int = 0) -> int:
+        return lib.spgx_group_num_colors(self.handle, eid)
+
+    def vertex_colors(self) -> np.ndarray:
+        c = np.empty(self.n, dtype=np.int32)
+        check(lib.spgx_get_vertex_colors(self.handle, _i(c)))
+        return c
+
+    def vertex_incidence(self):
+        n = C.c_int64(0)
+        check(lib.spgx_get_vertex_incidence(self.handle, None, None, C.byref(n)))
+        rowptr = np.empty(self.n * len(self.kinds) + 1, dtype=np.int64)
+        entries = np.empty((n.value, 2), dtype=np.int32)
+        check(lib.spgx_get_vertex_incidence(self.handle, rowptr.ctypes.data_as(_lp), _i(entries), C.byref(n)))
+        return rowptr, entries
+
+    def stencil_colors(self, eid: int) -> np.ndarray:
+        c = np.empty(self.n_stencils[eid], dtype=np.int32)
+        check(lib.spgx_get_stencil_colors(self.handle, eid, _i(c)))
+        return c
+
+    def download(self, want_v: bool = True):
+        x = np.empty((self.n, 3), dtype=np.float64)
+        v = np.empty((self.n, 3), dtype=np.float64) if want_v else None
+        check(lib.spgx_download(self.handle, _d(x), _d(v)))
+        return x, v
+
+    def download_into(self, x, v=None):
+        check(lib.spgx_download(self.handle, _d(x), _d(v)))
+
+    def upload(self, x=None, v=None):
+        x = None if x is None else _f64(x)
+        v = None if v is None else _f64(v)
+        check(lib.spgx_upload(self.handle, _d(x), _d(v)))
+
+    def reset(self):
+        check(lib.spgx_reset(self.handle))
+
+    def scale_masses(self, factor: float):
+        check(lib.spgx_scale_masses(self.handle, factor))
+
+    def set_graph_mode(self, enabled: bool):
+        check(lib.spgx_set_graph_mode(self.handle, int(enabled)))
+
+    def vbd_step(self, dt, substeps, iterations, gravity=(0.0, -9.8, 0.0), frames=1, sync=True):
+        g = _f64(gravity)
+        check(lib.spgx_vbd_step(self.handle, dt, substeps, iterations, _d(g), frames, int(sync)))
+
+    def xpbd_step(self, dt, substeps, iterations=1, gravity=(0.0, -9.8, 0.0), frames=1, sync=True):
+        g = _f64(gravity)
+        check(lib.spgx_xpbd_step(self.handle, dt, substeps, iterations, _d(g), frames, int(sync)))
+
+    def timings(self) -> Timings:
+        t = Timings()
+        check(lib.spgx_last_timings(self.handle, C.byref(t)))
+        return t
+
+    def eval_vertex_force_hessian(self, eid: int, stencil: int, local: int):
+        f = np.empty(3)
+        h = np.empty((3, 3))
+        check(lib.spgx_eval_vertex_force_hessian(self.handle, eid, stencil, local, _d(f), _d(h)))
+        return f, h
+
+    def eval_constraints(self, eid: int, stencil: int):
+        kind = self.kinds[eid]
+        nc = lib.spgx_kind_num_constraints(kind)
+        k = 3 * _scenes.STENCIL_SIZE[kind]
+        c = np.empty(nc)
+        g = np.empty((k, nc))
+        check(lib.spgx_eval_constraints(self.handle, eid, stencil, _d(c), _d(g)))
+        return c, g
+
+    def model_bytes(self):
+        a, b = C.c_double(0), C.c_double(0)
+        check(lib.spgx_model_bytes(self.handle, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
+    def close(self):
+        if self.handle:
+            lib.spgx_group_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class _BaseSolver:
+    """BaseSolver surface (baseSolver.h:14-41) for one or more particle groups."""
+    kind = SPGX_VBD
+
+    def __init__(self, ctx: Context | None = None, device: int = 0):
+        self.ctx = ctx or Context(device)
+        self.groups: list[Group] = []
+        self._dt, self._substeps, self._gravity = 0.01, 1, (0.0, -9.8, 0.0)  # baseSolver.h:36-39
+        self._iterations = 1
+
+    def addObject(self, scene_or_group) -> Group:
+        g = scene_or_group if isinstance(scene_or_group, Group) else Group.from_scene(self.ctx, scene_or_group)
+        g.finalize(self.kind)
+        self.groups.append(g)
+        return g
+
+    def setDt(self, dt: float):
+        self._dt = float(dt)
+
+    def setNumSubsteps(self, n: int):
+        self._substeps = int(n)
+
+    def setGravity(self, g):
+        self._gravity = tuple(float(a) for a in g)
+
+    def setIterations(self, n: int):
+        self._iterations = int(n)
+
+    def particleGroups(self):
+        return self.groups
+
+    def reset(self):
+        for g in self.groups:
+            g.reset()
+
+
+class VBD(_BaseSolver):
+    kind = SPGX_VBD
+
+    def step(self, frames: int = 1, sync: bool = True):
+        for g in self.groups:
+            g.vbd_step(self._dt, self._substeps, self._iterations, self._gravity, frames, sync)
+
+
+class XPBD(_BaseSolver):
+    kind = SPGX_XPBD
+
+    def __init__(self, ctx=None, device: int = 0, useParallelGaussSeidel: bool = True):
+        super().__init__(ctx, device)
+        self.kind = SPGX_XPBD if useParallelGaussSeidel else SPGX_XPBD_SERIAL
+
+    def step(self, frames: int = 1, sync: bool = True):
+        for g in self.groups:
+            g.xpbd_step(self._dt, self._substeps, self._iterations, self._gravity, frames, sync)

@@ -1,0 +1,441 @@
+// C-ABI, part 1: library queries, pure-host structure functions, context, group construction and
+// finalize (colouring + incidence + upload).  See include/spgx.h for the reference interface each
+// entry point replaces.
+#include <algorithm>
+#include <cstring>
+
+#include "energy_prepare.h"
+#include "group.h"
+#include "host_build.h"
+
+namespace spgx
+{
+static thread_local std::string g_lastError;
+void setLastError(const std::string &msg)
+{
+    g_lastError = msg;
+}
+
+static void checkKind(int kind)
+{
+    if (kind < 0 || kind >= K_COUNT) throw std::runtime_error("unknown energy kind");
+}
+
+// bytes of the element record the gather model charges per incidence (SURVEY.md 8d / DESIGN.md)
+static double modelRecordBytes(int kind)
+{
+    switch (kind) {
+    case K_SPRING:
+    case K_SPRING_CONTINUUM: return 24;
+    case K_DISCRETE_BENDING: return 32;
+    case K_QUADRATIC_BENDING: return 56;
+    case K_MEMBRANE_STVK:
+    case K_MEMBRANE_CHOI:
+    case K_MEMBRANE_BW: return 68;
+    case K_TET_STVK:
+    case K_TET_SNH: return 112;
+    case K_ANCHOR: return 36;
+    default: return 0;
+    }
+}
+}  // namespace spgx
+
+using namespace spgx;
+
+extern "C" {
+
+const char *spgx_last_error(void)
+{
+    return g_lastError.c_str();
+}
+const char *spgx_version(void)
+{
+    return "spgx 0.1 (sm_100a)";
+}
+int spgx_kind_stencil_size(int kind)
+{
+    return (kind >= 0 && kind < K_COUNT) ? kindStencilSize(kind) : -1;
+}
+int spgx_kind_num_constraints(int kind)
+{
+    return kindNumConstraints(kind);
+}
+int spgx_kind_num_model_params(int kind)
+{
+    return kindNumModelParams(kind);
+}
+int spgx_kind_num_record_params(int kind)
+{
+    return kindNumParams(kind);
+}
+
+int spgx_color_vertices(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                        const int32_t *stencilSizes, int32_t *colors)
+{
+    return guarded([&] {
+        std::vector<FlatStencilsView> sets;
+        for (int s = 0; s < nSets; ++s) sets.push_back({entries[s], nEntries[s], stencilSizes[s]});
+        const auto c = colorVertices(nVerts, sets);
+        std::copy(c.begin(), c.end(), colors);
+    });
+}
+
+int spgx_color_stencils(const int32_t *entries, int64_t nEntries, int stencilSize, int32_t *colors)
+{
+    return guarded([&] {
+        const auto c = colorStencils({entries, nEntries, stencilSize});
+        std::copy(c.begin(), c.end(), colors);
+    });
+}
+
+int spgx_prepare_energy(int kind, int nStencils, const int32_t *stencils, const double *modelParams, int nVerts,
+                        const double *x0, double *records)
+{
+    return guarded([&] {
+        checkKind(kind);
+        const int S = kindStencilSize(kind), NP = kindNumParams(kind), NM = kindNumModelParams(kind);
+        for (int i = 0; i < nStencils; ++i) {
+            for (int s = 0; s < S; ++s)
+                if (stencils[i * S + s] < 0 || stencils[i * S + s] >= nVerts)
+                    throw std::runtime_error("stencil vertex index out of range");
+            prepareStencil(kind, stencils + static_cast<size_t>(i) * S, modelParams + static_cast<size_t>(i) * NM, x0,
+                           records + static_cast<size_t>(i) * NP);
+        }
+    });
+}
+
+int spgx_ctx_create(int device, spgx_ctx **out)
+{
+    return guarded([&] {
+        int count = 0;
+        cudaError_t err = cudaGetDeviceCount(&count);
+        if (err != cudaSuccess || count == 0)
+            throw CudaError(std::string("no CUDA device available (there is no CPU fallback): ") +
+                            cudaGetErrorString(err));
+        if (device < 0 || device >= count) throw CudaError("CUDA device index out of range");
+        SPGX_CUDA(cudaSetDevice(device));
+        auto *ctx = new spgx_ctx;
+        ctx->device = device;
+        SPGX_CUDA(cudaGetDeviceProperties(&ctx->prop, device));
+        SPGX_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        *out = ctx;
+    });
+}
+
+void spgx_ctx_destroy(spgx_ctx *ctx)
+{
+    if (!ctx) return;
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int spgx_ctx_sync(spgx_ctx *ctx)
+{
+    return guarded([&] { SPGX_CUDA(cudaStreamSynchronize(ctx->stream)); });
+}
+
+int spgx_host_register(void *ptr, uint64_t bytes)
+{
+    return guarded([&] { SPGX_CUDA(cudaHostRegister(ptr, bytes, cudaHostRegisterDefault)); });
+}
+int spgx_host_unregister(void *ptr)
+{
+    return guarded([&] { SPGX_CUDA(cudaHostUnregister(ptr)); });
+}
+
+int spgx_group_create(spgx_ctx *ctx, int nVerts, const double *x, const double *x0, const double *mass,
+                      spgx_group **out)
+{
+    return guarded([&] {
+        if (!ctx) throw StateError("null context");
+        if (nVerts < 0) throw std::runtime_error("negative vertex count");
+        auto *g = new spgx_group;
+        g->ctx = ctx;
+        g->nVerts = nVerts;
+        g->xInitial.assign(x, x + 3 * static_cast<size_t>(nVerts));
+        g->xPending = g->xInitial;
+        g->vPending.assign(3 * static_cast<size_t>(nVerts), 0.0);
+        g->x0.assign(x0, x0 + 3 * static_cast<size_t>(nVerts));
+        g->mass.assign(mass, mass + nVerts);
+        *out = g;
+    });
+}
+
+void spgx_group_destroy(spgx_group *grp)
+{
+    if (!grp) return;
+    cudaSetDevice(grp->ctx->device);
+    delete grp;
+}
+
+int spgx_group_add_energy(spgx_group *grp, int kind, int nStencils, const int32_t *stencils,
+                          const double *modelParams, int *energyId)
+{
+    return guarded([&] {
+        checkKind(kind);
+        if (static_cast<int>(grp->energies.size()) >= kMaxEnergies)
+            throw std::runtime_error("too many energies in one particle group");
+        EnergyState e;
+        e.kind = kind;
+        e.S = kindStencilSize(kind);
+        e.NP = kindNumParams(kind);
+        e.NC = kindNumConstraints(kind);
+        e.n = nStencils;
+        e.stencils.assign(stencils, stencils + static_cast<size_t>(nStencils) * e.S);
+        e.records.resize(static_cast<size_t>(nStencils) * e.NP);
+        const int NM = kindNumModelParams(kind);
+        for (int i = 0; i < nStencils; ++i) {
+            for (int s = 0; s < e.S; ++s) {
+                const int v = stencils[static_cast<size_t>(i) * e.S + s];
+                if (v < 0 || v >= grp->nVerts) throw std::runtime_error("stencil vertex index out of range");
+            }
+            prepareStencil(kind, stencils + static_cast<size_t>(i) * e.S, modelParams + static_cast<size_t>(i) * NM,
+                           grp->x0.data(), e.records.data() + static_cast<size_t>(i) * e.NP);
+        }
+        grp->energies.push_back(std::move(e));
+        grp->finalized = false;
+        if (energyId) *energyId = static_cast<int>(grp->energies.size()) - 1;
+    });
+}
+
+int spgx_energy_get_records(spgx_group *grp, int energyId, double *records)
+{
+    return guarded([&] {
+        const auto &e = grp->energies.at(energyId);
+        std::copy(e.records.begin(), e.records.end(), records);
+    });
+}
+
+int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int offset, const double *values, int count)
+{
+    return guarded([&] {
+        auto &e = grp->energies.at(energyId);
+        if (stencil < 0 || stencil >= e.n || offset < 0 || offset + count > e.NP)
+            throw std::runtime_error("record update out of range");
+        std::copy(values, values + count, e.records.begin() + static_cast<size_t>(stencil) * e.NP + offset);
+        if (grp->finalized) {
+            SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+            const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
+            SPGX_CUDA(cudaMemcpyAsync(e.d_records.ptr + static_cast<size_t>(pos) * e.NP + offset, values,
+                                      count * sizeof(double), cudaMemcpyHostToDevice, grp->ctx->stream));
+            SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
+        }
+    });
+}
+
+int spgx_group_finalize(spgx_group *grp, int solverKind)
+{
+    return guarded([&] {
+        if (solverKind != SPGX_VBD && solverKind != SPGX_XPBD && solverKind != SPGX_XPBD_SERIAL)
+            throw std::runtime_error("unknown solver kind");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        cudaStream_t st = grp->ctx->stream;
+        const int V = grp->nVerts;
+        // preserve current state across a re-finalize
+        std::vector<double> xh, vh;
+        if (grp->finalized || grp->d_x.ptr) {
+            xh.resize(3 * static_cast<size_t>(V));
+            vh.resize(3 * static_cast<size_t>(V));
+            if (spgx_download(grp, xh.data(), vh.data()) != SPGX_OK) throw CudaError(spgx_last_error());
+        } else {
+            xh = grp->xPending;
+            vh = grp->vPending;
+        }
+        grp->solverKind = solverKind;
+        if (grp->graphExec) {
+            cudaGraphExecDestroy(grp->graphExec);
+            grp->graphExec = nullptr;
+        }
+        const size_t nE = grp->energies.size();
+        std::vector<FlatStencilsView> sets;
+        for (auto &e : grp->energies) sets.push_back({e.stencils.data(), static_cast<int64_t>(e.stencils.size()), e.S});
+
+        grp->slot2vert.resize(V);
+        grp->vert2slot.resize(V);
+        grp->uniqueNeighbourSum = 0;
+        if (solverKind == SPGX_VBD) {
+            std::vector<Incidence> inc;
+            for (auto &fs : sets) inc.push_back(buildIncidence(V, fs));
+            grp->vertexColors = colorVertices(V, sets, &inc);  // vbd.cpp:203-229
+            groupByKey(grp->vertexColors, grp->slot2vert, grp->colorOffsets);
+            for (int s = 0; s < V; ++s) grp->vert2slot[grp->slot2vert[s]] = s;
+            // incidence in slot order (vbd.cpp:231-268 keeps ascending flat index per vertex and energy)
+            std::vector<int32_t> nbr;
+            for (size_t ei = 0; ei < nE; ++ei) {
+                auto &e = grp->energies[ei];
+                if (static_cast<uint64_t>(e.n) >= (1ull << 30)) throw std::runtime_error("too many stencils in one energy");
+                std::vector<uint32_t> rowptr(static_cast<size_t>(V) + 1, 0), entries(e.stencils.size());
+                uint32_t cursor = 0;
+                for (int s = 0; s < V; ++s) {
+                    const int v = grp->slot2vert[s];
+                    rowptr[s] = cursor;
+                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                        const int64_t flat = inc[ei].flat[q];
+                        entries[cursor++] = (static_cast<uint32_t>(flat / e.S) << 2) | static_cast<uint32_t>(flat % e.S);
+                    }
+                }
+                rowptr[V] = cursor;
+                std::vector<int32_t> slotStencils(e.stencils.size());
+                for (size_t q = 0; q < e.stencils.size(); ++q) slotStencils[q] = grp->vert2slot[e.stencils[q]];
+                e.d_stencils.upload(slotStencils, st);
+                e.d_records.upload(e.records, st);
+                e.d_rowptr.upload(rowptr, st);
+                e.d_entries.upload(entries, st);
+                e.order.clear();
+                e.positionOf.clear();
+                SPGX_CUDA(cudaStreamSynchronize(st));
+            }
+            // distinct stencil neighbours per vertex (for the byte model)
+            for (int v = 0; v < V; ++v) {
+                nbr.clear();
+                for (size_t ei = 0; ei < nE; ++ei) {
+                    const auto &e = grp->energies[ei];
+                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                        const int64_t base = (inc[ei].flat[q] / e.S) * e.S;
+                        for (int l = 0; l < e.S; ++l)
+                            if (e.stencils[base + l] != v) nbr.push_back(e.stencils[base + l]);
+                    }
+                }
+                std::sort(nbr.begin(), nbr.end());
+                grp->uniqueNeighbourSum += static_cast<double>(std::unique(nbr.begin(), nbr.end()) - nbr.begin());
+            }
+        } else {
+            for (int s = 0; s < V; ++s) grp->slot2vert[s] = grp->vert2slot[s] = s;
+            grp->vertexColors.clear();
+            grp->colorOffsets.clear();
+            for (size_t ei = 0; ei < nE; ++ei) {
+                auto &e = grp->energies[ei];
+                if (solverKind == SPGX_XPBD) {
+                    e.stencilColors = colorStencils(sets[ei]);  // xpbd.cpp:133-160
+                    groupByKey(e.stencilColors, e.order, e.colorOffsets);
+                } else {
+                    e.stencilColors.assign(e.n, 0);
+                    e.order.resize(e.n);
+                    for (int i = 0; i < e.n; ++i) e.order[i] = i;
+                    e.colorOffsets = {0, e.n};
+                }
+                e.positionOf.resize(e.n);
+                std::vector<int32_t> st2(e.stencils.size());
+                std::vector<double> rec2(e.records.size());
+                for (int pos = 0; pos < e.n; ++pos) {
+                    const int i = e.order[pos];
+                    e.positionOf[i] = pos;
+                    std::copy(e.stencils.begin() + static_cast<size_t>(i) * e.S,
+                              e.stencils.begin() + static_cast<size_t>(i + 1) * e.S, st2.begin() + static_cast<size_t>(pos) * e.S);
+                    std::copy(e.records.begin() + static_cast<size_t>(i) * e.NP,
+                              e.records.begin() + static_cast<size_t>(i + 1) * e.NP, rec2.begin() + static_cast<size_t>(pos) * e.NP);
+                }
+                e.d_stencils.upload(st2, st);
+                e.d_records.upload(rec2, st);
+                e.d_lambda.alloc(static_cast<size_t>(e.n) * e.NC);
+                e.d_rowptr.release();
+                e.d_entries.release();
+                SPGX_CUDA(cudaStreamSynchronize(st));
+            }
+        }
+        // state
+        const size_t n3 = 3 * static_cast<size_t>(V);
+        grp->d_x.alloc(n3);
+        grp->d_v.alloc(n3);
+        grp->d_xOld.alloc(n3);
+        grp->d_xInertial.alloc(n3);
+        grp->d_stage.alloc(n3);
+        grp->d_g.alloc(3);
+        grp->d_eval.alloc(64);
+        std::vector<double> ms(V), ws(V);
+        for (int s = 0; s < V; ++s) {
+            const double m = grp->mass[grp->slot2vert[s]];
+            ms[s] = m;
+            ws[s] = (m == 0) ? 0 : 1 / m;  // particleGroup.cpp:81
+        }
+        grp->d_mass.upload(ms, st);
+        grp->d_invMass.upload(ws, st);
+        grp->d_slot2vert.upload(grp->slot2vert, st);
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        if (!grp->evStart) {
+            SPGX_CUDA(cudaEventCreate(&grp->evStart));
+            SPGX_CUDA(cudaEventCreate(&grp->evStop));
+        }
+        grp->finalized = true;
+        if (spgx_upload(grp, xh.data(), vh.data()) != SPGX_OK) throw CudaError(spgx_last_error());
+        grp->xPending.clear();
+        grp->vPending.clear();
+    });
+}
+
+int spgx_group_num_colors(spgx_group *grp, int energyId)
+{
+    if (!grp || !grp->finalized) return -1;
+    if (grp->solverKind == SPGX_VBD) return static_cast<int>(grp->colorOffsets.size()) - 1;
+    if (energyId < 0 || energyId >= static_cast<int>(grp->energies.size())) return -1;
+    return static_cast<int>(grp->energies[energyId].colorOffsets.size()) - 1;
+}
+
+int spgx_get_vertex_colors(spgx_group *grp, int32_t *colors)
+{
+    return guarded([&] {
+        if (!grp->finalized || grp->solverKind != SPGX_VBD) throw StateError("group is not finalized for VBD");
+        std::copy(grp->vertexColors.begin(), grp->vertexColors.end(), colors);
+    });
+}
+
+int spgx_get_vertex_incidence(spgx_group *grp, int64_t *rowptr, int32_t *entries, int64_t *nEntries)
+{
+    return guarded([&] {
+        const int V = grp->nVerts;
+        const size_t nE = grp->energies.size();
+        std::vector<Incidence> inc;
+        for (auto &e : grp->energies)
+            inc.push_back(buildIncidence(V, {e.stencils.data(), static_cast<int64_t>(e.stencils.size()), e.S}));
+        int64_t n = 0;
+        for (int v = 0; v < V; ++v)
+            for (size_t ei = 0; ei < nE; ++ei) {
+                if (rowptr) rowptr[static_cast<size_t>(v) * nE + ei] = n;
+                const int S = grp->energies[ei].S;
+                for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                    if (entries) {
+                        entries[2 * n] = static_cast<int32_t>(inc[ei].flat[q] / S);
+                        entries[2 * n + 1] = static_cast<int32_t>(inc[ei].flat[q] % S);
+                    }
+                    ++n;
+                }
+            }
+        if (rowptr) rowptr[static_cast<size_t>(V) * nE] = n;
+        if (nEntries) *nEntries = n;
+    });
+}
+
+int spgx_get_stencil_colors(spgx_group *grp, int energyId, int32_t *colors)
+{
+    return guarded([&] {
+        if (!grp->finalized || grp->solverKind == SPGX_VBD) throw StateError("group is not finalized for XPBD");
+        const auto &e = grp->energies.at(energyId);
+        std::copy(e.stencilColors.begin(), e.stencilColors.end(), colors);
+    });
+}
+
+int spgx_model_bytes(spgx_group *grp, double *bytesPerIteration, double *bytesLowerBound)
+{
+    return guarded([&] {
+        if (!grp->finalized) throw StateError("group is not finalized");
+        const double V = grp->nVerts;
+        double gather = 0, lower = 0;
+        if (grp->solverKind == SPGX_VBD) {
+            gather = 92.0 * V + 24.0 * grp->uniqueNeighbourSum;
+            lower = (24.0 + 24.0 + 24.0 + 8.0) * V;
+            for (const auto &e : grp->energies) {
+                const double incidences = static_cast<double>(e.n) * e.S;
+                gather += incidences * (4.0 + modelRecordBytes(e.kind));
+                lower += modelRecordBytes(e.kind) * e.n + 4.0 * incidences;
+            }
+        } else {
+            gather = 6.0 * 24.0 * V;
+            for (const auto &e : grp->energies) gather += static_cast<double>(e.n) * (modelRecordBytes(e.kind) + e.S * 56.0);
+            lower = gather;
+        }
+        if (bytesPerIteration) *bytesPerIteration = gather;
+        if (bytesLowerBound) *bytesLowerBound = lower;
+    });
+}
+
+}  // extern "C"

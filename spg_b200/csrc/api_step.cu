@@ -1,0 +1,345 @@
+// C-ABI, part 2: state transfer, the VBD / XPBD step drivers (launch sequences, CUDA-graph capture),
+// timings and the per-element evaluators.
+#include <cstring>
+
+#include "energies.cuh"
+#include "energy_prepare.h"
+#include "group.h"
+
+using namespace spgx;
+
+namespace
+{
+void requireFinalized(spgx_group *grp, bool vbd)
+{
+    if (!grp || !grp->finalized) throw StateError("group is not finalized (call spgx_group_finalize first)");
+    if (vbd && grp->solverKind != SPGX_VBD) throw StateError("group was finalized for XPBD, not VBD");
+    if (!vbd && grp->solverKind == SPGX_VBD) throw StateError("group was finalized for VBD, not XPBD");
+}
+
+unsigned kindMaskOf(const spgx_group *grp)
+{
+    unsigned m = 0;
+    for (const auto &e : grp->energies) m |= 1u << e.kind;
+    return m;
+}
+
+// the launch sequence of ONE VBD::step() (vbd.cpp:46-183)
+void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaStream_t st, bool timePhases)
+{
+    const double dt = dtStep / nsub;
+    const double invdt = 1. / dt;
+    const double invdtSquared = invdt * invdt;
+    VbdArgs args{};
+    args.x = grp->d_x.ptr;
+    args.xInertial = grp->d_xInertial.ptr;
+    args.mass = grp->d_mass.ptr;
+    args.nEnergies = static_cast<int>(grp->energies.size());
+    for (int e = 0; e < args.nEnergies; ++e) {
+        const auto &en = grp->energies[e];
+        args.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr};
+    }
+    const unsigned mask = kindMaskOf(grp);
+    const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+    for (int s = 0; s < nsub; ++s) {
+        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->d_xInertial.ptr, grp->nVerts, dt, grp->graphKey.g,
+                      st);
+        grp->launchCounter++;
+        if (timePhases) grp->markPhase(st);
+        for (int it = 0; it < iters; ++it)
+            for (int c = 0; c < nColors; ++c) {
+                const int b = static_cast<int>(grp->colorOffsets[c]), e = static_cast<int>(grp->colorOffsets[c + 1]);
+                if (e > b) {
+                    launchVbdPass(args, mask, b, e, invdtSquared, st);
+                    grp->launchCounter++;
+                }
+            }
+        if (timePhases) grp->markPhase(st);
+        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nVerts, invdt, st);
+        grp->launchCounter++;
+        if (timePhases) grp->markPhase(st);
+    }
+}
+
+// the launch sequence of ONE XPBD::step() (xpbd.cpp:44-123)
+void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaStream_t st, bool timePhases)
+{
+    const double dt = dtStep / nsub;
+    const double invdt = 1 / dt;
+    const bool serial = grp->solverKind == SPGX_XPBD_SERIAL;
+    const bool useLambda = iters > 1;
+    for (int s = 0; s < nsub; ++s) {
+        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nVerts, dt, grp->graphKey.g, st);
+        grp->launchCounter++;
+        if (timePhases) grp->markPhase(st);
+        if (useLambda)
+            for (auto &en : grp->energies)
+                if (en.d_lambda.ptr) SPGX_CUDA(cudaMemsetAsync(en.d_lambda.ptr, 0, en.d_lambda.count * sizeof(double), st));
+        for (int it = 0; it < iters; ++it)
+            for (auto &en : grp->energies) {
+                const int nColors = static_cast<int>(en.colorOffsets.size()) - 1;
+                for (int c = 0; c < nColors; ++c) {
+                    const int b = static_cast<int>(en.colorOffsets[c]), e = static_cast<int>(en.colorOffsets[c + 1]);
+                    if (e > b) {
+                        launchXpbdPass(en.kind, grp->d_x.ptr, grp->d_invMass.ptr, en.d_stencils.ptr, en.d_records.ptr,
+                                       useLambda ? en.d_lambda.ptr : nullptr, b, e, dt, serial, st);
+                        grp->launchCounter++;
+                    }
+                }
+            }
+        if (timePhases) grp->markPhase(st);
+        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nVerts, invdt, st);
+        grp->launchCounter++;
+        if (timePhases) grp->markPhase(st);
+    }
+}
+
+void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const double *gravity, int nFrames, int sync)
+{
+    if (nsub < 1 || iters < 0 || nFrames < 0) throw std::runtime_error("invalid step parameters");
+    SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+    cudaStream_t st = grp->ctx->stream;
+    spgx_group::GraphKey key;
+    key.solver = solver;
+    key.nsub = nsub;
+    key.iters = iters;
+    key.dt = dt;
+    static const double defaultG[3] = {0, -9.8, 0};  // baseSolver.h:39
+    const double *g = gravity ? gravity : defaultG;
+    key.g[0] = g[0];
+    key.g[1] = g[1];
+    key.g[2] = g[2];
+    const bool keyChanged = !(key == grp->graphKey);
+    grp->graphKey = key;
+    grp->launchCounter = 0;
+    const bool timePhases = !grp->graphMode && sync;
+    grp->phaseCursor = 0;
+    auto enqueue = [&] {
+        if (timePhases) grp->markPhase(st);
+        if (solver == SPGX_VBD)
+            enqueueVbdFrame(grp, dt, nsub, iters, st, timePhases);
+        else
+            enqueueXpbdFrame(grp, dt, nsub, iters, st, timePhases);
+    };
+    SPGX_CUDA(cudaEventRecord(grp->evStart, st));
+    if (grp->graphMode) {
+        if (!grp->graphExec || keyChanged) {
+            if (grp->graphExec) {
+                cudaGraphExecDestroy(grp->graphExec);
+                grp->graphExec = nullptr;
+            }
+            cudaGraph_t graph = nullptr;
+            SPGX_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            try {
+                enqueue();
+            } catch (...) {
+                cudaStreamEndCapture(st, &graph);
+                if (graph) cudaGraphDestroy(graph);
+                throw;
+            }
+            SPGX_CUDA(cudaStreamEndCapture(st, &graph));
+            cudaError_t err = cudaGraphInstantiate(&grp->graphExec, graph, 0);
+            cudaGraphDestroy(graph);
+            if (err != cudaSuccess) throw CudaError(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(err));
+            grp->graphLaunches = grp->launchCounter;
+        }
+        for (int f = 0; f < nFrames; ++f) SPGX_CUDA(cudaGraphLaunch(grp->graphExec, st));
+        grp->launchCounter = grp->graphLaunches * nFrames;
+    } else {
+        for (int f = 0; f < nFrames; ++f) enqueue();
+    }
+    SPGX_CUDA(cudaEventRecord(grp->evStop, st));
+    SPGX_CUDA(cudaGetLastError());
+    grp->timings.kernel_launches = grp->launchCounter;
+    if (sync) {
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        float ms = 0;
+        SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
+        grp->timings.total_ms = ms;
+        grp->timings.inertial_ms = grp->timings.solve_ms = grp->timings.update_ms = 0;
+        if (timePhases) {
+            // events per frame: [frame start] then per substep (after predict, after sweeps, after finalize)
+            size_t q = 0;
+            for (int f = 0; f < nFrames; ++f) {
+                cudaEvent_t prev = grp->phaseEvents[q++];
+                for (int s = 0; s < nsub; ++s)
+                    for (int ph = 0; ph < 3; ++ph) {
+                        cudaEvent_t cur = grp->phaseEvents[q++];
+                        float pms = 0;
+                        SPGX_CUDA(cudaEventElapsedTime(&pms, prev, cur));
+                        (ph == 0 ? grp->timings.inertial_ms : ph == 1 ? grp->timings.solve_ms : grp->timings.update_ms) += pms;
+                        prev = cur;
+                    }
+            }
+        }
+    }
+}
+}  // namespace
+
+extern "C" {
+
+int spgx_download(spgx_group *grp, double *x, double *v)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        const size_t n3 = 3 * static_cast<size_t>(grp->nVerts);
+        if (!grp->d_x.ptr) {  // nothing on the device yet: the pending host state is the state
+            if (grp->xPending.size() != n3) throw StateError("group has no state");
+            if (x) std::copy(grp->xPending.begin(), grp->xPending.end(), x);
+            if (v) std::copy(grp->vPending.begin(), grp->vPending.end(), v);
+            return;
+        }
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        cudaStream_t st = grp->ctx->stream;
+        const bool identity = grp->solverKind != SPGX_VBD;
+        for (int k = 0; k < 2; ++k) {
+            double *dst = k == 0 ? x : v;
+            const double *src = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
+            if (!dst) continue;
+            if (!identity) {
+                // stage[vertex] = src[slot]
+                launchPermute3(src, grp->d_stage.ptr, grp->d_slot2vert.ptr, grp->nVerts, /*gather=*/false, st);
+                src = grp->d_stage.ptr;
+            }
+            SPGX_CUDA(cudaMemcpyAsync(dst, src, n3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            SPGX_CUDA(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int spgx_upload(spgx_group *grp, const double *x, const double *v)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        const size_t n3 = 3 * static_cast<size_t>(grp->nVerts);
+        if (!grp->finalized) {
+            if (x) grp->xPending.assign(x, x + n3);
+            if (v) grp->vPending.assign(v, v + n3);
+            return;
+        }
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        cudaStream_t st = grp->ctx->stream;
+        const bool identity = grp->solverKind != SPGX_VBD;
+        for (int k = 0; k < 2; ++k) {
+            const double *src = k == 0 ? x : v;
+            double *dst = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
+            if (!src) continue;
+            if (identity) {
+                SPGX_CUDA(cudaMemcpyAsync(dst, src, n3 * sizeof(double), cudaMemcpyHostToDevice, st));
+            } else {
+                SPGX_CUDA(cudaMemcpyAsync(grp->d_stage.ptr, src, n3 * sizeof(double), cudaMemcpyHostToDevice, st));
+                // dst[slot] = stage[slot2vert[slot]]
+                launchPermute3(grp->d_stage.ptr, dst, grp->d_slot2vert.ptr, grp->nVerts, /*gather=*/true, st);
+            }
+            SPGX_CUDA(cudaStreamSynchronize(st));
+        }
+    });
+}
+
+int spgx_reset(spgx_group *grp)
+{
+    return guarded([&] {
+        std::vector<double> zeros(3 * static_cast<size_t>(grp->nVerts), 0.0);
+        if (spgx_upload(grp, grp->xInitial.data(), zeros.data()) != SPGX_OK) throw CudaError(spgx_last_error());
+    });
+}
+
+int spgx_scale_masses(spgx_group *grp, double factor)
+{
+    return guarded([&] {
+        for (auto &m : grp->mass)
+            if (m != 0) m *= factor;
+        if (grp->finalized) {
+            SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+            std::vector<double> ms(grp->nVerts), ws(grp->nVerts);
+            for (int s = 0; s < grp->nVerts; ++s) {
+                const double m = grp->mass[grp->slot2vert[s]];
+                ms[s] = m;
+                ws[s] = (m == 0) ? 0 : 1 / m;
+            }
+            grp->d_mass.upload(ms, grp->ctx->stream);
+            grp->d_invMass.upload(ws, grp->ctx->stream);
+            SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
+            if (grp->graphExec) {  // buffers were re-allocated
+                cudaGraphExecDestroy(grp->graphExec);
+                grp->graphExec = nullptr;
+            }
+        }
+    });
+}
+
+int spgx_vbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, const double *gravity, int nFrames, int sync)
+{
+    return guarded([&] {
+        requireFinalized(grp, true);
+        runStep(grp, SPGX_VBD, dt, nsubsteps, iterations, gravity, nFrames, sync);
+    });
+}
+
+int spgx_xpbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, const double *gravity, int nFrames,
+                   int sync)
+{
+    return guarded([&] {
+        requireFinalized(grp, false);
+        if (iterations < 1) throw std::runtime_error("XPBD needs at least one iteration");
+        runStep(grp, grp->solverKind, dt, nsubsteps, iterations, gravity, nFrames, sync);
+    });
+}
+
+int spgx_last_timings(spgx_group *grp, spgx_timings *out)
+{
+    return guarded([&] {
+        if (!grp || !out) throw StateError("null argument");
+        *out = grp->timings;
+    });
+}
+
+int spgx_set_graph_mode(spgx_group *grp, int enabled)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        grp->graphMode = enabled != 0;
+    });
+}
+
+int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, double *force3, double *hess9)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        auto &e = grp->energies.at(energyId);
+        if (stencil < 0 || stencil >= e.n || local < 0 || local >= e.S) throw std::runtime_error("stencil out of range");
+        const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
+        cudaStream_t st = grp->ctx->stream;
+        launchEvalVertexForceHessian(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
+                                     e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, st);
+        double out[12];
+        SPGX_CUDA(cudaMemcpyAsync(out, grp->d_eval.ptr, sizeof(out), cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+        std::copy(out, out + 3, force3);
+        std::copy(out + 3, out + 12, hess9);
+    });
+}
+
+int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C, double *grad)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        auto &e = grp->energies.at(energyId);
+        if (stencil < 0 || stencil >= e.n) throw std::runtime_error("stencil out of range");
+        const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
+        cudaStream_t st = grp->ctx->stream;
+        launchEvalConstraints(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
+                              e.d_records.ptr + static_cast<size_t>(pos) * e.NP, grp->d_eval.ptr, grp->d_eval.ptr + 4, st);
+        double out[64];
+        SPGX_CUDA(cudaMemcpyAsync(out, grp->d_eval.ptr, sizeof(out), cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+        std::copy(out, out + e.NC, C);
+        std::copy(out + 4, out + 4 + 3 * e.S * e.NC, grad);
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+// Internal state behind the opaque C-ABI handles.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/spgx.h"
+#include "kernels.h"
+
+namespace spgx
+{
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+struct StateError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+#define SPGX_CUDA(call)                                                                                         \
+    do {                                                                                                        \
+        cudaError_t err__ = (call);                                                                             \
+        if (err__ != cudaSuccess)                                                                               \
+            throw spgx::CudaError(std::string(#call) + ": " + cudaGetErrorString(err__));                       \
+    } while (0)
+
+void setLastError(const std::string &msg);
+
+// run f, translate exceptions into status codes + thread-local message
+template <class F>
+int guarded(F &&f)
+{
+    try {
+        f();
+        return SPGX_OK;
+    } catch (const CudaError &e) {
+        setLastError(e.what());
+        return SPGX_ERR_CUDA;
+    } catch (const StateError &e) {
+        setLastError(e.what());
+        return SPGX_ERR_STATE;
+    } catch (const std::exception &e) {
+        setLastError(e.what());
+        return SPGX_ERR_INVALID;
+    } catch (...) {
+        setLastError("unknown exception");
+        return SPGX_ERR_INVALID;
+    }
+}
+
+template <class T>
+struct DevBuf {
+    T *ptr = nullptr;
+    size_t count = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    DevBuf(DevBuf &&o) noexcept : ptr(o.ptr), count(o.count)
+    {
+        o.ptr = nullptr;
+        o.count = 0;
+    }
+    DevBuf &operator=(DevBuf &&o) noexcept
+    {
+        if (this != &o) {
+            release();
+            ptr = o.ptr;
+            count = o.count;
+            o.ptr = nullptr;
+            o.count = 0;
+        }
+        return *this;
+    }
+    ~DevBuf() { release(); }
+    void release()
+    {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        count = 0;
+    }
+    void alloc(size_t n)
+    {
+        release();
+        if (n == 0) return;
+        SPGX_CUDA(cudaMalloc(&ptr, n * sizeof(T)));
+        count = n;
+    }
+    void upload(const std::vector<T> &h, cudaStream_t s)
+    {
+        alloc(h.size());
+        if (!h.empty()) SPGX_CUDA(cudaMemcpyAsync(ptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s));
+    }
+};
+}  // namespace spgx
+
+struct spgx_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaDeviceProp prop{};
+};
+
+namespace spgx
+{
+struct EnergyState {
+    int kind = 0, S = 0, NP = 0, NC = 0, n = 0;
+    std::vector<int32_t> stencils;  // original vertex ids, reference order
+    std::vector<double> records;    // NP per stencil, reference order
+    // --- device copies (stencils in slot ids; XPBD: both reordered by colour) ---
+    DevBuf<int32_t> d_stencils;
+    DevBuf<double> d_records;
+    // VBD
+    DevBuf<uint32_t> d_rowptr, d_entries;
+    // XPBD
+    std::vector<int32_t> stencilColors;  // per stencil, reference order
+    std::vector<int32_t> order;          // position -> stencil id
+    std::vector<int32_t> positionOf;     // stencil id -> position
+    std::vector<int64_t> colorOffsets;   // nColors + 1
+    DevBuf<double> d_lambda;
+};
+}  // namespace spgx
+
+struct spgx_group {
+    spgx_ctx *ctx = nullptr;
+    int nVerts = 0;
+    std::vector<double> x0, xInitial, mass;  // host, reference vertex order
+    std::vector<double> xPending, vPending;  // state held on host until finalize uploads it
+    std::vector<spgx::EnergyState> energies;
+
+    int solverKind = -1;
+    bool finalized = false;
+    // vertex colouring / ordering (VBD); identity ordering for XPBD
+    std::vector<int32_t> vertexColors;
+    std::vector<int32_t> slot2vert, vert2slot;
+    std::vector<int64_t> colorOffsets;
+    double uniqueNeighbourSum = 0;  // sum over vertices of the number of distinct stencil neighbours
+
+    spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
+    spgx::DevBuf<int32_t> d_slot2vert;
+    spgx::DevBuf<double> d_eval;
+
+    // CUDA graph of one step() (keyed by the step parameters)
+    bool graphMode = true;
+    cudaGraphExec_t graphExec = nullptr;
+    struct GraphKey {
+        int solver = -1, nsub = 0, iters = 0;
+        double dt = 0, g[3] = {0, 0, 0};
+        bool operator==(const GraphKey &o) const
+        {
+            return solver == o.solver && nsub == o.nsub && iters == o.iters && dt == o.dt && g[0] == o.g[0] &&
+                   g[1] == o.g[1] && g[2] == o.g[2];
+        }
+    } graphKey;
+    int64_t graphLaunches = 0;
+
+    spgx_timings timings{};
+    cudaEvent_t evStart = nullptr, evStop = nullptr;
+    int64_t launchCounter = 0;
+    // per-phase events (plain-launch mode only; a captured graph is timed as a whole)
+    std::vector<cudaEvent_t> phaseEvents;
+    size_t phaseCursor = 0;
+    void markPhase(cudaStream_t st)
+    {
+        if (phaseCursor == phaseEvents.size()) {
+            cudaEvent_t ev = nullptr;
+            if (cudaEventCreate(&ev) != cudaSuccess) throw spgx::CudaError("cudaEventCreate failed");
+            phaseEvents.push_back(ev);
+        }
+        if (cudaEventRecord(phaseEvents[phaseCursor++], st) != cudaSuccess) throw spgx::CudaError("cudaEventRecord failed");
+    }
+
+    ~spgx_group()
+    {
+        for (auto ev : phaseEvents) cudaEventDestroy(ev);
+        if (graphExec) cudaGraphExecDestroy(graphExec);
+        if (evStart) cudaEventDestroy(evStart);
+        if (evStop) cudaEventDestroy(evStop);
+    }
+};

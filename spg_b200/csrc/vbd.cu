@@ -1,0 +1,205 @@
+// Vertex Block Descent colour pass (reference: spg/source/sim/solver/vbd.cpp:99-157).
+//
+// One thread group of G lanes owns one vertex of the colour.  Lanes stride over the vertex's incident
+// (stencil, local) entries energy by energy (all lanes of a warp are inside the same energy kind at the
+// same time, so kinds never diverge), each lane evaluates the element energy with second-order duals
+// seeded on the OWNING vertex only (K = 3: value, 3-gradient, packed 3x3 Hessian) -- the diagonal block the
+// reference extracts from a full 3S x 3S autodiff pass (energy.h:240-258) -- and the lanes' partial
+// force / Hessian are reduced with warp shuffles.  Lane 0 adds the inertia term, applies the
+// det(H) > 1e-10 gate and the cofactor solve, and writes the vertex.
+#include "energies.cuh"
+#include "kernels.h"
+
+namespace spgx
+{
+namespace
+{
+using D2 = Dual<3, true>;
+
+template <int KIND>
+__device__ __forceinline__ void accumulateKind(const VbdEnergyDev &en, const double *__restrict__ x, int slot, int lane,
+                                               int G, V3d &f, Sym3 &H)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int S = EK::S;
+    const uint32_t rb = en.rowptr[slot], re = en.rowptr[slot + 1];
+    for (uint32_t q = rb + lane; q < re; q += G) {
+        const uint32_t ent = en.entries[q];
+        const uint32_t st = ent >> 2;
+        const int local = ent & 3u;
+        const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
+        V3<D2> xs[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const int id = ids[s];
+            const double px = x[3 * static_cast<size_t>(id)], py = x[3 * static_cast<size_t>(id) + 1],
+                         pz = x[3 * static_cast<size_t>(id) + 2];
+            const bool own = (s == local);
+            xs[s] = V3<D2>(D2(px, own ? 0 : -1), D2(py, own ? 1 : -1), D2(pz, own ? 2 : -1));
+        }
+        const D2 E = stencilEnergy<KIND, D2>(xs, en.records + static_cast<size_t>(st) * EK::NP);
+        f.x -= E.g[0];
+        f.y -= E.g[1];
+        f.z -= E.g[2];
+        H.xx += E.h[0];
+        H.xy += E.h[1];
+        H.xz += E.h[2];
+        H.yy += E.h[3];
+        H.yz += E.h[4];
+        H.zz += E.h[5];
+    }
+}
+
+template <unsigned MASK, int KIND>
+__device__ __forceinline__ void accumulateIfPresent(const VbdEnergyDev &en, const double *__restrict__ x, int slot,
+                                                    int lane, int G, V3d &f, Sym3 &H)
+{
+    if constexpr ((MASK >> KIND) & 1u) {
+        if (en.kind == KIND) accumulateKind<KIND>(en, x, slot, lane, G, f, H);
+    }
+}
+
+__device__ __forceinline__ double groupSum(double v, int G)
+{
+    for (int o = G >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <unsigned MASK, int G>
+__global__ void __launch_bounds__(128) vbdPassKernel(const VbdArgs a, int begin, int end, double invdtSquared)
+{
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    const int slot = begin + tid / G;
+    const int lane = tid % G;
+    const bool valid = slot < end;
+    V3d f(0.0, 0.0, 0.0);
+    Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (valid) {
+        for (int e = 0; e < a.nEnergies; ++e) {
+            const VbdEnergyDev &en = a.e[e];
+            accumulateIfPresent<MASK, K_SPRING>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_SPRING_CONTINUUM>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_DISCRETE_BENDING>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_QUADRATIC_BENDING>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_MEMBRANE_STVK>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_MEMBRANE_CHOI>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_MEMBRANE_BW>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_TET_STVK>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_TET_SNH>(en, a.x, slot, lane, G, f, H);
+            accumulateIfPresent<MASK, K_ANCHOR>(en, a.x, slot, lane, G, f, H);
+        }
+    }
+    if (G > 1) {
+        f.x = groupSum(f.x, G);
+        f.y = groupSum(f.y, G);
+        f.z = groupSum(f.z, G);
+        H.xx = groupSum(H.xx, G);
+        H.xy = groupSum(H.xy, G);
+        H.xz = groupSum(H.xz, G);
+        H.yy = groupSum(H.yy, G);
+        H.yz = groupSum(H.yz, G);
+        H.zz = groupSum(H.zz, G);
+    }
+    if (valid && lane == 0) {
+        const size_t o = 3 * static_cast<size_t>(slot);
+        const double px = a.x[o], py = a.x[o + 1], pz = a.x[o + 2];
+        const double mOverdtSquared = a.mass[slot] * invdtSquared;
+        // vbd.cpp:109-112, :123
+        f.x += -mOverdtSquared * (px - a.xInertial[o]);
+        f.y += -mOverdtSquared * (py - a.xInertial[o + 1]);
+        f.z += -mOverdtSquared * (pz - a.xInertial[o + 2]);
+        H.xx += mOverdtSquared;
+        H.yy += mOverdtSquared;
+        H.zz += mOverdtSquared;
+        const double d = det(H);
+        if (d > 1e-10) {  // vbd.cpp:139
+            const V3d dx = solveSym3(H, d, f);
+            a.x[o] = px + dx.x;
+            a.x[o + 1] = py + dx.y;
+            a.x[o + 2] = pz + dx.z;
+        }
+    }
+}
+
+template <unsigned MASK>
+void launchMasked(const VbdArgs &args, int begin, int end, double invdtSquared, cudaStream_t stream)
+{
+    constexpr int G = 4;
+    const int n = end - begin;
+    if (n <= 0) return;
+    const int threads = 128;
+    const long long total = static_cast<long long>(n) * G;
+    const int blocks = static_cast<int>((total + threads - 1) / threads);
+    vbdPassKernel<MASK, G><<<blocks, threads, 0, stream>>>(args, begin, end, invdtSquared);
+}
+
+constexpr unsigned bit(int k)
+{
+    return 1u << k;
+}
+constexpr unsigned kMaskCloth = bit(K_DISCRETE_BENDING) | bit(K_MEMBRANE_STVK) | bit(K_ANCHOR);
+constexpr unsigned kMaskClothQuad = bit(K_QUADRATIC_BENDING) | bit(K_SPRING) | bit(K_ANCHOR);
+constexpr unsigned kMaskSnh = bit(K_TET_SNH) | bit(K_ANCHOR);
+constexpr unsigned kMaskTetStvk = bit(K_TET_STVK) | bit(K_ANCHOR);
+constexpr unsigned kMaskAll = (1u << K_COUNT) - 1u;
+}  // namespace
+
+void launchVbdPass(const VbdArgs &args, unsigned kindMask, int begin, int end, double invdtSquared, cudaStream_t stream)
+{
+    auto subset = [&](unsigned m) { return (kindMask & ~m) == 0; };
+    if (subset(kMaskCloth))
+        launchMasked<kMaskCloth>(args, begin, end, invdtSquared, stream);
+    else if (subset(kMaskSnh))
+        launchMasked<kMaskSnh>(args, begin, end, invdtSquared, stream);
+    else if (subset(kMaskTetStvk))
+        launchMasked<kMaskTetStvk>(args, begin, end, invdtSquared, stream);
+    else if (subset(kMaskClothQuad))
+        launchMasked<kMaskClothQuad>(args, begin, end, invdtSquared, stream);
+    else
+        launchMasked<kMaskAll>(args, begin, end, invdtSquared, stream);
+}
+
+// ---- single-thread evaluator for the per-element parity tests (energy.h:240-258) -----------------
+namespace
+{
+template <int KIND>
+__device__ void evalOne(const double *x, const int32_t *ids, const double *rec, int local, double *out12)
+{
+    using EK = EnergyKind<KIND>;
+    V3<D2> xs[EK::S];
+    for (int s = 0; s < EK::S; ++s) {
+        const int id = ids[s];
+        const bool own = (s == local);
+        xs[s] = V3<D2>(D2(x[3 * id], own ? 0 : -1), D2(x[3 * id + 1], own ? 1 : -1), D2(x[3 * id + 2], own ? 2 : -1));
+    }
+    const D2 E = stencilEnergy<KIND, D2>(xs, rec);
+    for (int i = 0; i < 3; ++i) out12[i] = -E.g[i];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) out12[3 + 3 * i + j] = E.hess(i, j);
+}
+
+__global__ void evalVertexKernel(int kind, const double *x, const int32_t *ids, const double *rec, int local,
+                                 double *out12)
+{
+    switch (kind) {
+    case K_SPRING: evalOne<K_SPRING>(x, ids, rec, local, out12); break;
+    case K_SPRING_CONTINUUM: evalOne<K_SPRING_CONTINUUM>(x, ids, rec, local, out12); break;
+    case K_DISCRETE_BENDING: evalOne<K_DISCRETE_BENDING>(x, ids, rec, local, out12); break;
+    case K_QUADRATIC_BENDING: evalOne<K_QUADRATIC_BENDING>(x, ids, rec, local, out12); break;
+    case K_MEMBRANE_STVK: evalOne<K_MEMBRANE_STVK>(x, ids, rec, local, out12); break;
+    case K_MEMBRANE_CHOI: evalOne<K_MEMBRANE_CHOI>(x, ids, rec, local, out12); break;
+    case K_MEMBRANE_BW: evalOne<K_MEMBRANE_BW>(x, ids, rec, local, out12); break;
+    case K_TET_STVK: evalOne<K_TET_STVK>(x, ids, rec, local, out12); break;
+    case K_TET_SNH: evalOne<K_TET_SNH>(x, ids, rec, local, out12); break;
+    case K_ANCHOR: evalOne<K_ANCHOR>(x, ids, rec, local, out12); break;
+    default: break;
+    }
+}
+}  // namespace
+
+void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
+                                  double *out12, cudaStream_t stream)
+{
+    evalVertexKernel<<<1, 1, 0, stream>>>(kind, x, stencil, record, local, out12);
+}
+}  // namespace spgx
