@@ -1,0 +1,307 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the spgx hot path (contract: see DESIGN.md, "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl spgx|reference] [--config 3|5|4|2|1]
+
+A "step" is one Solver::step() (one frame, dt = 0.01) on the workload:
+  N = 1 : BASELINE config 3 — cloth 1024x1024 (1 048 576 vertices), StVK membrane + discrete bending + 2 corner
+          anchors, VBD 10 iterations/substep, 1 substep.
+  N > 1 : the same cloth with 1024 rows PER GPU ((1024 N) x 1024 vertices), row-strip domain decomposition with a
+          per-colour halo exchange (weak scaling); `--config 5` runs the fixed 4096x4096 cloth instead (strong scaling).
+metric = VBD vertex-iterations per second (vertices x iterations x substeps x frames / time), whole job.
+`value` is device-resident (state already in HBM), `e2e` goes through the public API with pinned host buffers
+(upload x, v -> step -> download x, v every frame).  `--impl reference` times the reference's own OpenMP CPU path
+(oracle/_ref, else the CPU port) on the host cores on a bounded sample (BASELINE config 1: the same scene at 64x64).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+for p in (str(ROOT), str(ROOT / "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+DT = 0.01
+CONFIGS = {
+    # name: (builder, args, solver, substeps, iterations)
+    1: ("cloth", (64, 64), "vbd", 1, 10),
+    2: ("cloth_xpbd", (256, 256), "xpbd", 20, 1),
+    3: ("cloth", (1024, 1024), "vbd", 1, 10),
+    4: ("beam", (149, 38, 38), "vbd", 1, 20),
+    5: ("cloth", (4096, 4096), "vbd", 1, 10),
+}
+
+
+def build_scene(builder, args):
+    from spg_b200 import scenes as S
+    if builder == "cloth":
+        return S.cloth(*args)
+    if builder == "cloth_xpbd":
+        return S.cloth(*args, S.K_SPRING, S.K_QUADRATIC_BENDING)
+    if builder == "beam":
+        return S.tet_beam(*args, S.K_TET_SNH)
+    raise ValueError(builder)
+
+
+def workload_name(builder, args, solver, substeps, iterations):
+    if builder == "cloth":
+        return (f"cloth {args[0]}x{args[1]} StVK membrane + discrete bending + 2 anchors, VBD {iterations} iters/substep, "
+                f"{substeps} substep, dt {DT}")
+    if builder == "cloth_xpbd":
+        return (f"cloth {args[0]}x{args[1]} springs + quadratic bending + 2 anchors, XPBD {substeps} substeps x "
+                f"{iterations} pass, dt {DT}")
+    return (f"Stable Neo-Hookean tet beam {args[0]}x{args[1]}x{args[2]} + anchors, VBD {iterations} iters/substep, "
+            f"{substeps} substep, dt {DT}")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device=0):
+        self.device = device
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons, power = [], None, set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [a.strip() for a in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax = float(f[2])
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[4:8]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
+                "power_w_max": max(power) if power else None, "samples": len(sm)}
+
+
+def peaks():
+    f = ROOT / "MEASURED_PEAKS.json"
+    if f.exists():
+        try:
+            return float(json.loads(f.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def time_oracle(cfg_id, frames, warmup, threads=None):
+    """The reference's OpenMP path (or the CPU port) on the host cores: returns (units/s, ms/frame, info)."""
+    import oracle_api
+    builder, args, solver, substeps, iterations = CONFIGS[cfg_id]
+    oracle = oracle_api.load()
+    if threads:
+        oracle.set_threads(threads)
+    cores = threads or oracle.max_threads()
+    sc = build_scene(builder, args)
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, 0 if solver == "vbd" else 1, DT, substeps, iterations)
+    osol.step(max(warmup, 1))  # first frame includes the (quadratic) colouring
+    t = time.perf_counter()
+    osol.step(frames)
+    el = time.perf_counter() - t
+    units = sc.n_vertices * iterations * substeps * frames if solver == "vbd" else \
+        sum(e.stencils.shape[0] for e in sc.energies) * iterations * substeps * frames
+    return units / el, 1e3 * el / frames, {"kind": oracle.kind, "cores": cores,
+                                            "sample": f"{workload_name(*CONFIGS[cfg_id])}, {frames} frames after "
+                                                      f"{max(warmup, 1)} warm-up"}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    builder, a, solver, substeps, iterations = CONFIGS[args.config]
+    # bounded sample of the workload: same scene family at the reference's own CPU-runnable size (config 1 / 2 at 64^2)
+    sample_cfg = 1 if solver == "vbd" and builder == "cloth" else args.config
+    if builder == "beam":
+        CONFIGS[40] = ("beam", (17, 5, 5), "vbd", substeps, iterations)
+        sample_cfg = 40
+    if builder == "cloth_xpbd":
+        CONFIGS[20] = ("cloth_xpbd", (64, 64), "xpbd", substeps, iterations)
+        sample_cfg = 20
+    value, ms, info = time_oracle(sample_cfg, args.steps, args.warmup)
+    unit = "vertex-iters/s" if solver == "vbd" else "constraint-projections/s"
+    line = {"impl": "reference", "metric": metric_name(solver), "value": value, "unit": unit, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(builder, a, solver, substeps, iterations),
+                       "note": "CPU arm timed on a bounded sample of the workload (rate is size-independent, SURVEY 8d)"},
+            "cpu_baseline": {"value": value, "unit": unit, **info},
+            "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def metric_name(solver):
+    return "vbd_vertex_iters_per_sec" if solver == "vbd" else "xpbd_constraint_projections_per_sec"
+
+
+def run_single(args):
+    from spg_b200 import api
+    builder, a, solver, substeps, iterations = CONFIGS[args.config]
+    sc = build_scene(builder, a)
+    ctx = api.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    g = api.Group.from_scene(ctx, sc)
+    g.finalize(api.SPGX_VBD if solver == "vbd" else api.SPGX_XPBD)
+    V = sc.n_vertices
+    n_stencils = sum(e.stencils.shape[0] for e in sc.energies)
+
+    def step(frames, sync=True):
+        if solver == "vbd":
+            g.vbd_step(DT, substeps, iterations, frames=frames, sync=sync)
+        else:
+            g.xpbd_step(DT, substeps, iterations, frames=frames, sync=sync)
+
+    units_per_frame = V * iterations * substeps if solver == "vbd" else n_stencils * iterations * substeps
+    unit = "vertex-iters/s" if solver == "vbd" else "constraint-projections/s"
+    bytes_iter, bytes_lower = g.model_bytes()  # per VBD iteration (all colours) / per XPBD substep
+
+    # ---- device-resident value: CUDA-graph replay of K frames, timed with CUDA events on the library's stream ----
+    step(max(args.warmup, 3))
+    sampler = ClockSampler(ctx.device)
+    sampler.start()
+    time.sleep(0.3)
+    step(args.steps)
+    t = g.timings()
+    total_ms = t.total_ms
+    launches = int(t.kernel_launches)
+    time.sleep(0.2)
+    clocks = sampler.stop()
+    value = units_per_frame * args.steps / (total_ms * 1e-3)
+
+    # ---- dominant kernel (the colour pass): plain launches with per-phase events over the same region ----
+    g.set_graph_mode(False)
+    step(1)
+    rf = max(min(args.steps, 5), 1)
+    step(rf)
+    tp = g.timings()
+    g.set_graph_mode(True)
+    passes_per_frame = substeps * iterations * (g.num_colors() if solver == "vbd" else
+                                                sum(g.num_colors(e) for e in range(len(sc.energies))))
+    solve_ms_per_frame = tp.solve_ms / rf
+    sweeps = iterations * substeps if solver == "vbd" else substeps
+    achieved = bytes_iter * sweeps / (solve_ms_per_frame * 1e-3) / 1e9
+    peak, peak_src = peaks()
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": None, "kernel": "vbdPassKernel" if solver == "vbd" else "xpbdPassKernel",
+                "launches_per_step": passes_per_frame,
+                "avg_launch_us": 1e3 * solve_ms_per_frame / max(passes_per_frame, 1),
+                "algorithmic_bytes_per_launch": bytes_iter * sweeps / max(passes_per_frame, 1),
+                "algorithmic_bytes_per_unit": bytes_iter * sweeps / units_per_frame,
+                "lower_bound_frac": bytes_lower * sweeps / (solve_ms_per_frame * 1e-3) / 1e9 / peak,
+                "kernel_share_of_step": solve_ms_per_frame / (tp.total_ms / rf), "peak_source": peak_src}
+    prof = ROOT / "profiles" / "traffic.json"
+    if prof.exists():
+        try:
+            roofline["traffic"] = json.loads(prof.read_text()).get(str(args.config))
+        except Exception:
+            pass
+
+    # ---- end to end through the public API: pinned host buffers, H2D + step + D2H every frame ----
+    xh, vh = api.pinned_empty((V, 3)), api.pinned_empty((V, 3))
+    g.download_into(xh, vh)
+    ef = max(min(args.steps, 10), 1)
+    for _ in range(2):
+        g.upload(xh, vh)
+        step(1)
+        g.download_into(xh, vh)
+    t0 = time.perf_counter()
+    for _ in range(ef):
+        g.upload(xh, vh)
+        step(1)
+        g.download_into(xh, vh)
+    e2e_s = time.perf_counter() - t0
+    e2e = {"value": units_per_frame * ef / e2e_s, "unit": unit, "h2d_bytes_per_step": int(xh.nbytes + vh.nbytes),
+           "d2h_bytes_per_step": int(xh.nbytes + vh.nbytes), "ms_per_step": 1e3 * e2e_s / ef, "steps": ef}
+    assert np.isfinite(xh).all()
+
+    # ---- CPU baseline on the host cores, bounded sample ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        try:
+            sample_cfg = 1 if (solver == "vbd" and builder == "cloth") else None
+            if builder == "beam":
+                CONFIGS[40] = ("beam", (17, 5, 5), "vbd", substeps, iterations)
+                sample_cfg = 40
+            if builder == "cloth_xpbd":
+                CONFIGS[20] = ("cloth_xpbd", (64, 64), "xpbd", substeps, iterations)
+                sample_cfg = 20
+            v_cpu, ms_cpu, info = time_oracle(sample_cfg, 3, 1)
+            cpu = {"value": v_cpu, "unit": unit, "ms_per_frame_on_sample": ms_cpu, **info}
+        except Exception as e:  # the oracle is test infrastructure; its absence must not hide the GPU number
+            cpu = {"value": None, "unit": unit, "error": str(e)}
+
+    line = {"metric": metric_name(solver), "value": value, "unit": unit, "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": workload_name(builder, a, solver, substeps, iterations), "vertices": V,
+                       "stencils": n_stencils, "colours": g.num_colors() if solver == "vbd" else None,
+                       "l2": "inputs larger than L2 (element records + incidence ~0.4 GB per iteration vs 126 MB L2)",
+                       "launch": "CUDA graph replay of one step()", "parallelism": "1 GPU"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="spgx", choices=["spgx", "reference"])
+    ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.gpus > 1 or world > 1:
+        from bench_multi import run_multi
+        return run_multi(args)
+    return run_single(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -156,9 +156,10 @@ int spgx_set_graph_mode(spgx_group *grp, int enabled);
 
 /* ---- per-element evaluators (tests; reference: energy.h:240-258, :117-153, :289) -------------- */
 /* accumulateVertexForce + accumulateVertexHessian of (stencil, local) on the CURRENT device positions:
- * force3 = -dE/dx_v, hess9 = d2E/dx_v2 row-major. */
-int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, double *force3,
-                                   double *hess9);
+ * force3 = -dE/dx_v, hess9 = d2E/dx_v2 row-major. handDerived = 0: the generic dual-number evaluator;
+ * 1: the kind's hand-derived override when it has one (what the VBD kernel runs), else the generic one. */
+int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, int handDerived,
+                                   double *force3, double *hess9);
 /* constraintsAndGradient: C (nC) and gradient (3S x nC row-major) on the current device positions */
 int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C, double *grad);
 

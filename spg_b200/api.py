@@ -65,7 +65,7 @@ SIGNATURES = {
     "spgx_xpbd_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_int, _dp, C.c_int, C.c_int]),
     "spgx_last_timings": (C.c_int, [C.c_void_p, C.POINTER(Timings)]),
     "spgx_set_graph_mode": (C.c_int, [C.c_void_p, C.c_int]),
-    "spgx_eval_vertex_force_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]),
+    "spgx_eval_vertex_force_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]),
     "spgx_eval_constraints": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "spgx_model_bytes": (C.c_int, [C.c_void_p, _dp, _dp]),
 }
@@ -257,10 +257,10 @@ class Group:
         check(lib.spgx_last_timings(self.handle, C.byref(t)))
         return t
 
-    def eval_vertex_force_hessian(self, eid: int, stencil: int, local: int):
+    def eval_vertex_force_hessian(self, eid: int, stencil: int, local: int, hand_derived: bool = True):
         f = np.empty(3)
         h = np.empty((3, 3))
-        check(lib.spgx_eval_vertex_force_hessian(self.handle, eid, stencil, local, _d(f), _d(h)))
+        check(lib.spgx_eval_vertex_force_hessian(self.handle, eid, stencil, local, int(hand_derived), _d(f), _d(h)))
         return f, h
 
     def eval_constraints(self, eid: int, stencil: int):

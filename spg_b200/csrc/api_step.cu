@@ -302,7 +302,8 @@ int spgx_set_graph_mode(spgx_group *grp, int enabled)
     });
 }
 
-int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, double *force3, double *hess9)
+int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, int local, int handDerived,
+                                   double *force3, double *hess9)
 {
     return guarded([&] {
         if (!grp || !grp->finalized) throw StateError("group is not finalized");
@@ -312,7 +313,8 @@ int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, i
         const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
         cudaStream_t st = grp->ctx->stream;
         launchEvalVertexForceHessian(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
-                                     e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, st);
+                                     e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, handDerived != 0,
+                                     st);
         double out[12];
         SPGX_CUDA(cudaMemcpyAsync(out, grp->d_eval.ptr, sizeof(out), cudaMemcpyDeviceToHost, st));
         SPGX_CUDA(cudaStreamSynchronize(st));

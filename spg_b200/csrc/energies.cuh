@@ -29,6 +29,28 @@ enum Kind : int {
 template <int KIND>
 struct EnergyKind;
 
+// accumulate the symmetric outer product scale * (u v^T + v u^T) into H
+SPGX_HD void addSymOuter2(Sym3 &H, const V3d &u, const V3d &v, double scale)
+{
+    H.xx += scale * (2.0 * u.x * v.x);
+    H.yy += scale * (2.0 * u.y * v.y);
+    H.zz += scale * (2.0 * u.z * v.z);
+    H.xy += scale * (u.x * v.y + u.y * v.x);
+    H.xz += scale * (u.x * v.z + u.z * v.x);
+    H.yz += scale * (u.y * v.z + u.z * v.y);
+}
+// accumulate scale * u u^T into H
+SPGX_HD void addOuter(Sym3 &H, const V3d &u, double scale)
+{
+    const double sx = scale * u.x, sy = scale * u.y, sz = scale * u.z;
+    H.xx += sx * u.x;
+    H.xy += sx * u.y;
+    H.xz += sx * u.z;
+    H.yy += sy * u.y;
+    H.yz += sy * u.z;
+    H.zz += sz * u.z;
+}
+
 // deformation gradient columns of a triangle: F = [x1-x0, x2-x0] * Dinv, Dinv row-major 2x2 in p[0..3]
 template <class T>
 SPGX_HD void membraneF(const V3<T> *x, const double *p, V3<T> &F0, V3<T> &F1)
@@ -100,6 +122,58 @@ struct EnergyKind<K_DISCRETE_BENDING> {
     }
     SPGX_HD static double K(const double *p, int, int) { return p[1]; }
     SPGX_HD static double alpha(const double *p, int, int) { return p[2]; }
+
+    // Hand-derived override of the VBD vertex block (north_star: "hand-derived overrides where ncu shows
+    // register or spill pressure"): g += dE/dx_local, H += d2E/dx_local^2 for E = K/2 (theta - theta0)^2, i.e.
+    //   g = K d grad(theta),  H = K (grad grad^T + d Hess(theta)),  d = theta - theta0.
+    // With e = x1 - x0, (a, b) = (x2, x3) - q (q = x1, or x0 when the owner is x1), N1 = e x a, N2 = b x e:
+    //   theta = atan2(-|e| N1.b, N1.N2)          [(N1 x N2).e = -|e|^2 N1.b]
+    //   owner x2: grad = -|e| N1/|N1|^2,  Hess = -|e|/|N1|^4 (N1 T^T + T N1^T), T = e x N1   (x3: N2, sign +)
+    //   owner x0/x1: grad = -+(phi_a W1 + phi_b W2), W = N/|N|^2, phi_a = a.e/|e|, and
+    //     Hess = sym(W1 dphi_a^T) + sym(W2 dphi_b^T) - phi_a (t1 N1^T + N1 t1^T)/|N1|^4 + phi_b (t2 N2^T + N2 t2^T)/|N2|^4
+    //     with dphi_a = a/|e| - e (a.e)/|e|^3, t1 = a x N1, t2 = b x N2.
+    // Equal to the autodiff block of the constraint above up to rounding (tests/test_gpu_elements.py).
+    static constexpr bool kHandDerived = true;
+    SPGX_HD static void vertexGradHess(const V3d *x, const double *p, int local, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d e = x[1] - x[0];
+        const V3d q = (local == 1) ? x[0] : x[1];
+        const V3d a = x[2] - q, b = x[3] - q;
+        const V3d N1 = cross(e, a), N2 = cross(b, e);
+        const double ee = dot(e, e);
+        const double ie = rsqrt(ee);
+        const double le = ee * ie;
+        const double d = ::atan2(-le * dot(N1, b), dot(N1, N2)) - p[0];
+        const double K = p[1];
+        const double Kd = K * d;
+        V3d g;  // grad theta
+        if (local >= 2) {
+            const V3d N = (local == 2) ? N1 : N2;
+            const double i = 1.0 / dot(N, N);
+            const double c = -le * i;
+            g = N * c;
+            const V3d T = cross(e, N);
+            addSymOuter2(HAcc, N, T, (local == 2 ? Kd : -Kd) * c * i);
+        } else {
+            const double i1 = 1.0 / dot(N1, N1), i2 = 1.0 / dot(N2, N2);
+            const double ae = dot(a, e), be = dot(b, e);
+            const double phia = ae * ie, phib = be * ie;
+            const double ie3 = ie * ie * ie;
+            const V3d W1 = N1 * i1, W2 = N2 * i2;
+            const V3d ga = a * ie - e * (ae * ie3), gb = b * ie - e * (be * ie3);
+            const V3d sumW = W1 * phia + W2 * phib;
+            g = (local == 0) ? -sumW : sumW;
+            const V3d t1 = cross(a, N1), t2 = cross(b, N2);
+            addSymOuter2(HAcc, W1, ga, 0.5 * Kd);
+            addSymOuter2(HAcc, W2, gb, 0.5 * Kd);
+            addSymOuter2(HAcc, t1, N1, -Kd * phia * i1 * i1);
+            addSymOuter2(HAcc, t2, N2, Kd * phib * i2 * i2);
+        }
+        gAcc.x += Kd * g.x;
+        gAcc.y += Kd * g.y;
+        gAcc.z += Kd * g.z;
+        addOuter(HAcc, g, K);
+    }
 };
 
 // ---- QuadraticBendingEnergy (quadraticBendingEnergy.cpp:9-29): C = L x, L = [c0 I, c1 I, c2 I, c3 I].
@@ -142,6 +216,34 @@ struct EnergyKind<K_MEMBRANE_STVK> {
     }
     SPGX_HD static double K(const double *p, int i, int j) { return pat(p + 4, i, j); }
     SPGX_HD static double alpha(const double *p, int i, int j) { return pat(p + 7, i, j); }
+
+    // Hand-derived VBD vertex block. With (ga, gb) the owner's row of the shape-gradient matrix
+    // (F = sum_s x_s g_s^T: g_1 = Dinv row 0, g_2 = Dinv row 1, g_0 = -g_1 - g_2), s = K C and
+    //   u0 = ga F0, u1 = gb F1, u2 = gb F0 + ga F1           (dC_i = u_i . dx)
+    //   grad = sum_i s_i u_i,   Hess = sum_ij K_ij u_i u_j^T + (s0 ga^2 + s1 gb^2 + 2 s2 ga gb) I.
+    static constexpr bool kHandDerived = true;
+    SPGX_HD static void vertexGradHess(const V3d *x, const double *p, int local, V3d &gAcc, Sym3 &HAcc)
+    {
+        V3d F0, F1;
+        membraneF(x, p, F0, F1);
+        const double C0 = 0.5 * (dot(F0, F0) - 1.0), C1 = 0.5 * (dot(F1, F1) - 1.0), C2 = dot(F0, F1);
+        const double K00 = p[4], K01 = p[5], K22 = p[6];
+        const double s0 = K00 * C0 + K01 * C1, s1 = K01 * C0 + K00 * C1, s2 = K22 * C2;
+        const double ga = (local == 0) ? -(p[0] + p[2]) : (local == 1 ? p[0] : p[2]);
+        const double gb = (local == 0) ? -(p[1] + p[3]) : (local == 1 ? p[1] : p[3]);
+        const V3d u0 = F0 * ga, u1 = F1 * gb, u2 = F0 * gb + F1 * ga;
+        gAcc.x += s0 * u0.x + s1 * u1.x + s2 * u2.x;
+        gAcc.y += s0 * u0.y + s1 * u1.y + s2 * u2.y;
+        gAcc.z += s0 * u0.z + s1 * u1.z + s2 * u2.z;
+        const V3d w0 = u0 * K00 + u1 * K01, w1 = u0 * K01 + u1 * K00, w2 = u2 * K22;
+        const double geo = s0 * ga * ga + s1 * gb * gb + 2.0 * s2 * ga * gb;
+        HAcc.xx += u0.x * w0.x + u1.x * w1.x + u2.x * w2.x + geo;
+        HAcc.yy += u0.y * w0.y + u1.y * w1.y + u2.y * w2.y + geo;
+        HAcc.zz += u0.z * w0.z + u1.z * w1.z + u2.z * w2.z + geo;
+        HAcc.xy += u0.x * w0.y + u1.x * w1.y + u2.x * w2.y;
+        HAcc.xz += u0.x * w0.z + u1.x * w1.z + u2.x * w2.z;
+        HAcc.yz += u0.y * w0.z + u1.y * w1.z + u2.y * w2.z;
+    }
 };
 
 // ---- MembraneChoiEnergy (membraneChoiEnergy.cpp:9-28).  p = {Dinv(4), K0..K3, a0..a3} (diagonal)
@@ -307,6 +409,16 @@ SPGX_HD T stencilEnergy(const V3<T> *x, const double *p)
         return 0.5 * e;
     }
 }
+
+// does the kind carry a hand-derived vertexGradHess override?
+template <class EK, class = void>
+struct HasHandDerived {
+    static constexpr bool value = false;
+};
+template <class EK>
+struct HasHandDerived<EK, decltype(void(EK::kHandDerived))> {
+    static constexpr bool value = EK::kHandDerived;
+};
 
 SPGX_HD int kindStencilSize(int kind)
 {

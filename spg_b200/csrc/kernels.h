@@ -44,7 +44,7 @@ void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *s
 
 // single-thread evaluators for the per-element parity tests
 void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
-                                  double *out12, cudaStream_t stream);
+                                  double *out12, bool handDerived, cudaStream_t stream);
 void launchEvalConstraints(int kind, const double *x, const int32_t *stencil, const double *record, double *outC,
                            double *outGrad, cudaStream_t stream);
 }  // namespace spgx

@@ -18,7 +18,7 @@ using D2 = Dual<3, true>;
 
 template <int KIND>
 __device__ __forceinline__ void accumulateKind(const VbdEnergyDev &en, const double *__restrict__ x, int slot, int lane,
-                                               int G, V3d &f, Sym3 &H)
+                                               int G, V3d &g, Sym3 &H)
 {
     using EK = EnergyKind<KIND>;
     constexpr int S = EK::S;
@@ -28,25 +28,34 @@ __device__ __forceinline__ void accumulateKind(const VbdEnergyDev &en, const dou
         const uint32_t st = ent >> 2;
         const int local = ent & 3u;
         const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
-        V3<D2> xs[S];
+        const double *rec = en.records + static_cast<size_t>(st) * EK::NP;
+        if constexpr (HasHandDerived<EK>::value) {
+            V3d xs[S];
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
-            const int id = ids[s];
-            const double px = x[3 * static_cast<size_t>(id)], py = x[3 * static_cast<size_t>(id) + 1],
-                         pz = x[3 * static_cast<size_t>(id) + 2];
-            const bool own = (s == local);
-            xs[s] = V3<D2>(D2(px, own ? 0 : -1), D2(py, own ? 1 : -1), D2(pz, own ? 2 : -1));
+            for (int s = 0; s < S; ++s) {
+                const size_t o = 3 * static_cast<size_t>(ids[s]);
+                xs[s] = V3d(x[o], x[o + 1], x[o + 2]);
+            }
+            EK::vertexGradHess(xs, rec, local, g, H);
+        } else {
+            V3<D2> xs[S];
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const size_t o = 3 * static_cast<size_t>(ids[s]);
+                const bool own = (s == local);
+                xs[s] = V3<D2>(D2(x[o], own ? 0 : -1), D2(x[o + 1], own ? 1 : -1), D2(x[o + 2], own ? 2 : -1));
+            }
+            const D2 E = stencilEnergy<KIND, D2>(xs, rec);
+            g.x += E.g[0];
+            g.y += E.g[1];
+            g.z += E.g[2];
+            H.xx += E.h[0];
+            H.xy += E.h[1];
+            H.xz += E.h[2];
+            H.yy += E.h[3];
+            H.yz += E.h[4];
+            H.zz += E.h[5];
         }
-        const D2 E = stencilEnergy<KIND, D2>(xs, en.records + static_cast<size_t>(st) * EK::NP);
-        f.x -= E.g[0];
-        f.y -= E.g[1];
-        f.z -= E.g[2];
-        H.xx += E.h[0];
-        H.xy += E.h[1];
-        H.xz += E.h[2];
-        H.yy += E.h[3];
-        H.yz += E.h[4];
-        H.zz += E.h[5];
     }
 }
 
@@ -104,10 +113,10 @@ __global__ void __launch_bounds__(128) vbdPassKernel(const VbdArgs a, int begin,
         const size_t o = 3 * static_cast<size_t>(slot);
         const double px = a.x[o], py = a.x[o + 1], pz = a.x[o + 2];
         const double mOverdtSquared = a.mass[slot] * invdtSquared;
-        // vbd.cpp:109-112, :123
-        f.x += -mOverdtSquared * (px - a.xInertial[o]);
-        f.y += -mOverdtSquared * (py - a.xInertial[o + 1]);
-        f.z += -mOverdtSquared * (pz - a.xInertial[o + 2]);
+        // f holds the accumulated energy gradient: force = -gradient; inertia term of vbd.cpp:109-112, :123
+        f.x = -f.x - mOverdtSquared * (px - a.xInertial[o]);
+        f.y = -f.y - mOverdtSquared * (py - a.xInertial[o + 1]);
+        f.z = -f.z - mOverdtSquared * (pz - a.xInertial[o + 2]);
         H.xx += mOverdtSquared;
         H.yy += mOverdtSquared;
         H.zz += mOverdtSquared;
@@ -163,9 +172,23 @@ void launchVbdPass(const VbdArgs &args, unsigned kindMask, int begin, int end, d
 namespace
 {
 template <int KIND>
-__device__ void evalOne(const double *x, const int32_t *ids, const double *rec, int local, double *out12)
+__device__ void evalOne(const double *x, const int32_t *ids, const double *rec, int local, double *out12, bool fast)
 {
     using EK = EnergyKind<KIND>;
+    if constexpr (HasHandDerived<EK>::value) {
+        if (fast) {
+            V3d xs[EK::S];
+            for (int s = 0; s < EK::S; ++s) xs[s] = V3d(x[3 * ids[s]], x[3 * ids[s] + 1], x[3 * ids[s] + 2]);
+            V3d g(0.0, 0.0, 0.0);
+            Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+            EK::vertexGradHess(xs, rec, local, g, H);
+            out12[0] = -g.x, out12[1] = -g.y, out12[2] = -g.z;
+            out12[3] = H.xx, out12[4] = H.xy, out12[5] = H.xz;
+            out12[6] = H.xy, out12[7] = H.yy, out12[8] = H.yz;
+            out12[9] = H.xz, out12[10] = H.yz, out12[11] = H.zz;
+            return;
+        }
+    }
     V3<D2> xs[EK::S];
     for (int s = 0; s < EK::S; ++s) {
         const int id = ids[s];
@@ -179,27 +202,27 @@ __device__ void evalOne(const double *x, const int32_t *ids, const double *rec, 
 }
 
 __global__ void evalVertexKernel(int kind, const double *x, const int32_t *ids, const double *rec, int local,
-                                 double *out12)
+                                 double *out12, bool fast)
 {
     switch (kind) {
-    case K_SPRING: evalOne<K_SPRING>(x, ids, rec, local, out12); break;
-    case K_SPRING_CONTINUUM: evalOne<K_SPRING_CONTINUUM>(x, ids, rec, local, out12); break;
-    case K_DISCRETE_BENDING: evalOne<K_DISCRETE_BENDING>(x, ids, rec, local, out12); break;
-    case K_QUADRATIC_BENDING: evalOne<K_QUADRATIC_BENDING>(x, ids, rec, local, out12); break;
-    case K_MEMBRANE_STVK: evalOne<K_MEMBRANE_STVK>(x, ids, rec, local, out12); break;
-    case K_MEMBRANE_CHOI: evalOne<K_MEMBRANE_CHOI>(x, ids, rec, local, out12); break;
-    case K_MEMBRANE_BW: evalOne<K_MEMBRANE_BW>(x, ids, rec, local, out12); break;
-    case K_TET_STVK: evalOne<K_TET_STVK>(x, ids, rec, local, out12); break;
-    case K_TET_SNH: evalOne<K_TET_SNH>(x, ids, rec, local, out12); break;
-    case K_ANCHOR: evalOne<K_ANCHOR>(x, ids, rec, local, out12); break;
+    case K_SPRING: evalOne<K_SPRING>(x, ids, rec, local, out12, fast); break;
+    case K_SPRING_CONTINUUM: evalOne<K_SPRING_CONTINUUM>(x, ids, rec, local, out12, fast); break;
+    case K_DISCRETE_BENDING: evalOne<K_DISCRETE_BENDING>(x, ids, rec, local, out12, fast); break;
+    case K_QUADRATIC_BENDING: evalOne<K_QUADRATIC_BENDING>(x, ids, rec, local, out12, fast); break;
+    case K_MEMBRANE_STVK: evalOne<K_MEMBRANE_STVK>(x, ids, rec, local, out12, fast); break;
+    case K_MEMBRANE_CHOI: evalOne<K_MEMBRANE_CHOI>(x, ids, rec, local, out12, fast); break;
+    case K_MEMBRANE_BW: evalOne<K_MEMBRANE_BW>(x, ids, rec, local, out12, fast); break;
+    case K_TET_STVK: evalOne<K_TET_STVK>(x, ids, rec, local, out12, fast); break;
+    case K_TET_SNH: evalOne<K_TET_SNH>(x, ids, rec, local, out12, fast); break;
+    case K_ANCHOR: evalOne<K_ANCHOR>(x, ids, rec, local, out12, fast); break;
     default: break;
     }
 }
 }  // namespace
 
 void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
-                                  double *out12, cudaStream_t stream)
+                                  double *out12, bool handDerived, cudaStream_t stream)
 {
-    evalVertexKernel<<<1, 1, 0, stream>>>(kind, x, stencil, record, local, out12);
+    evalVertexKernel<<<1, 1, 0, stream>>>(kind, x, stencil, record, local, out12, handDerived);
 }
 }  // namespace spgx
