@@ -2,6 +2,7 @@
 // finalize (colouring + incidence + upload).  See include/spgx.h for the reference interface each
 // entry point replaces.
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "energy_prepare.h"
@@ -37,6 +38,61 @@ static double modelRecordBytes(int kind)
     case K_ANCHOR: return 36;
     default: return 0;
     }
+}
+
+// Sliced-ELL incidence records of one energy for the streaming VBD layout (kernels.h): per warp-slice of
+// VW = 32 / G consecutive slots, ceil(maxDegree / G) steps; incidence j of the slice's vertex v sits in step
+// j / G at lane (j % G) * VW + v.
+template <int KIND>
+static void buildEll(EnergyState &e, const spgx_group &grp, const Incidence &inc, cudaStream_t st)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int NI = EK::NI, NQ = EK::NQ, S = EK::S;
+    const int G = grp.vbdLanes, VW = 32 / G;
+    const int nColors = static_cast<int>(grp.colorOffsets.size()) - 1;
+    std::vector<uint32_t> offsets(1, 0);
+    auto degree = [&](int slot) {
+        const int v = grp.slot2vert[slot];
+        return static_cast<int>(inc.rowptr[v + 1] - inc.rowptr[v]);
+    };
+    for (int c = 0; c < nColors; ++c) {
+        const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+        for (int s0 = b; s0 < en; s0 += VW) {
+            int steps = 0;
+            for (int s = s0; s < std::min(s0 + VW, en); ++s) steps = std::max(steps, (degree(s) + G - 1) / G);
+            offsets.push_back(offsets.back() + static_cast<uint32_t>(steps));
+        }
+    }
+    const size_t T = offsets.back();
+    std::vector<uint32_t> ids(T * NI * 32, 0xFFFFFFFFu);
+    std::vector<double> params(T * NQ * 32, 0.0);
+    size_t slice = 0;
+    for (int c = 0; c < nColors; ++c) {
+        const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+        for (int s0 = b; s0 < en; s0 += VW, ++slice) {
+            for (int s = s0; s < std::min(s0 + VW, en); ++s) {
+                const int v = grp.slot2vert[s];
+                int j = 0;
+                for (int64_t q = inc.rowptr[v]; q < inc.rowptr[v + 1]; ++q, ++j) {
+                    const int64_t stencil = inc.flat[q] / S;
+                    const int local = static_cast<int>(inc.flat[q] % S);
+                    int32_t slots[S];
+                    for (int l = 0; l < S; ++l) slots[l] = grp.vert2slot[e.stencils[stencil * S + l]];
+                    uint32_t rid[NI];
+                    double rq[NQ];
+                    EK::makeIncidence(slots, e.records.data() + stencil * e.NP, local, rid, rq);
+                    const size_t t = offsets[slice] + j / G;
+                    const int lane = (j % G) * VW + (s - s0);
+                    for (int k = 0; k < NI; ++k) ids[(t * NI + k) * 32 + lane] = rid[k];
+                    for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = rq[k];
+                }
+            }
+        }
+    }
+    e.d_ellOffsets.upload(offsets, st);
+    e.d_ellIds.upload(ids, st);
+    e.d_ellParams.upload(params, st);
+    SPGX_CUDA(cudaStreamSynchronize(st));
 }
 }  // namespace spgx
 
@@ -259,6 +315,24 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->vertexColors = colorVertices(V, sets, &inc);  // vbd.cpp:203-229
             groupByKey(grp->vertexColors, grp->slot2vert, grp->colorOffsets);
             for (int s = 0; s < V; ++s) grp->vert2slot[grp->slot2vert[s]] = s;
+            {
+                // threads per vertex: big colours are throughput-bound and run best with one thread per vertex (long
+                // software-pipelined incidence loops, no shuffles); small meshes need the extra parallelism
+                int64_t largest = 0;
+                for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c)
+                    largest = std::max(largest, grp->colorOffsets[c + 1] - grp->colorOffsets[c]);
+                grp->vbdLanes = largest >= 65536 ? 1 : (largest >= 16384 ? 2 : 4);
+            }
+            if (const char *env = getenv("SPGX_VBD_LANES")) {
+                const int l = atoi(env);
+                if (l == 1 || l == 2 || l == 4 || l == 8) grp->vbdLanes = l;
+            }
+            grp->sliceBase.assign(grp->colorOffsets.size(), 0);
+            for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
+                const int64_t n = grp->colorOffsets[c + 1] - grp->colorOffsets[c];
+                const int VW = 32 / grp->vbdLanes;
+                grp->sliceBase[c + 1] = grp->sliceBase[c] + static_cast<int32_t>((n + VW - 1) / VW);
+            }
             // incidence in slot order (vbd.cpp:231-268 keeps ascending flat index per vertex and energy)
             std::vector<int32_t> nbr;
             for (size_t ei = 0; ei < nE; ++ei) {
@@ -281,6 +355,13 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 e.d_records.upload(e.records, st);
                 e.d_rowptr.upload(rowptr, st);
                 e.d_entries.upload(entries, st);
+                e.d_ellOffsets.release();
+                e.d_ellIds.release();
+                e.d_ellParams.release();
+                if (!getenv("SPGX_NO_ELL")) {
+                    if (e.kind == K_DISCRETE_BENDING) buildEll<K_DISCRETE_BENDING>(e, *grp, inc[ei], st);
+                    if (e.kind == K_MEMBRANE_STVK) buildEll<K_MEMBRANE_STVK>(e, *grp, inc[ei], st);
+                }
                 e.order.clear();
                 e.positionOf.clear();
                 SPGX_CUDA(cudaStreamSynchronize(st));

@@ -37,7 +37,8 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.nEnergies = static_cast<int>(grp->energies.size());
     for (int e = 0; e < args.nEnergies; ++e) {
         const auto &en = grp->energies[e];
-        args.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr};
+        args.e[e] = {en.kind,           en.n,           en.d_stencils.ptr,   en.d_records.ptr,  en.d_rowptr.ptr,
+                     en.d_entries.ptr,  en.d_ellOffsets.ptr, en.d_ellIds.ptr, en.d_ellParams.ptr};
     }
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
@@ -50,7 +51,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
             for (int c = 0; c < nColors; ++c) {
                 const int b = static_cast<int>(grp->colorOffsets[c]), e = static_cast<int>(grp->colorOffsets[c + 1]);
                 if (e > b) {
-                    launchVbdPass(args, mask, b, e, invdtSquared, st);
+                    launchVbdPass(args, mask, grp->vbdLanes, b, e, grp->sliceBase[c], invdtSquared, st);
                     grp->launchCounter++;
                 }
             }

@@ -8,6 +8,8 @@
 // Per-stencil parameter record `p` (doubles) is produced on the host by prepare() in
 // energy_prepare.h, which restates each energy's addStencil + preparePrecomputations.
 #pragma once
+#include <cstdint>
+
 #include "linalg.cuh"
 
 namespace spgx
@@ -174,6 +176,28 @@ struct EnergyKind<K_DISCRETE_BENDING> {
         gAcc.z += Kd * g.z;
         addOuter(HAcc, g, K);
     }
+
+    // Owner-centric incidence record of the streaming layout: the three other vertices in stencil order (the
+    // owner's local index rides in the top two bits of the first id) and q = {theta0, K}.
+    static constexpr int NI = 3, NQ = 2;
+    static void makeIncidence(const int32_t *slots, const double *p, int local, uint32_t *ids, double *q)
+    {
+        int k = 0;
+        for (int s = 0; s < 4; ++s)
+            if (s != local) ids[k++] = static_cast<uint32_t>(slots[s]);
+        ids[0] |= static_cast<uint32_t>(local) << 30;
+        q[0] = p[0];
+        q[1] = p[1];
+    }
+    SPGX_HD static void incidenceGradHess(const V3d &xo, const V3d *xn, const double *q, int local, V3d &gAcc, Sym3 &HAcc)
+    {
+        V3d xs[4];
+        xs[0] = (local == 0) ? xo : xn[0];
+        xs[1] = (local == 1) ? xo : (local == 0 ? xn[0] : xn[1]);
+        xs[2] = (local == 2) ? xo : (local == 3 ? xn[2] : xn[1]);
+        xs[3] = (local == 3) ? xo : xn[2];
+        vertexGradHess(xs, q, local, gAcc, HAcc);
+    }
 };
 
 // ---- QuadraticBendingEnergy (quadraticBendingEnergy.cpp:9-29): C = L x, L = [c0 I, c1 I, c2 I, c3 I].
@@ -222,15 +246,11 @@ struct EnergyKind<K_MEMBRANE_STVK> {
     //   u0 = ga F0, u1 = gb F1, u2 = gb F0 + ga F1           (dC_i = u_i . dx)
     //   grad = sum_i s_i u_i,   Hess = sum_ij K_ij u_i u_j^T + (s0 ga^2 + s1 gb^2 + 2 s2 ga gb) I.
     static constexpr bool kHandDerived = true;
-    SPGX_HD static void vertexGradHess(const V3d *x, const double *p, int local, V3d &gAcc, Sym3 &HAcc)
+    SPGX_HD static void blockFromF(const V3d &F0, const V3d &F1, double ga, double gb, double K00, double K01, double K22,
+                                   V3d &gAcc, Sym3 &HAcc)
     {
-        V3d F0, F1;
-        membraneF(x, p, F0, F1);
         const double C0 = 0.5 * (dot(F0, F0) - 1.0), C1 = 0.5 * (dot(F1, F1) - 1.0), C2 = dot(F0, F1);
-        const double K00 = p[4], K01 = p[5], K22 = p[6];
         const double s0 = K00 * C0 + K01 * C1, s1 = K01 * C0 + K00 * C1, s2 = K22 * C2;
-        const double ga = (local == 0) ? -(p[0] + p[2]) : (local == 1 ? p[0] : p[2]);
-        const double gb = (local == 0) ? -(p[1] + p[3]) : (local == 1 ? p[1] : p[3]);
         const V3d u0 = F0 * ga, u1 = F1 * gb, u2 = F0 * gb + F1 * ga;
         gAcc.x += s0 * u0.x + s1 * u1.x + s2 * u2.x;
         gAcc.y += s0 * u0.y + s1 * u1.y + s2 * u2.y;
@@ -243,6 +263,33 @@ struct EnergyKind<K_MEMBRANE_STVK> {
         HAcc.xy += u0.x * w0.y + u1.x * w1.y + u2.x * w2.y;
         HAcc.xz += u0.x * w0.z + u1.x * w1.z + u2.x * w2.z;
         HAcc.yz += u0.y * w0.z + u1.y * w1.z + u2.y * w2.z;
+    }
+    SPGX_HD static void vertexGradHess(const V3d *x, const double *p, int local, V3d &gAcc, Sym3 &HAcc)
+    {
+        V3d F0, F1;
+        membraneF(x, p, F0, F1);
+        const double ga = (local == 0) ? -(p[0] + p[2]) : (local == 1 ? p[0] : p[2]);
+        const double gb = (local == 0) ? -(p[1] + p[3]) : (local == 1 ? p[1] : p[3]);
+        blockFromF(F0, F1, ga, gb, p[4], p[5], p[6], gAcc, HAcc);
+    }
+
+    // Owner-centric incidence record of the streaming layout: the two other vertices (p, q in cyclic order after
+    // the owner) and q = {g_p(2), g_q(2), K00, K01, K22}; F = (x_p - x_o) g_p^T + (x_q - x_o) g_q^T, g_o = -g_p - g_q.
+    static constexpr int NI = 2, NQ = 7;
+    static void makeIncidence(const int32_t *slots, const double *p, int local, uint32_t *ids, double *q)
+    {
+        const int ip = (local + 1) % 3, iq = (local + 2) % 3;
+        const double gs[3][2] = {{-(p[0] + p[2]), -(p[1] + p[3])}, {p[0], p[1]}, {p[2], p[3]}};
+        ids[0] = static_cast<uint32_t>(slots[ip]);
+        ids[1] = static_cast<uint32_t>(slots[iq]);
+        q[0] = gs[ip][0], q[1] = gs[ip][1], q[2] = gs[iq][0], q[3] = gs[iq][1];
+        q[4] = p[4], q[5] = p[5], q[6] = p[6];
+    }
+    SPGX_HD static void incidenceGradHess(const V3d &xo, const V3d *xn, const double *q, int, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d dp = xn[0] - xo, dq = xn[1] - xo;
+        const V3d F0 = dp * q[0] + dq * q[2], F1 = dp * q[1] + dq * q[3];
+        blockFromF(F0, F1, -(q[0] + q[2]), -(q[1] + q[3]), q[4], q[5], q[6], gAcc, HAcc);
     }
 };
 
@@ -409,6 +456,16 @@ SPGX_HD T stencilEnergy(const V3<T> *x, const double *p)
         return 0.5 * e;
     }
 }
+
+// does the kind carry an owner-centric incidence record (streaming sliced-ELL layout of the VBD kernel)?
+template <class EK, class = void>
+struct HasIncidenceRecord {
+    static constexpr bool value = false;
+};
+template <class EK>
+struct HasIncidenceRecord<EK, decltype(void(EK::NQ))> {
+    static constexpr bool value = true;
+};
 
 // does the kind carry a hand-derived vertexGradHess override?
 template <class EK, class = void>

@@ -112,6 +112,8 @@ struct EnergyState {
     DevBuf<double> d_records;
     // VBD
     DevBuf<uint32_t> d_rowptr, d_entries;
+    DevBuf<uint32_t> d_ellOffsets, d_ellIds;  // streaming sliced-ELL incidence records (kernels.h)
+    DevBuf<double> d_ellParams;
     // XPBD
     std::vector<int32_t> stencilColors;  // per stencil, reference order
     std::vector<int32_t> order;          // position -> stencil id
@@ -134,6 +136,8 @@ struct spgx_group {
     std::vector<int32_t> vertexColors;
     std::vector<int32_t> slot2vert, vert2slot;
     std::vector<int64_t> colorOffsets;
+    int vbdLanes = 4;                   // threads per vertex in the VBD colour pass
+    std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)
     double uniqueNeighbourSum = 0;  // sum over vertices of the number of distinct stencil neighbours
 
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;

@@ -15,6 +15,12 @@ struct VbdEnergyDev {
     const double *records;     // NP doubles per stencil (energies.cuh)
     const uint32_t *rowptr;    // nVerts + 1, indexed by slot
     const uint32_t *entries;   // (stencil << 2) | local, ascending per row
+    // streaming layout (kinds with an owner-centric incidence record; null otherwise): a sliced ELL over
+    // warp-slices of 32 / G vertices.  Step t of a slice holds one incidence per lane:
+    //   ids    [t][NI][32] uint32 (0xFFFFFFFF in field 0 = padding), params [t][NQ][32] double
+    const uint32_t *ellOffsets;  // per warp-slice first step, nSlices + 1
+    const uint32_t *ellIds;
+    const double *ellParams;
 };
 
 struct VbdArgs {
@@ -26,8 +32,9 @@ struct VbdArgs {
 };
 
 // vbd.cpp:99-147 for the slots [begin, end) of one colour
-void launchVbdPass(const VbdArgs &args, unsigned kindMask, int begin, int end, double invdtSquared,
-                   cudaStream_t stream);
+// lanes: threads per vertex (1, 2, 4 or 8); sliceBase: index of the colour's first warp-slice
+void launchVbdPass(const VbdArgs &args, unsigned kindMask, int lanes, int begin, int end, int sliceBase,
+                   double invdtSquared, cudaStream_t stream);
 
 // vbd.cpp:49-75 / xpbd.cpp:48-74: xOld <- x; v += dt g; x += v dt; (xInertial <- x when not null)
 void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nVerts, double dt, const double *g3,
