@@ -257,7 +257,7 @@ class Group:
         check(lib.spgx_last_timings(self.handle, C.byref(t)))
         return t
 
-    def eval_vertex_force_hessian(self, eid: int, stencil: int, local: int, hand_derived: bool = True):
+    def eval_vertex_force_hessian(self, eid: int, stencil: int, local: int, hand_derived: int = 1):
         f = np.empty(3)
         h = np.empty((3, 3))
         check(lib.spgx_eval_vertex_force_hessian(self.handle, eid, stencil, local, int(hand_derived), _d(f), _d(h)))

@@ -8,6 +8,7 @@
 #include "energy_prepare.h"
 #include "group.h"
 #include "host_build.h"
+#include "streams.cuh"
 
 namespace spgx
 {
@@ -40,59 +41,151 @@ static double modelRecordBytes(int kind)
     }
 }
 
-// Sliced-ELL incidence records of one energy for the streaming VBD layout (kernels.h): per warp-slice of
-// VW = 32 / G consecutive slots, ceil(maxDegree / G) steps; incidence j of the slice's vertex v sits in step
-// j / G at lane (j % G) * VW + v.
-template <int KIND>
-static void buildEll(EnergyState &e, const spgx_group &grp, const Incidence &inc, cudaStream_t st)
+// Streaming layout of the VBD colour pass (kernels.h, streams.cuh).  For every vertex (in slot order): the list of its
+// unique neighbours over all streamed incidences (first-seen order), and per (energy, stream type) the canonical
+// incidence records referencing that list by 8-bit index.  Both are packed as sliced ELL over warp-slices of
+// VW = 32 / G consecutive slots of one colour: incidence j of the slice's vertex v sits in step j / G at lane
+// (j % G) * VW + v; neighbour k of vertex v sits in row k at column v.
+// Returns false (and leaves the group on the CSR path) when a vertex has more than 255 unique neighbours or there
+// are more (energy, type) pairs than kMaxStreams.
+static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cudaStream_t st)
 {
-    using EK = EnergyKind<KIND>;
-    constexpr int NI = EK::NI, NQ = EK::NQ, S = EK::S;
-    const int G = grp.vbdLanes, VW = 32 / G;
+    const int V = grp.nVerts, G = grp.vbdLanes, VW = 32 / G;
     const int nColors = static_cast<int>(grp.colorOffsets.size()) - 1;
-    std::vector<uint32_t> offsets(1, 0);
-    auto degree = [&](int slot) {
-        const int v = grp.slot2vert[slot];
-        return static_cast<int>(inc.rowptr[v + 1] - inc.rowptr[v]);
+    struct HostStream {
+        int energy, type, NQ;
+        std::vector<uint32_t> rowptr;  // per slot
+        std::vector<uint32_t> idx;     // per incidence
+        std::vector<double> q;         // NQ per incidence
     };
-    for (int c = 0; c < nColors; ++c) {
-        const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-        for (int s0 = b; s0 < en; s0 += VW) {
-            int steps = 0;
-            for (int s = s0; s < std::min(s0 + VW, en); ++s) steps = std::max(steps, (degree(s) + G - 1) / G);
-            offsets.push_back(offsets.back() + static_cast<uint32_t>(steps));
+    std::vector<HostStream> hs;
+    std::vector<int> streamOf(grp.energies.size() * ST_COUNT, -1);
+    for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+        const auto &e = grp.energies[ei];
+        for (int local = 0; local < e.S; ++local) {
+            const int t = streamTypeOf(e.kind, local);
+            if (t < 0 || streamOf[ei * ST_COUNT + t] >= 0) continue;
+            streamOf[ei * ST_COUNT + t] = static_cast<int>(hs.size());
+            hs.push_back({static_cast<int>(ei), t, streamNQ(t), std::vector<uint32_t>(static_cast<size_t>(V) + 1, 0), {}, {}});
         }
     }
-    const size_t T = offsets.back();
-    std::vector<uint32_t> ids(T * NI * 32, 0xFFFFFFFFu);
-    std::vector<double> params(T * NQ * 32, 0.0);
-    size_t slice = 0;
-    for (int c = 0; c < nColors; ++c) {
-        const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-        for (int s0 = b; s0 < en; s0 += VW, ++slice) {
-            for (int s = s0; s < std::min(s0 + VW, en); ++s) {
-                const int v = grp.slot2vert[s];
-                int j = 0;
-                for (int64_t q = inc.rowptr[v]; q < inc.rowptr[v + 1]; ++q, ++j) {
-                    const int64_t stencil = inc.flat[q] / S;
-                    const int local = static_cast<int>(inc.flat[q] % S);
-                    int32_t slots[S];
-                    for (int l = 0; l < S; ++l) slots[l] = grp.vert2slot[e.stencils[stencil * S + l]];
-                    uint32_t rid[NI];
-                    double rq[NQ];
-                    EK::makeIncidence(slots, e.records.data() + stencil * e.NP, local, rid, rq);
-                    const size_t t = offsets[slice] + j / G;
-                    const int lane = (j % G) * VW + (s - s0);
-                    for (int k = 0; k < NI; ++k) ids[(t * NI + k) * 32 + lane] = rid[k];
-                    for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = rq[k];
+    if (hs.empty() || hs.size() > static_cast<size_t>(kMaxStreams)) return false;
+
+    std::vector<uint32_t> nbrRowptr(static_cast<size_t>(V) + 1, 0);
+    std::vector<uint32_t> nbrList;
+    std::vector<int32_t> mark(static_cast<size_t>(V), -1), localIdx(static_cast<size_t>(V), 0);
+    int maxNbr = 0;
+    for (int s = 0; s < V; ++s) {
+        const int v = grp.slot2vert[s];
+        const uint32_t nb0 = static_cast<uint32_t>(nbrList.size());
+        for (auto &h : hs) h.rowptr[s] = static_cast<uint32_t>(h.idx.size());
+        for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+            const auto &e = grp.energies[ei];
+            if (streamTypeOf(e.kind, 0) < 0) continue;
+            for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                const int64_t stencil = inc[ei].flat[q] / e.S;
+                const int local = static_cast<int>(inc[ei].flat[q] % e.S);
+                HostStream &h = hs[streamOf[ei * ST_COUNT + streamTypeOf(e.kind, local)]];
+                int32_t nbr[3];
+                double rq[16];
+                makeStreamRecord(e.kind, e.stencils.data() + stencil * e.S, e.records.data() + stencil * e.NP, local, nbr, rq);
+                uint32_t word = 0;
+                for (int k = 0; k < streamNI(h.type); ++k) {
+                    const int u = nbr[k];
+                    if (mark[u] != s) {
+                        mark[u] = s;
+                        localIdx[u] = static_cast<int32_t>(nbrList.size() - nb0);
+                        nbrList.push_back(static_cast<uint32_t>(grp.vert2slot[u]));
+                    }
+                    word |= static_cast<uint32_t>(localIdx[u]) << (8 * k);
                 }
+                h.idx.push_back(word);
+                h.q.insert(h.q.end(), rq, rq + h.NQ);
             }
         }
+        const int cnt = static_cast<int>(nbrList.size() - nb0);
+        if (cnt > 255) return false;
+        maxNbr = std::max(maxNbr, cnt);
+        nbrRowptr[s + 1] = static_cast<uint32_t>(nbrList.size());
     }
-    e.d_ellOffsets.upload(offsets, st);
-    e.d_ellIds.upload(ids, st);
-    e.d_ellParams.upload(params, st);
-    SPGX_CUDA(cudaStreamSynchronize(st));
+    for (auto &h : hs) h.rowptr[V] = static_cast<uint32_t>(h.idx.size());
+
+    // ---- sliced-ELL packing ----
+    size_t nSlices = 0;
+    for (int c = 0; c < nColors; ++c) nSlices += static_cast<size_t>((grp.colorOffsets[c + 1] - grp.colorOffsets[c] + VW - 1) / VW);
+    double bytes = 0;
+    {
+        std::vector<uint32_t> offsets(1, 0);
+        offsets.reserve(nSlices + 1);
+        for (int c = 0; c < nColors; ++c) {
+            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+            for (int s0 = b; s0 < en; s0 += VW) {
+                uint32_t rows = 0;
+                for (int s = s0; s < std::min(s0 + VW, en); ++s) rows = std::max(rows, nbrRowptr[s + 1] - nbrRowptr[s]);
+                offsets.push_back(offsets.back() + rows);
+            }
+        }
+        std::vector<uint32_t> ids(static_cast<size_t>(offsets.back()) * VW, 0u);
+        size_t slice = 0;
+        for (int c = 0; c < nColors; ++c) {
+            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+            for (int s0 = b; s0 < en; s0 += VW, ++slice)
+                for (int s = s0; s < std::min(s0 + VW, en); ++s)
+                    for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
+                        ids[(static_cast<size_t>(offsets[slice]) + (k - nbrRowptr[s])) * VW + (s - s0)] = nbrList[k];
+        }
+        grp.d_nbrOffsets.upload(offsets, st);
+        grp.d_nbrIds.upload(ids, st);
+        bytes += 4.0 * ids.size() + 4.0 * offsets.size();
+        SPGX_CUDA(cudaStreamSynchronize(st));
+    }
+    grp.streams.clear();
+    grp.streams.resize(hs.size());
+    grp.streamMask = 0;
+    for (size_t i = 0; i < hs.size(); ++i) {
+        const HostStream &h = hs[i];
+        const int NQ = h.NQ;
+        std::vector<uint32_t> offsets(1, 0);
+        offsets.reserve(nSlices + 1);
+        for (int c = 0; c < nColors; ++c) {
+            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+            for (int s0 = b; s0 < en; s0 += VW) {
+                uint32_t steps = 0;
+                for (int s = s0; s < std::min(s0 + VW, en); ++s)
+                    steps = std::max(steps, (h.rowptr[s + 1] - h.rowptr[s] + G - 1) / G);
+                offsets.push_back(offsets.back() + steps);
+            }
+        }
+        const size_t T = offsets.back();
+        std::vector<uint32_t> idx(T * 32, 0xFFFFFFFFu);
+        std::vector<double> params(T * NQ * 32, 0.0);
+        size_t slice = 0;
+        for (int c = 0; c < nColors; ++c) {
+            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+            for (int s0 = b; s0 < en; s0 += VW, ++slice)
+                for (int s = s0; s < std::min(s0 + VW, en); ++s) {
+                    uint32_t j = 0;
+                    for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
+                        const size_t t = offsets[slice] + j / G;
+                        const int lane = static_cast<int>(j % G) * VW + (s - s0);
+                        idx[t * 32 + lane] = h.idx[r];
+                        for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
+                    }
+                }
+        }
+        auto &out = grp.streams[i];
+        out.type = h.type;
+        out.d_offsets.upload(offsets, st);
+        out.d_idx.upload(idx, st);
+        out.d_params.upload(params, st);
+        grp.streamMask |= 1u << h.type;
+        bytes += 4.0 * idx.size() + 8.0 * params.size() + 4.0 * offsets.size();
+        SPGX_CUDA(cudaStreamSynchronize(st));
+    }
+    grp.maxNbr = std::max(maxNbr, 1);
+    grp.streamBytes = bytes;
+    for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
+    return true;
 }
 }  // namespace spgx
 
@@ -321,11 +414,16 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 int64_t largest = 0;
                 for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c)
                     largest = std::max(largest, grp->colorOffsets[c + 1] - grp->colorOffsets[c]);
-                grp->vbdLanes = largest >= 65536 ? 1 : (largest >= 16384 ? 2 : 4);
+                grp->vbdLanes = largest >= 65536 ? 2 : 4;
             }
             if (const char *env = getenv("SPGX_VBD_LANES")) {
                 const int l = atoi(env);
-                if (l == 1 || l == 2 || l == 4 || l == 8) grp->vbdLanes = l;
+                if (l == 1 || l == 2 || l == 4) grp->vbdLanes = l;
+            }
+            grp->vbdOcc = 4;
+            if (const char *env = getenv("SPGX_VBD_OCC")) {
+                const int o = atoi(env);
+                if (o >= 3 && o <= 5) grp->vbdOcc = o;
             }
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
@@ -355,16 +453,33 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 e.d_records.upload(e.records, st);
                 e.d_rowptr.upload(rowptr, st);
                 e.d_entries.upload(entries, st);
-                e.d_ellOffsets.release();
-                e.d_ellIds.release();
-                e.d_ellParams.release();
-                if (!getenv("SPGX_NO_ELL")) {
-                    if (e.kind == K_DISCRETE_BENDING) buildEll<K_DISCRETE_BENDING>(e, *grp, inc[ei], st);
-                    if (e.kind == K_MEMBRANE_STVK) buildEll<K_MEMBRANE_STVK>(e, *grp, inc[ei], st);
-                }
+                e.streamed = false;
                 e.order.clear();
                 e.positionOf.clear();
                 SPGX_CUDA(cudaStreamSynchronize(st));
+            }
+            // streaming layout, when the group's mix of energies has a compiled streaming kernel
+            grp->streams.clear();
+            grp->streamMask = 0;
+            grp->maxNbr = 0;
+            grp->streamBytes = 0;
+            grp->d_nbrOffsets.release();
+            grp->d_nbrIds.release();
+            {
+                unsigned smask = 0, kmask = 0;
+                for (auto &e : grp->energies) {
+                    bool any = false;
+                    for (int l = 0; l < e.S; ++l)
+                        if (streamTypeOf(e.kind, l) >= 0) smask |= 1u << streamTypeOf(e.kind, l), any = true;
+                    if (!any) kmask |= 1u << e.kind;
+                }
+                if (!getenv("SPGX_NO_STREAMS") && vbdStreamComboSupported(smask, kmask)) {
+                    if (!buildStreams(*grp, inc, st)) {
+                        grp->streams.clear();
+                        grp->streamMask = 0;
+                        for (auto &e : grp->energies) e.streamed = false;
+                    }
+                }
             }
             // distinct stencil neighbours per vertex (for the byte model)
             for (int v = 0; v < V; ++v) {

@@ -37,9 +37,17 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.nEnergies = static_cast<int>(grp->energies.size());
     for (int e = 0; e < args.nEnergies; ++e) {
         const auto &en = grp->energies[e];
-        args.e[e] = {en.kind,           en.n,           en.d_stencils.ptr,   en.d_records.ptr,  en.d_rowptr.ptr,
-                     en.d_entries.ptr,  en.d_ellOffsets.ptr, en.d_ellIds.ptr, en.d_ellParams.ptr};
+        args.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr,
+                     en.streamed ? 1 : 0};
     }
+    args.nStreams = static_cast<int>(grp->streams.size());
+    for (int s = 0; s < args.nStreams; ++s) {
+        const auto &sd = grp->streams[s];
+        args.s[s] = {sd.type, sd.d_offsets.ptr, sd.d_idx.ptr, sd.d_params.ptr};
+    }
+    args.nbrOffsets = grp->d_nbrOffsets.ptr;
+    args.nbrIds = grp->d_nbrIds.ptr;
+    args.maxNbr = grp->maxNbr;
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
     for (int s = 0; s < nsub; ++s) {
@@ -51,7 +59,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
             for (int c = 0; c < nColors; ++c) {
                 const int b = static_cast<int>(grp->colorOffsets[c]), e = static_cast<int>(grp->colorOffsets[c + 1]);
                 if (e > b) {
-                    launchVbdPass(args, mask, grp->vbdLanes, b, e, grp->sliceBase[c], invdtSquared, st);
+                    launchVbdPass(args, mask, grp->streamMask, grp->vbdLanes, grp->vbdOcc, b, e, grp->sliceBase[c], invdtSquared, st);
                     grp->launchCounter++;
                 }
             }
@@ -314,7 +322,7 @@ int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, i
         const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
         cudaStream_t st = grp->ctx->stream;
         launchEvalVertexForceHessian(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
-                                     e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, handDerived != 0,
+                                     e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, handDerived,
                                      st);
         double out[12];
         SPGX_CUDA(cudaMemcpyAsync(out, grp->d_eval.ptr, sizeof(out), cudaMemcpyDeviceToHost, st));

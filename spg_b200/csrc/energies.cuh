@@ -143,7 +143,7 @@ struct EnergyKind<K_DISCRETE_BENDING> {
         const V3d a = x[2] - q, b = x[3] - q;
         const V3d N1 = cross(e, a), N2 = cross(b, e);
         const double ee = dot(e, e);
-        const double ie = rsqrt(ee);
+        const double ie = 1.0 / ::sqrt(ee);
         const double le = ee * ie;
         const double d = ::atan2(-le * dot(N1, b), dot(N1, N2)) - p[0];
         const double K = p[1];
@@ -175,28 +175,6 @@ struct EnergyKind<K_DISCRETE_BENDING> {
         gAcc.y += Kd * g.y;
         gAcc.z += Kd * g.z;
         addOuter(HAcc, g, K);
-    }
-
-    // Owner-centric incidence record of the streaming layout: the three other vertices in stencil order (the
-    // owner's local index rides in the top two bits of the first id) and q = {theta0, K}.
-    static constexpr int NI = 3, NQ = 2;
-    static void makeIncidence(const int32_t *slots, const double *p, int local, uint32_t *ids, double *q)
-    {
-        int k = 0;
-        for (int s = 0; s < 4; ++s)
-            if (s != local) ids[k++] = static_cast<uint32_t>(slots[s]);
-        ids[0] |= static_cast<uint32_t>(local) << 30;
-        q[0] = p[0];
-        q[1] = p[1];
-    }
-    SPGX_HD static void incidenceGradHess(const V3d &xo, const V3d *xn, const double *q, int local, V3d &gAcc, Sym3 &HAcc)
-    {
-        V3d xs[4];
-        xs[0] = (local == 0) ? xo : xn[0];
-        xs[1] = (local == 1) ? xo : (local == 0 ? xn[0] : xn[1]);
-        xs[2] = (local == 2) ? xo : (local == 3 ? xn[2] : xn[1]);
-        xs[3] = (local == 3) ? xo : xn[2];
-        vertexGradHess(xs, q, local, gAcc, HAcc);
     }
 };
 
@@ -271,25 +249,6 @@ struct EnergyKind<K_MEMBRANE_STVK> {
         const double ga = (local == 0) ? -(p[0] + p[2]) : (local == 1 ? p[0] : p[2]);
         const double gb = (local == 0) ? -(p[1] + p[3]) : (local == 1 ? p[1] : p[3]);
         blockFromF(F0, F1, ga, gb, p[4], p[5], p[6], gAcc, HAcc);
-    }
-
-    // Owner-centric incidence record of the streaming layout: the two other vertices (p, q in cyclic order after
-    // the owner) and q = {g_p(2), g_q(2), K00, K01, K22}; F = (x_p - x_o) g_p^T + (x_q - x_o) g_q^T, g_o = -g_p - g_q.
-    static constexpr int NI = 2, NQ = 7;
-    static void makeIncidence(const int32_t *slots, const double *p, int local, uint32_t *ids, double *q)
-    {
-        const int ip = (local + 1) % 3, iq = (local + 2) % 3;
-        const double gs[3][2] = {{-(p[0] + p[2]), -(p[1] + p[3])}, {p[0], p[1]}, {p[2], p[3]}};
-        ids[0] = static_cast<uint32_t>(slots[ip]);
-        ids[1] = static_cast<uint32_t>(slots[iq]);
-        q[0] = gs[ip][0], q[1] = gs[ip][1], q[2] = gs[iq][0], q[3] = gs[iq][1];
-        q[4] = p[4], q[5] = p[5], q[6] = p[6];
-    }
-    SPGX_HD static void incidenceGradHess(const V3d &xo, const V3d *xn, const double *q, int, V3d &gAcc, Sym3 &HAcc)
-    {
-        const V3d dp = xn[0] - xo, dq = xn[1] - xo;
-        const V3d F0 = dp * q[0] + dq * q[2], F1 = dp * q[1] + dq * q[3];
-        blockFromF(F0, F1, -(q[0] + q[2]), -(q[1] + q[3]), q[4], q[5], q[6], gAcc, HAcc);
     }
 };
 
@@ -456,16 +415,6 @@ SPGX_HD T stencilEnergy(const V3<T> *x, const double *p)
         return 0.5 * e;
     }
 }
-
-// does the kind carry an owner-centric incidence record (streaming sliced-ELL layout of the VBD kernel)?
-template <class EK, class = void>
-struct HasIncidenceRecord {
-    static constexpr bool value = false;
-};
-template <class EK>
-struct HasIncidenceRecord<EK, decltype(void(EK::NQ))> {
-    static constexpr bool value = true;
-};
 
 // does the kind carry a hand-derived vertexGradHess override?
 template <class EK, class = void>

@@ -112,8 +112,7 @@ struct EnergyState {
     DevBuf<double> d_records;
     // VBD
     DevBuf<uint32_t> d_rowptr, d_entries;
-    DevBuf<uint32_t> d_ellOffsets, d_ellIds;  // streaming sliced-ELL incidence records (kernels.h)
-    DevBuf<double> d_ellParams;
+    bool streamed = false;  // all of its incidences live in streams (kernels.h)
     // XPBD
     std::vector<int32_t> stencilColors;  // per stencil, reference order
     std::vector<int32_t> order;          // position -> stencil id
@@ -137,6 +136,18 @@ struct spgx_group {
     std::vector<int32_t> slot2vert, vert2slot;
     std::vector<int64_t> colorOffsets;
     int vbdLanes = 4;                   // threads per vertex in the VBD colour pass
+    int vbdOcc = 4;                     // resident-blocks-per-SM hint of the streaming kernel
+    // streaming layout (kernels.h): unique-neighbour tables + one stream per (energy, stream type)
+    struct StreamState {
+        int type = 0;
+        spgx::DevBuf<uint32_t> d_offsets, d_idx;
+        spgx::DevBuf<double> d_params;
+    };
+    std::vector<StreamState> streams;
+    spgx::DevBuf<uint32_t> d_nbrOffsets, d_nbrIds;
+    int maxNbr = 0;
+    unsigned streamMask = 0;
+    double streamBytes = 0;  // bytes of stream + neighbour tables one full sweep reads (reported)
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)
     double uniqueNeighbourSum = 0;  // sum over vertices of the number of distinct stencil neighbours
 

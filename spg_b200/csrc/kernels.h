@@ -15,12 +15,19 @@ struct VbdEnergyDev {
     const double *records;     // NP doubles per stencil (energies.cuh)
     const uint32_t *rowptr;    // nVerts + 1, indexed by slot
     const uint32_t *entries;   // (stencil << 2) | local, ascending per row
-    // streaming layout (kinds with an owner-centric incidence record; null otherwise): a sliced ELL over
-    // warp-slices of 32 / G vertices.  Step t of a slice holds one incidence per lane:
-    //   ids    [t][NI][32] uint32 (0xFFFFFFFF in field 0 = padding), params [t][NQ][32] double
-    const uint32_t *ellOffsets;  // per warp-slice first step, nSlices + 1
-    const uint32_t *ellIds;
-    const double *ellParams;
+    int streamed;              // 1: every incidence of this energy lives in a stream below (the CSR path skips it)
+};
+
+constexpr int kMaxStreams = 6;
+// One owner-centric incidence stream (streams.cuh): a sliced ELL over warp-slices of VW = 32 / G consecutive slots of
+// one colour.  Step t of a slice holds one incidence per lane (lane = sub * VW + v carries incidence t * G + sub of the
+// slice's vertex v):  idx [t][32] uint32 = the NI neighbour positions as 8-bit indices into the owner's unique-neighbour
+// list (0xFFFFFFFF = padding),  params [t][NQ][32] double.
+struct VbdStreamDev {
+    int type;                 // StreamType
+    const uint32_t *offsets;  // per warp-slice first step, nSlices + 1
+    const uint32_t *idx;
+    const double *params;
 };
 
 struct VbdArgs {
@@ -29,12 +36,22 @@ struct VbdArgs {
     const double *mass;        // per slot
     int nEnergies;
     VbdEnergyDev e[kMaxEnergies];
+    // streaming layout (nStreams == 0: CSR path only)
+    int nStreams;
+    VbdStreamDev s[kMaxStreams];
+    const uint32_t *nbrOffsets;  // per warp-slice first row of its unique-neighbour table, nSlices + 1
+    const uint32_t *nbrIds;      // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
+    int maxNbr;                  // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
 };
+
+// can launchVbdPass run this combination of stream types + CSR kinds through the streaming kernel?
+bool vbdStreamComboSupported(unsigned streamMask, unsigned csrKindMask);
 
 // vbd.cpp:99-147 for the slots [begin, end) of one colour
 // lanes: threads per vertex (1, 2, 4 or 8); sliceBase: index of the colour's first warp-slice
-void launchVbdPass(const VbdArgs &args, unsigned kindMask, int lanes, int begin, int end, int sliceBase,
-                   double invdtSquared, cudaStream_t stream);
+// kindMask: kinds that go through the CSR path; streamMask: stream types present; occ: resident blocks per SM hint
+void launchVbdPass(const VbdArgs &args, unsigned kindMask, unsigned streamMask, int lanes, int occ, int begin, int end,
+                   int sliceBase, double invdtSquared, cudaStream_t stream);
 
 // vbd.cpp:49-75 / xpbd.cpp:48-74: xOld <- x; v += dt g; x += v dt; (xInertial <- x when not null)
 void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nVerts, double dt, const double *g3,
@@ -51,7 +68,7 @@ void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *s
 
 // single-thread evaluators for the per-element parity tests
 void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
-                                  double *out12, bool handDerived, cudaStream_t stream);
+                                  double *out12, int handDerived, cudaStream_t stream);
 void launchEvalConstraints(int kind, const double *x, const int32_t *stencil, const double *record, double *outC,
                            double *outGrad, cudaStream_t stream);
 }  // namespace spgx

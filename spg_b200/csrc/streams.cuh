@@ -1,0 +1,325 @@
+// Owner-centric incidence streams of the VBD colour pass.
+//
+// The reference evaluates, for every (vertex, incident stencil) pair, the full stencil gradient and Hessian by
+// autodiff and keeps one 3-segment / 3x3 block (spg/include/spg/sim/energy/energy.h:240-258).  Here every such
+// pair ("incidence") of a streamed energy kind becomes one small record in a per-warp, fully coalesced stream,
+// written once on the host at finalize time:
+//   * the stencil is CANONICALISED around the owning vertex, so that the device code has no `local`-dependent
+//     selects or branches: discrete bending splits into two stream types (owner on the hinge edge / owner opposite
+//     to it) and uses the symmetries theta(x1,x0,x2,x3) = theta(x0,x1,x3,x2) = -theta(x0,x1,x2,x3) of the hinge
+//     angle of discreteBendingEnergy.cpp:9-30 (the sign moves into theta0);
+//   * the other stencil vertices are referenced by their index in the owner's UNIQUE-NEIGHBOUR list (8 bits each),
+//     whose positions the kernel gathers once per vertex into shared memory (a cloth vertex has 8-12 unique
+//     neighbours but 36-72 neighbour references);
+//   * the per-element constants the block needs ride along as NQ doubles.
+// Each evaluator adds dE/dx_owner to g and d2E/dx_owner^2 to H; they are the hand-derived overrides north_star asks
+// for ("hand-derived overrides where ncu shows register or spill pressure") and are checked against the generic
+// dual-number evaluation of the same energy (tests/test_host_elements.py, tests/test_gpu_elements.py).
+#pragma once
+#include "energies.cuh"
+
+namespace spgx
+{
+enum StreamType : int {
+    ST_BEND_EDGE = 0,      // discrete bending, owner is an end of the hinge edge
+    ST_BEND_OPP = 1,       // discrete bending, owner is opposite to the hinge edge
+    ST_MEMBRANE_STVK = 2,  // StVK membrane triangle
+    ST_TET_SNH = 3,        // stable Neo-Hookean tetrahedron
+    ST_TET_STVK = 4,       // StVK tetrahedron
+    ST_COUNT = 5
+};
+
+// 1 / x and 1 / sqrt(x) to double precision from the hardware seed (MUFU.RCP64H / RSQ64H) and two Newton steps,
+// without the special-case slow path of the IEEE division (denominators here are squared lengths of mesh edges
+// and triangle normals: finite, positive, far from the denormal range)
+SPGX_HD double fastRcp(double x)
+{
+#if defined(__CUDA_ARCH__)
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    double e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    e = fma(-x, r, 1.0);
+    r = fma(r, e, r);
+    return r;
+#else
+    return 1.0 / x;
+#endif
+}
+SPGX_HD double fastRsqrt(double x)
+{
+#if defined(__CUDA_ARCH__)
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    double e = fma(-hx * y, y, 0.5);  // (1 - x y^2) / 2
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    y = fma(y, e, y);
+    return y;
+#else
+    return 1.0 / ::sqrt(x);
+#endif
+}
+
+template <int ST>
+struct Stream;
+
+// ---- discrete bending, E = K/2 (theta - theta0)^2 (discreteBendingEnergy.cpp:9-30) ---------------------------------
+// With e = x1 - x0, a = x2 - x1, b = x3 - x1, N1 = e x a, N2 = b x e:
+//   theta = atan2(-|e| N1.b, N1.N2)                 [(n1 x n2).e^ = -|e| N1.b / (|N1||N2|),  n1.n2 = N1.N2 / (|N1||N2|)]
+//   g = K d grad(theta),  H = K (grad grad^T + d Hess(theta)),  d = theta - theta0.
+//
+// Owner opposite to the edge (canonical position x2; neighbours {x0, x1, x3}; q = {theta0, K}):
+//   grad = -|e| N1 / |N1|^2,   Hess = -|e| / |N1|^4 (N1 T^T + T N1^T),  T = e x N1.
+template <>
+struct Stream<ST_BEND_OPP> {
+    static constexpr int NI = 3, NQ = 2;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d e = xn[1] - xn[0];
+        const V3d a = xo - xn[1], b = xn[2] - xn[1];
+        const V3d N1 = cross(e, a), N2 = cross(b, e);
+        const double ee = dot(e, e);
+        const double le = ee * fastRsqrt(ee);
+        const double d = ::atan2(-le * dot(N1, b), dot(N1, N2)) - q[0];
+        const double K = q[1], Kd = K * d;
+        const double i = fastRcp(dot(N1, N1));
+        const double c = -le * i;
+        const V3d g = N1 * c;
+        const V3d T = cross(e, N1);
+        addSymOuter2(HAcc, N1, T, Kd * c * i);
+        gAcc.x += Kd * g.x;
+        gAcc.y += Kd * g.y;
+        gAcc.z += Kd * g.z;
+        addOuter(HAcc, g, K);
+    }
+};
+
+// Owner at the start of the edge (canonical position x0; neighbours {x1, x2, x3}; q = {theta0, K}):
+//   W = N / |N|^2, phi_a = a.e / |e|, phi_b = b.e / |e|,   grad = -(phi_a W1 + phi_b W2),
+//   Hess = sym(W1 dphi_a^T) + sym(W2 dphi_b^T) - phi_a (t1 N1^T + N1 t1^T) / |N1|^4 + phi_b (t2 N2^T + N2 t2^T) / |N2|^4,
+//   dphi_a = a / |e| - e (a.e) / |e|^3,  t1 = a x N1,  t2 = b x N2.
+template <>
+struct Stream<ST_BEND_EDGE> {
+    static constexpr int NI = 3, NQ = 2;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d e = xn[0] - xo;
+        const V3d a = xn[1] - xn[0], b = xn[2] - xn[0];
+        const V3d N1 = cross(e, a), N2 = cross(b, e);
+        const double ee = dot(e, e);
+        const double ie = fastRsqrt(ee);
+        const double le = ee * ie;
+        const double d = ::atan2(-le * dot(N1, b), dot(N1, N2)) - q[0];
+        const double K = q[1], Kd = K * d;
+        const double i1 = fastRcp(dot(N1, N1)), i2 = fastRcp(dot(N2, N2));
+        const double ae = dot(a, e), be = dot(b, e);
+        const double phia = ae * ie, phib = be * ie;
+        const double ie3 = ie * ie * ie;
+        const V3d W1 = N1 * i1, W2 = N2 * i2;
+        const V3d ga = a * ie - e * (ae * ie3), gb = b * ie - e * (be * ie3);
+        const V3d g = -(W1 * phia + W2 * phib);
+        const V3d t1 = cross(a, N1), t2 = cross(b, N2);
+        addSymOuter2(HAcc, W1, ga, 0.5 * Kd);
+        addSymOuter2(HAcc, W2, gb, 0.5 * Kd);
+        addSymOuter2(HAcc, t1, N1, -Kd * phia * i1 * i1);
+        addSymOuter2(HAcc, t2, N2, Kd * phib * i2 * i2);
+        gAcc.x += Kd * g.x;
+        gAcc.y += Kd * g.y;
+        gAcc.z += Kd * g.z;
+        addOuter(HAcc, g, K);
+    }
+};
+
+// ---- StVK membrane (membraneStvkEnergy.cpp:9-28): C = (E00, E11, 2 E01), E = 1/2 C^T K C ---------------------------
+// Neighbours {p, q} in cyclic order after the owner; q = {g_p(2), g_q(2), K00, K01, K22} with g_s the rows of the
+// shape-gradient matrix (F = sum_s x_s g_s^T, g_o = -g_p - g_q = (ga, gb)).  With s = K C:
+//   grad = (s0 ga + s2 gb) F0 + (s1 gb + s2 ga) F1
+//   Hess = A F0 F0^T + B F1 F1^T + C (F0 F1^T + F1 F0^T) + (s0 ga^2 + s1 gb^2 + 2 s2 ga gb) I,
+//   A = K00 ga^2 + K22 gb^2,  B = K00 gb^2 + K22 ga^2,  C = (K01 + K22) ga gb.
+template <>
+struct Stream<ST_MEMBRANE_STVK> {
+    static constexpr int NI = 2, NQ = 7;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d dp = xn[0] - xo, dq = xn[1] - xo;
+        const V3d F0 = dp * q[0] + dq * q[2], F1 = dp * q[1] + dq * q[3];
+        const double K00 = q[4], K01 = q[5], K22 = q[6];
+        const double C0 = 0.5 * (dot(F0, F0) - 1.0), C1 = 0.5 * (dot(F1, F1) - 1.0), C2 = dot(F0, F1);
+        const double s0 = K00 * C0 + K01 * C1, s1 = K01 * C0 + K00 * C1, s2 = K22 * C2;
+        const double ga = -(q[0] + q[2]), gb = -(q[1] + q[3]);
+        const double al0 = s0 * ga + s2 * gb, al1 = s1 * gb + s2 * ga;
+        gAcc.x += al0 * F0.x + al1 * F1.x;
+        gAcc.y += al0 * F0.y + al1 * F1.y;
+        gAcc.z += al0 * F0.z + al1 * F1.z;
+        const double gaa = ga * ga, gbb = gb * gb, gab = ga * gb;
+        const double geo = s0 * gaa + s1 * gbb + 2.0 * (s2 * gab);
+        const double A = K00 * gaa + K22 * gbb, B = K00 * gbb + K22 * gaa, C = (K01 + K22) * gab;
+        const V3d P0 = F0 * A + F1 * C, P1 = F1 * B + F0 * C;
+        HAcc.xx += F0.x * P0.x + F1.x * P1.x + geo;
+        HAcc.yy += F0.y * P0.y + F1.y * P1.y + geo;
+        HAcc.zz += F0.z * P0.z + F1.z * P1.z + geo;
+        HAcc.xy += F0.x * P0.y + F1.x * P1.y;
+        HAcc.xz += F0.x * P0.z + F1.x * P1.z;
+        HAcc.yz += F0.y * P0.z + F1.y * P1.z;
+    }
+};
+
+// ---- tetrahedra: neighbours {p, q, r} = the other three vertices in cyclic stencil order after the owner; the first
+// 9 doubles are the rows g_p, g_q, g_r of the shape-gradient matrix (F = sum_s x_s g_s^T, g_o = -(g_p + g_q + g_r)),
+// so that F = (x_p - x_o) g_p^T + (x_q - x_o) g_q^T + (x_r - x_o) g_r^T and dF = dx_o g_o^T.
+SPGX_HD void tetFfromOwner(const V3d &xo, const V3d *xn, const double *q, V3d &F0, V3d &F1, V3d &F2, V3d &go)
+{
+    const V3d dp = xn[0] - xo, dq = xn[1] - xo, dr = xn[2] - xo;
+    F0 = dp * q[0] + dq * q[3] + dr * q[6];
+    F1 = dp * q[1] + dq * q[4] + dr * q[7];
+    F2 = dp * q[2] + dq * q[5] + dr * q[8];
+    go = V3d(-(q[0] + q[3] + q[6]), -(q[1] + q[4] + q[7]), -(q[2] + q[5] + q[8]));
+}
+
+// Stable Neo-Hookean (stableNeoHookeanEnergy.cpp:33-61): E = lambda/2 (J - alpha)^2 + mu/2 (tr(F^T F) - 3).
+// J = det F is affine in a single vertex (dF = dx g^T is rank one), so with c = cof(F) g = dJ/dx_o:
+//   grad = lambda (J - alpha) c + mu F g,   Hess = lambda c c^T + mu |g|^2 I.      q = {g_p, g_q, g_r, lambda V, mu V, alpha}
+template <>
+struct Stream<ST_TET_SNH> {
+    static constexpr int NI = 3, NQ = 12;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        V3d F0, F1, F2, go;
+        tetFfromOwner(xo, xn, q, F0, F1, F2, go);
+        const double lam = q[9], mu = q[10], alpha = q[11];
+        // cof(F) columns: F1 x F2, F2 x F0, F0 x F1  (J = F0 . (F1 x F2))
+        const V3d c0 = cross(F1, F2), c1 = cross(F2, F0), c2 = cross(F0, F1);
+        const double J = dot(F0, c0);
+        const V3d c = c0 * go.x + c1 * go.y + c2 * go.z;
+        const V3d Fg = F0 * go.x + F1 * go.y + F2 * go.z;
+        const double h = lam * (J - alpha);
+        gAcc.x += h * c.x + mu * Fg.x;
+        gAcc.y += h * c.y + mu * Fg.y;
+        gAcc.z += h * c.z + mu * Fg.z;
+        addOuter(HAcc, c, lam);
+        const double iso = mu * dot(go, go);
+        HAcc.xx += iso;
+        HAcc.yy += iso;
+        HAcc.zz += iso;
+    }
+};
+
+// StVK tetrahedron (stvkEnergy.cpp:41-65): E = lambda/2 tr(E)^2 + mu tr(E^2), E = (F^T F - I)/2.
+// With S = lambda tr(E) I + 2 mu E (second Piola-Kirchhoff), w = F g:
+//   grad = F S g,   Hess = (g^T S g) I + (lambda + mu) w w^T + mu |g|^2 F F^T.        q = {g_p, g_q, g_r, lambda V, mu V}
+template <>
+struct Stream<ST_TET_STVK> {
+    static constexpr int NI = 3, NQ = 11;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        V3d F0, F1, F2, go;
+        tetFfromOwner(xo, xn, q, F0, F1, F2, go);
+        const double lam = q[9], mu = q[10];
+        const double e00 = 0.5 * (dot(F0, F0) - 1.0), e11 = 0.5 * (dot(F1, F1) - 1.0), e22 = 0.5 * (dot(F2, F2) - 1.0);
+        const double e01 = 0.5 * dot(F0, F1), e02 = 0.5 * dot(F0, F2), e12 = 0.5 * dot(F1, F2);
+        const double ltr = lam * (e00 + e11 + e22), mu2 = 2.0 * mu;
+        // S g
+        const double sg0 = (ltr + mu2 * e00) * go.x + mu2 * (e01 * go.y + e02 * go.z);
+        const double sg1 = (ltr + mu2 * e11) * go.y + mu2 * (e01 * go.x + e12 * go.z);
+        const double sg2 = (ltr + mu2 * e22) * go.z + mu2 * (e02 * go.x + e12 * go.y);
+        gAcc.x += F0.x * sg0 + F1.x * sg1 + F2.x * sg2;
+        gAcc.y += F0.y * sg0 + F1.y * sg1 + F2.y * sg2;
+        gAcc.z += F0.z * sg0 + F1.z * sg1 + F2.z * sg2;
+        const V3d w = F0 * go.x + F1 * go.y + F2 * go.z;
+        addOuter(HAcc, w, lam + mu);
+        const double mg = mu * dot(go, go);
+        addOuter(HAcc, F0, mg);
+        addOuter(HAcc, F1, mg);
+        addOuter(HAcc, F2, mg);
+        const double iso = go.x * sg0 + go.y * sg1 + go.z * sg2;
+        HAcc.xx += iso;
+        HAcc.yy += iso;
+        HAcc.zz += iso;
+    }
+};
+
+// ---- host side: which stream an incidence of `kind` at stencil position `local` goes to, and its canonical record ----
+// returns -1 when the kind has no stream (it then runs through the generic CSR path of the kernel)
+SPGX_HD int streamTypeOf(int kind, int local)
+{
+    switch (kind) {
+    case K_DISCRETE_BENDING: return local < 2 ? ST_BEND_EDGE : ST_BEND_OPP;
+    case K_MEMBRANE_STVK: return ST_MEMBRANE_STVK;
+    case K_TET_SNH: return ST_TET_SNH;
+    case K_TET_STVK: return ST_TET_STVK;
+    default: return -1;
+    }
+}
+SPGX_HD int streamNI(int st)
+{
+    return st == ST_MEMBRANE_STVK ? 2 : 3;
+}
+SPGX_HD int streamNQ(int st)
+{
+    switch (st) {
+    case ST_BEND_EDGE:
+    case ST_BEND_OPP: return 2;
+    case ST_MEMBRANE_STVK: return 7;
+    case ST_TET_SNH: return 12;
+    case ST_TET_STVK: return 11;
+    default: return 0;
+    }
+}
+// stencil: the S vertex ids of the stencil (any id space), p: the kind's record (energies.cuh); nbr: NI ids out
+SPGX_HD void makeStreamRecord(int kind, const int32_t *stencil, const double *p, int local, int32_t *nbr, double *q)
+{
+    switch (kind) {
+    case K_DISCRETE_BENDING:
+        if (local < 2) {  // owner on the edge: canonical x0; local 1 flips the edge, which negates theta
+            nbr[0] = stencil[1 - local], nbr[1] = stencil[2], nbr[2] = stencil[3];
+            q[0] = local == 0 ? p[0] : -p[0];
+        } else {  // owner opposite: canonical x2; local 3 swaps the opposite vertices, which negates theta
+            nbr[0] = stencil[0], nbr[1] = stencil[1], nbr[2] = stencil[local == 2 ? 3 : 2];
+            q[0] = local == 2 ? p[0] : -p[0];
+        }
+        q[1] = p[1];
+        break;
+    case K_MEMBRANE_STVK: {
+        const int ip = (local + 1) % 3, iq = (local + 2) % 3;
+        const double gs[3][2] = {{-(p[0] + p[2]), -(p[1] + p[3])}, {p[0], p[1]}, {p[2], p[3]}};
+        nbr[0] = stencil[ip], nbr[1] = stencil[iq];
+        q[0] = gs[ip][0], q[1] = gs[ip][1], q[2] = gs[iq][0], q[3] = gs[iq][1];
+        q[4] = p[4], q[5] = p[5], q[6] = p[6];
+        break;
+    }
+    case K_TET_SNH:
+    case K_TET_STVK: {
+        // rows of the shape-gradient matrix: g_1..g_3 = rows of Dinv (p[0..8] row-major), g_0 = -(g_1 + g_2 + g_3)
+        double gs[4][3];
+        for (int c = 0; c < 3; ++c) {
+            gs[1][c] = p[c], gs[2][c] = p[3 + c], gs[3][c] = p[6 + c];
+            gs[0][c] = -(p[c] + p[3 + c] + p[6 + c]);
+        }
+        for (int k = 0; k < 3; ++k) {
+            const int s = (local + 1 + k) % 4;
+            nbr[k] = stencil[s];
+            for (int c = 0; c < 3; ++c) q[3 * k + c] = gs[s][c];
+        }
+        q[9] = p[9], q[10] = p[10];
+        if (kind == K_TET_SNH) q[11] = p[13];
+        break;
+    }
+    default: break;
+    }
+}
+
+// run one canonical evaluator by runtime stream type (tests, host and device)
+SPGX_HD void evalStream(int st, const V3d &xo, const V3d *xn, const double *q, V3d &g, Sym3 &H)
+{
+    switch (st) {
+    case ST_BEND_EDGE: Stream<ST_BEND_EDGE>::eval(xo, xn, q, g, H); break;
+    case ST_BEND_OPP: Stream<ST_BEND_OPP>::eval(xo, xn, q, g, H); break;
+    case ST_MEMBRANE_STVK: Stream<ST_MEMBRANE_STVK>::eval(xo, xn, q, g, H); break;
+    case ST_TET_SNH: Stream<ST_TET_SNH>::eval(xo, xn, q, g, H); break;
+    case ST_TET_STVK: Stream<ST_TET_STVK>::eval(xo, xn, q, g, H); break;
+    default: break;
+    }
+}
+}  // namespace spgx

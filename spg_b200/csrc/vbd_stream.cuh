@@ -1,0 +1,314 @@
+// Streaming Vertex Block Descent colour pass (reference: spg/source/sim/solver/vbd.cpp:99-157).
+//
+// A group of G lanes owns one vertex of the colour (VW = 32 / G vertices per warp).  Per warp:
+//   1. the unique-neighbour positions of its VW vertices are gathered ONCE into a shared-memory tile with
+//      cp.async (LDGSTS: no registers held while the L2 gathers are in flight), laid out [neighbour][xyz][vertex]
+//      so that every later read is bank-conflict free;
+//   2. each incidence stream (streams.cuh) of the slice is read fully coalesced (one 128 B / 256 B line per field
+//      per warp), two steps ahead in registers; the canonical evaluator picks its neighbour positions out of the
+//      tile by 8-bit local index and accumulates dE/dx and the 3x3 block d2E/dx2;
+//   3. energies without a stream (anchors, and any kind without a hand-derived block) run through the generic
+//      CSR path with second-order duals seeded on the owning vertex;
+//   4. the G partial sums are reduced with warp shuffles; lane group 0 adds the inertia term, applies the
+//      det(H) > 1e-10 gate (vbd.cpp:139) and the cofactor solve, and writes the vertex.
+#pragma once
+#include "kernels.h"
+#include "streams.cuh"
+
+namespace spgx
+{
+using D2 = Dual<3, true>;
+
+__device__ __forceinline__ void cpAsync8(double *smemDst, const double *gmemSrc)
+{
+    const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smemDst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmemSrc));
+}
+__device__ __forceinline__ void cpAsyncCommit()
+{
+    asm volatile("cp.async.commit_group;");
+}
+__device__ __forceinline__ void cpAsyncWaitAll()
+{
+    asm volatile("cp.async.wait_all;" ::: "memory");
+}
+
+// generic CSR path: lanes of the vertex stride over its (stencil, local) entries of one energy
+template <int KIND>
+__device__ __forceinline__ void accumulateKind(const VbdEnergyDev &en, const double *__restrict__ x, int slot, int sub,
+                                               int G, V3d &g, Sym3 &H)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int S = EK::S;
+    const uint32_t rb = en.rowptr[slot], re = en.rowptr[slot + 1];
+    for (uint32_t q = rb + sub; q < re; q += G) {
+        const uint32_t ent = en.entries[q];
+        const uint32_t st = ent >> 2;
+        const int local = ent & 3u;
+        const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
+        const double *rec = en.records + static_cast<size_t>(st) * EK::NP;
+        if constexpr (HasHandDerived<EK>::value) {
+            V3d xs[S];
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const size_t o = 3 * static_cast<size_t>(ids[s]);
+                xs[s] = V3d(x[o], x[o + 1], x[o + 2]);
+            }
+            EK::vertexGradHess(xs, rec, local, g, H);
+        } else {
+            V3<D2> xs[S];
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const size_t o = 3 * static_cast<size_t>(ids[s]);
+                const bool own = (s == local);
+                xs[s] = V3<D2>(D2(x[o], own ? 0 : -1), D2(x[o + 1], own ? 1 : -1), D2(x[o + 2], own ? 2 : -1));
+            }
+            const D2 E = stencilEnergy<KIND, D2>(xs, rec);
+            g.x += E.g[0];
+            g.y += E.g[1];
+            g.z += E.g[2];
+            H.xx += E.h[0];
+            H.xy += E.h[1];
+            H.xz += E.h[2];
+            H.yy += E.h[3];
+            H.yz += E.h[4];
+            H.zz += E.h[5];
+        }
+    }
+}
+
+template <unsigned KMASK, int KIND>
+__device__ __forceinline__ void accumulateKindIfPresent(const VbdEnergyDev &en, const double *__restrict__ x, int slot,
+                                                        int sub, int G, V3d &g, Sym3 &H)
+{
+    if constexpr ((KMASK >> KIND) & 1u) {
+        if (en.kind == KIND) accumulateKind<KIND>(en, x, slot, sub, G, g, H);
+    }
+}
+
+template <unsigned KMASK>
+__device__ __forceinline__ void accumulateCsrEnergies(const VbdArgs &a, int slot, int sub, int G, V3d &g, Sym3 &H)
+{
+    for (int e = 0; e < a.nEnergies; ++e) {
+        const VbdEnergyDev &en = a.e[e];
+        if (en.streamed) continue;
+        accumulateKindIfPresent<KMASK, K_SPRING>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_SPRING_CONTINUUM>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_DISCRETE_BENDING>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_QUADRATIC_BENDING>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_MEMBRANE_STVK>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_MEMBRANE_CHOI>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_MEMBRANE_BW>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_TET_STVK>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_TET_SNH>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_ANCHOR>(en, a.x, slot, sub, G, g, H);
+    }
+}
+
+// butterfly over the sub-lane bits (lanes of one vertex sit VW apart), inertia term, gate, solve, write
+template <int G>
+__device__ __forceinline__ void reduceSolveWrite(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, V3d f,
+                                                 Sym3 H, double invdtSquared)
+{
+    constexpr int VW = 32 / G;
+#pragma unroll
+    for (int o = VW; o < 32; o <<= 1) {
+        f.x += __shfl_xor_sync(0xffffffffu, f.x, o);
+        f.y += __shfl_xor_sync(0xffffffffu, f.y, o);
+        f.z += __shfl_xor_sync(0xffffffffu, f.z, o);
+        H.xx += __shfl_xor_sync(0xffffffffu, H.xx, o);
+        H.xy += __shfl_xor_sync(0xffffffffu, H.xy, o);
+        H.xz += __shfl_xor_sync(0xffffffffu, H.xz, o);
+        H.yy += __shfl_xor_sync(0xffffffffu, H.yy, o);
+        H.yz += __shfl_xor_sync(0xffffffffu, H.yz, o);
+        H.zz += __shfl_xor_sync(0xffffffffu, H.zz, o);
+    }
+    if (valid && sub == 0) {
+        const size_t o = 3 * static_cast<size_t>(slot);
+        const double mOverdtSquared = a.mass[slot] * invdtSquared;
+        // f holds the accumulated energy gradient: force = -gradient; inertia term of vbd.cpp:109-112, :123
+        f.x = -f.x - mOverdtSquared * (xo.x - a.xInertial[o]);
+        f.y = -f.y - mOverdtSquared * (xo.y - a.xInertial[o + 1]);
+        f.z = -f.z - mOverdtSquared * (xo.z - a.xInertial[o + 2]);
+        H.xx += mOverdtSquared;
+        H.yy += mOverdtSquared;
+        H.zz += mOverdtSquared;
+        const double d = det(H);
+        if (d > 1e-10) {  // vbd.cpp:139
+            const V3d dx = solveSym3(H, d, f);
+            a.x[o] = xo.x + dx.x;
+            a.x[o + 1] = xo.y + dx.y;
+            a.x[o + 2] = xo.z + dx.z;
+        }
+    }
+}
+
+template <int ST>
+struct StreamRec {
+    using SK = Stream<ST>;
+    uint32_t idx;
+    double q[SK::NQ];
+    __device__ __forceinline__ void load(const VbdStreamDev &sd, uint32_t t, int lane)
+    {
+        idx = __ldg(sd.idx + static_cast<size_t>(t) * 32 + lane);
+        const double *qp = sd.params + static_cast<size_t>(t) * (SK::NQ * 32) + lane;
+#pragma unroll
+        for (int k = 0; k < SK::NQ; ++k) q[k] = __ldg(qp + k * 32);
+    }
+    // P: the warp's neighbour tile, already offset to this lane's vertex column; element (k, c) at P[(3 k + c) * VW]
+    template <int VW>
+    __device__ __forceinline__ void eval(const double *P, const V3d &xo, V3d &g, Sym3 &H) const
+    {
+        if (idx == 0xFFFFFFFFu) return;
+        V3d xn[SK::NI];
+#pragma unroll
+        for (int k = 0; k < SK::NI; ++k) {
+            const double *p = P + ((idx >> (8 * k)) & 0xFFu) * (3 * VW);
+            xn[k] = V3d(p[0], p[VW], p[2 * VW]);
+        }
+        SK::eval(xo, xn, q, g, H);
+    }
+};
+
+template <int ST, int VW>
+__device__ __forceinline__ void accumulateStream(const VbdStreamDev &sd, const double *P, int slice, int lane,
+                                                 const V3d &xo, V3d &g, Sym3 &H)
+{
+    uint32_t t = sd.offsets[slice];
+    const uint32_t te = sd.offsets[slice + 1];
+    if (t >= te) return;
+    StreamRec<ST> r0, r1;
+    r0.load(sd, t, lane);
+    r1 = r0;
+    if (t + 1 < te) r1.load(sd, t + 1, lane);
+    for (;;) {
+        r0.template eval<VW>(P, xo, g, H);
+        if (t + 2 < te) r0.load(sd, t + 2, lane);
+        if (++t >= te) break;
+        r1.template eval<VW>(P, xo, g, H);
+        if (t + 2 < te) r1.load(sd, t + 2, lane);
+        if (++t >= te) break;
+    }
+}
+
+template <unsigned SMASK, int ST, int VW>
+__device__ __forceinline__ void accumulateStreamIfPresent(const VbdStreamDev &sd, const double *P, int slice, int lane,
+                                                          const V3d &xo, V3d &g, Sym3 &H)
+{
+    if constexpr ((SMASK >> ST) & 1u) {
+        if (sd.type == ST) accumulateStream<ST, VW>(sd, P, slice, lane, xo, g, H);
+    }
+}
+
+constexpr int kStreamBlockThreads = 128;
+
+template <unsigned SMASK, unsigned KMASK, int G, int OCC>
+__global__ void __launch_bounds__(kStreamBlockThreads, OCC)
+    vbdStreamKernel(const __grid_constant__ VbdArgs a, int begin, int end, int sliceBase, double invdtSquared)
+{
+    constexpr int VW = 32 / G;  // vertices per warp
+    extern __shared__ double tile[];
+    const int warpInBlock = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int warp = blockIdx.x * (kStreamBlockThreads / 32) + warpInBlock;
+    const int v = lane % VW, sub = lane / VW;
+    if (begin + warp * VW >= end) return;  // whole warp past the colour
+    const int slot = begin + warp * VW + v;
+    const bool valid = slot < end;
+    const int slice = sliceBase + warp;
+    double *P = tile + static_cast<size_t>(warpInBlock) * (a.maxNbr * 3 * VW) + v;
+
+    // 1. unique-neighbour gather (rows of padding lanes hold slot 0: harmless reads)
+    {
+        const uint32_t nb = a.nbrOffsets[slice], ne = a.nbrOffsets[slice + 1];
+        for (uint32_t k = nb + sub; k < ne; k += G) {
+            const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
+            const double *src = a.x + 3 * static_cast<size_t>(id);
+            double *dst = P + (k - nb) * (3 * VW);
+            cpAsync8(dst, src);
+            cpAsync8(dst + VW, src + 1);
+            cpAsync8(dst + 2 * VW, src + 2);
+        }
+        cpAsyncCommit();
+    }
+    V3d xo(0.0, 0.0, 0.0);
+    if (valid) {
+        const size_t o = 3 * static_cast<size_t>(slot);
+        xo = V3d(a.x[o], a.x[o + 1], a.x[o + 2]);
+    }
+    cpAsyncWaitAll();
+    if constexpr (G > 1) __syncwarp();
+
+    // 2. incidence streams
+    V3d f(0.0, 0.0, 0.0);
+    Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    for (int s = 0; s < a.nStreams; ++s) {
+        const VbdStreamDev &sd = a.s[s];
+        accumulateStreamIfPresent<SMASK, ST_BEND_EDGE, VW>(sd, P, slice, lane, xo, f, H);
+        accumulateStreamIfPresent<SMASK, ST_BEND_OPP, VW>(sd, P, slice, lane, xo, f, H);
+        accumulateStreamIfPresent<SMASK, ST_MEMBRANE_STVK, VW>(sd, P, slice, lane, xo, f, H);
+        accumulateStreamIfPresent<SMASK, ST_TET_SNH, VW>(sd, P, slice, lane, xo, f, H);
+        accumulateStreamIfPresent<SMASK, ST_TET_STVK, VW>(sd, P, slice, lane, xo, f, H);
+    }
+    // 3. energies without a stream
+    if (valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
+    // 4. reduce, solve, write
+    reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
+}
+
+template <unsigned SMASK, unsigned KMASK, int G, int OCC>
+void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
+{
+    constexpr int VW = 32 / G;
+    const int n = end - begin;
+    if (n <= 0) return;
+    const int warps = (n + VW - 1) / VW;
+    constexpr int warpsPerBlock = kStreamBlockThreads / 32;
+    const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
+    const size_t smem = static_cast<size_t>(warpsPerBlock) * args.maxNbr * 3 * VW * sizeof(double);
+    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC>;
+    static size_t configured = 0;  // per instantiation
+    if (smem > configured) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured = smem;
+    }
+    kernel<<<blocks, kStreamBlockThreads, smem, stream>>>(args, begin, end, sliceBase, invdtSquared);
+}
+
+template <unsigned SMASK, unsigned KMASK, int G>
+void launchStreamG(const VbdArgs &args, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                   cudaStream_t stream)
+{
+    switch (occ) {
+    case 3: launchStreamGO<SMASK, KMASK, G, 3>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    case 5: launchStreamGO<SMASK, KMASK, G, 5>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    default: launchStreamGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    }
+}
+
+template <unsigned SMASK, unsigned KMASK>
+void launchStream(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                  cudaStream_t stream)
+{
+    switch (lanes) {
+    case 1: launchStreamG<SMASK, KMASK, 1>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
+    case 4: launchStreamG<SMASK, KMASK, 4>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
+    default: launchStreamG<SMASK, KMASK, 2>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
+    }
+}
+
+constexpr unsigned sbit(int k)
+{
+    return 1u << k;
+}
+constexpr unsigned kStreamsCloth = sbit(ST_BEND_EDGE) | sbit(ST_BEND_OPP) | sbit(ST_MEMBRANE_STVK);
+constexpr unsigned kStreamsTets = sbit(ST_TET_SNH) | sbit(ST_TET_STVK);
+constexpr unsigned kKindsAnchor = sbit(K_ANCHOR);
+
+// one translation unit per combination (compile time)
+void launchStreamCloth(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                       cudaStream_t stream);
+void launchStreamTets(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                      cudaStream_t stream);
+}  // namespace spgx

@@ -1,0 +1,12 @@
+// Streaming VBD colour pass instantiated for cloth: discrete bending (two canonical streams) + StVK membrane streams,
+// anchors through the CSR path.
+#include "vbd_stream.cuh"
+
+namespace spgx
+{
+void launchStreamCloth(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                       cudaStream_t stream)
+{
+    launchStream<kStreamsCloth, kKindsAnchor>(args, lanes, occ, begin, end, sliceBase, invdtSquared, stream);
+}
+}  // namespace spgx

@@ -33,7 +33,9 @@ def _compare_group(ctx, oracle, sc, solver_kind, n_samples=12):
         for i in np.unique(np.linspace(0, n - 1, n_samples).astype(int)):
             for local in range(S.STENCIL_SIZE[en.kind]):
                 fr, hr = og.vertex_force_hessian(e, int(i), local)
-                for hand in (False, True):  # generic dual numbers, and the hand-derived override the kernel runs
+                # 0: generic dual numbers, 1: the kind's hand-derived block (CSR path), 2: the canonical stream
+                # evaluator behind the host-side canonicalisation (what the streaming kernel runs, streams.cuh)
+                for hand in (0, 1, 2):
                     f, h = g.eval_vertex_force_hessian(e, int(i), local, hand)
                     _relclose(f, fr)
                     _relclose(h, hr)

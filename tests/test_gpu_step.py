@@ -175,3 +175,30 @@ def test_xpbd_lambda_iterations_equal_reference_at_one(ctx):
     x3, _ = g.download()
     assert np.isfinite(x3).all() and not np.array_equal(x1, x3)
     assert np.abs(x1 - x3).max() < 1e-2
+
+
+@pytest.mark.parametrize("scene", ["cloth", "snh", "tstvk"])
+def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
+    """The streaming kernel (owner-centric incidence streams, every lanes-per-vertex / occupancy variant) against the
+    generic CSR kernel and the oracle on the same scene: all within the 1e-9 gate of each other."""
+    sc = {"cloth": lambda: S.cloth(23, 17), "snh": lambda: S.tet_beam(9, 4, 3, S.K_TET_SNH),
+          "tstvk": lambda: S.tet_beam(7, 3, 4, S.K_TET_STVK)}[scene]()
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, 0, 0.01, 2, 6)
+    osol.step(1)
+    xr, vr = osol.state()
+    results = {}
+    for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [
+            (f"g{l}o{o}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_OCC": str(o)}) for l in (1, 2, 4) for o in (3, 4, 5)]:
+        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_OCC"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = api.Group.from_scene(ctx, sc)
+        g.finalize(api.SPGX_VBD)
+        g.vbd_step(0.01, 2, 6)
+        results[name] = g.download()
+        g.close()
+    for name, (x, v) in results.items():
+        assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8, name
+        assert _rel(x, results["csr"][0]) <= 1e-11, name
