@@ -42,55 +42,67 @@ static double modelRecordBytes(int kind)
 }
 
 // Streaming layout of the VBD colour pass (kernels.h, streams.cuh).  For every vertex (in slot order): the list of its
-// unique neighbours over all streamed incidences (first-seen order), and per (energy, stream type) the canonical
-// incidence records referencing that list by 8-bit index.  Both are packed as sliced ELL over warp-slices of
-// VW = 32 / G consecutive slots of one colour: incidence j of the slice's vertex v sits in step j / G at lane
-// (j % G) * VW + v; neighbour k of vertex v sits in row k at column v.
-// Returns false (and leaves the group on the CSR path) when a vertex has more than 255 unique neighbours or there
-// are more (energy, type) pairs than kMaxStreams.
+// unique neighbours over all streamed incidences (first-seen order), and per stream type the canonical incidence
+// records referencing that list by 8-bit index.  Both are packed as sliced ELL over warp-slices of VW = 32 / G
+// consecutive slots of one colour: incidence j of the slice's vertex v sits in step j / G at lane (j % G) * VW + v;
+// neighbour k of vertex v sits in row k at column v.  One 32-byte descriptor per slice holds where each of its
+// ranges starts.
+// Returns false (and leaves the group on the CSR path) when a vertex has more than 255 unique neighbours, two
+// energies map to the same stream type, or the neighbour tile would not fit in shared memory.
 static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cudaStream_t st)
 {
     const int V = grp.nVerts, G = grp.vbdLanes, VW = 32 / G;
     const int nColors = static_cast<int>(grp.colorOffsets.size()) - 1;
     struct HostStream {
-        int energy, type, NQ;
+        int energy = -1, NQ = 0;
         std::vector<uint32_t> rowptr;  // per slot
         std::vector<uint32_t> idx;     // per incidence
         std::vector<double> q;         // NQ per incidence
     };
-    std::vector<HostStream> hs;
-    std::vector<int> streamOf(grp.energies.size() * ST_COUNT, -1);
+    HostStream hs[ST_COUNT];
+    bool any = false;
     for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
         const auto &e = grp.energies[ei];
         for (int local = 0; local < e.S; ++local) {
             const int t = streamTypeOf(e.kind, local);
-            if (t < 0 || streamOf[ei * ST_COUNT + t] >= 0) continue;
-            streamOf[ei * ST_COUNT + t] = static_cast<int>(hs.size());
-            hs.push_back({static_cast<int>(ei), t, streamNQ(t), std::vector<uint32_t>(static_cast<size_t>(V) + 1, 0), {}, {}});
+            if (t < 0) continue;
+            if (hs[t].energy >= 0 && hs[t].energy != static_cast<int>(ei)) return false;
+            if (hs[t].energy < 0) {
+                hs[t].energy = static_cast<int>(ei);
+                hs[t].NQ = streamNQ(t);
+                hs[t].rowptr.assign(static_cast<size_t>(V) + 1, 0);
+                any = true;
+            }
         }
     }
-    if (hs.empty() || hs.size() > static_cast<size_t>(kMaxStreams)) return false;
+    if (!any) return false;
 
     std::vector<uint32_t> nbrRowptr(static_cast<size_t>(V) + 1, 0);
     std::vector<uint32_t> nbrList;
     std::vector<int32_t> mark(static_cast<size_t>(V), -1), localIdx(static_cast<size_t>(V), 0);
+    std::vector<uint8_t> hasCsr(static_cast<size_t>(V), 0);
     int maxNbr = 0;
     for (int s = 0; s < V; ++s) {
         const int v = grp.slot2vert[s];
         const uint32_t nb0 = static_cast<uint32_t>(nbrList.size());
-        for (auto &h : hs) h.rowptr[s] = static_cast<uint32_t>(h.idx.size());
+        for (auto &h : hs)
+            if (h.energy >= 0) h.rowptr[s] = static_cast<uint32_t>(h.idx.size());
         for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
             const auto &e = grp.energies[ei];
-            if (streamTypeOf(e.kind, 0) < 0) continue;
+            if (streamTypeOf(e.kind, 0) < 0) {
+                if (inc[ei].rowptr[v + 1] > inc[ei].rowptr[v]) hasCsr[s] = 1;
+                continue;
+            }
             for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
                 const int64_t stencil = inc[ei].flat[q] / e.S;
                 const int local = static_cast<int>(inc[ei].flat[q] % e.S);
-                HostStream &h = hs[streamOf[ei * ST_COUNT + streamTypeOf(e.kind, local)]];
+                const int type = streamTypeOf(e.kind, local);
+                HostStream &h = hs[type];
                 int32_t nbr[3];
                 double rq[16];
                 makeStreamRecord(e.kind, e.stencils.data() + stencil * e.S, e.records.data() + stencil * e.NP, local, nbr, rq);
                 uint32_t word = 0;
-                for (int k = 0; k < streamNI(h.type); ++k) {
+                for (int k = 0; k < streamNI(type); ++k) {
                     const int u = nbr[k];
                     if (mark[u] != s) {
                         mark[u] = s;
@@ -104,85 +116,93 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
             }
         }
         const int cnt = static_cast<int>(nbrList.size() - nb0);
-        if (cnt > 255) return false;
+        if (cnt > 254) return false;
         maxNbr = std::max(maxNbr, cnt);
         nbrRowptr[s + 1] = static_cast<uint32_t>(nbrList.size());
     }
-    for (auto &h : hs) h.rowptr[V] = static_cast<uint32_t>(h.idx.size());
+    maxNbr = std::max(maxNbr, 1);
+    if (static_cast<size_t>(maxNbr) * 3 * VW * 8 * 4 > 200 * 1024) return false;  // 4 warps per block (vbd_stream.cuh)
+    for (auto &h : hs)
+        if (h.energy >= 0) h.rowptr[V] = static_cast<uint32_t>(h.idx.size());
 
-    // ---- sliced-ELL packing ----
-    size_t nSlices = 0;
-    for (int c = 0; c < nColors; ++c) nSlices += static_cast<size_t>((grp.colorOffsets[c + 1] - grp.colorOffsets[c] + VW - 1) / VW);
-    double bytes = 0;
+    // ---- slices and their descriptors ----
+    std::vector<int> sliceSlot;  // first slot of every slice
+    std::vector<int> sliceEnd;   // one past its last slot
+    for (int c = 0; c < nColors; ++c) {
+        const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
+        for (int s0 = b; s0 < en; s0 += VW) {
+            sliceSlot.push_back(s0);
+            sliceEnd.push_back(std::min(s0 + VW, en));
+        }
+    }
+    const size_t nSlices = sliceSlot.size();
+    std::vector<uint32_t> desc((nSlices + 1) * kSliceDescWords, 0u);
+    double bytes = 4.0 * desc.size();
     {
-        std::vector<uint32_t> offsets(1, 0);
-        offsets.reserve(nSlices + 1);
-        for (int c = 0; c < nColors; ++c) {
-            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-            for (int s0 = b; s0 < en; s0 += VW) {
-                uint32_t rows = 0;
-                for (int s = s0; s < std::min(s0 + VW, en); ++s) rows = std::max(rows, nbrRowptr[s + 1] - nbrRowptr[s]);
-                offsets.push_back(offsets.back() + rows);
+        uint32_t row = 0;
+        for (size_t sl = 0; sl < nSlices; ++sl) {
+            desc[sl * kSliceDescWords + 0] = static_cast<uint32_t>(sliceSlot[sl]);
+            desc[sl * kSliceDescWords + 1] = row;
+            uint32_t rows = 0, csr = 0;
+            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
+                rows = std::max(rows, nbrRowptr[s + 1] - nbrRowptr[s]);
+                csr |= hasCsr[s];
             }
+            desc[sl * kSliceDescWords + 7] = csr;
+            row += rows;
         }
-        std::vector<uint32_t> ids(static_cast<size_t>(offsets.back()) * VW, 0u);
-        size_t slice = 0;
-        for (int c = 0; c < nColors; ++c) {
-            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-            for (int s0 = b; s0 < en; s0 += VW, ++slice)
-                for (int s = s0; s < std::min(s0 + VW, en); ++s)
-                    for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
-                        ids[(static_cast<size_t>(offsets[slice]) + (k - nbrRowptr[s])) * VW + (s - s0)] = nbrList[k];
-        }
-        grp.d_nbrOffsets.upload(offsets, st);
+        desc[nSlices * kSliceDescWords + 0] = static_cast<uint32_t>(V);
+        desc[nSlices * kSliceDescWords + 1] = row;
+        std::vector<uint32_t> ids(static_cast<size_t>(row) * VW, 0u);
+        for (size_t sl = 0; sl < nSlices; ++sl)
+            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s)
+                for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
+                    ids[(static_cast<size_t>(desc[sl * kSliceDescWords + 1]) + (k - nbrRowptr[s])) * VW + (s - sliceSlot[sl])] =
+                        nbrList[k];
         grp.d_nbrIds.upload(ids, st);
-        bytes += 4.0 * ids.size() + 4.0 * offsets.size();
+        bytes += 4.0 * ids.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
     grp.streams.clear();
-    grp.streams.resize(hs.size());
+    grp.streams.resize(ST_COUNT);
     grp.streamMask = 0;
-    for (size_t i = 0; i < hs.size(); ++i) {
-        const HostStream &h = hs[i];
+    for (int type = 0; type < ST_COUNT; ++type) {
+        const HostStream &h = hs[type];
+        if (h.energy < 0) continue;
         const int NQ = h.NQ;
-        std::vector<uint32_t> offsets(1, 0);
-        offsets.reserve(nSlices + 1);
-        for (int c = 0; c < nColors; ++c) {
-            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-            for (int s0 = b; s0 < en; s0 += VW) {
-                uint32_t steps = 0;
-                for (int s = s0; s < std::min(s0 + VW, en); ++s)
-                    steps = std::max(steps, (h.rowptr[s + 1] - h.rowptr[s] + G - 1) / G);
-                offsets.push_back(offsets.back() + steps);
-            }
+        uint32_t step = 0;
+        for (size_t sl = 0; sl < nSlices; ++sl) {
+            desc[sl * kSliceDescWords + 2 + type] = step;
+            uint32_t steps = 0;
+            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) steps = std::max(steps, (h.rowptr[s + 1] - h.rowptr[s] + G - 1) / G);
+            step += steps;
         }
-        const size_t T = offsets.back();
+        desc[nSlices * kSliceDescWords + 2 + type] = step;
+        const size_t T = step;
         std::vector<uint32_t> idx(T * 32, 0xFFFFFFFFu);
         std::vector<double> params(T * NQ * 32, 0.0);
-        size_t slice = 0;
-        for (int c = 0; c < nColors; ++c) {
-            const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
-            for (int s0 = b; s0 < en; s0 += VW, ++slice)
-                for (int s = s0; s < std::min(s0 + VW, en); ++s) {
-                    uint32_t j = 0;
-                    for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
-                        const size_t t = offsets[slice] + j / G;
-                        const int lane = static_cast<int>(j % G) * VW + (s - s0);
-                        idx[t * 32 + lane] = h.idx[r];
-                        for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
-                    }
+        for (size_t sl = 0; sl < nSlices; ++sl)
+            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
+                uint32_t j = 0;
+                for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
+                    const size_t t = desc[sl * kSliceDescWords + 2 + type] + j / G;
+                    const int lane = static_cast<int>(j % G) * VW + (s - sliceSlot[sl]);
+                    idx[t * 32 + lane] = h.idx[r];
+                    for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
                 }
-        }
-        auto &out = grp.streams[i];
-        out.type = h.type;
-        out.d_offsets.upload(offsets, st);
+            }
+        auto &out = grp.streams[type];
+        out.type = type;
         out.d_idx.upload(idx, st);
         out.d_params.upload(params, st);
-        grp.streamMask |= 1u << h.type;
-        bytes += 4.0 * idx.size() + 8.0 * params.size() + 4.0 * offsets.size();
+        grp.streamMask |= 1u << type;
+        bytes += 4.0 * idx.size() + 8.0 * params.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
-    grp.maxNbr = std::max(maxNbr, 1);
+    grp.d_sliceDesc.upload(desc, st);
+    SPGX_CUDA(cudaStreamSynchronize(st));
+    grp.nSlices = static_cast<int>(nSlices);
+    grp.maxNbr = maxNbr;
     grp.streamBytes = bytes;
     for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
     return true;
@@ -414,7 +434,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 int64_t largest = 0;
                 for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c)
                     largest = std::max(largest, grp->colorOffsets[c + 1] - grp->colorOffsets[c]);
-                grp->vbdLanes = largest >= 65536 ? 2 : 4;
+                grp->vbdLanes = largest >= 65536 ? 1 : (largest >= 8192 ? 2 : 4);
             }
             if (const char *env = getenv("SPGX_VBD_LANES")) {
                 const int l = atoi(env);
@@ -463,8 +483,11 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->streamMask = 0;
             grp->maxNbr = 0;
             grp->streamBytes = 0;
-            grp->d_nbrOffsets.release();
+            grp->d_sliceDesc.release();
             grp->d_nbrIds.release();
+            grp->nSlices = 0;
+            grp->vbdLookahead = 1024;
+            if (const char *env = getenv("SPGX_VBD_LOOKAHEAD")) grp->vbdLookahead = std::max(0, atoi(env));
             {
                 unsigned smask = 0, kmask = 0;
                 for (auto &e : grp->energies) {

@@ -40,14 +40,19 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
         args.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr,
                      en.streamed ? 1 : 0};
     }
-    args.nStreams = static_cast<int>(grp->streams.size());
-    for (int s = 0; s < args.nStreams; ++s) {
-        const auto &sd = grp->streams[s];
-        args.s[s] = {sd.type, sd.d_offsets.ptr, sd.d_idx.ptr, sd.d_params.ptr};
+    args.nStreams = 0;
+    for (int t = 0; t < kNumStreamTypes; ++t) {
+        args.s[t] = {nullptr, nullptr};
+        if (t < static_cast<int>(grp->streams.size()) && grp->streams[t].d_idx.ptr) {
+            args.s[t] = {grp->streams[t].d_idx.ptr, grp->streams[t].d_params.ptr};
+            args.nStreams++;
+        }
     }
-    args.nbrOffsets = grp->d_nbrOffsets.ptr;
+    args.sliceDesc = grp->d_sliceDesc.ptr;
     args.nbrIds = grp->d_nbrIds.ptr;
     args.maxNbr = grp->maxNbr;
+    args.nSlices = grp->nSlices;
+    args.lookahead = std::min(grp->vbdLookahead, std::max(grp->nSlices - 1, 0));
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
     for (int s = 0; s < nsub; ++s) {

@@ -140,12 +140,12 @@ struct spgx_group {
     // streaming layout (kernels.h): unique-neighbour tables + one stream per (energy, stream type)
     struct StreamState {
         int type = 0;
-        spgx::DevBuf<uint32_t> d_offsets, d_idx;
+        spgx::DevBuf<uint32_t> d_idx;
         spgx::DevBuf<double> d_params;
     };
-    std::vector<StreamState> streams;
-    spgx::DevBuf<uint32_t> d_nbrOffsets, d_nbrIds;
-    int maxNbr = 0;
+    std::vector<StreamState> streams;  // indexed by stream type when non-empty
+    spgx::DevBuf<uint32_t> d_sliceDesc, d_nbrIds;
+    int maxNbr = 0, nSlices = 0, vbdLookahead = 1024;
     unsigned streamMask = 0;
     double streamBytes = 0;  // bytes of stream + neighbour tables one full sweep reads (reported)
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)

@@ -18,15 +18,14 @@ struct VbdEnergyDev {
     int streamed;              // 1: every incidence of this energy lives in a stream below (the CSR path skips it)
 };
 
-constexpr int kMaxStreams = 6;
+constexpr int kNumStreamTypes = 5;  // StreamType (streams.cuh)
+constexpr int kSliceDescWords = 8;
 // One owner-centric incidence stream (streams.cuh): a sliced ELL over warp-slices of VW = 32 / G consecutive slots of
 // one colour.  Step t of a slice holds one incidence per lane (lane = sub * VW + v carries incidence t * G + sub of the
 // slice's vertex v):  idx [t][32] uint32 = the NI neighbour positions as 8-bit indices into the owner's unique-neighbour
-// list (0xFFFFFFFF = padding),  params [t][NQ][32] double.
+// list (0xFFFFFFFF = padding),  params [t][NQ][32] double.  A group has at most one stream per type.
 struct VbdStreamDev {
-    int type;                 // StreamType
-    const uint32_t *offsets;  // per warp-slice first step, nSlices + 1
-    const uint32_t *idx;
+    const uint32_t *idx;  // null: the group has no stream of this type
     const double *params;
 };
 
@@ -38,10 +37,15 @@ struct VbdArgs {
     VbdEnergyDev e[kMaxEnergies];
     // streaming layout (nStreams == 0: CSR path only)
     int nStreams;
-    VbdStreamDev s[kMaxStreams];
-    const uint32_t *nbrOffsets;  // per warp-slice first row of its unique-neighbour table, nSlices + 1
-    const uint32_t *nbrIds;      // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
-    int maxNbr;                  // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
+    VbdStreamDev s[kNumStreamTypes];  // indexed by StreamType
+    // per warp-slice descriptor, kSliceDescWords uint32 each, nSlices + 1 entries (the last one closes the ranges):
+    //   [0] first slot, [1] first row of the unique-neighbour table, [2 + t] first step of stream type t,
+    //   [7] bit 0: some vertex of the slice has incidences on the CSR path
+    const uint32_t *sliceDesc;
+    const uint32_t *nbrIds;  // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
+    int maxNbr;              // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
+    int nSlices;             // all colours
+    int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
 };
 
 // can launchVbdPass run this combination of stream types + CSR kinds through the streaming kernel?

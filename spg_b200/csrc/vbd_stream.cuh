@@ -170,12 +170,11 @@ struct StreamRec {
     }
 };
 
+// steps [t, te) of one stream of the slice, records two steps ahead in registers
 template <int ST, int VW>
-__device__ __forceinline__ void accumulateStream(const VbdStreamDev &sd, const double *P, int slice, int lane,
-                                                 const V3d &xo, V3d &g, Sym3 &H)
+__device__ __forceinline__ void accumulateStream(const VbdStreamDev &sd, uint32_t t, const uint32_t te, const double *P,
+                                                 int lane, const V3d &xo, V3d &g, Sym3 &H)
 {
-    uint32_t t = sd.offsets[slice];
-    const uint32_t te = sd.offsets[slice + 1];
     if (t >= te) return;
     StreamRec<ST> r0, r1;
     r0.load(sd, t, lane);
@@ -191,12 +190,48 @@ __device__ __forceinline__ void accumulateStream(const VbdStreamDev &sd, const d
     }
 }
 
+// pull [ptr, ptr + bytes) into L2 with one TMA bulk prefetch (bytes: multiple of 16, ptr 16-byte aligned)
+__device__ __forceinline__ void bulkPrefetchL2(const void *ptr, uint32_t bytes)
+{
+    if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes));
+}
+__device__ __forceinline__ void prefetchLineL2(const void *ptr)
+{
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+}
+
+struct SliceDesc {
+    uint4 lo, hi;  // [slot, nbrRow, s0, s1], [s2, s3, s4, flags]
+    __device__ __forceinline__ void load(const uint32_t *desc, int slice)
+    {
+        const uint4 *p = reinterpret_cast<const uint4 *>(desc) + 2 * static_cast<size_t>(slice);
+        lo = __ldg(p);
+        hi = __ldg(p + 1);
+    }
+    template <int ST>
+    __device__ __forceinline__ uint32_t stream() const
+    {
+        return ST == 0 ? lo.z : ST == 1 ? lo.w : ST == 2 ? hi.x : ST == 3 ? hi.y : hi.z;
+    }
+};
+
 template <unsigned SMASK, int ST, int VW>
-__device__ __forceinline__ void accumulateStreamIfPresent(const VbdStreamDev &sd, const double *P, int slice, int lane,
-                                                          const V3d &xo, V3d &g, Sym3 &H)
+__device__ __forceinline__ void streamIfPresent(const VbdArgs &a, const SliceDesc &d, const SliceDesc &n, const double *P,
+                                                int lane, const V3d &xo, V3d &g, Sym3 &H)
 {
     if constexpr ((SMASK >> ST) & 1u) {
-        if (sd.type == ST) accumulateStream<ST, VW>(sd, P, slice, lane, xo, g, H);
+        if (a.s[ST].idx) accumulateStream<ST, VW>(a.s[ST], d.stream<ST>(), n.stream<ST>(), P, lane, xo, g, H);
+    }
+}
+template <unsigned SMASK, int ST>
+__device__ __forceinline__ void prefetchStreamIfPresent(const VbdArgs &a, const SliceDesc &d, const SliceDesc &n)
+{
+    if constexpr ((SMASK >> ST) & 1u) {
+        if (a.s[ST].idx) {
+            const uint32_t t = d.stream<ST>(), steps = n.stream<ST>() - t;
+            bulkPrefetchL2(a.s[ST].idx + static_cast<size_t>(t) * 32, steps * 128u);
+            bulkPrefetchL2(a.s[ST].params + static_cast<size_t>(t) * (Stream<ST>::NQ * 32), steps * (Stream<ST>::NQ * 256u));
+        }
     }
 }
 
@@ -204,23 +239,27 @@ constexpr int kStreamBlockThreads = 128;
 
 template <unsigned SMASK, unsigned KMASK, int G, int OCC>
 __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
-    vbdStreamKernel(const __grid_constant__ VbdArgs a, int begin, int end, int sliceBase, double invdtSquared)
+    vbdStreamKernel(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
     extern __shared__ double tile[];
     const int warpInBlock = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int warp = blockIdx.x * (kStreamBlockThreads / 32) + warpInBlock;
+    if (warp >= nSlicesOfColour) return;  // whole warp past the colour
     const int v = lane % VW, sub = lane / VW;
-    if (begin + warp * VW >= end) return;  // whole warp past the colour
-    const int slot = begin + warp * VW + v;
-    const bool valid = slot < end;
     const int slice = sliceBase + warp;
     double *P = tile + static_cast<size_t>(warpInBlock) * (a.maxNbr * 3 * VW) + v;
 
-    // 1. unique-neighbour gather (rows of padding lanes hold slot 0: harmless reads)
+    SliceDesc d, n;
+    d.load(a.sliceDesc, slice);
+    n.load(a.sliceDesc, slice + 1);
+    const int slot = static_cast<int>(d.lo.x) + v;
+    const bool valid = slot < end;
+
+    // 1. unique-neighbour gather (columns of padding lanes hold slot 0: harmless reads)
     {
-        const uint32_t nb = a.nbrOffsets[slice], ne = a.nbrOffsets[slice + 1];
+        const uint32_t nb = d.lo.y, ne = n.lo.y;
         for (uint32_t k = nb + sub; k < ne; k += G) {
             const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
             const double *src = a.x + 3 * static_cast<size_t>(id);
@@ -235,24 +274,43 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     if (valid) {
         const size_t o = 3 * static_cast<size_t>(slot);
         xo = V3d(a.x[o], a.x[o + 1], a.x[o + 2]);
+        prefetchLineL2(a.xInertial + o);
+        prefetchLineL2(a.mass + slot);
+    }
+    // 2. while the gather is in flight: pull the streams of the slice `lookahead` slices further on (wrapping into the
+    // next colour / the next sweep) from HBM into L2, so that every later load of that slice is an L2 hit
+    if (a.lookahead > 0) {
+        int la = slice + a.lookahead;
+        if (la >= a.nSlices) la -= a.nSlices;
+        if (lane == 0) {
+            int la2 = la + a.lookahead;
+            if (la2 >= a.nSlices) la2 -= a.nSlices;
+            prefetchLineL2(a.sliceDesc + static_cast<size_t>(la2) * kSliceDescWords);
+            SliceDesc pd, pn;
+            pd.load(a.sliceDesc, la);
+            pn.load(a.sliceDesc, la + 1);
+            bulkPrefetchL2(a.nbrIds + static_cast<size_t>(pd.lo.y) * VW, (pn.lo.y - pd.lo.y) * (VW * 4u));
+            prefetchStreamIfPresent<SMASK, ST_BEND_EDGE>(a, pd, pn);
+            prefetchStreamIfPresent<SMASK, ST_BEND_OPP>(a, pd, pn);
+            prefetchStreamIfPresent<SMASK, ST_MEMBRANE_STVK>(a, pd, pn);
+            prefetchStreamIfPresent<SMASK, ST_TET_SNH>(a, pd, pn);
+            prefetchStreamIfPresent<SMASK, ST_TET_STVK>(a, pd, pn);
+        }
     }
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
 
-    // 2. incidence streams
+    // 3. incidence streams
     V3d f(0.0, 0.0, 0.0);
     Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    for (int s = 0; s < a.nStreams; ++s) {
-        const VbdStreamDev &sd = a.s[s];
-        accumulateStreamIfPresent<SMASK, ST_BEND_EDGE, VW>(sd, P, slice, lane, xo, f, H);
-        accumulateStreamIfPresent<SMASK, ST_BEND_OPP, VW>(sd, P, slice, lane, xo, f, H);
-        accumulateStreamIfPresent<SMASK, ST_MEMBRANE_STVK, VW>(sd, P, slice, lane, xo, f, H);
-        accumulateStreamIfPresent<SMASK, ST_TET_SNH, VW>(sd, P, slice, lane, xo, f, H);
-        accumulateStreamIfPresent<SMASK, ST_TET_STVK, VW>(sd, P, slice, lane, xo, f, H);
-    }
-    // 3. energies without a stream
-    if (valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
-    // 4. reduce, solve, write
+    streamIfPresent<SMASK, ST_BEND_EDGE, VW>(a, d, n, P, lane, xo, f, H);
+    streamIfPresent<SMASK, ST_BEND_OPP, VW>(a, d, n, P, lane, xo, f, H);
+    streamIfPresent<SMASK, ST_MEMBRANE_STVK, VW>(a, d, n, P, lane, xo, f, H);
+    streamIfPresent<SMASK, ST_TET_SNH, VW>(a, d, n, P, lane, xo, f, H);
+    streamIfPresent<SMASK, ST_TET_STVK, VW>(a, d, n, P, lane, xo, f, H);
+    // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
+    if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
+    // 5. reduce, solve, write
     reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
 }
 
@@ -263,6 +321,7 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     const int n = end - begin;
     if (n <= 0) return;
     const int warps = (n + VW - 1) / VW;
+    if (args.maxNbr * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
     constexpr int warpsPerBlock = kStreamBlockThreads / 32;
     const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
     const size_t smem = static_cast<size_t>(warpsPerBlock) * args.maxNbr * 3 * VW * sizeof(double);
@@ -273,7 +332,7 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
         cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         configured = smem;
     }
-    kernel<<<blocks, kStreamBlockThreads, smem, stream>>>(args, begin, end, sliceBase, invdtSquared);
+    kernel<<<blocks, kStreamBlockThreads, smem, stream>>>(args, end, sliceBase, warps, invdtSquared);
 }
 
 template <unsigned SMASK, unsigned KMASK, int G>
