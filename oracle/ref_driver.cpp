@@ -264,6 +264,18 @@ int ref_group_add_energy(void *h, int kind, int nStencils, const int32_t *stenci
     });
 }
 
+// SpringAnchorEnergy::updateAnchor (springAnchorEnergy.h:13); energies are shared_ptr, so solvers that copied the
+// group see the edit (particleGroup.h:35)
+int ref_update_anchor(void *h, int e, int stencil, const double *anchor3)
+{
+    return guarded([&] {
+        auto *g = static_cast<RefGroup *>(h);
+        auto a = std::dynamic_pointer_cast<spg::SpringAnchorEnergy>(g->energies.at(e));
+        if (!a) throw std::runtime_error("energy is not a SpringAnchorEnergy");
+        a->updateAnchor(stencil, spg::Vector3(anchor3[0], anchor3[1], anchor3[2]));
+    });
+}
+
 int ref_group_size(void *h)
 {
     return static_cast<RefGroup *>(h)->pg.size();

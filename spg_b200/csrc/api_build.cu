@@ -434,7 +434,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 int64_t largest = 0;
                 for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c)
                     largest = std::max(largest, grp->colorOffsets[c + 1] - grp->colorOffsets[c]);
-                grp->vbdLanes = largest >= 65536 ? 1 : (largest >= 8192 ? 2 : 4);
+                grp->vbdLanes = largest >= 200000 ? 1 : (largest >= 30000 ? 2 : 4);
             }
             if (const char *env = getenv("SPGX_VBD_LANES")) {
                 const int l = atoi(env);
@@ -486,8 +486,10 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->d_sliceDesc.release();
             grp->d_nbrIds.release();
             grp->nSlices = 0;
-            grp->vbdLookahead = 1024;
+            grp->vbdLookahead = 512;
             if (const char *env = getenv("SPGX_VBD_LOOKAHEAD")) grp->vbdLookahead = std::max(0, atoi(env));
+            grp->vbdPdl = 1;
+            if (const char *env = getenv("SPGX_VBD_PDL")) grp->vbdPdl = atoi(env) != 0;
             {
                 unsigned smask = 0, kmask = 0;
                 for (auto &e : grp->energies) {

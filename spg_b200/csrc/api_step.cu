@@ -53,6 +53,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.maxNbr = grp->maxNbr;
     args.nSlices = grp->nSlices;
     args.lookahead = std::min(grp->vbdLookahead, std::max(grp->nSlices - 1, 0));
+    args.pdl = grp->vbdPdl;
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
     for (int s = 0; s < nsub; ++s) {

@@ -41,6 +41,16 @@ SPGX_HD void addSymOuter2(Sym3 &H, const V3d &u, const V3d &v, double scale)
     H.xz += scale * (u.x * v.z + u.z * v.x);
     H.yz += scale * (u.y * v.z + u.z * v.y);
 }
+// accumulate u v^T + v u^T into H
+SPGX_HD void addSymOuter2u(Sym3 &H, const V3d &u, const V3d &v)
+{
+    H.xx += 2.0 * (u.x * v.x);
+    H.yy += 2.0 * (u.y * v.y);
+    H.zz += 2.0 * (u.z * v.z);
+    H.xy += u.x * v.y + u.y * v.x;
+    H.xz += u.x * v.z + u.z * v.x;
+    H.yz += u.y * v.z + u.z * v.y;
+}
 // accumulate scale * u u^T into H
 SPGX_HD void addOuter(Sym3 &H, const V3d &u, double scale)
 {

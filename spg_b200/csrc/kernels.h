@@ -46,6 +46,7 @@ struct VbdArgs {
     int maxNbr;              // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
     int nSlices;             // all colours
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
+    int pdl;                 // 1: launch colour passes with programmatic stream serialization
 };
 
 // can launchVbdPass run this combination of stream types + CSR kinds through the streaming kernel?

@@ -143,63 +143,6 @@ __device__ __forceinline__ void reduceSolveWrite(const VbdArgs &a, int slot, boo
     }
 }
 
-template <int ST>
-struct StreamRec {
-    using SK = Stream<ST>;
-    uint32_t idx;
-    double q[SK::NQ];
-    __device__ __forceinline__ void load(const VbdStreamDev &sd, uint32_t t, int lane)
-    {
-        idx = __ldg(sd.idx + static_cast<size_t>(t) * 32 + lane);
-        const double *qp = sd.params + static_cast<size_t>(t) * (SK::NQ * 32) + lane;
-#pragma unroll
-        for (int k = 0; k < SK::NQ; ++k) q[k] = __ldg(qp + k * 32);
-    }
-    // P: the warp's neighbour tile, already offset to this lane's vertex column; element (k, c) at P[(3 k + c) * VW]
-    template <int VW>
-    __device__ __forceinline__ void eval(const double *P, const V3d &xo, V3d &g, Sym3 &H) const
-    {
-        if (idx == 0xFFFFFFFFu) return;
-        V3d xn[SK::NI];
-#pragma unroll
-        for (int k = 0; k < SK::NI; ++k) {
-            const double *p = P + ((idx >> (8 * k)) & 0xFFu) * (3 * VW);
-            xn[k] = V3d(p[0], p[VW], p[2 * VW]);
-        }
-        SK::eval(xo, xn, q, g, H);
-    }
-};
-
-// steps [t, te) of one stream of the slice, records two steps ahead in registers
-template <int ST, int VW>
-__device__ __forceinline__ void accumulateStream(const VbdStreamDev &sd, uint32_t t, const uint32_t te, const double *P,
-                                                 int lane, const V3d &xo, V3d &g, Sym3 &H)
-{
-    if (t >= te) return;
-    StreamRec<ST> r0, r1;
-    r0.load(sd, t, lane);
-    r1 = r0;
-    if (t + 1 < te) r1.load(sd, t + 1, lane);
-    for (;;) {
-        r0.template eval<VW>(P, xo, g, H);
-        if (t + 2 < te) r0.load(sd, t + 2, lane);
-        if (++t >= te) break;
-        r1.template eval<VW>(P, xo, g, H);
-        if (t + 2 < te) r1.load(sd, t + 2, lane);
-        if (++t >= te) break;
-    }
-}
-
-// pull [ptr, ptr + bytes) into L2 with one TMA bulk prefetch (bytes: multiple of 16, ptr 16-byte aligned)
-__device__ __forceinline__ void bulkPrefetchL2(const void *ptr, uint32_t bytes)
-{
-    if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes));
-}
-__device__ __forceinline__ void prefetchLineL2(const void *ptr)
-{
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
-}
-
 struct SliceDesc {
     uint4 lo, hi;  // [slot, nbrRow, s0, s1], [s2, s3, s4, flags]
     __device__ __forceinline__ void load(const uint32_t *desc, int slice)
@@ -215,14 +158,117 @@ struct SliceDesc {
     }
 };
 
-template <unsigned SMASK, int ST, int VW>
-__device__ __forceinline__ void streamIfPresent(const VbdArgs &a, const SliceDesc &d, const SliceDesc &n, const double *P,
-                                                int lane, const V3d &xo, V3d &g, Sym3 &H)
+constexpr int maxStreamNQ(unsigned smask)
 {
-    if constexpr ((SMASK >> ST) & 1u) {
-        if (a.s[ST].idx) accumulateStream<ST, VW>(a.s[ST], d.stream<ST>(), n.stream<ST>(), P, lane, xo, g, H);
-    }
+    int m = 1;
+    if ((smask >> ST_BEND_EDGE) & 1u) m = Stream<ST_BEND_EDGE>::NQ > m ? Stream<ST_BEND_EDGE>::NQ : m;
+    if ((smask >> ST_BEND_OPP) & 1u) m = Stream<ST_BEND_OPP>::NQ > m ? Stream<ST_BEND_OPP>::NQ : m;
+    if ((smask >> ST_MEMBRANE_STVK) & 1u) m = Stream<ST_MEMBRANE_STVK>::NQ > m ? Stream<ST_MEMBRANE_STVK>::NQ : m;
+    if ((smask >> ST_TET_SNH) & 1u) m = Stream<ST_TET_SNH>::NQ > m ? Stream<ST_TET_SNH>::NQ : m;
+    if ((smask >> ST_TET_STVK) & 1u) m = Stream<ST_TET_STVK>::NQ > m ? Stream<ST_TET_STVK>::NQ : m;
+    return m;
 }
+
+// one incidence record of any stream type of the kernel variant (register storage shared between the types)
+template <unsigned SMASK>
+struct StreamRec {
+    uint32_t idx;
+    double q[maxStreamNQ(SMASK)];
+    template <int ST>
+    __device__ __forceinline__ void load(const VbdStreamDev &sd, uint32_t t, int lane)
+    {
+        using SK = Stream<ST>;
+        idx = __ldg(sd.idx + static_cast<size_t>(t) * 32 + lane);
+        const double *qp = sd.params + static_cast<size_t>(t) * (SK::NQ * 32) + lane;
+#pragma unroll
+        for (int k = 0; k < SK::NQ; ++k) q[k] = __ldg(qp + k * 32);
+    }
+    // P: the warp's neighbour tile, already offset to this lane's vertex column; element (k, c) at P[(3 k + c) * VW]
+    template <int ST, int VW>
+    __device__ __forceinline__ void eval(const double *P, const V3d &xo, V3d &g, Sym3 &H) const
+    {
+        using SK = Stream<ST>;
+        if (idx == 0xFFFFFFFFu) return;
+        V3d xn[SK::NI];
+#pragma unroll
+        for (int k = 0; k < SK::NI; ++k) {
+            const double *p = P + ((idx >> (8 * k)) & 0xFFu) * (3 * VW);
+            xn[k] = V3d(p[0], p[VW], p[2 * VW]);
+        }
+        SK::eval(xo, xn, q, g, H);
+    }
+};
+
+// The streams of one slice as ONE concatenated step sequence [0, total): step s belongs to the first type whose
+// cumulative count exceeds s (a warp-uniform branch).  Running the two-deep register prefetch over the concatenated
+// sequence keeps the record loads two steps ahead across stream boundaries as well, so only the first two loads of a
+// warp are exposed (and those overlap the neighbour gather).
+template <unsigned SMASK, int VW>
+struct StreamPipe {
+    uint32_t base[kNumStreamTypes];  // first step of the type minus the concatenated index where the type begins
+    uint32_t cum[kNumStreamTypes];   // concatenated index one past the type's last step
+    uint32_t total;
+
+    template <int ST>
+    __device__ __forceinline__ void init(const SliceDesc &d, const SliceDesc &n, uint32_t &acc)
+    {
+        if constexpr ((SMASK >> ST) & 1u) {
+            const uint32_t t0 = d.stream<ST>(), t1 = n.stream<ST>();
+            base[ST] = t0 - acc;
+            acc += t1 - t0;
+            cum[ST] = acc;
+        }
+    }
+    __device__ __forceinline__ StreamPipe(const SliceDesc &d, const SliceDesc &n)
+    {
+        uint32_t acc = 0;
+        init<0>(d, n, acc);
+        init<1>(d, n, acc);
+        init<2>(d, n, acc);
+        init<3>(d, n, acc);
+        init<4>(d, n, acc);
+        total = acc;
+    }
+    template <int ST>
+    __device__ __forceinline__ void loadFrom(const VbdArgs &a, StreamRec<SMASK> &r, uint32_t s, int lane) const
+    {
+        if constexpr (ST < kNumStreamTypes) {
+            if constexpr ((SMASK >> ST) & 1u) {
+                if (s < cum[ST]) {
+                    r.template load<ST>(a.s[ST], base[ST] + s, lane);
+                    return;
+                }
+            }
+            loadFrom<ST + 1>(a, r, s, lane);
+        }
+    }
+    template <int ST>
+    __device__ __forceinline__ void evalFrom(const StreamRec<SMASK> &r, uint32_t s, const double *P, const V3d &xo, V3d &g,
+                                             Sym3 &H) const
+    {
+        if constexpr (ST < kNumStreamTypes) {
+            if constexpr ((SMASK >> ST) & 1u) {
+                if (s < cum[ST]) {
+                    r.template eval<ST, VW>(P, xo, g, H);
+                    return;
+                }
+            }
+            evalFrom<ST + 1>(r, s, P, xo, g, H);
+        }
+    }
+};
+
+// pull [ptr, ptr + bytes) into L2 with one TMA bulk prefetch (bytes: multiple of 16, ptr 16-byte aligned)
+__device__ __forceinline__ void bulkPrefetchL2(const void *ptr, uint32_t bytes)
+{
+    if (bytes) asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ptr), "r"(bytes));
+}
+__device__ __forceinline__ void prefetchLineL2(const void *ptr)
+{
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr));
+}
+
+
 template <unsigned SMASK, int ST>
 __device__ __forceinline__ void prefetchStreamIfPresent(const VbdArgs &a, const SliceDesc &d, const SliceDesc &n)
 {
@@ -246,6 +292,7 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     const int warpInBlock = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int warp = blockIdx.x * (kStreamBlockThreads / 32) + warpInBlock;
+    asm volatile("griddepcontrol.launch_dependents;");  // the next colour pass may start its prologue
     if (warp >= nSlicesOfColour) return;  // whole warp past the colour
     const int v = lane % VW, sub = lane / VW;
     const int slice = sliceBase + warp;
@@ -257,28 +304,18 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     const int slot = static_cast<int>(d.lo.x) + v;
     const bool valid = slot < end;
 
-    // 1. unique-neighbour gather (columns of padding lanes hold slot 0: harmless reads)
-    {
-        const uint32_t nb = d.lo.y, ne = n.lo.y;
-        for (uint32_t k = nb + sub; k < ne; k += G) {
-            const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
-            const double *src = a.x + 3 * static_cast<size_t>(id);
-            double *dst = P + (k - nb) * (3 * VW);
-            cpAsync8(dst, src);
-            cpAsync8(dst + VW, src + 1);
-            cpAsync8(dst + 2 * VW, src + 2);
-        }
-        cpAsyncCommit();
-    }
-    V3d xo(0.0, 0.0, 0.0);
+    // 1. everything that does not depend on the previous colour pass: the first two incidence records, and the
+    // streams of the slice `lookahead` slices further on (wrapping into the next colour / the next sweep) pulled from
+    // HBM into L2 with TMA bulk prefetches, so that every later load of that slice is an L2 hit
+    const StreamPipe<SMASK, VW> pipe(d, n);
+    StreamRec<SMASK> r0, r1;
+    r0.idx = r1.idx = 0xFFFFFFFFu;
+    if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
+    if (pipe.total > 1) pipe.template loadFrom<0>(a, r1, 1, lane);
     if (valid) {
-        const size_t o = 3 * static_cast<size_t>(slot);
-        xo = V3d(a.x[o], a.x[o + 1], a.x[o + 2]);
-        prefetchLineL2(a.xInertial + o);
+        prefetchLineL2(a.xInertial + 3 * static_cast<size_t>(slot));
         prefetchLineL2(a.mass + slot);
     }
-    // 2. while the gather is in flight: pull the streams of the slice `lookahead` slices further on (wrapping into the
-    // next colour / the next sweep) from HBM into L2, so that every later load of that slice is an L2 hit
     if (a.lookahead > 0) {
         int la = slice + a.lookahead;
         if (la >= a.nSlices) la -= a.nSlices;
@@ -297,17 +334,39 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
             prefetchStreamIfPresent<SMASK, ST_TET_STVK>(a, pd, pn);
         }
     }
+    // 2. positions: wait for the previous colour pass (programmatic dependent launch: this grid may have started
+    // while that one was draining), then gather the unique neighbours (columns of padding lanes hold slot 0)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    {
+        const uint32_t nb = d.lo.y, ne = n.lo.y;
+        for (uint32_t k = nb + sub; k < ne; k += G) {
+            const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
+            const double *src = a.x + 3 * static_cast<size_t>(id);
+            double *dst = P + (k - nb) * (3 * VW);
+            cpAsync8(dst, src);
+            cpAsync8(dst + VW, src + 1);
+            cpAsync8(dst + 2 * VW, src + 2);
+        }
+        cpAsyncCommit();
+    }
+    V3d xo(0.0, 0.0, 0.0);
+    if (valid) {
+        const size_t o = 3 * static_cast<size_t>(slot);
+        xo = V3d(a.x[o], a.x[o + 1], a.x[o + 2]);
+    }
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
 
     // 3. incidence streams
     V3d f(0.0, 0.0, 0.0);
     Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    streamIfPresent<SMASK, ST_BEND_EDGE, VW>(a, d, n, P, lane, xo, f, H);
-    streamIfPresent<SMASK, ST_BEND_OPP, VW>(a, d, n, P, lane, xo, f, H);
-    streamIfPresent<SMASK, ST_MEMBRANE_STVK, VW>(a, d, n, P, lane, xo, f, H);
-    streamIfPresent<SMASK, ST_TET_SNH, VW>(a, d, n, P, lane, xo, f, H);
-    streamIfPresent<SMASK, ST_TET_STVK, VW>(a, d, n, P, lane, xo, f, H);
+    for (uint32_t s = 0; s < pipe.total; s += 2) {
+        pipe.template evalFrom<0>(r0, s, P, xo, f, H);
+        if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, lane);
+        if (s + 1 >= pipe.total) break;
+        pipe.template evalFrom<0>(r1, s + 1, P, xo, f, H);
+        if (s + 3 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 3, lane);
+    }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
     // 5. reduce, solve, write
@@ -332,7 +391,17 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
         cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         configured = smem;
     }
-    kernel<<<blocks, kStreamBlockThreads, smem, stream>>>(args, end, sliceBase, warps, invdtSquared);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(kStreamBlockThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = args.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
 }
 
 template <unsigned SMASK, unsigned KMASK, int G>

@@ -58,6 +58,7 @@ class Oracle:
         L.ref_group_destroy.argtypes = [C.c_void_p]
         L.ref_group_add_energy.argtypes = [C.c_void_p, C.c_int, C.c_int, _ip, _dp]
         L.ref_group_get_state.argtypes = [C.c_void_p, _dp, _dp]
+        L.ref_update_anchor.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
         L.ref_group_set_state.argtypes = [C.c_void_p, _dp, _dp]
         L.ref_group_get_masses.argtypes = [C.c_void_p, _dp, _dp]
         L.ref_energy_value.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
@@ -178,6 +179,10 @@ class OracleGroup:
         x = None if x is None else _f64(x)
         v = None if v is None else _f64(v)
         self.o.lib.ref_group_set_state(self.h, _d(x), _d(v))
+
+    def update_anchor(self, e, stencil, anchor):
+        a = _f64(anchor)
+        self.o.check(self.o.lib.ref_update_anchor(self.h, e, stencil, _d(a)))
 
     def masses(self):
         m, w = np.empty(self.n), np.empty(self.n)

@@ -1,0 +1,45 @@
+"""The C++ facade (include/spgx/spgx.hpp) driven by examples/rope_facade.cpp, against the oracle on the same rope
+(apps/solverCompare.cpp:56-102 style scene): VBD and XPBD, with a live anchor edit half way
+(SpringAnchorEnergy::updateAnchor, solverCompare.cpp:1524)."""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import oracle_api
+from spg_b200 import scenes as S
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _rope_scene(n):
+    dl = 1.0 / (n - 1)
+    x = np.zeros((n, 3))
+    x[:, 0] = np.arange(n) * dl
+    sc = S.Scene(x.copy(), x.copy(), np.full(n, 1.0 / n))
+    st = np.stack([np.arange(n - 1), np.arange(1, n)], 1).astype(np.int32)
+    sc.energies.append(S.SceneEnergy(S.K_SPRING, st, np.tile([dl, 1e3], (n - 1, 1))))
+    sc.energies.append(S.SceneEnergy(S.K_ANCHOR, np.array([[0]], np.int32), np.array([[0.0, 0.0, 0.0, 1e5]])))
+    return sc
+
+
+@pytest.mark.parametrize("solver,substeps,iters", [("vbd", 2, 8), ("xpbd", 10, 1)])
+def test_rope_facade_matches_oracle(tmp_path, oracle, solver, substeps, iters):
+    exe = tmp_path / "rope_facade"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", str(ROOT / "include"), str(ROOT / "examples" / "rope_facade.cpp"),
+                    "-L", str(ROOT / "spg_b200" / "lib"), "-lspgx", f"-Wl,-rpath,{ROOT / 'spg_b200' / 'lib'}", "-o", str(exe)],
+                   check=True)
+    n, frames = 24, 6
+    res = subprocess.run([str(exe), solver, str(n), str(frames), str(substeps), str(iters)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    x = np.array([[float(a) for a in l.split()] for l in res.stdout.strip().splitlines()])
+    sc = _rope_scene(n)
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, 0 if solver == "vbd" else 1, 0.01, substeps, iters)
+    osol.step(frames // 2)
+    og.update_anchor(1, 0, [0.0, 0.05, 0.0])
+    osol.step(frames - frames // 2)
+    xr, _ = osol.state()
+    assert np.abs(x - xr).max() <= 1e-9 * np.abs(xr).max()
