@@ -258,6 +258,14 @@ struct StreamPipe {
     }
 };
 
+// returns `lane`, through an instruction that reads `loaded`: whatever is computed from the result is ordered after the
+// arrival of the load that produced `loaded` (a record index never equals 0xFFFFFFFE, so the value is always `lane`)
+__device__ __forceinline__ int orderAfter(int lane, uint32_t loaded)
+{
+    asm volatile("{ .reg .pred p; setp.eq.u32 p, %1, 0xFFFFFFFE; selp.s32 %0, -1, %0, p; }" : "+r"(lane) : "r"(loaded));
+    return lane;
+}
+
 // pull [ptr, ptr + bytes) into L2 with one TMA bulk prefetch (bytes: multiple of 16, ptr 16-byte aligned)
 __device__ __forceinline__ void bulkPrefetchL2(const void *ptr, uint32_t bytes)
 {
@@ -304,14 +312,21 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     const int slot = static_cast<int>(d.lo.x) + v;
     const bool valid = slot < end;
 
-    // 1. everything that does not depend on the previous colour pass: the first two incidence records, and the
-    // streams of the slice `lookahead` slices further on (wrapping into the next colour / the next sweep) pulled from
-    // HBM into L2 with TMA bulk prefetches, so that every later load of that slice is an L2 hit
+    // 1. everything that does not depend on the previous colour pass: the first incidence record, the ids of the
+    // unique neighbours, and the streams of the slice `lookahead` slices further on (wrapping into the next colour /
+    // the next sweep) pulled from HBM into L2 with TMA bulk prefetches
     const StreamPipe<SMASK, VW> pipe(d, n);
     StreamRec<SMASK> r0, r1;
     r0.idx = r1.idx = 0xFFFFFFFFu;
     if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
-    if (pipe.total > 1) pipe.template loadFrom<0>(a, r1, 1, lane);
+    constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
+    const uint32_t nb = d.lo.y, ne = n.lo.y;
+    uint32_t nid[PRE];
+#pragma unroll
+    for (int j = 0; j < PRE; ++j) {
+        const uint32_t k = nb + sub + j * G;
+        nid[j] = k < ne ? __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v) : 0u;
+    }
     if (valid) {
         prefetchLineL2(a.xInertial + 3 * static_cast<size_t>(slot));
         prefetchLineL2(a.mass + slot);
@@ -337,18 +352,26 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     // 2. positions: wait for the previous colour pass (programmatic dependent launch: this grid may have started
     // while that one was draining), then gather the unique neighbours (columns of padding lanes hold slot 0)
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    {
-        const uint32_t nb = d.lo.y, ne = n.lo.y;
-        for (uint32_t k = nb + sub; k < ne; k += G) {
-            const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
-            const double *src = a.x + 3 * static_cast<size_t>(id);
+#pragma unroll
+    for (int j = 0; j < PRE; ++j) {
+        const uint32_t k = nb + sub + j * G;
+        if (k < ne) {
+            const double *src = a.x + 3 * static_cast<size_t>(nid[j]);
             double *dst = P + (k - nb) * (3 * VW);
             cpAsync8(dst, src);
             cpAsync8(dst + VW, src + 1);
             cpAsync8(dst + 2 * VW, src + 2);
         }
-        cpAsyncCommit();
     }
+    for (uint32_t k = nb + sub + PRE * G; k < ne; k += G) {
+        const uint32_t id = __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v);
+        const double *src = a.x + 3 * static_cast<size_t>(id);
+        double *dst = P + (k - nb) * (3 * VW);
+        cpAsync8(dst, src);
+        cpAsync8(dst + VW, src + 1);
+        cpAsync8(dst + 2 * VW, src + 2);
+    }
+    cpAsyncCommit();
     V3d xo(0.0, 0.0, 0.0);
     if (valid) {
         const size_t o = 3 * static_cast<size_t>(slot);
@@ -357,15 +380,20 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
 
-    // 3. incidence streams
+    // 3. incidence streams.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
+    // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
+    // current one has arrived (orderAfter) and right BEFORE it is evaluated, which puts one whole evaluation
+    // between every request and its wait.
     V3d f(0.0, 0.0, 0.0);
     Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (uint32_t s = 0; s < pipe.total; s += 2) {
+        int l = orderAfter(lane, r0.idx);
+        if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
         pipe.template evalFrom<0>(r0, s, P, xo, f, H);
-        if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, lane);
         if (s + 1 >= pipe.total) break;
+        l = orderAfter(lane, r1.idx);
+        if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
         pipe.template evalFrom<0>(r1, s + 1, P, xo, f, H);
-        if (s + 3 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 3, lane);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
