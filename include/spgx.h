@@ -98,6 +98,12 @@ int spgx_ctx_create(int device, spgx_ctx **out);
 void spgx_ctx_destroy(spgx_ctx *ctx);
 int spgx_ctx_sync(spgx_ctx *ctx);
 
+/* ---- multi-GPU (one process per GPU; the reference is single-process) ------ */
+/* ncclGetUniqueId: 128 bytes the caller broadcasts from rank 0 to every rank (e.g. with torch.distributed) */
+int spgx_comm_unique_id(void *id128);
+/* ncclCommInitRank on the context's device; collective over all ranks */
+int spgx_ctx_init_comm(spgx_ctx *ctx, int rank, int nranks, const void *id128);
+
 /* page-lock / unlock a caller-owned host buffer so spgx_upload / spgx_download run at full PCIe rate */
 int spgx_host_register(void *ptr, uint64_t bytes);
 int spgx_host_unregister(void *ptr);
@@ -121,6 +127,27 @@ int spgx_energy_get_records(spgx_group *grp, int energyId, double *records);
  * XPBD::computeParallelStencilGroups (xpbd.cpp:133-160), then upload. Must be called once before stepping;
  * calling it again re-does the precomputation (requirePrecomputationUpdate). */
 int spgx_group_finalize(spgx_group *grp, int solverKind);
+
+/* Domain decomposition for VBD: every rank creates the SAME global group (same vertices, same energies), then declares
+ * which vertices it owns (owner[v] in [0, nranks); NULL = nranks equal contiguous index ranges, i.e. row strips of a
+ * cloth grid / slabs of a beam) BEFORE spgx_group_finalize.  Colouring stays global (bit-exact with the reference);
+ * the rank keeps the stencils touching its vertices, holds the other vertices of those stencils as halo copies and
+ * exchanges the boundary vertices of colour c with its neighbours after colour pass c (vbd.cpp:151-157 runs the colour
+ * groups one after another; vertices of one colour never share a stencil, so the result is identical to one domain).
+ * spgx_upload / spgx_download keep taking global-sized arrays: upload reads the entries of the local vertices,
+ * download writes the entries of the OWNED vertices only. */
+int spgx_group_set_partition(spgx_group *grp, int rank, int nranks, const int32_t *owner);
+/* after finalize: out8 = [nOwned, nLocal, nPeers, localLo, localHi, ownedLo, ownedHi, nColors] (global index ranges the
+ * local / owned vertices span: what spgx_upload reads and spgx_download writes) */
+int spgx_group_partition_info(spgx_group *grp, int64_t *out8);
+/* pure host: the local view rank `rank` builds (spg_b200/csrc/partition.h). sizes: [nOwned, nLocal, nPeers, nColors,
+ * nSend] out; the arrays may be NULL to query the sizes first. slot2vert: nLocal global ids (owned first);
+ * peers: nPeers ranks; sendOffsets: nColors * nPeers + 1 into sendVerts (global ids, (colour, peer)-major);
+ * recvSlot / recvCount: nColors * nPeers halo slot ranges. */
+int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                        const int32_t *stencilSizes, const int32_t *owner, int rank, int nranks, int64_t *sizes,
+                        int32_t *slot2vert, int32_t *peers, int64_t *sendOffsets, int32_t *sendVerts, int64_t *recvSlot,
+                        int64_t *recvCount);
 
 /* structure queries for the bit-exactness gates */
 int spgx_group_num_colors(spgx_group *grp, int energyId /* ignored for VBD */);

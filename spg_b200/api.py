@@ -45,6 +45,12 @@ SIGNATURES = {
     "spgx_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "spgx_ctx_destroy": (None, [C.c_void_p]),
     "spgx_ctx_sync": (C.c_int, [C.c_void_p]),
+    "spgx_comm_unique_id": (C.c_int, [C.c_void_p]),
+    "spgx_ctx_init_comm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "spgx_group_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip]),
+    "spgx_group_partition_info": (C.c_int, [C.c_void_p, _lp]),
+    "spgx_partition_plan": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.c_int, C.c_int, _lp, _ip, _ip, _lp, _ip,
+                                      _lp, _lp]),
     "spgx_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),
     "spgx_host_unregister": (C.c_int, [C.c_void_p]),
     "spgx_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
@@ -131,6 +137,39 @@ def prepare_energy(kind: int, stencils, params, x0) -> np.ndarray:
     return rec
 
 
+def comm_unique_id() -> np.ndarray:
+    """ncclGetUniqueId: 128 bytes to broadcast from rank 0 to all ranks."""
+    buf = np.zeros(128, dtype=np.uint8)
+    check(lib.spgx_comm_unique_id(buf.ctypes.data_as(C.c_void_p)))
+    return buf
+
+
+def partition_plan(n_verts: int, stencil_sets, rank: int, nranks: int, owner=None) -> dict:
+    """Pure host: the local view (owned / halo slots, per-colour send / receive tables) rank `rank` of `nranks` builds
+    for the VBD sweep (spg_b200/csrc/partition.h). owner=None: equal contiguous index ranges."""
+    sets = [_i32(s) for s in stencil_sets]
+    ptrs = (_ip * len(sets))(*[_i(s) for s in sets])
+    n_entries = np.array([s.size for s in sets], dtype=np.int64)
+    sizes_s = np.array([s.shape[1] for s in sets], dtype=np.int32)
+    own = None if owner is None else _i32(owner)
+    op = None if own is None else _i(own)
+    sizes = np.zeros(5, dtype=np.int64)
+    lp = lambda a: a.ctypes.data_as(_lp)
+    check(lib.spgx_partition_plan(n_verts, len(sets), ptrs, lp(n_entries), _i(sizes_s), op, rank, nranks, lp(sizes),
+                                  None, None, None, None, None, None))
+    n_owned, n_local, n_peers, n_colors, n_send = (int(a) for a in sizes)
+    slot2vert = np.empty(n_local, np.int32)
+    peers = np.empty(n_peers, np.int32)
+    send_off = np.empty(n_colors * n_peers + 1, np.int64)
+    send_verts = np.empty(n_send, np.int32)
+    recv_slot = np.empty(n_colors * n_peers, np.int64)
+    recv_count = np.empty(n_colors * n_peers, np.int64)
+    check(lib.spgx_partition_plan(n_verts, len(sets), ptrs, lp(n_entries), _i(sizes_s), op, rank, nranks, lp(sizes),
+                                  _i(slot2vert), _i(peers), lp(send_off), _i(send_verts), lp(recv_slot), lp(recv_count)))
+    return {"n_owned": n_owned, "n_local": n_local, "n_colors": n_colors, "peers": peers, "slot2vert": slot2vert,
+            "send_offsets": send_off, "send_verts": send_verts, "recv_slot": recv_slot, "recv_count": recv_count}
+
+
 def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
     """A page-locked numpy array (cudaHostRegister) for the end-to-end upload / download path."""
     a = np.empty(shape, dtype=dtype)
@@ -147,6 +186,11 @@ class Context:
 
     def sync(self):
         check(lib.spgx_ctx_sync(self.handle))
+
+    def init_comm(self, rank: int, nranks: int, unique_id: np.ndarray):
+        """ncclCommInitRank (collective): unique_id = comm_unique_id() of rank 0, broadcast by the caller."""
+        uid = np.ascontiguousarray(unique_id, dtype=np.uint8)
+        check(lib.spgx_ctx_init_comm(self.handle, rank, nranks, uid.ctypes.data_as(C.c_void_p)))
 
     def close(self):
         if self.handle:
@@ -187,6 +231,18 @@ class Group:
         self.kinds.append(kind)
         self.n_stencils.append(n)
         return eid.value
+
+    def set_partition(self, rank: int, nranks: int, owner=None):
+        """Domain decomposition (before finalize): this rank owns the vertices with owner[v] == rank (None: equal
+        contiguous index ranges)."""
+        own = None if owner is None else _i32(owner)
+        check(lib.spgx_group_set_partition(self.handle, rank, nranks, None if own is None else _i(own)))
+
+    def partition_info(self) -> dict:
+        o = np.zeros(8, dtype=np.int64)
+        check(lib.spgx_group_partition_info(self.handle, o.ctypes.data_as(_lp)))
+        return {"n_owned": int(o[0]), "n_local": int(o[1]), "n_peers": int(o[2]), "local_range": (int(o[3]), int(o[4])),
+                "owned_range": (int(o[5]), int(o[6])), "n_colors": int(o[7])}
 
     def finalize(self, solver_kind: int):
         check(lib.spgx_group_finalize(self.handle, solver_kind))

@@ -8,6 +8,7 @@
 #include "energy_prepare.h"
 #include "group.h"
 #include "host_build.h"
+#include "partition.h"
 #include "streams.cuh"
 
 namespace spgx
@@ -51,7 +52,7 @@ static double modelRecordBytes(int kind)
 // energies map to the same stream type, or the neighbour tile would not fit in shared memory.
 static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cudaStream_t st)
 {
-    const int V = grp.nVerts, G = grp.vbdLanes, VW = 32 / G;
+    const int V = grp.nVerts, NO = grp.nOwned, G = grp.vbdLanes, VW = 32 / G;  // V: global vertices, NO: owned slots
     const int nColors = static_cast<int>(grp.colorOffsets.size()) - 1;
     struct HostStream {
         int energy = -1, NQ = 0;
@@ -70,19 +71,19 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
             if (hs[t].energy < 0) {
                 hs[t].energy = static_cast<int>(ei);
                 hs[t].NQ = streamNQ(t);
-                hs[t].rowptr.assign(static_cast<size_t>(V) + 1, 0);
+                hs[t].rowptr.assign(static_cast<size_t>(NO) + 1, 0);
                 any = true;
             }
         }
     }
     if (!any) return false;
 
-    std::vector<uint32_t> nbrRowptr(static_cast<size_t>(V) + 1, 0);
+    std::vector<uint32_t> nbrRowptr(static_cast<size_t>(NO) + 1, 0);
     std::vector<uint32_t> nbrList;
     std::vector<int32_t> mark(static_cast<size_t>(V), -1), localIdx(static_cast<size_t>(V), 0);
-    std::vector<uint8_t> hasCsr(static_cast<size_t>(V), 0);
+    std::vector<uint8_t> hasCsr(static_cast<size_t>(NO), 0);
     int maxNbr = 0;
-    for (int s = 0; s < V; ++s) {
+    for (int s = 0; s < NO; ++s) {
         const int v = grp.slot2vert[s];
         const uint32_t nb0 = static_cast<uint32_t>(nbrList.size());
         for (auto &h : hs)
@@ -123,7 +124,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     maxNbr = std::max(maxNbr, 1);
     if (static_cast<size_t>(maxNbr) * 3 * VW * 8 * 4 > 200 * 1024) return false;  // 4 warps per block (vbd_stream.cuh)
     for (auto &h : hs)
-        if (h.energy >= 0) h.rowptr[V] = static_cast<uint32_t>(h.idx.size());
+        if (h.energy >= 0) h.rowptr[NO] = static_cast<uint32_t>(h.idx.size());
 
     // ---- slices and their descriptors ----
     std::vector<int> sliceSlot;  // first slot of every slice
@@ -151,7 +152,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
             desc[sl * kSliceDescWords + 7] = csr;
             row += rows;
         }
-        desc[nSlices * kSliceDescWords + 0] = static_cast<uint32_t>(V);
+        desc[nSlices * kSliceDescWords + 0] = static_cast<uint32_t>(NO);
         desc[nSlices * kSliceDescWords + 1] = row;
         std::vector<uint32_t> ids(static_cast<size_t>(row) * VW, 0u);
         for (size_t sl = 0; sl < nSlices; ++sl)
@@ -291,9 +292,81 @@ int spgx_ctx_create(int device, spgx_ctx **out)
     });
 }
 
+int spgx_comm_unique_id(void *id128)
+{
+    return guarded([&] { commUniqueId(id128); });
+}
+
+int spgx_ctx_init_comm(spgx_ctx *ctx, int rank, int nranks, const void *id128)
+{
+    return guarded([&] {
+        if (!ctx) throw StateError("null context");
+        if (nranks < 1 || rank < 0 || rank >= nranks) throw std::runtime_error("invalid rank / nranks");
+        SPGX_CUDA(cudaSetDevice(ctx->device));
+        commInit(ctx, rank, nranks, id128);
+    });
+}
+
+int spgx_group_set_partition(spgx_group *grp, int rank, int nranks, const int32_t *owner)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        if (nranks < 1 || rank < 0 || rank >= nranks) throw std::runtime_error("invalid rank / nranks");
+        grp->rank = rank;
+        grp->nRanks = nranks;
+        grp->partitioned = nranks > 1;
+        grp->owner.resize(static_cast<size_t>(grp->nVerts));
+        for (int v = 0; v < grp->nVerts; ++v) {
+            // equal contiguous index ranges: row strips of a grid, slabs of a beam
+            const int o = owner ? owner[v] : static_cast<int>(static_cast<int64_t>(v) * nranks / std::max(grp->nVerts, 1));
+            if (o < 0 || o >= nranks) throw std::runtime_error("vertex owner out of range");
+            grp->owner[v] = o;
+        }
+        grp->finalized = false;
+    });
+}
+
+int spgx_group_partition_info(spgx_group *grp, int64_t *out8)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        out8[0] = grp->nOwned, out8[1] = grp->nLocal, out8[2] = static_cast<int64_t>(grp->peers.size());
+        out8[3] = grp->localLo, out8[4] = grp->localHi, out8[5] = grp->ownedLo, out8[6] = grp->ownedHi;
+        out8[7] = static_cast<int64_t>(grp->colorOffsets.size()) - 1;
+    });
+}
+
+int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                        const int32_t *stencilSizes, const int32_t *owner, int rank, int nranks, int64_t *sizes,
+                        int32_t *slot2vert, int32_t *peers, int64_t *sendOffsets, int32_t *sendVerts, int64_t *recvSlot,
+                        int64_t *recvCount)
+{
+    return guarded([&] {
+        std::vector<FlatStencilsView> sets;
+        for (int s = 0; s < nSets; ++s) sets.push_back({entries[s], nEntries[s], stencilSizes[s]});
+        const auto colors = colorVertices(nVerts, sets);
+        std::vector<int32_t> own(static_cast<size_t>(nVerts));
+        for (int v = 0; v < nVerts; ++v)
+            own[v] = owner ? owner[v] : static_cast<int>(static_cast<int64_t>(v) * nranks / std::max(nVerts, 1));
+        const LocalView lv = buildLocalView(nVerts, colors, sets, nranks > 1 ? own.data() : nullptr, rank, nranks);
+        if (sizes) {
+            sizes[0] = lv.nOwned, sizes[1] = lv.nLocal, sizes[2] = static_cast<int64_t>(lv.peers.size());
+            sizes[3] = lv.nColors, sizes[4] = static_cast<int64_t>(lv.sendSlots.size());
+        }
+        if (slot2vert) std::copy(lv.slot2vert.begin(), lv.slot2vert.end(), slot2vert);
+        if (peers) std::copy(lv.peers.begin(), lv.peers.end(), peers);
+        if (sendOffsets) std::copy(lv.sendOffsets.begin(), lv.sendOffsets.end(), sendOffsets);
+        if (sendVerts)
+            for (size_t i = 0; i < lv.sendSlots.size(); ++i) sendVerts[i] = lv.slot2vert[lv.sendSlots[i]];
+        if (recvSlot) std::copy(lv.recvSlot.begin(), lv.recvSlot.end(), recvSlot);
+        if (recvCount) std::copy(lv.recvCount.begin(), lv.recvCount.end(), recvCount);
+    });
+}
+
 void spgx_ctx_destroy(spgx_ctx *ctx)
 {
     if (!ctx) return;
+    commDestroy(ctx);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -385,9 +458,11 @@ int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int of
         if (grp->finalized) {
             SPGX_CUDA(cudaSetDevice(grp->ctx->device));
             const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
-            SPGX_CUDA(cudaMemcpyAsync(e.d_records.ptr + static_cast<size_t>(pos) * e.NP + offset, values,
-                                      count * sizeof(double), cudaMemcpyHostToDevice, grp->ctx->stream));
-            SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
+            if (pos >= 0) {  // a partitioned rank keeps only the stencils touching its vertices
+                SPGX_CUDA(cudaMemcpyAsync(e.d_records.ptr + static_cast<size_t>(pos) * e.NP + offset, values,
+                                          count * sizeof(double), cudaMemcpyHostToDevice, grp->ctx->stream));
+                SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
+            }
         }
     });
 }
@@ -403,8 +478,8 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         // preserve current state across a re-finalize
         std::vector<double> xh, vh;
         if (grp->finalized || grp->d_x.ptr) {
-            xh.resize(3 * static_cast<size_t>(V));
-            vh.resize(3 * static_cast<size_t>(V));
+            xh = grp->xInitial;  // a partitioned rank only gets its owned entries back
+            vh.assign(3 * static_cast<size_t>(V), 0.0);
             if (spgx_download(grp, xh.data(), vh.data()) != SPGX_OK) throw CudaError(spgx_last_error());
         } else {
             xh = grp->xPending;
@@ -419,15 +494,21 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         std::vector<FlatStencilsView> sets;
         for (auto &e : grp->energies) sets.push_back({e.stencils.data(), static_cast<int64_t>(e.stencils.size()), e.S});
 
-        grp->slot2vert.resize(V);
-        grp->vert2slot.resize(V);
+        grp->slot2vert.assign(V, 0);
+        grp->vert2slot.assign(V, 0);
         grp->uniqueNeighbourSum = 0;
         if (solverKind == SPGX_VBD) {
             std::vector<Incidence> inc;
             for (auto &fs : sets) inc.push_back(buildIncidence(V, fs));
-            grp->vertexColors = colorVertices(V, sets, &inc);  // vbd.cpp:203-229
-            groupByKey(grp->vertexColors, grp->slot2vert, grp->colorOffsets);
-            for (int s = 0; s < V; ++s) grp->vert2slot[grp->slot2vert[s]] = s;
+            grp->vertexColors = colorVertices(V, sets, &inc);  // vbd.cpp:203-229 (global: identical on every rank)
+            LocalView lv = buildLocalView(V, grp->vertexColors, sets, grp->partitioned ? grp->owner.data() : nullptr,
+                                          grp->rank, grp->nRanks);
+            grp->nOwned = lv.nOwned;
+            grp->nLocal = lv.nLocal;
+            grp->slot2vert = lv.slot2vert;
+            grp->vert2slot = lv.vert2slot;
+            grp->colorOffsets = lv.colorOffsets;
+            const int nOwned = lv.nOwned, nLocal = lv.nLocal;
             {
                 // threads per vertex: big colours are throughput-bound and run best with one thread per vertex (long
                 // software-pipelined incidence loops, no shuffles); small meshes need the extra parallelism
@@ -456,26 +537,39 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             for (size_t ei = 0; ei < nE; ++ei) {
                 auto &e = grp->energies[ei];
                 if (static_cast<uint64_t>(e.n) >= (1ull << 30)) throw std::runtime_error("too many stencils in one energy");
-                std::vector<uint32_t> rowptr(static_cast<size_t>(V) + 1, 0), entries(e.stencils.size());
+                // global stencil id -> position among the stencils this rank keeps (-1: not kept)
+                const auto &kept = lv.localStencils[ei];
+                e.positionOf.assign(static_cast<size_t>(e.n), -1);
+                for (size_t k = 0; k < kept.size(); ++k) e.positionOf[kept[k]] = static_cast<int32_t>(k);
+                std::vector<uint32_t> rowptr(static_cast<size_t>(nLocal) + 1, 0), entries;
                 uint32_t cursor = 0;
-                for (int s = 0; s < V; ++s) {
+                e.ownedIncidences = 0;
+                for (int s = 0; s < nLocal; ++s) {
                     const int v = grp->slot2vert[s];
                     rowptr[s] = cursor;
+                    if (s >= nOwned) continue;  // halo vertices are never updated here
                     for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
                         const int64_t flat = inc[ei].flat[q];
-                        entries[cursor++] = (static_cast<uint32_t>(flat / e.S) << 2) | static_cast<uint32_t>(flat % e.S);
+                        entries.push_back((static_cast<uint32_t>(e.positionOf[flat / e.S]) << 2) | static_cast<uint32_t>(flat % e.S));
+                        ++cursor;
                     }
                 }
-                rowptr[V] = cursor;
-                std::vector<int32_t> slotStencils(e.stencils.size());
-                for (size_t q = 0; q < e.stencils.size(); ++q) slotStencils[q] = grp->vert2slot[e.stencils[q]];
+                rowptr[nLocal] = cursor;
+                e.ownedIncidences = cursor;
+                std::vector<int32_t> slotStencils(kept.size() * e.S);
+                std::vector<double> keptRecords(kept.size() * e.NP);
+                for (size_t k = 0; k < kept.size(); ++k) {
+                    for (int l = 0; l < e.S; ++l)
+                        slotStencils[k * e.S + l] = grp->vert2slot[e.stencils[static_cast<size_t>(kept[k]) * e.S + l]];
+                    std::copy(e.records.begin() + static_cast<size_t>(kept[k]) * e.NP,
+                              e.records.begin() + static_cast<size_t>(kept[k] + 1) * e.NP, keptRecords.begin() + k * e.NP);
+                }
                 e.d_stencils.upload(slotStencils, st);
-                e.d_records.upload(e.records, st);
+                e.d_records.upload(keptRecords, st);
                 e.d_rowptr.upload(rowptr, st);
                 e.d_entries.upload(entries, st);
                 e.streamed = false;
                 e.order.clear();
-                e.positionOf.clear();
                 SPGX_CUDA(cudaStreamSynchronize(st));
             }
             // streaming layout, when the group's mix of energies has a compiled streaming kernel
@@ -508,6 +602,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             }
             // distinct stencil neighbours per vertex (for the byte model)
             for (int v = 0; v < V; ++v) {
+                if (grp->vert2slot[v] < 0 || grp->vert2slot[v] >= nOwned) continue;
                 nbr.clear();
                 for (size_t ei = 0; ei < nE; ++ei) {
                     const auto &e = grp->energies[ei];
@@ -520,7 +615,18 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 std::sort(nbr.begin(), nbr.end());
                 grp->uniqueNeighbourSum += static_cast<double>(std::unique(nbr.begin(), nbr.end()) - nbr.begin());
             }
+            // halo exchange tables
+            grp->peers = lv.peers;
+            grp->sendOffsets = lv.sendOffsets;
+            grp->recvSlot = lv.recvSlot;
+            grp->recvCount = lv.recvCount;
+            grp->d_sendSlots.upload(lv.sendSlots, st);
+            grp->d_sendBuf.alloc(3 * lv.sendSlots.size());
+            SPGX_CUDA(cudaStreamSynchronize(st));
         } else {
+            if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
+            grp->nOwned = grp->nLocal = V;
+            grp->peers.clear();
             for (int s = 0; s < V; ++s) grp->slot2vert[s] = grp->vert2slot[s] = s;
             grp->vertexColors.clear();
             grp->colorOffsets.clear();
@@ -554,23 +660,40 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 SPGX_CUDA(cudaStreamSynchronize(st));
             }
         }
-        // state
-        const size_t n3 = 3 * static_cast<size_t>(V);
+        // state: local vertices (owned + halo) on the device; the staging buffer spans the global index range
+        const int nLocalAll = grp->nLocal;
+        const size_t n3 = 3 * static_cast<size_t>(nLocalAll);
         grp->d_x.alloc(n3);
         grp->d_v.alloc(n3);
         grp->d_xOld.alloc(n3);
         grp->d_xInertial.alloc(n3);
-        grp->d_stage.alloc(n3);
+        grp->d_stage.alloc(3 * static_cast<size_t>(V));
         grp->d_g.alloc(3);
         grp->d_eval.alloc(64);
-        std::vector<double> ms(V), ws(V);
-        for (int s = 0; s < V; ++s) {
+        std::vector<double> ms(nLocalAll), ws(nLocalAll);
+        for (int s = 0; s < nLocalAll; ++s) {
             const double m = grp->mass[grp->slot2vert[s]];
             ms[s] = m;
             ws[s] = (m == 0) ? 0 : 1 / m;  // particleGroup.cpp:81
         }
         grp->d_mass.upload(ms, st);
         grp->d_invMass.upload(ws, st);
+        // global index range the local vertices span (upload / download move only that range)
+        grp->localLo = V;
+        grp->localHi = 0;
+        grp->ownedLo = V;
+        grp->ownedHi = 0;
+        for (int s = 0; s < nLocalAll; ++s) {
+            const int v = grp->slot2vert[s];
+            grp->localLo = std::min(grp->localLo, v);
+            grp->localHi = std::max(grp->localHi, v + 1);
+            if (s < grp->nOwned) {
+                grp->ownedLo = std::min(grp->ownedLo, v);
+                grp->ownedHi = std::max(grp->ownedHi, v + 1);
+            }
+        }
+        if (nLocalAll == 0) grp->localLo = grp->localHi = grp->ownedLo = grp->ownedHi = 0;
+        grp->ownedContiguous = (grp->ownedHi - grp->ownedLo) == grp->nOwned;
         grp->d_slot2vert.upload(grp->slot2vert, st);
         SPGX_CUDA(cudaStreamSynchronize(st));
         if (!grp->evStart) {
@@ -639,15 +762,15 @@ int spgx_model_bytes(spgx_group *grp, double *bytesPerIteration, double *bytesLo
 {
     return guarded([&] {
         if (!grp->finalized) throw StateError("group is not finalized");
-        const double V = grp->nVerts;
+        const double V = grp->nOwned;
         double gather = 0, lower = 0;
         if (grp->solverKind == SPGX_VBD) {
             gather = 92.0 * V + 24.0 * grp->uniqueNeighbourSum;
             lower = (24.0 + 24.0 + 24.0 + 8.0) * V;
             for (const auto &e : grp->energies) {
-                const double incidences = static_cast<double>(e.n) * e.S;
+                const double incidences = static_cast<double>(e.ownedIncidences);
                 gather += incidences * (4.0 + modelRecordBytes(e.kind));
-                lower += modelRecordBytes(e.kind) * e.n + 4.0 * incidences;
+                lower += modelRecordBytes(e.kind) * (grp->partitioned ? incidences / e.S : static_cast<double>(e.n)) + 4.0 * incidences;
             }
         } else {
             gather = 6.0 * 24.0 * V;

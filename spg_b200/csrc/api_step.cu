@@ -57,7 +57,9 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
     for (int s = 0; s < nsub; ++s) {
-        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->d_xInertial.ptr, grp->nVerts, dt, grp->graphKey.g,
+        // predict / finalize run over owned AND halo vertices: a halo copy goes through the same arithmetic as on its
+        // owner, so no exchange is needed outside the colour passes
+        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->d_xInertial.ptr, grp->nLocal, dt, grp->graphKey.g,
                       st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
@@ -68,9 +70,11 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
                     launchVbdPass(args, mask, grp->streamMask, grp->vbdLanes, grp->vbdOcc, b, e, grp->sliceBase[c], invdtSquared, st);
                     grp->launchCounter++;
                 }
+                // every rank takes part in the exchange of colour c, whether or not it owns vertices of that colour
+                if (grp->partitioned) grp->launchCounter += enqueueHaloExchange(grp, c, st);
             }
         if (timePhases) grp->markPhase(st);
-        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nVerts, invdt, st);
+        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
     }
@@ -84,7 +88,7 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const bool serial = grp->solverKind == SPGX_XPBD_SERIAL;
     const bool useLambda = iters > 1;
     for (int s = 0; s < nsub; ++s) {
-        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nVerts, dt, grp->graphKey.g, st);
+        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nLocal, dt, grp->graphKey.g, st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
         if (useLambda)
@@ -103,7 +107,7 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
                 }
             }
         if (timePhases) grp->markPhase(st);
-        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nVerts, invdt, st);
+        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
     }
@@ -136,6 +140,14 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
         else
             enqueueXpbdFrame(grp, dt, nsub, iters, st, timePhases);
     };
+    if (grp->partitioned && !grp->commWarm) {
+        // NCCL sets up its peer connections on first use (allocations, not capturable): exchange every colour once,
+        // eagerly.  Halo copies already equal their owners' values, so this changes nothing.
+        const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+        for (int c = 0; c < nColors; ++c) enqueueHaloExchange(grp, c, st);
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        grp->commWarm = true;
+    }
     SPGX_CUDA(cudaEventRecord(grp->evStart, st));
     if (grp->graphMode) {
         if (!grp->graphExec || keyChanged) {
@@ -211,12 +223,25 @@ int spgx_download(spgx_group *grp, double *x, double *v)
             double *dst = k == 0 ? x : v;
             const double *src = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
             if (!dst) continue;
-            if (!identity) {
-                // stage[vertex] = src[slot]
-                launchPermute3(src, grp->d_stage.ptr, grp->d_slot2vert.ptr, grp->nVerts, /*gather=*/false, st);
-                src = grp->d_stage.ptr;
+            if (identity) {
+                SPGX_CUDA(cudaMemcpyAsync(dst, src, n3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+            } else {
+                // stage[vertex] = src[slot] for the owned slots, then the owned index range goes to the host
+                launchPermute3(src, grp->d_stage.ptr, grp->d_slot2vert.ptr, grp->nOwned, /*gather=*/false, st);
+                const size_t lo = 3 * static_cast<size_t>(grp->ownedLo), cnt = 3 * static_cast<size_t>(grp->ownedHi - grp->ownedLo);
+                if (grp->ownedContiguous) {
+                    if (cnt) SPGX_CUDA(cudaMemcpyAsync(dst + lo, grp->d_stage.ptr + lo, cnt * sizeof(double), cudaMemcpyDeviceToHost, st));
+                } else {
+                    // scattered ownership: through a host copy of the range, keeping the entries of other ranks intact
+                    std::vector<double> tmp(cnt);
+                    if (cnt) SPGX_CUDA(cudaMemcpyAsync(tmp.data(), grp->d_stage.ptr + lo, cnt * sizeof(double), cudaMemcpyDeviceToHost, st));
+                    SPGX_CUDA(cudaStreamSynchronize(st));
+                    for (int s = 0; s < grp->nOwned; ++s) {
+                        const size_t o = 3 * static_cast<size_t>(grp->slot2vert[s]);
+                        dst[o] = tmp[o - lo], dst[o + 1] = tmp[o - lo + 1], dst[o + 2] = tmp[o - lo + 2];
+                    }
+                }
             }
-            SPGX_CUDA(cudaMemcpyAsync(dst, src, n3 * sizeof(double), cudaMemcpyDeviceToHost, st));
             SPGX_CUDA(cudaStreamSynchronize(st));
         }
     });
@@ -242,9 +267,11 @@ int spgx_upload(spgx_group *grp, const double *x, const double *v)
             if (identity) {
                 SPGX_CUDA(cudaMemcpyAsync(dst, src, n3 * sizeof(double), cudaMemcpyHostToDevice, st));
             } else {
-                SPGX_CUDA(cudaMemcpyAsync(grp->d_stage.ptr, src, n3 * sizeof(double), cudaMemcpyHostToDevice, st));
+                // only the index range the local vertices (owned + halo) span crosses the bus
+                const size_t lo = 3 * static_cast<size_t>(grp->localLo), cnt = 3 * static_cast<size_t>(grp->localHi - grp->localLo);
+                if (cnt) SPGX_CUDA(cudaMemcpyAsync(grp->d_stage.ptr + lo, src + lo, cnt * sizeof(double), cudaMemcpyHostToDevice, st));
                 // dst[slot] = stage[slot2vert[slot]]
-                launchPermute3(grp->d_stage.ptr, dst, grp->d_slot2vert.ptr, grp->nVerts, /*gather=*/true, st);
+                launchPermute3(grp->d_stage.ptr, dst, grp->d_slot2vert.ptr, grp->nLocal, /*gather=*/true, st);
             }
             SPGX_CUDA(cudaStreamSynchronize(st));
         }
@@ -266,8 +293,8 @@ int spgx_scale_masses(spgx_group *grp, double factor)
             if (m != 0) m *= factor;
         if (grp->finalized) {
             SPGX_CUDA(cudaSetDevice(grp->ctx->device));
-            std::vector<double> ms(grp->nVerts), ws(grp->nVerts);
-            for (int s = 0; s < grp->nVerts; ++s) {
+            std::vector<double> ms(grp->nLocal), ws(grp->nLocal);
+            for (int s = 0; s < grp->nLocal; ++s) {
                 const double m = grp->mass[grp->slot2vert[s]];
                 ms[s] = m;
                 ws[s] = (m == 0) ? 0 : 1 / m;
@@ -326,6 +353,7 @@ int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, i
         auto &e = grp->energies.at(energyId);
         if (stencil < 0 || stencil >= e.n || local < 0 || local >= e.S) throw std::runtime_error("stencil out of range");
         const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
+        if (pos < 0) throw std::runtime_error("stencil is not held by this rank");
         cudaStream_t st = grp->ctx->stream;
         launchEvalVertexForceHessian(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
                                      e.d_records.ptr + static_cast<size_t>(pos) * e.NP, local, grp->d_eval.ptr, handDerived,
@@ -347,6 +375,7 @@ int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C,
         auto &e = grp->energies.at(energyId);
         if (stencil < 0 || stencil >= e.n) throw std::runtime_error("stencil out of range");
         const int pos = e.positionOf.empty() ? stencil : e.positionOf[stencil];
+        if (pos < 0) throw std::runtime_error("stencil is not held by this rank");
         cudaStream_t st = grp->ctx->stream;
         launchEvalConstraints(e.kind, grp->d_x.ptr, e.d_stencils.ptr + static_cast<size_t>(pos) * e.S,
                               e.d_records.ptr + static_cast<size_t>(pos) * e.NP, grp->d_eval.ptr, grp->d_eval.ptr + 4, st);

@@ -18,6 +18,9 @@ struct CudaError : std::runtime_error {
 struct StateError : std::runtime_error {
     using std::runtime_error::runtime_error;
 };
+struct CommError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
 
 #define SPGX_CUDA(call)                                                                                         \
     do {                                                                                                        \
@@ -41,6 +44,9 @@ int guarded(F &&f)
     } catch (const StateError &e) {
         setLastError(e.what());
         return SPGX_ERR_STATE;
+    } catch (const CommError &e) {
+        setLastError(e.what());
+        return SPGX_ERR_COMM;
     } catch (const std::exception &e) {
         setLastError(e.what());
         return SPGX_ERR_INVALID;
@@ -99,7 +105,17 @@ struct spgx_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     cudaDeviceProp prop{};
+    void *comm = nullptr;  // ncclComm_t (comm.cu)
+    int rank = 0, nRanks = 1;
 };
+
+namespace spgx
+{
+// comm.cu
+void commUniqueId(void *id128);
+void commInit(spgx_ctx *ctx, int rank, int nRanks, const void *id128);
+void commDestroy(spgx_ctx *ctx);
+}  // namespace spgx
 
 namespace spgx
 {
@@ -113,6 +129,7 @@ struct EnergyState {
     // VBD
     DevBuf<uint32_t> d_rowptr, d_entries;
     bool streamed = false;  // all of its incidences live in streams (kernels.h)
+    int64_t ownedIncidences = 0;  // incidences of vertices this rank owns
     // XPBD
     std::vector<int32_t> stencilColors;  // per stencil, reference order
     std::vector<int32_t> order;          // position -> stencil id
@@ -131,6 +148,19 @@ struct spgx_group {
 
     int solverKind = -1;
     bool finalized = false;
+    // domain decomposition (partition.h): this rank's share of the group
+    bool partitioned = false;
+    int rank = 0, nRanks = 1;
+    std::vector<int32_t> owner;  // per global vertex
+    int nOwned = 0, nLocal = 0;  // local slots: [0, nOwned) owned, [nOwned, nLocal) halo
+    int localLo = 0, localHi = 0, ownedLo = 0, ownedHi = 0;  // global index ranges spanned
+    bool ownedContiguous = true;
+    std::vector<int> peers;
+    std::vector<int64_t> sendOffsets, recvSlot, recvCount;  // (colour, peer)-major, partition.h
+    spgx::DevBuf<int32_t> d_sendSlots;
+    spgx::DevBuf<double> d_sendBuf;
+    int64_t haloBytesPerSweep = 0;
+    bool commWarm = false;
     // vertex colouring / ordering (VBD); identity ordering for XPBD
     std::vector<int32_t> vertexColors;
     std::vector<int32_t> slot2vert, vert2slot;
@@ -193,3 +223,8 @@ struct spgx_group {
         if (evStop) cudaEventDestroy(evStop);
     }
 };
+
+namespace spgx
+{
+int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
+}

