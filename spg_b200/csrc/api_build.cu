@@ -510,12 +510,12 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->colorOffsets = lv.colorOffsets;
             const int nOwned = lv.nOwned, nLocal = lv.nLocal;
             {
-                // threads per vertex: big colours are throughput-bound and run best with one thread per vertex (long
-                // software-pipelined incidence loops, no shuffles); small meshes need the extra parallelism
+                // threads per vertex (measured on B200, profiles/): two lanes per vertex for big colours (shorter
+                // per-warp chains, half the neighbour tile, more resident slices), four below 100 k vertices per colour
                 int64_t largest = 0;
                 for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c)
                     largest = std::max(largest, grp->colorOffsets[c + 1] - grp->colorOffsets[c]);
-                grp->vbdLanes = largest >= 200000 ? 1 : (largest >= 30000 ? 2 : 4);
+                grp->vbdLanes = largest >= 100000 ? 2 : 4;
             }
             if (const char *env = getenv("SPGX_VBD_LANES")) {
                 const int l = atoi(env);
