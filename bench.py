@@ -225,7 +225,7 @@ def run_single(args):
     achieved = bytes_iter * sweeps / (solve_ms_per_frame * 1e-3) / 1e9
     peak, peak_src = peaks()
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": "vbdPassKernel" if solver == "vbd" else "xpbdPassKernel",
+                "traffic": None, "kernel": ("vbdStreamKernel" if g.streamed() else "vbdPassKernel") if solver == "vbd" else "xpbdPassKernel",
                 "launches_per_step": passes_per_frame,
                 "avg_launch_us": 1e3 * solve_ms_per_frame / max(passes_per_frame, 1),
                 "algorithmic_bytes_per_launch": bytes_iter * sweeps / max(passes_per_frame, 1),
@@ -293,6 +293,7 @@ def main():
     ap.add_argument("--impl", default="spgx", choices=["spgx", "reference"])
     ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--halo", default="p2p", choices=["p2p", "nccl"], help="multi-GPU halo exchange (bench_multi.py)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -1,7 +1,9 @@
 """Multi-GPU arm of bench.py: one process per GPU (torchrun), torch.distributed (NCCL) for the plumbing -- rendezvous,
 the broadcast of the NCCL unique id the library's own communicator is built from, barriers and the max-over-ranks
 reduction of the device times.  The data path (per-colour halo exchange inside the VBD sweep) is the library's own
-ncclSend / ncclRecv schedule captured in its CUDA graph (spg_b200/csrc/comm.cu).
+fused peer-memory exchange (spg_b200/csrc/halo.cuh: boundary vertices stored into the neighbours' halo slots by the
+colour-pass kernel itself, event counters in peer memory; `--halo nccl` selects the ncclSend / ncclRecv schedule
+captured in the step graph instead, spg_b200/csrc/comm.cu).
 
 Workloads (row-strip domain decomposition, global colouring):
   default / --config 3 : weak scaling, cloth (1024 N) x 1024 (1024 rows per GPU), VBD 10 iterations
@@ -50,6 +52,14 @@ def run_multi(args):
     g = api.Group.from_scene(ctx, sc)
     g.set_partition(rank, world)
     g.finalize(api.SPGX_VBD)
+    halo = getattr(args, "halo", "p2p")
+    if halo == "p2p":
+        # CUDA IPC handles all-gathered with torch.distributed; from here on the colour-pass kernel stores boundary
+        # vertices straight into the neighbours' halo slots and synchronises through event counters in peer memory
+        g.connect_peers(dist)
+    halo_name = {api.SPGX_HALO_NCCL: "ncclSend/ncclRecv per colour, captured in the step graph",
+                 api.SPGX_HALO_P2P: "peer-memory stores from the colour-pass kernel + event counters over NVLink (no NCCL on the data path)",
+                 api.SPGX_HALO_NONE: "none"}[g.halo_mode()]
     info = g.partition_info()
     bytes_iter, bytes_lower = g.model_bytes()  # owned share of this rank
 
@@ -105,7 +115,7 @@ def run_multi(args):
     achieved = bytes_all * sweeps / (solve_ms * 1e-3) / 1e9
     ncol = g.num_colors()
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak * world, "unit": "GB/s", "frac": achieved / (peak * world),
-                "traffic": None, "kernel": "vbdStreamKernel (+ per-colour ncclSend/ncclRecv halo exchange inside the phase)",
+                "traffic": None, "kernel": "vbdStreamKernel (halo exchange inside the phase: " + halo_name + ")",
                 "launches_per_step": sweeps * ncol, "avg_launch_us": 1e3 * solve_ms / max(sweeps * ncol, 1),
                 "algorithmic_bytes_per_unit": bytes_all * sweeps / (V * sweeps),
                 "lower_bound_frac": lower_all * sweeps / (solve_ms * 1e-3) / 1e9 / (peak * world),
@@ -135,7 +145,7 @@ def run_multi(args):
     unit = "vertex-iters/s"
     e2e = {"value": V * iterations * substeps * ef / (e2e_ms * 1e-3), "unit": unit, "h2d_bytes_per_step": int(h2d),
            "d2h_bytes_per_step": int(d2h), "ms_per_step": e2e_ms / ef, "steps": ef}
-    halo = sum_over_ranks(info["n_local"] - info["n_owned"])
+    halo_total = sum_over_ranks(info["n_local"] - info["n_owned"])
     owned = info["owned_range"]
     ok = bool(np.isfinite(xh[owned[0]:owned[1]]).all())
     ok = max_over_ranks(0.0 if ok else 1.0) == 0.0
@@ -146,12 +156,14 @@ def run_multi(args):
                 "scaling": scaling, "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": B.workload_name(builder, a, solver, substeps, iterations), "vertices": V,
                            "colours": ncol, "parallelism": f"domain decomposition, {world} contiguous index ranges "
-                           f"(row strips / slabs), per-colour halo exchange over NCCL point-to-point",
-                           "halo_vertices_total": int(halo), "launch": "CUDA graph replay of one step() per rank",
+                           f"(row strips / slabs), per-colour halo exchange: {halo_name}",
+                           "halo_vertices_total": int(halo_total), "launch": "CUDA graph replay of one step() per rank",
                            "l2": "inputs larger than L2 (incidence streams ~0.7 GB per sweep per 1M vertices)"},
                 "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": None,
                 "wall_ms_per_step": wall_ms / args.steps, "finite": ok}
         print(json.dumps(line), flush=True)
+    g.disconnect_peers(dist)
+    g.close()
     dist.barrier()
     dist.destroy_process_group()
     return 0

@@ -149,6 +149,26 @@ int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, co
                         int32_t *slot2vert, int32_t *peers, int64_t *sendOffsets, int32_t *sendVerts, int64_t *recvSlot,
                         int64_t *recvCount);
 
+/* Peer-memory halo exchange (replaces the ncclSend / ncclRecv schedule once connected; the reference is single-process,
+ * the dependency it serves is the colour order of vbd.cpp:151-157).  After spgx_group_finalize every rank exports a
+ * blob (CUDA IPC handles of its position array and flag array + its halo layout), the caller all-gathers the blobs
+ * (e.g. torch.distributed.all_gather_object) and hands ALL of them, indexed by rank, to spgx_group_p2p_connect.  From
+ * then on the colour-pass kernel stores boundary vertices straight into the neighbours' halo slots over NVLink and
+ * raises / waits for per-pass event counters in peer memory: no pack kernel, no NCCL launch, no host involvement.
+ * blob == NULL: only *size is written.  Re-finalizing the group disconnects it. */
+int spgx_group_p2p_export(spgx_group *grp, void *blob, int64_t capacity, int64_t *size);
+int spgx_group_p2p_connect(spgx_group *grp, int nBlobs, const void *const *blobs, const int64_t *sizes);
+/* unmap the neighbours' arrays (collective by convention: every rank disconnects, THEN groups may be destroyed, so that
+ * nobody frees an array a neighbour still has mapped); the exchange falls back to NCCL */
+int spgx_group_p2p_disconnect(spgx_group *grp);
+enum spgx_halo_mode { SPGX_HALO_NONE = 0, SPGX_HALO_NCCL = 1, SPGX_HALO_P2P = 2 };
+/* choose the exchange of the next step() (P2P needs a connected group); *mode out when not NULL */
+int spgx_group_set_halo_mode(spgx_group *grp, int mode);
+int spgx_group_get_halo_mode(spgx_group *grp, int *mode);
+/* out8 = [streaming kernel in use, lanes per vertex, warp-slices, largest unique-neighbour count, halo mode,
+ * boundary stores per sweep, 0, 0] */
+int spgx_group_kernel_info(spgx_group *grp, int64_t *out8);
+
 /* structure queries for the bit-exactness gates */
 int spgx_group_num_colors(spgx_group *grp, int energyId /* ignored for VBD */);
 int spgx_get_vertex_colors(spgx_group *grp, int32_t *colors /* nVerts */);

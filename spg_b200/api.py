@@ -21,6 +21,7 @@ if not _LIB_PATH.exists():
 lib = C.CDLL(str(_LIB_PATH))
 
 SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL = 0, 1, 2
+SPGX_HALO_NONE, SPGX_HALO_NCCL, SPGX_HALO_P2P = 0, 1, 2
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
 _lp = C.POINTER(C.c_int64)
@@ -51,6 +52,12 @@ SIGNATURES = {
     "spgx_group_partition_info": (C.c_int, [C.c_void_p, _lp]),
     "spgx_partition_plan": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.c_int, C.c_int, _lp, _ip, _ip, _lp, _ip,
                                       _lp, _lp]),
+    "spgx_group_p2p_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, _lp]),
+    "spgx_group_p2p_connect": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), _lp]),
+    "spgx_group_p2p_disconnect": (C.c_int, [C.c_void_p]),
+    "spgx_group_set_halo_mode": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_group_get_halo_mode": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
+    "spgx_group_kernel_info": (C.c_int, [C.c_void_p, _lp]),
     "spgx_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),
     "spgx_host_unregister": (C.c_int, [C.c_void_p]),
     "spgx_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
@@ -246,6 +253,54 @@ class Group:
 
     def finalize(self, solver_kind: int):
         check(lib.spgx_group_finalize(self.handle, solver_kind))
+
+    # ---- peer-memory halo exchange (include/spgx.h: spgx_group_p2p_*) ----
+    def p2p_export(self) -> bytes:
+        n = C.c_int64(0)
+        check(lib.spgx_group_p2p_export(self.handle, None, 0, C.byref(n)))
+        buf = C.create_string_buffer(n.value)
+        check(lib.spgx_group_p2p_export(self.handle, buf, n.value, C.byref(n)))
+        return buf.raw[:n.value]
+
+    def p2p_connect(self, blobs):
+        """blobs[r] = p2p_export() of rank r (all ranks, e.g. from torch.distributed.all_gather_object)."""
+        keep = [C.create_string_buffer(b, len(b)) for b in blobs]
+        ptrs = (C.c_void_p * len(keep))(*[C.cast(k, C.c_void_p) for k in keep])
+        sizes = (C.c_int64 * len(keep))(*[len(b) for b in blobs])
+        check(lib.spgx_group_p2p_connect(self.handle, len(keep), ptrs, sizes))
+
+    def connect_peers(self, dist):
+        """Collective: all-gather the export blobs over `dist` (torch.distributed) and connect; returns the halo mode."""
+        blobs = [None] * dist.get_world_size()
+        dist.all_gather_object(blobs, self.p2p_export())
+        self.p2p_connect(blobs)
+        dist.barrier()
+        return self.halo_mode()
+
+    def disconnect_peers(self, dist=None):
+        """Unmap the neighbours' arrays; with `dist`, bracketed by barriers so no rank frees what another still maps."""
+        if dist is not None:
+            dist.barrier()
+        check(lib.spgx_group_p2p_disconnect(self.handle))
+        if dist is not None:
+            dist.barrier()
+
+    def set_halo_mode(self, mode: int):
+        check(lib.spgx_group_set_halo_mode(self.handle, int(mode)))
+
+    def halo_mode(self) -> int:
+        m = C.c_int(0)
+        check(lib.spgx_group_get_halo_mode(self.handle, C.byref(m)))
+        return m.value
+
+    def kernel_info(self) -> dict:
+        o = np.zeros(8, dtype=np.int64)
+        check(lib.spgx_group_kernel_info(self.handle, o.ctypes.data_as(_lp)))
+        return {"streamed": bool(o[0]), "lanes": int(o[1]), "slices": int(o[2]), "max_neighbours": int(o[3]),
+                "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5])}
+
+    def streamed(self) -> bool:
+        return self.kernel_info()["streamed"]
 
     def records(self, eid: int) -> np.ndarray:
         rec = np.empty((self.n_stencils[eid], lib.spgx_kind_num_record_params(self.kinds[eid])), dtype=np.float64)

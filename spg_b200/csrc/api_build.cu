@@ -129,13 +129,30 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     // ---- slices and their descriptors ----
     std::vector<int> sliceSlot;  // first slot of every slice
     std::vector<int> sliceEnd;   // one past its last slot
+    std::vector<int> sliceColour;
     for (int c = 0; c < nColors; ++c) {
         const int b = static_cast<int>(grp.colorOffsets[c]), en = static_cast<int>(grp.colorOffsets[c + 1]);
         for (int s0 = b; s0 < en; s0 += VW) {
             sliceSlot.push_back(s0);
             sliceEnd.push_back(std::min(s0 + VW, en));
+            sliceColour.push_back(c);
         }
     }
+    // push list of the peer-memory halo exchange (comm.cu), ascending slot = slice order
+    std::vector<spgx_group::PushEntry> pushAll;
+    std::vector<int> pushWarps(static_cast<size_t>(std::max(nColors, 1)), 0);
+    {
+        const int nPeers = static_cast<int>(grp.peers.size());
+        for (int c = 0; c < nColors && nPeers > 0; ++c)
+            for (int p = 0; p < nPeers; ++p) {
+                const size_t q = static_cast<size_t>(c) * nPeers + p;
+                for (int64_t i = grp.sendOffsets[q]; i < grp.sendOffsets[q + 1]; ++i)
+                    pushAll.push_back({grp.p2p.sendSlots[static_cast<size_t>(i)], p, c, static_cast<int32_t>(i - grp.sendOffsets[q])});
+            }
+        std::stable_sort(pushAll.begin(), pushAll.end(),
+                         [](const spgx_group::PushEntry &a, const spgx_group::PushEntry &b) { return a.slot < b.slot; });
+    }
+    size_t pushCursor = 0, pushBefore = 0;
     const size_t nSlices = sliceSlot.size();
     std::vector<uint32_t> desc((nSlices + 1) * kSliceDescWords, 0u);
     double bytes = 4.0 * desc.size();
@@ -144,16 +161,26 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         for (size_t sl = 0; sl < nSlices; ++sl) {
             desc[sl * kSliceDescWords + 0] = static_cast<uint32_t>(sliceSlot[sl]);
             desc[sl * kSliceDescWords + 1] = row;
-            uint32_t rows = 0, csr = 0;
+            uint32_t rows = 0, csr = 0, readsHalo = 0;
             for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
                 rows = std::max(rows, nbrRowptr[s + 1] - nbrRowptr[s]);
                 csr |= hasCsr[s];
+                for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
+                    if (nbrList[k] >= static_cast<uint32_t>(NO)) readsHalo = 1;
             }
-            desc[sl * kSliceDescWords + 7] = csr;
+            // boundary vertices of the slice: one push entry per (vertex, neighbouring rank that holds it as halo)
+            while (pushCursor < pushAll.size() && pushAll[pushCursor].slot < sliceEnd[sl]) ++pushCursor;
+            if (pushCursor >= (1u << 30)) throw std::runtime_error("too many boundary vertices for the slice descriptor");
+            if (pushCursor > pushBefore) pushWarps[sliceColour[sl]]++;
+            desc[sl * kSliceDescWords + 7] = csr | (readsHalo << 1) | (static_cast<uint32_t>(pushBefore) << 2);
+            pushBefore = pushCursor;
             row += rows;
         }
         desc[nSlices * kSliceDescWords + 0] = static_cast<uint32_t>(NO);
         desc[nSlices * kSliceDescWords + 1] = row;
+        desc[nSlices * kSliceDescWords + 7] = static_cast<uint32_t>(pushBefore) << 2;
+        grp.p2p.pushLocal = pushAll;
+        grp.p2p.pushWarps = pushWarps;
         std::vector<uint32_t> ids(static_cast<size_t>(row) * VW, 0u);
         for (size_t sl = 0; sl < nSlices; ++sl)
             for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s)
@@ -336,6 +363,66 @@ int spgx_group_partition_info(spgx_group *grp, int64_t *out8)
     });
 }
 
+int spgx_group_p2p_export(spgx_group *grp, void *blob, int64_t capacity, int64_t *size)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        const int64_t n = p2pExport(grp, blob, capacity);
+        if (size) *size = n;
+    });
+}
+
+int spgx_group_p2p_connect(spgx_group *grp, int nBlobs, const void *const *blobs, const int64_t *sizes)
+{
+    return guarded([&] {
+        if (!grp || !blobs || !sizes) throw StateError("null argument");
+        p2pConnect(grp, nBlobs, blobs, sizes);
+    });
+}
+
+int spgx_group_p2p_disconnect(spgx_group *grp)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
+        p2pDisconnect(grp);
+    });
+}
+
+int spgx_group_set_halo_mode(spgx_group *grp, int mode)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        if (mode == SPGX_HALO_P2P && !grp->p2p.connected) throw StateError("the group is not connected to its neighbours (spgx_group_p2p_connect)");
+        if (mode == SPGX_HALO_NONE && grp->partitioned && !grp->peers.empty()) throw StateError("a partitioned group needs a halo exchange");
+        if (mode != SPGX_HALO_NONE && mode != SPGX_HALO_NCCL && mode != SPGX_HALO_P2P) throw std::runtime_error("unknown halo mode");
+        if (!grp->partitioned) mode = SPGX_HALO_NONE;
+        if (mode != grp->p2p.mode && grp->graphExec) {
+            cudaGraphExecDestroy(grp->graphExec);
+            grp->graphExec = nullptr;
+        }
+        grp->p2p.mode = mode;
+    });
+}
+
+int spgx_group_get_halo_mode(spgx_group *grp, int *mode)
+{
+    return guarded([&] {
+        if (!grp || !mode) throw StateError("null argument");
+        *mode = grp->p2p.mode;
+    });
+}
+
+int spgx_group_kernel_info(spgx_group *grp, int64_t *out8)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized || !out8) throw StateError("group is not finalized");
+        out8[0] = grp->streamMask != 0, out8[1] = grp->vbdLanes, out8[2] = grp->nSlices, out8[3] = grp->maxNbr;
+        out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = 0, out8[7] = 0;
+    });
+}
+
 int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
                         const int32_t *stencilSizes, const int32_t *owner, int rank, int nranks, int64_t *sizes,
                         int32_t *slot2vert, int32_t *peers, int64_t *sendOffsets, int32_t *sendVerts, int64_t *recvSlot,
@@ -509,6 +596,17 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->vert2slot = lv.vert2slot;
             grp->colorOffsets = lv.colorOffsets;
             const int nOwned = lv.nOwned, nLocal = lv.nLocal;
+            // halo exchange tables
+            grp->peers = lv.peers;
+            grp->sendOffsets = lv.sendOffsets;
+            grp->recvSlot = lv.recvSlot;
+            grp->recvCount = lv.recvCount;
+            grp->p2p.sendSlots = lv.sendSlots;
+            grp->p2p.pushLocal.clear();
+            grp->p2p.pushWarps.clear();
+            grp->d_sendSlots.upload(lv.sendSlots, st);
+            grp->d_sendBuf.alloc(3 * lv.sendSlots.size());
+            SPGX_CUDA(cudaStreamSynchronize(st));
             {
                 // threads per vertex (measured on B200, profiles/): two lanes per vertex for big colours (shorter
                 // per-warp chains, half the neighbour tile, more resident slices), four below 100 k vertices per colour
@@ -615,14 +713,6 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 std::sort(nbr.begin(), nbr.end());
                 grp->uniqueNeighbourSum += static_cast<double>(std::unique(nbr.begin(), nbr.end()) - nbr.begin());
             }
-            // halo exchange tables
-            grp->peers = lv.peers;
-            grp->sendOffsets = lv.sendOffsets;
-            grp->recvSlot = lv.recvSlot;
-            grp->recvCount = lv.recvCount;
-            grp->d_sendSlots.upload(lv.sendSlots, st);
-            grp->d_sendBuf.alloc(3 * lv.sendSlots.size());
-            SPGX_CUDA(cudaStreamSynchronize(st));
         } else {
             if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
             grp->nOwned = grp->nLocal = V;
@@ -696,6 +786,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         grp->ownedContiguous = (grp->ownedHi - grp->ownedLo) == grp->nOwned;
         grp->d_slot2vert.upload(grp->slot2vert, st);
         SPGX_CUDA(cudaStreamSynchronize(st));
+        p2pPrepare(grp, st);  // the position array is new: earlier peer mappings of it are void
         if (!grp->evStart) {
             SPGX_CUDA(cudaEventCreate(&grp->evStart));
             SPGX_CUDA(cudaEventCreate(&grp->evStop));

@@ -56,23 +56,46 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.pdl = grp->vbdPdl;
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+    // halo exchange of a partitioned group: fused peer-memory stores + event counters (halo.cuh), or ncclSend / ncclRecv
+    const bool p2p = grp->partitioned && grp->p2p.mode == SPGX_HALO_P2P && grp->p2p.connected && args.nStreams > 0;
+    const bool viaNccl = grp->partitioned && !p2p;
+    args.halo = p2p ? grp->p2p.dev : VbdHaloDev{};
+    const bool signalling = p2p && args.halo.nPeers > 0;
     for (int s = 0; s < nsub; ++s) {
         // predict / finalize run over owned AND halo vertices: a halo copy goes through the same arithmetic as on its
         // owner, so no exchange is needed outside the colour passes
         launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->d_xInertial.ptr, grp->nLocal, dt, grp->graphKey.g,
                       st);
         grp->launchCounter++;
+        if (signalling) {
+            // event 0: this rank's halo copies have been predicted; neighbours may store into them from now on
+            launchHaloSignal(args.halo, 0, st);
+            grp->launchCounter++;
+        }
         if (timePhases) grp->markPhase(st);
+        int event = 0;
         for (int it = 0; it < iters; ++it)
             for (int c = 0; c < nColors; ++c) {
                 const int b = static_cast<int>(grp->colorOffsets[c]), e = static_cast<int>(grp->colorOffsets[c + 1]);
+                ++event;
+                args.halo.event = event;
+                args.halo.pushWarps = signalling ? grp->p2p.pushWarps[c] : 0;
                 if (e > b) {
                     launchVbdPass(args, mask, grp->streamMask, grp->vbdLanes, grp->vbdOcc, b, e, grp->sliceBase[c], invdtSquared, st);
                     grp->launchCounter++;
+                } else if (signalling) {
+                    launchHaloSignal(args.halo, event, st);  // no vertex of this colour here: the event is still owed
+                    grp->launchCounter++;
                 }
                 // every rank takes part in the exchange of colour c, whether or not it owns vertices of that colour
-                if (grp->partitioned) grp->launchCounter += enqueueHaloExchange(grp, c, st);
+                if (viaNccl) grp->launchCounter += enqueueHaloExchange(grp, c, st);
             }
+        if (signalling) {
+            // the neighbours' stores of the last pass must have landed before the halo copies are finalized; the epoch
+            // advances by the events of this substep
+            launchHaloWaitAdvance(args.halo, event, grp->p2p.d_sync.ptr + kMaxPeers, st);
+            grp->launchCounter++;
+        }
         if (timePhases) grp->markPhase(st);
         launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
         grp->launchCounter++;
@@ -140,7 +163,7 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
         else
             enqueueXpbdFrame(grp, dt, nsub, iters, st, timePhases);
     };
-    if (grp->partitioned && !grp->commWarm) {
+    if (grp->partitioned && !grp->commWarm && !(grp->p2p.mode == SPGX_HALO_P2P && grp->p2p.connected)) {
         // NCCL sets up its peer connections on first use (allocations, not capturable): exchange every colour once,
         // eagerly.  Halo copies already equal their owners' values, so this changes nothing.
         const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
@@ -180,6 +203,11 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
     grp->timings.kernel_launches = grp->launchCounter;
     if (sync) {
         SPGX_CUDA(cudaStreamSynchronize(st));
+        if (grp->p2p.hostError && *grp->p2p.hostError) {
+            *grp->p2p.hostError = 0;
+            throw CommError("halo exchange: a neighbouring rank did not raise its event counter within the timeout "
+                            "(SPGX_HALO_TIMEOUT_S): ranks out of step, or a rank died");
+        }
         float ms = 0;
         SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
         grp->timings.total_ms = ms;

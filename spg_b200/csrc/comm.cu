@@ -7,9 +7,12 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "group.h"
+#include "halo.cuh"
 
 namespace spgx
 {
@@ -67,7 +70,198 @@ __global__ void packKernel(const double *__restrict__ x, const int32_t *__restri
     out[3 * static_cast<size_t>(i) + 1] = x[o + 1];
     out[3 * static_cast<size_t>(i) + 2] = x[o + 2];
 }
+// peer-memory exchange outside the colour passes: one thread raises an event / waits for one and advances the epoch
+__global__ void haloSignalKernel(const VbdHaloDev h, int event)
+{
+    __threadfence_system();
+    haloRaise(h, haloEpochBase(h) + static_cast<uint32_t>(event) + 1u);
+}
+__global__ void haloWaitAdvanceKernel(const VbdHaloDev h, int event, uint32_t *epochBase)
+{
+    const uint32_t value = haloEpochBase(h) + static_cast<uint32_t>(event) + 1u;
+    haloWaitAll(h, value);
+    *reinterpret_cast<volatile uint32_t *>(epochBase) = value;
+}
+
+constexpr uint32_t kBlobMagic = 0x53504758u;  // "SPGX"
+struct BlobHeader {
+    uint32_t magic;
+    int32_t rank, nRanks, nPeers, nColors, reserved;
+    int64_t nLocal;
+    cudaIpcMemHandle_t x, sync;
+};
+// followed by: int32 peers[nPeers] (padded to 8 bytes); int64 recvSlot[nColors * nPeers]; int64 recvCount[nColors * nPeers]
+size_t paddedPeersBytes(int nPeers)
+{
+    return (static_cast<size_t>(nPeers) * 4 + 7) / 8 * 8;
+}
+size_t blobBytes(int nPeers, int nColors)
+{
+    return sizeof(BlobHeader) + paddedPeersBytes(nPeers) + 2 * sizeof(int64_t) * static_cast<size_t>(nColors) * nPeers;
+}
 }  // namespace
+
+void launchHaloSignal(const VbdHaloDev &h, int event, cudaStream_t stream)
+{
+    haloSignalKernel<<<1, 1, 0, stream>>>(h, event);
+}
+void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, cudaStream_t stream)
+{
+    haloWaitAdvanceKernel<<<1, 1, 0, stream>>>(h, event, epochBase);
+}
+
+void p2pDisconnect(spgx_group *grp)
+{
+    auto &p = grp->p2p;
+    for (void *m : p.mapped) cudaIpcCloseMemHandle(m);
+    p.mapped.clear();
+    if (p.connected && grp->graphExec) {  // the captured launches hold the neighbours' pointers
+        cudaGraphExecDestroy(grp->graphExec);
+        grp->graphExec = nullptr;
+    }
+    p.connected = false;
+    if (p.mode == SPGX_HALO_P2P) p.mode = grp->partitioned ? SPGX_HALO_NCCL : SPGX_HALO_NONE;
+    p.dev = VbdHaloDev{};
+}
+
+void p2pRelease(spgx_group *grp)
+{
+    p2pDisconnect(grp);
+    auto &p = grp->p2p;
+    if (p.hostError) cudaFreeHost(p.hostError);
+    p.hostError = p.devError = nullptr;
+    p.d_sync.release();
+    p.d_push.release();
+}
+
+// after finalize (the position array has just been allocated): fresh sync words, fresh error word
+void p2pPrepare(spgx_group *grp, cudaStream_t st)
+{
+    p2pRelease(grp);
+    auto &p = grp->p2p;
+    p.mode = grp->partitioned ? SPGX_HALO_NCCL : SPGX_HALO_NONE;
+    if (!grp->partitioned || grp->peers.empty()) return;
+    if (static_cast<int>(grp->peers.size()) > kMaxPeers) return;  // NCCL exchange only
+    p.d_sync.alloc(kMaxPeers + 8);
+    SPGX_CUDA(cudaMemsetAsync(p.d_sync.ptr, 0, p.d_sync.count * sizeof(uint32_t), st));
+    SPGX_CUDA(cudaHostAlloc(reinterpret_cast<void **>(&p.hostError), sizeof(uint32_t), cudaHostAllocMapped));
+    *p.hostError = 0;
+    SPGX_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void **>(&p.devError), p.hostError, 0));
+    SPGX_CUDA(cudaStreamSynchronize(st));
+}
+
+int64_t p2pExport(spgx_group *grp, void *blob, int64_t capacity)
+{
+    if (!grp->finalized || grp->solverKind != SPGX_VBD) throw StateError("p2p export needs a group finalized for VBD");
+    if (!grp->partitioned) throw StateError("p2p export needs a partitioned group (spgx_group_set_partition)");
+    const int nPeers = static_cast<int>(grp->peers.size());
+    const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+    const size_t bytes = blobBytes(nPeers, nColors);
+    if (!blob) return static_cast<int64_t>(bytes);
+    if (capacity < static_cast<int64_t>(bytes)) throw std::runtime_error("p2p export: blob too small");
+    std::memset(blob, 0, bytes);
+    BlobHeader h{};
+    h.magic = kBlobMagic;
+    h.rank = grp->rank;
+    h.nRanks = grp->nRanks;
+    h.nPeers = nPeers;
+    h.nColors = nColors;
+    h.nLocal = grp->nLocal;
+    if (nPeers > 0) {
+        if (!grp->p2p.d_sync.ptr) throw StateError("p2p export: more neighbours than the peer-memory exchange supports");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        SPGX_CUDA(cudaIpcGetMemHandle(&h.x, grp->d_x.ptr));
+        SPGX_CUDA(cudaIpcGetMemHandle(&h.sync, grp->p2p.d_sync.ptr));
+    }
+    char *out = static_cast<char *>(blob);
+    std::memcpy(out, &h, sizeof(h));
+    out += sizeof(h);
+    std::memcpy(out, grp->peers.data(), sizeof(int32_t) * nPeers);
+    out += paddedPeersBytes(nPeers);
+    std::memcpy(out, grp->recvSlot.data(), sizeof(int64_t) * grp->recvSlot.size());
+    out += sizeof(int64_t) * static_cast<size_t>(nColors) * nPeers;
+    std::memcpy(out, grp->recvCount.data(), sizeof(int64_t) * grp->recvCount.size());
+    return static_cast<int64_t>(bytes);
+}
+
+// blobs[r] = what rank r exported.  Opens the neighbours' arrays and turns the local push list into device entries
+// (local slot, neighbour << 28 | slot on the neighbour): what peer p receives from this rank after colour c lands in
+// its halo range recvSlot[c, me], in the order of this rank's (c, p) send list (partition.h).
+void p2pConnect(spgx_group *grp, int nBlobs, const void *const *blobs, const int64_t *sizes)
+{
+    if (!grp->finalized || grp->solverKind != SPGX_VBD || !grp->partitioned)
+        throw StateError("p2p connect needs a partitioned group finalized for VBD");
+    if (nBlobs != grp->nRanks) throw std::runtime_error("p2p connect: one blob per rank expected");
+    if (grp->streamMask == 0) throw StateError("p2p connect: the group's energies have no streaming colour-pass kernel");
+    auto &p = grp->p2p;
+    const int nPeers = static_cast<int>(grp->peers.size());
+    const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+    if (nPeers > kMaxPeers) throw StateError("p2p connect: more neighbours than the peer-memory exchange supports");
+    SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+    for (void *m : p.mapped) cudaIpcCloseMemHandle(m);
+    p.mapped.clear();
+    p.connected = false;
+    VbdHaloDev dev{};
+    dev.nPeers = nPeers;
+    std::vector<const int64_t *> peerRecvSlot(nPeers), peerRecvCount(nPeers);
+    std::vector<int> idxAtPeer(nPeers, -1), peerNPeers(nPeers, 0);
+    for (int q = 0; q < nPeers; ++q) {
+        const int r = grp->peers[q];
+        const char *b = static_cast<const char *>(blobs[r]);
+        BlobHeader h;
+        if (!b || sizes[r] < static_cast<int64_t>(sizeof(h))) throw std::runtime_error("p2p connect: blob missing or truncated");
+        std::memcpy(&h, b, sizeof(h));
+        if (h.magic != kBlobMagic || h.rank != r || h.nRanks != grp->nRanks || h.nColors != nColors)
+            throw std::runtime_error("p2p connect: blob does not match this group (rank / ranks / colours)");
+        if (sizes[r] < static_cast<int64_t>(blobBytes(h.nPeers, h.nColors))) throw std::runtime_error("p2p connect: blob truncated");
+        const int32_t *peersOfR = reinterpret_cast<const int32_t *>(b + sizeof(h));
+        for (int i = 0; i < h.nPeers; ++i)
+            if (peersOfR[i] == grp->rank) idxAtPeer[q] = i;
+        if (idxAtPeer[q] < 0) throw std::runtime_error("p2p connect: neighbour does not list this rank as its neighbour");
+        peerNPeers[q] = h.nPeers;
+        peerRecvSlot[q] = reinterpret_cast<const int64_t *>(b + sizeof(h) + paddedPeersBytes(h.nPeers));
+        peerRecvCount[q] = peerRecvSlot[q] + static_cast<size_t>(h.nColors) * h.nPeers;
+        for (int c = 0; c < nColors; ++c) {
+            const int64_t mine = grp->sendOffsets[static_cast<size_t>(c) * nPeers + q + 1] - grp->sendOffsets[static_cast<size_t>(c) * nPeers + q];
+            if (mine != peerRecvCount[q][static_cast<size_t>(c) * h.nPeers + idxAtPeer[q]])
+                throw std::runtime_error("p2p connect: send list and the neighbour's halo range disagree");
+        }
+        if (h.nLocal >= (1ll << 28)) throw std::runtime_error("p2p connect: neighbour holds too many slots for the packed push entry");
+        void *px = nullptr, *ps = nullptr;
+        SPGX_CUDA(cudaIpcOpenMemHandle(&px, h.x, cudaIpcMemLazyEnablePeerAccess));
+        p.mapped.push_back(px);
+        SPGX_CUDA(cudaIpcOpenMemHandle(&ps, h.sync, cudaIpcMemLazyEnablePeerAccess));
+        p.mapped.push_back(ps);
+        dev.peerX[q] = static_cast<double *>(px);
+        dev.peerFlag[q] = static_cast<uint32_t *>(ps) + idxAtPeer[q];
+    }
+    std::vector<uint2> push(p.pushLocal.size());
+    for (size_t i = 0; i < push.size(); ++i) {
+        const auto &e = p.pushLocal[i];
+        const int64_t remote = peerRecvSlot[e.peer][static_cast<size_t>(e.colour) * peerNPeers[e.peer] + idxAtPeer[e.peer]] + e.pos;
+        push[i] = make_uint2(static_cast<uint32_t>(e.slot), (static_cast<uint32_t>(e.peer) << 28) | static_cast<uint32_t>(remote));
+    }
+    cudaStream_t st = grp->ctx->stream;
+    p.d_push.alloc(std::max<size_t>(push.size(), 1));
+    if (!push.empty())
+        SPGX_CUDA(cudaMemcpyAsync(p.d_push.ptr, push.data(), push.size() * sizeof(uint2), cudaMemcpyHostToDevice, st));
+    SPGX_CUDA(cudaStreamSynchronize(st));
+    dev.myFlag = p.d_sync.ptr;
+    dev.epochBase = p.d_sync.ptr + kMaxPeers;
+    dev.pushDone = p.d_sync.ptr + kMaxPeers + 1;
+    dev.push = p.d_push.ptr;
+    dev.error = p.devError;
+    double timeoutS = 10.0;
+    if (const char *env = getenv("SPGX_HALO_TIMEOUT_S")) timeoutS = std::max(0.001, atof(env));
+    dev.timeoutNs = static_cast<unsigned long long>(timeoutS * 1e9);
+    p.dev = dev;
+    p.connected = true;
+    p.mode = SPGX_HALO_P2P;
+    if (grp->graphExec) {
+        cudaGraphExecDestroy(grp->graphExec);
+        grp->graphExec = nullptr;
+    }
+}
 
 void commUniqueId(void *id128)
 {

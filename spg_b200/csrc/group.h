@@ -139,6 +139,11 @@ struct EnergyState {
 };
 }  // namespace spgx
 
+namespace spgx
+{
+void p2pRelease(spgx_group *grp);
+}
+
 struct spgx_group {
     spgx_ctx *ctx = nullptr;
     int nVerts = 0;
@@ -161,6 +166,22 @@ struct spgx_group {
     spgx::DevBuf<double> d_sendBuf;
     int64_t haloBytesPerSweep = 0;
     bool commWarm = false;
+    // peer-memory halo exchange fused into the colour pass (comm.cu, halo.cuh)
+    struct PushEntry {
+        int32_t slot, peer, colour, pos;  // owned slot, index into `peers`, its colour, position in the (colour, peer) send list
+    };
+    struct P2PState {
+        bool connected = false;
+        int mode = 0;                       // SPGX_HALO_*: what the next step() uses
+        std::vector<int32_t> sendSlots;     // host copy of d_sendSlots
+        std::vector<PushEntry> pushLocal;   // in slice order
+        std::vector<int> pushWarps;         // per colour: slices that hold push entries
+        spgx::DevBuf<uint32_t> d_sync;      // [0, kMaxPeers) flags raised by the neighbours, [kMaxPeers] epoch base, [+1] push counter
+        spgx::DevBuf<uint2> d_push;
+        uint32_t *hostError = nullptr, *devError = nullptr;  // mapped pinned word: a wait ran into its timeout
+        std::vector<void *> mapped;         // cudaIpcOpenMemHandle results to close
+        spgx::VbdHaloDev dev{};
+    } p2p;
     // vertex colouring / ordering (VBD); identity ordering for XPBD
     std::vector<int32_t> vertexColors;
     std::vector<int32_t> slot2vert, vert2slot;
@@ -221,10 +242,17 @@ struct spgx_group {
         if (graphExec) cudaGraphExecDestroy(graphExec);
         if (evStart) cudaEventDestroy(evStart);
         if (evStop) cudaEventDestroy(evStop);
+        spgx::p2pRelease(this);
     }
 };
 
 namespace spgx
 {
 int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
+// peer-memory exchange (comm.cu)
+void p2pPrepare(spgx_group *grp, cudaStream_t st);   // after finalize: sync words, error word; closes old mappings
+void p2pRelease(spgx_group *grp);
+void p2pDisconnect(spgx_group *grp);                 // unmap the neighbours' arrays, keep this rank's own buffers
+int64_t p2pExport(spgx_group *grp, void *blob, int64_t capacity);
+void p2pConnect(spgx_group *grp, int nBlobs, const void *const *blobs, const int64_t *sizes);
 }

@@ -29,6 +29,26 @@ struct VbdStreamDev {
     const double *params;
 };
 
+constexpr int kMaxPeers = 8;
+// Peer-memory halo exchange fused into the colour pass (comm.cu): every owned boundary vertex is stored straight into
+// the halo slot of each neighbouring rank's position array (CUDA IPC mapping, NVLink), the last warp of the pass to
+// finish its stores raises an event counter in the neighbours' flag arrays, and the slices of the next pass that read
+// halo slots wait for the neighbours' counters.  Events of one substep: 0 = predict done, j = colour pass j done
+// (j = 1..P); the value written for event j is *epochBase + j + 1; *epochBase advances by P + 1 per substep.
+struct VbdHaloDev {
+    int nPeers;                      // 0: single domain, or the NCCL exchange is used instead
+    int event;                       // event this pass raises (waits for event - 1)
+    int pushWarps;                   // warps of this pass that hold push entries (the last one to finish raises the event)
+    double *peerX[kMaxPeers];        // the neighbours' position arrays
+    uint32_t *peerFlag[kMaxPeers];   // this rank's entry in each neighbour's flag array
+    const uint32_t *myFlag;          // this rank's flag array, one entry per neighbour
+    const uint2 *push;               // (local slot, neighbour << 28 | slot on the neighbour), in slice order
+    uint32_t *pushDone;              // warps of the running pass that have finished their stores
+    const uint32_t *epochBase;
+    uint32_t *error;                 // set to 1 when a wait ran into the timeout
+    unsigned long long timeoutNs;
+};
+
 struct VbdArgs {
     double *x;                 // 3 doubles per slot
     const double *xInertial;   // 3 doubles per slot
@@ -40,13 +60,15 @@ struct VbdArgs {
     VbdStreamDev s[kNumStreamTypes];  // indexed by StreamType
     // per warp-slice descriptor, kSliceDescWords uint32 each, nSlices + 1 entries (the last one closes the ranges):
     //   [0] first slot, [1] first row of the unique-neighbour table, [2 + t] first step of stream type t,
-    //   [7] bit 0: some vertex of the slice has incidences on the CSR path
+    //   [7] bit 0: some vertex of the slice has incidences on the CSR path; bit 1: the slice reads halo slots;
+    //       bits 2..31: number of push entries (VbdHaloDev::push) of all earlier slices
     const uint32_t *sliceDesc;
     const uint32_t *nbrIds;  // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
     int maxNbr;              // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
     int nSlices;             // all colours
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
     int pdl;                 // 1: launch colour passes with programmatic stream serialization
+    VbdHaloDev halo;
 };
 
 // can launchVbdPass run this combination of stream types + CSR kinds through the streaming kernel?
@@ -63,6 +85,9 @@ void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nV
                    cudaStream_t stream);
 // particleGroup.cpp:65-72: v <- (x - xOld) * invdt
 void launchFinalize(const double *x, const double *xOld, double *v, int nVerts, double invdt, cudaStream_t stream);
+// peer-memory halo exchange outside the colour passes (comm.cu): raise event `event` / wait for it and advance the epoch
+void launchHaloSignal(const VbdHaloDev &h, int event, cudaStream_t stream);
+void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, cudaStream_t stream);
 // dst[perm[i]] = src[i] (scatter) or dst[i] = src[perm[i]] (gather) over 3-vectors
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream);
 

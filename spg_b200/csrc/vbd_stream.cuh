@@ -12,6 +12,7 @@
 //   4. the G partial sums are reduced with warp shuffles; lane group 0 adds the inertia term, applies the
 //      det(H) > 1e-10 gate (vbd.cpp:139) and the cofactor solve, and writes the vertex.
 #pragma once
+#include "halo.cuh"
 #include "kernels.h"
 #include "streams.cuh"
 
@@ -106,10 +107,12 @@ __device__ __forceinline__ void accumulateCsrEnergies(const VbdArgs &a, int slot
 }
 
 // butterfly over the sub-lane bits (lanes of one vertex sit VW apart), inertia term, gate, solve, write
+// returns the position the vertex ends the pass with (meaningful on its sub == 0 lane)
 template <int G>
-__device__ __forceinline__ void reduceSolveWrite(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, V3d f,
-                                                 Sym3 H, double invdtSquared)
+__device__ __forceinline__ V3d reduceSolveWrite(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, V3d f,
+                                                Sym3 H, double invdtSquared)
 {
+    V3d xn = xo;
     constexpr int VW = 32 / G;
 #pragma unroll
     for (int o = VW; o < 32; o <<= 1) {
@@ -136,9 +139,43 @@ __device__ __forceinline__ void reduceSolveWrite(const VbdArgs &a, int slot, boo
         const double d = det(H);
         if (d > 1e-10) {  // vbd.cpp:139
             const V3d dx = solveSym3(H, d, f);
-            a.x[o] = xo.x + dx.x;
-            a.x[o + 1] = xo.y + dx.y;
-            a.x[o + 2] = xo.z + dx.z;
+            xn = V3d(xo.x + dx.x, xo.y + dx.y, xo.z + dx.z);
+            a.x[o] = xn.x;
+            a.x[o + 1] = xn.y;
+            a.x[o + 2] = xn.z;
+        }
+    }
+    return xn;
+}
+
+// Peer-memory halo push (kernels.h: VbdHaloDev): the slice's boundary vertices go straight into the neighbours' halo
+// slots; the last warp of the pass to finish its stores raises the pass's event on every neighbour.
+__device__ __forceinline__ void haloPushSlice(const VbdHaloDev &h, uint32_t firstSlot, uint32_t pb, uint32_t pe, int lane,
+                                              const V3d &xn)
+{
+    for (uint32_t i = pb; i < pe; i += 32) {
+        const bool has = i + lane < pe;
+        uint2 e = make_uint2(firstSlot, 0u);
+        if (has) e = __ldg(h.push + i + lane);
+        const int src = static_cast<int>(e.x - firstSlot);  // the vertex's sub == 0 lane
+        const double px = __shfl_sync(0xffffffffu, xn.x, src);
+        const double py = __shfl_sync(0xffffffffu, xn.y, src);
+        const double pz = __shfl_sync(0xffffffffu, xn.z, src);
+        if (has) {
+            double *dst = h.peerX[e.y >> 28] + 3 * static_cast<size_t>(e.y & 0x0FFFFFFFu);
+            dst[0] = px;
+            dst[1] = py;
+            dst[2] = pz;
+        }
+    }
+    __threadfence_system();
+    __syncwarp();
+    if (lane == 0) {
+        const uint32_t done = atomicAdd(h.pushDone, 1u) + 1u;
+        if (done == static_cast<uint32_t>(h.pushWarps)) {
+            *reinterpret_cast<volatile uint32_t *>(h.pushDone) = 0u;  // the next pass counts from zero
+            __threadfence_system();
+            haloRaise(h, haloEpochBase(h) + static_cast<uint32_t>(h.event) + 1u);
         }
     }
 }
@@ -352,6 +389,19 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     // 2. positions: wait for the previous colour pass (programmatic dependent launch: this grid may have started
     // while that one was draining), then gather the unique neighbours (columns of padding lanes hold slot 0)
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (a.halo.nPeers) {
+        // multi-GPU: a slice that reads halo slots needs the neighbours' stores of the previous event
+        if (a.halo.pushWarps == 0 && slice == sliceBase && lane == 0) {
+            // no boundary vertex of this colour here: the pass still owes its neighbours the event (the previous
+            // pass, stores included, is complete at this point)
+            __threadfence_system();
+            haloRaise(a.halo, haloEpochBase(a.halo) + static_cast<uint32_t>(a.halo.event) + 1u);
+        }
+        if (d.hi.w & 2u) {
+            if (lane == 0) haloWaitAll(a.halo, haloEpochBase(a.halo) + static_cast<uint32_t>(a.halo.event));
+            __syncwarp();
+        }
+    }
 #pragma unroll
     for (int j = 0; j < PRE; ++j) {
         const uint32_t k = nb + sub + j * G;
@@ -399,7 +449,12 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
     // 5. reduce, solve, write
-    reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
+    const V3d xn = reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
+    // 6. multi-GPU: boundary vertices of the slice go to the neighbours' halo slots over NVLink
+    if (a.halo.nPeers) {
+        const uint32_t pb = d.hi.w >> 2, pe = n.hi.w >> 2;
+        if (pe > pb) haloPushSlice(a.halo, d.lo.x, pb, pe, lane, xn);
+    }
 }
 
 template <unsigned SMASK, unsigned KMASK, int G, int OCC>

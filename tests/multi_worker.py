@@ -26,32 +26,37 @@ def main():
     dist.broadcast(uid, 0)
     ctx.init_comm(rank, world, uid.cpu().numpy())
     results = {}
-    for graph in (True, False):
-        g = api.Group.from_scene(ctx, sc)
-        g.set_partition(rank, world)
-        g.finalize(api.SPGX_VBD)
-        g.set_graph_mode(graph)
-        g.vbd_step(0.01, 2, 5, frames=3)
-        x = np.full((sc.n_vertices, 3), np.nan)
-        v = np.full((sc.n_vertices, 3), np.nan)
-        g.download_into(x, v)
-        info = g.partition_info()
-        lo, hi = info["owned_range"]
-        assert np.isfinite(x[lo:hi]).all() and np.isnan(x[:lo]).all() and np.isnan(x[hi:]).all()
-        # upload / download round trip in partitioned mode, then one more frame
-        xs, vs = np.nan_to_num(x), np.nan_to_num(v)
-        tx = torch.from_numpy(xs).cuda()
-        tv = torch.from_numpy(vs).cuda()
-        dist.all_reduce(tx)  # every vertex is owned exactly once: the sum assembles the global state
-        dist.all_reduce(tv)
-        results[graph] = (tx.cpu().numpy(), tv.cpu().numpy())
-        g.close()
+    for mode in ("nccl", "p2p"):
+        for graph in (True, False):
+            g = api.Group.from_scene(ctx, sc)
+            g.set_partition(rank, world)
+            g.finalize(api.SPGX_VBD)
+            assert g.halo_mode() == api.SPGX_HALO_NCCL
+            if mode == "p2p":
+                assert g.connect_peers(dist) == api.SPGX_HALO_P2P
+            g.set_graph_mode(graph)
+            g.vbd_step(0.01, 2, 5, frames=3)
+            x = np.full((sc.n_vertices, 3), np.nan)
+            v = np.full((sc.n_vertices, 3), np.nan)
+            g.download_into(x, v)
+            info = g.partition_info()
+            lo, hi = info["owned_range"]
+            assert np.isfinite(x[lo:hi]).all() and np.isnan(x[:lo]).all() and np.isnan(x[hi:]).all()
+            xs, vs = np.nan_to_num(x), np.nan_to_num(v)
+            tx = torch.from_numpy(xs).cuda()
+            tv = torch.from_numpy(vs).cuda()
+            dist.all_reduce(tx)  # every vertex is owned exactly once: the sum assembles the global state
+            dist.all_reduce(tv)
+            results[(mode, graph)] = (tx.cpu().numpy(), tv.cpu().numpy())
+            g.disconnect_peers(dist)  # nobody frees an array a neighbour still maps or stores into
+            g.close()
     if rank == 0:
         g1 = api.Group.from_scene(ctx, sc)
         g1.finalize(api.SPGX_VBD)
         g1.vbd_step(0.01, 2, 5, frames=3)
         x1, v1 = g1.download()
-        np.savez(out, xg=results[True][0], vg=results[True][1], xp=results[False][0], vp=results[False][1], x1=x1, v1=v1)
+        np.savez(out, x1=x1, v1=v1, **{f"x_{m}_{int(gr)}": r[0] for (m, gr), r in results.items()},
+                 **{f"v_{m}_{int(gr)}": r[1] for (m, gr), r in results.items()})
     dist.barrier()
     dist.destroy_process_group()
 
