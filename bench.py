@@ -181,6 +181,8 @@ def metric_name(solver):
 def run_single(args):
     from spg_b200 import api
     builder, a, solver, substeps, iterations = CONFIGS[args.config]
+    if args.rows and builder.startswith("cloth"):
+        a = (args.rows, a[1])
     sc = build_scene(builder, a)
     ctx = api.Context(int(os.environ.get("LOCAL_RANK", "0")))
     g = api.Group.from_scene(ctx, sc)
@@ -293,6 +295,7 @@ def main():
     ap.add_argument("--impl", default="spgx", choices=["spgx", "reference"])
     ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rows", type=int, default=0, help="diagnostics: override the first grid dimension of a cloth config")
     ap.add_argument("--halo", default="p2p", choices=["p2p", "nccl"], help="multi-GPU halo exchange (bench_multi.py)")
     args = ap.parse_args()
     if args.impl == "reference":

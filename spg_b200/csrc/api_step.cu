@@ -1,5 +1,6 @@
 // C-ABI, part 2: state transfer, the VBD / XPBD step drivers (launch sequences, CUDA-graph capture),
 // timings and the per-element evaluators.
+#include <cstdlib>
 #include <cstring>
 
 #include "energies.cuh"
@@ -58,9 +59,11 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
     // halo exchange of a partitioned group: fused peer-memory stores + event counters (halo.cuh), or ncclSend / ncclRecv
     const bool p2p = grp->partitioned && grp->p2p.mode == SPGX_HALO_P2P && grp->p2p.connected && args.nStreams > 0;
-    const bool viaNccl = grp->partitioned && !p2p;
-    args.halo = p2p ? grp->p2p.dev : VbdHaloDev{};
-    const bool signalling = p2p && args.halo.nPeers > 0;
+    // SPGX_DEBUG_SKIP_HALO=1 (timing experiments only, results are wrong): run the partitioned sweep with no exchange
+    static const bool skipHalo = getenv("SPGX_DEBUG_SKIP_HALO") && atoi(getenv("SPGX_DEBUG_SKIP_HALO")) != 0;
+    const bool viaNccl = grp->partitioned && !p2p && !skipHalo;
+    args.halo = (p2p && !skipHalo) ? grp->p2p.dev : VbdHaloDev{};
+    const bool signalling = p2p && !skipHalo && args.halo.nPeers > 0;
     for (int s = 0; s < nsub; ++s) {
         // predict / finalize run over owned AND halo vertices: a halo copy goes through the same arithmetic as on its
         // owner, so no exchange is needed outside the colour passes

@@ -5,7 +5,7 @@
 // `owner[v] == rank`, keeps every stencil that touches an owned vertex, and holds the other vertices of those
 // stencils as HALO copies.  Within a colour pass all vertices on all ranks are independent, so the only exchange is:
 // after colour pass c every rank sends the positions of its owned colour-c vertices that sit in a neighbour's halo.
-// Local slot order:  [ owned, sorted by (colour, vertex id) | halo, sorted by (owner, colour, vertex id) ]
+// Local slot order:  [ owned, sorted by (colour, boundary first, vertex id) | halo, sorted by (owner, colour, vertex id) ]
 // so a colour is a contiguous range of owned slots and what arrives from peer p after colour c lands in one contiguous
 // range of halo slots (no unpack); the sender packs the matching list (same order, by construction, on both sides).
 #pragma once
@@ -88,10 +88,19 @@ inline LocalView buildLocalView(int nVerts, const std::vector<int32_t> &colors, 
         if (peerIndex[r] >= 0) lv.peers.push_back(r);
     const int nPeers = static_cast<int>(lv.peers.size());
 
-    // owned slots: (colour, id)
+    // owned slots: (colour, boundary first, id).  A boundary vertex is one some neighbour holds as halo; putting them at
+    // the head of their colour makes them the first warps of the colour pass, so their peer-memory stores (and the
+    // system-scope fence behind them) overlap the interior work instead of trailing the pass (halo.cuh).
+    std::vector<uint8_t> isBoundary(static_cast<size_t>(nVerts), 0);
+    for (const auto &need : needs)
+        for (int v = 0; v < nVerts; ++v) isBoundary[v] |= need[v];
     lv.colorOffsets.assign(static_cast<size_t>(nColors) + 1, 0);
+    std::vector<int64_t> boundaryCount(static_cast<size_t>(nColors), 0);
     for (int v = 0; v < nVerts; ++v)
-        if (mine(v)) lv.colorOffsets[colors[v] + 1]++;
+        if (mine(v)) {
+            lv.colorOffsets[colors[v] + 1]++;
+            boundaryCount[colors[v]] += isBoundary[v];
+        }
     for (int c = 0; c < nColors; ++c) lv.colorOffsets[c + 1] += lv.colorOffsets[c];
     lv.nOwned = static_cast<int>(lv.colorOffsets[nColors]);
     // halo slots: (owner, colour, id)
@@ -103,11 +112,13 @@ inline LocalView buildLocalView(int nVerts, const std::vector<int32_t> &colors, 
     lv.nLocal = lv.nOwned + static_cast<int>(haloOffsets.back());
     lv.slot2vert.assign(static_cast<size_t>(lv.nLocal), -1);
     {
-        std::vector<int64_t> cursor(lv.colorOffsets.begin(), lv.colorOffsets.end() - 1);
+        std::vector<int64_t> cursor(lv.colorOffsets.begin(), lv.colorOffsets.end() - 1);  // boundary vertices
+        std::vector<int64_t> icursor(static_cast<size_t>(nColors), 0);                      // interior vertices
+        for (int c = 0; c < nColors; ++c) icursor[c] = lv.colorOffsets[c] + boundaryCount[c];
         std::vector<int64_t> hcursor(haloOffsets.begin(), haloOffsets.end() - 1);
         for (int v = 0; v < nVerts; ++v) {
             if (mine(v)) {
-                const int s = static_cast<int>(cursor[colors[v]]++);
+                const int s = static_cast<int>(isBoundary[v] ? cursor[colors[v]]++ : icursor[colors[v]]++);
                 lv.slot2vert[s] = v;
                 lv.vert2slot[v] = s;
             } else if (isHalo[v]) {

@@ -26,8 +26,11 @@ def _check_consistency(sc, nranks, owner=None):
         halo = p["slot2vert"][p["n_owned"]:]
         seen[owned] += 1
         assert np.all(own[owned] == r) and np.all(own[halo] != r)
-        # owned slots sorted by (colour, id); halo by (owner, colour, id)
-        key = colors[owned].astype(np.int64) * V + owned
+        # owned slots sorted by (colour, boundary first, id); halo by (owner, colour, id)
+        boundary = np.zeros(V, bool)
+        if len(p["send_verts"]):
+            boundary[p["send_verts"]] = True
+        key = (colors[owned].astype(np.int64) * 2 + (~boundary[owned])) * V + owned
         assert np.all(np.diff(key) > 0)
         hkey = (own[halo] * (colors.max() + 1) + colors[halo]) * V + halo
         assert np.all(np.diff(hkey) > 0)
