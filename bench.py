@@ -237,7 +237,10 @@ def run_single(args):
     prof = ROOT / "profiles" / "traffic.json"
     if prof.exists():
         try:
-            roofline["traffic"] = json.loads(prof.read_text()).get(str(args.config))
+            tj = json.loads(prof.read_text())
+            roofline["traffic"] = tj.get(str(args.config))
+            # the FP64 pipe co-binds this kernel: its utilisation from the same ncu capture rides along
+            roofline["fp64_pipe_pct_ncu"] = tj.get(f"fp64_pipe_pct_{args.config}")
         except Exception:
             pass
 

@@ -682,6 +682,8 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (const char *env = getenv("SPGX_VBD_LOOKAHEAD")) grp->vbdLookahead = std::max(0, atoi(env));
             grp->vbdPdl = 1;
             if (const char *env = getenv("SPGX_VBD_PDL")) grp->vbdPdl = atoi(env) != 0;
+            grp->vbdPersist = 0;
+            if (const char *env = getenv("SPGX_VBD_PERSIST")) grp->vbdPersist = atoi(env) != 0;
             {
                 unsigned smask = 0, kmask = 0;
                 for (auto &e : grp->energies) {

@@ -68,6 +68,7 @@ struct VbdArgs {
     int nSlices;             // all colours
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
     int pdl;                 // 1: launch colour passes with programmatic stream serialization
+    int persist;             // 1: persistent warps that prefetch their next slice (vbd_stream_persist.cuh)
     VbdHaloDev halo;
 };
 

@@ -108,9 +108,10 @@ __device__ __forceinline__ void accumulateCsrEnergies(const VbdArgs &a, int slot
 
 // butterfly over the sub-lane bits (lanes of one vertex sit VW apart), inertia term, gate, solve, write
 // returns the position the vertex ends the pass with (meaningful on its sub == 0 lane)
+// mass, xi: the vertex's mass and inertial position (read by the caller; used on the valid sub == 0 lane only)
 template <int G>
-__device__ __forceinline__ V3d reduceSolveWrite(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, V3d f,
-                                                Sym3 H, double invdtSquared)
+__device__ __forceinline__ V3d reduceSolveWriteWith(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, V3d f,
+                                                    Sym3 H, double invdtSquared, double mass, const V3d &xi)
 {
     V3d xn = xo;
     constexpr int VW = 32 / G;
@@ -128,11 +129,11 @@ __device__ __forceinline__ V3d reduceSolveWrite(const VbdArgs &a, int slot, bool
     }
     if (valid && sub == 0) {
         const size_t o = 3 * static_cast<size_t>(slot);
-        const double mOverdtSquared = a.mass[slot] * invdtSquared;
+        const double mOverdtSquared = mass * invdtSquared;
         // f holds the accumulated energy gradient: force = -gradient; inertia term of vbd.cpp:109-112, :123
-        f.x = -f.x - mOverdtSquared * (xo.x - a.xInertial[o]);
-        f.y = -f.y - mOverdtSquared * (xo.y - a.xInertial[o + 1]);
-        f.z = -f.z - mOverdtSquared * (xo.z - a.xInertial[o + 2]);
+        f.x = -f.x - mOverdtSquared * (xo.x - xi.x);
+        f.y = -f.y - mOverdtSquared * (xo.y - xi.y);
+        f.z = -f.z - mOverdtSquared * (xo.z - xi.z);
         H.xx += mOverdtSquared;
         H.yy += mOverdtSquared;
         H.zz += mOverdtSquared;
@@ -146,6 +147,20 @@ __device__ __forceinline__ V3d reduceSolveWrite(const VbdArgs &a, int slot, bool
         }
     }
     return xn;
+}
+
+template <int G>
+__device__ __forceinline__ V3d reduceSolveWrite(const VbdArgs &a, int slot, bool valid, int sub, const V3d &xo, const V3d &f,
+                                                const Sym3 &H, double invdtSquared)
+{
+    double mass = 0.0;
+    V3d xi(0.0, 0.0, 0.0);
+    if (valid && sub == 0) {
+        const size_t o = 3 * static_cast<size_t>(slot);
+        mass = a.mass[slot];
+        xi = V3d(a.xInertial[o], a.xInertial[o + 1], a.xInertial[o + 2]);
+    }
+    return reduceSolveWriteWith<G>(a, slot, valid, sub, xo, f, H, invdtSquared, mass, xi);
 }
 
 // Peer-memory halo push (kernels.h: VbdHaloDev): the slice's boundary vertices go straight into the neighbours' halo
@@ -488,10 +503,18 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
 }
 
+// vbd_stream_persist.cuh (included by the translation units that instantiate the launchers)
+template <unsigned SMASK, unsigned KMASK, int G, int OCC>
+void launchStreamPersistGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream);
+
 template <unsigned SMASK, unsigned KMASK, int G>
 void launchStreamG(const VbdArgs &args, int occ, int begin, int end, int sliceBase, double invdtSquared,
                    cudaStream_t stream)
 {
+    if (args.persist) {  // persistent warps with next-slice prefetch (one occupancy variant)
+        launchStreamPersistGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream);
+        return;
+    }
     switch (occ) {
     case 3: launchStreamGO<SMASK, KMASK, G, 3>(args, begin, end, sliceBase, invdtSquared, stream); break;
     case 5: launchStreamGO<SMASK, KMASK, G, 5>(args, begin, end, sliceBase, invdtSquared, stream); break;

@@ -189,8 +189,10 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     xr, vr = osol.state()
     results = {}
     for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [
-            (f"g{l}o{o}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_OCC": str(o)}) for l in (1, 2, 4) for o in (3, 4, 5)]:
-        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_OCC"):
+            (f"g{l}o{o}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_OCC": str(o)}) for l in (1, 2, 4) for o in (3, 4, 5)] + [
+            (f"g{l}{p}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_PERSIST": "1" if p == "persist" else "0"})
+            for l in (1, 2, 4) for p in ("persist", "oneslice")]:
+        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_OCC", "SPGX_VBD_PERSIST"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -202,3 +204,6 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     for name, (x, v) in results.items():
         assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8, name
         assert _rel(x, results["csr"][0]) <= 1e-11, name
+    for l in (1, 2, 4):  # persistent warps walk the same slices in the same per-vertex order: bit-identical
+        assert np.array_equal(results[f"g{l}persist"][0], results[f"g{l}oneslice"][0]), l
+        assert np.array_equal(results[f"g{l}persist"][1], results[f"g{l}oneslice"][1]), l
