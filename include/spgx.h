@@ -40,6 +40,11 @@ extern "C" {
  *  TET_STVK          .../stvkEnergy.cpp:68                                {young, poisson}
  *  TET_SNH           .../stableNeoHookeanEnergy.cpp:64                    {young, poisson}
  *  ANCHOR            .../springAnchorEnergy.cpp:29                        {anchor.x, anchor.y, anchor.z, stiffness}
+ *  BENDING_BW        .../baraffWitkinBendingEnergy.cpp:40                 {restTheta, stiffness}
+ *  SPRING_SQUARED_CONTINUUM .../springSquaredContinuumEnergy.cpp:20       {restLength, stiffness}
+ *  TET_SSNH          .../stableSquaredNeoHookeanEnergy.cpp:34             {young, poisson}
+ *  STATIC_LOAD       spg/include/spg/sim/energy/staticLoadEnergy.h:11     {dir.x, dir.y, dir.z, stiffness}  (VBD only: its
+ *                    constraint form throws in the reference, staticLoadEnergy.cpp:8-13, and so does spgx_xpbd_step)
  */
 enum spgx_kind {
     SPGX_SPRING = 0,
@@ -52,7 +57,11 @@ enum spgx_kind {
     SPGX_TET_STVK = 7,
     SPGX_TET_SNH = 8,
     SPGX_ANCHOR = 9,
-    SPGX_KIND_COUNT = 10
+    SPGX_BENDING_BW = 10,
+    SPGX_SPRING_SQUARED_CONTINUUM = 11,
+    SPGX_TET_SSNH = 12,
+    SPGX_STATIC_LOAD = 13,
+    SPGX_KIND_COUNT = 14
 };
 
 enum spgx_solver_kind {

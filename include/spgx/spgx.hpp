@@ -105,6 +105,9 @@ SPGX_ENERGY_3(MembraneChoiEnergy, SPGX_MEMBRANE_CHOI, 3, kWeft, kWarp, kBias);
 SPGX_ENERGY_3(MembraneBaraffWitkinEnergy, SPGX_MEMBRANE_BW, 3, kWeft, kWarp, kBias);
 SPGX_ENERGY_2(StvkEnergy, SPGX_TET_STVK, 4, young, poisson);
 SPGX_ENERGY_2(StableNeoHookeanEnergy, SPGX_TET_SNH, 4, young, poisson);
+SPGX_ENERGY_2(BaraffWitkinBendingEnergy, SPGX_BENDING_BW, 4, restTheta, stiffness);    // baraffWitkinBendingEnergy.h
+SPGX_ENERGY_2(SpringSquaredContinuumEnergy, SPGX_SPRING_SQUARED_CONTINUUM, 2, restLength, stiffness);
+SPGX_ENERGY_2(StableSquaredNeoHookeanEnergy, SPGX_TET_SSNH, 4, young, poisson);
 #undef SPGX_ENERGY_2
 #undef SPGX_ENERGY_3
 
@@ -128,6 +131,17 @@ public:
 
 protected:
     unsigned long long m_anchorRevision{0};  // solvers compare it with the revision they last uploaded
+};
+
+class StaticLoadEnergy : public Energy  // staticLoadEnergy.h:7-28 (energy only: XPBD::step throws, as in the reference)
+{
+public:
+    static constexpr int s_stencilSize = 1;
+    StaticLoadEnergy() : Energy(SPGX_STATIC_LOAD, "StaticLoadEnergy") {}
+    void addStencil(std::array<int, 1> stencil, const Vector3 &loadDirection, Real stiffness)
+    {
+        push<1, 4>(stencil, {loadDirection.x, loadDirection.y, loadDirection.z, stiffness});
+    }
 };
 
 // ---- ParticleGroup (particleGroup.h:14-60) ------------------------------------------------------------------------

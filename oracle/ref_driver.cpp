@@ -27,6 +27,10 @@
 #include <spg/sim/energy/stvkEnergy.h>
 #include <spg/sim/energy/stableNeoHookeanEnergy.h>
 #include <spg/sim/energy/springAnchorEnergy.h>
+#include <spg/sim/energy/baraffWitkinBendingEnergy.h>
+#include <spg/sim/energy/springSquaredContinuumEnergy.h>
+#include <spg/sim/energy/stableSquaredNeoHookeanEnergy.h>
+#include <spg/sim/energy/staticLoadEnergy.h>
 #include <spg/sim/solver/vbd.h>
 #include <spg/sim/solver/xpbd.h>
 #include <spg/utils/graphColoring.h>
@@ -56,10 +60,14 @@ enum Kind {
     K_TET_STVK = 7,
     K_TET_SNH = 8,
     K_ANCHOR = 9,
-    K_COUNT = 10
+    K_BENDING_BW = 10,
+    K_SPRING_SQUARED_CONTINUUM = 11,
+    K_TET_SSNH = 12,
+    K_STATIC_LOAD = 13,
+    K_COUNT = 14
 };
-const int kStencilSize[K_COUNT] = {2, 2, 4, 4, 3, 3, 3, 4, 4, 1};
-const int kNumModelParams[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4};
+const int kStencilSize[K_COUNT] = {2, 2, 4, 4, 3, 3, 3, 4, 4, 1, 4, 2, 4, 1};
+const int kNumModelParams[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4};
 
 thread_local std::string g_error;
 
@@ -192,6 +200,29 @@ std::shared_ptr<spg::ParticleGroup::EnergyT> makeEnergy(int kind, int n, const i
     }
     case K_ANCHOR: {
         auto e = std::make_shared<SpringAnchorEnergy>();
+        for (int i = 0; i < n; ++i)
+            e->addStencil({st[i]}, Vector3(p[4 * i], p[4 * i + 1], p[4 * i + 2]), p[4 * i + 3]);
+        return e;
+    }
+    case K_BENDING_BW: {
+        auto e = std::make_shared<BaraffWitkinBendingEnergy>();
+        for (int i = 0; i < n; ++i)
+            e->addStencil({st[4 * i], st[4 * i + 1], st[4 * i + 2], st[4 * i + 3]}, p[2 * i], p[2 * i + 1]);
+        return e;
+    }
+    case K_SPRING_SQUARED_CONTINUUM: {
+        auto e = std::make_shared<SpringSquaredContinuumEnergy>();
+        for (int i = 0; i < n; ++i) e->addStencil({st[2 * i], st[2 * i + 1]}, p[2 * i], p[2 * i + 1]);
+        return e;
+    }
+    case K_TET_SSNH: {
+        auto e = std::make_shared<StableSquaredNeoHookeanEnergy>();
+        for (int i = 0; i < n; ++i)
+            e->addStencil({st[4 * i], st[4 * i + 1], st[4 * i + 2], st[4 * i + 3]}, p[2 * i], p[2 * i + 1]);
+        return e;
+    }
+    case K_STATIC_LOAD: {
+        auto e = std::make_shared<StaticLoadEnergy>();
         for (int i = 0; i < n; ++i)
             e->addStencil({st[i]}, Vector3(p[4 * i], p[4 * i + 1], p[4 * i + 2]), p[4 * i + 3]);
         return e;
@@ -384,7 +415,11 @@ int ref_constraints_and_gradient(void *h, int e, int stencil, double *C, double 
                   tryConstraints<MembraneBaraffWitkinEnergy>(en, g->pg, stencil, C, grad) ||
                   tryConstraints<StvkEnergy>(en, g->pg, stencil, C, grad) ||
                   tryConstraints<StableNeoHookeanEnergy>(en, g->pg, stencil, C, grad) ||
-                  tryConstraints<SpringAnchorEnergy>(en, g->pg, stencil, C, grad);
+                  tryConstraints<SpringAnchorEnergy>(en, g->pg, stencil, C, grad) ||
+                  tryConstraints<BaraffWitkinBendingEnergy>(en, g->pg, stencil, C, grad) ||
+                  tryConstraints<SpringSquaredContinuumEnergy>(en, g->pg, stencil, C, grad) ||
+                  tryConstraints<StableSquaredNeoHookeanEnergy>(en, g->pg, stencil, C, grad) ||
+                  tryConstraints<StaticLoadEnergy>(en, g->pg, stencil, C, grad);
         if (!ok) throw std::runtime_error("unsupported energy type");
     });
 }
@@ -427,7 +462,9 @@ int ref_effective_stiffness(void *h, int e, int stencil, double *K, double *A)
                   tryStiffness<MembraneChoiEnergy>(en, stencil, K, A) ||
                   tryStiffness<MembraneBaraffWitkinEnergy>(en, stencil, K, A) ||
                   tryStiffness<StvkEnergy>(en, stencil, K, A) || tryStiffness<StableNeoHookeanEnergy>(en, stencil, K, A) ||
-                  tryStiffness<SpringAnchorEnergy>(en, stencil, K, A);
+                  tryStiffness<SpringAnchorEnergy>(en, stencil, K, A) || tryStiffness<BaraffWitkinBendingEnergy>(en, stencil, K, A) ||
+                  tryStiffness<SpringSquaredContinuumEnergy>(en, stencil, K, A) ||
+                  tryStiffness<StableSquaredNeoHookeanEnergy>(en, stencil, K, A) || tryStiffness<StaticLoadEnergy>(en, stencil, K, A);
         if (!ok) throw std::runtime_error("unsupported energy type");
     });
 }
@@ -467,6 +504,12 @@ int ref_rest_data(void *h, int e, int stencil, double *out, int *n)
         } else if (auto *p = dynamic_cast<StableNeoHookeanEnergy *>(en)) {
             put3(p->inverseReferenceMats()[stencil]);
             out[(*n)++] = p->hydrostaticCorrectionTerms()[stencil];
+        } else if (auto *p = dynamic_cast<BaraffWitkinBendingEnergy *>(en)) {
+            out[(*n)++] = p->restThetas()[stencil];
+        } else if (auto *p = dynamic_cast<StableSquaredNeoHookeanEnergy *>(en)) {
+            put3(p->inverseReferenceMats()[stencil]);
+        } else if (auto *p = dynamic_cast<StaticLoadEnergy *>(en)) {
+            for (int c = 0; c < 3; ++c) out[(*n)++] = p->loadDirections()[stencil][c];
         }
     });
 }

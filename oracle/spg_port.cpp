@@ -26,11 +26,12 @@ namespace port
 {
 enum Kind {
     K_SPRING = 0, K_SPRING_CONTINUUM, K_DISCRETE_BENDING, K_QUADRATIC_BENDING, K_MEMBRANE_STVK, K_MEMBRANE_CHOI,
-    K_MEMBRANE_BW, K_TET_STVK, K_TET_SNH, K_ANCHOR, K_COUNT
+    K_MEMBRANE_BW, K_TET_STVK, K_TET_SNH, K_ANCHOR, K_BENDING_BW, K_SPRING_SQUARED_CONTINUUM, K_TET_SSNH, K_STATIC_LOAD,
+    K_COUNT
 };
-constexpr int kStencilSize[K_COUNT] = {2, 2, 4, 4, 3, 3, 3, 4, 4, 1};
-constexpr int kNumConstraints[K_COUNT] = {1, 1, 1, 3, 3, 4, 3, 2, 2, 1};
-constexpr int kNumModelParams[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4};
+constexpr int kStencilSize[K_COUNT] = {2, 2, 4, 4, 3, 3, 3, 4, 4, 1, 4, 2, 4, 1};
+constexpr int kNumConstraints[K_COUNT] = {1, 1, 1, 3, 3, 4, 3, 2, 2, 1, 1, 1, 2, 1};
+constexpr int kNumModelParams[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4};
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Forward-mode scalar with dense gradient and Hessian: external/TinyAD/include/TinyAD/Scalar.hh
@@ -325,6 +326,32 @@ inline void addStencil(Energy &e, const int32_t *st, const double *p)
         pushDiag(e, {p[3]});
         e.anchor.insert(e.anchor.end(), p, p + 3);
         break;
+    case K_BENDING_BW:  // baraffWitkinBendingEnergy.cpp:40-53
+        if (p[0] < -3.12 || p[0] > 3.12) throw std::runtime_error("Invalid restTheta");
+        e.restTheta.push_back(p[0]);
+        pushDiag(e, {p[1]});
+        break;
+    case K_SPRING_SQUARED_CONTINUUM: {  // springSquaredContinuumEnergy.cpp:20-34
+        if (p[0] <= 0) throw std::runtime_error("Zero/negative rest length invalid");
+        e.restLength.push_back(p[0]);
+        pushDiag(e, {p[1]});
+        e.K(e.Keff, e.n)[0] = p[1] * p[0];
+        e.K(e.Aeff, e.n)[0] = 1.0 / (p[1] * p[0]);
+        break;
+    }
+    case K_TET_SSNH: {  // stableSquaredNeoHookeanEnergy.cpp:34-50
+        const double young = p[0], poisson = p[1];
+        const double mu = young / (2 * (1 + poisson));
+        const double lambda = young * poisson / ((1 + poisson) * (1 - 2 * poisson)) + 1e-20;
+        pushDiag(e, {lambda, mu});
+        break;
+    }
+    case K_STATIC_LOAD: {  // staticLoadEnergy.h:11-19: direction stored normalised; `anchor` holds it
+        pushDiag(e, {p[3]});
+        const Vec3 d = normalized(Vec3{p[0], p[1], p[2]});
+        e.anchor.push_back(d.x), e.anchor.push_back(d.y), e.anchor.push_back(d.z);
+        break;
+    }
     default: throw std::runtime_error("unknown energy kind");
     }
     e.n++;
@@ -388,13 +415,22 @@ inline void prepare(Energy &e, const Group &g)
             scaleEffective(i, area);
             break;
         }
+        case K_BENDING_BW: {  // baraffWitkinBendingEnergy.cpp:55-77: no area factor, rest angle from the rest pose
+            const Vec3 x0 = pos(g.x0, s[0]), x1 = pos(g.x0, s[1]), x2 = pos(g.x0, s[2]), x3 = pos(g.x0, s[3]);
+            const Vec3 e0 = x1 - x0, e3 = x2 - x1, e4 = x3 - x1;
+            const Vec3 n1 = normalized(cross(e0, e3)), n2 = -normalized(cross(e0, e4));
+            e.restTheta[i] = std::atan2(dot(cross(n1, n2), normalized(e0)), dot(n1, n2));
+            break;
+        }
+        case K_TET_SSNH:  // stableSquaredNeoHookeanEnergy.cpp:52-78
         case K_TET_STVK:
         case K_TET_SNH: {  // stvkEnergy.cpp:84-110, stableNeoHookeanEnergy.cpp:82-108
             const Vec3 x0 = pos(g.x0, s[0]), x1 = pos(g.x0, s[1]), x2 = pos(g.x0, s[2]), x3 = pos(g.x0, s[3]);
             const Vec3 u = x1 - x0, v = x2 - x0, w = x3 - x0;
             const double Dm[9] = {u.x, v.x, w.x, u.y, v.y, w.y, u.z, v.z, w.z};
             const double volume = 1. / 6. * detN(Dm, 3, 3);
-            if (volume <= 0) throw std::runtime_error("SNH tetrahedron rest volume is not positive");
+            if (volume <= 0)
+                throw std::runtime_error(std::string(e.kind == K_TET_SSNH ? "SSNH" : "SNH") + " tetrahedron rest volume is not positive");
             if (e.DmInv.size() < 9 * static_cast<size_t>(e.n)) e.DmInv.resize(9 * static_cast<size_t>(e.n));
             inverseN(Dm, 3, e.DmInv.data() + 9 * static_cast<size_t>(i));
             scaleEffective(i, volume);
@@ -502,6 +538,31 @@ void constraints(const Energy &e, int i, const V3<T> *xs, T *C)
         C[1] = sqrt(dot(F[0], F[0]) + dot(F[1], F[1]) + dot(F[2], F[2]));
         break;
     }
+    case K_BENDING_BW: {  // baraffWitkinBendingEnergy.cpp:9-37: the three norms are passive values (:25-31)
+        const V3<T> e0 = xs[1] - xs[0], e3 = xs[2] - xs[1], e4 = xs[3] - xs[1];
+        const double e0NormInv = 1 / valueOf(norm(e0));
+        const V3<T> n1 = cross(e0, e3);
+        const double n1NormInv = 1 / valueOf(norm(n1));
+        const V3<T> n2 = -cross(e0, e4);
+        const double n2NormInv = 1 / valueOf(norm(n2));
+        const V3<T> a = scale(n1, n1NormInv), b = scale(n2, n2NormInv);
+        C[0] = atan2(dot(cross(a, b), scale(e0, e0NormInv)), dot(a, b)) - e.restTheta[i];
+        break;
+    }
+    case K_SPRING_SQUARED_CONTINUUM: {  // springSquaredContinuumEnergy.cpp:8-17
+        const V3<T> d = xs[0] - xs[1];
+        C[0] = dot(d, d) / (e.restLength[i] * e.restLength[i]) - 1.;
+        break;
+    }
+    case K_TET_SSNH: {  // stableSquaredNeoHookeanEnergy.cpp:9-31
+        V3<T> F[3];
+        deformationGradient33(xs, e.DmInv.data() + 9 * static_cast<size_t>(i), F);
+        C[0] = det3(F) - 1.0;
+        C[1] = dot(F[0], F[0]) + dot(F[1], F[1]) + dot(F[2], F[2]) - 3.0;
+        break;
+    }
+    case K_STATIC_LOAD:  // staticLoadEnergy.cpp:8-13
+        throw std::runtime_error("Constraint-based load energy not implemented");
     case K_ANCHOR: {  // springAnchorEnergy.cpp:8-19 (zero guard :16-18)
         const double *a = e.anchor.data() + 3 * static_cast<size_t>(i);
         const V3<T> d = {xs[0].x - a[0], xs[0].y - a[1], xs[0].z - a[2]};
@@ -542,6 +603,10 @@ T energyOf(const Energy &e, int i, const V3<T> *xs)
         const T hyd = det3(F) - e.alpha[i];
         const T dev = dot(F[0], F[0]) + dot(F[1], F[1]) + dot(F[2], F[2]) - 3.0;
         return 0.5 * lambda * hyd * hyd + 0.5 * mu * dev;
+    }
+    case K_STATIC_LOAD: {  // staticLoadEnergy.cpp:15-20: E = k * -(d . x)
+        const double *d = e.anchor.data() + 3 * static_cast<size_t>(i);
+        return e.K(e.Kmodel, i)[0] * -(d[0] * xs[0].x + d[1] * xs[0].y + d[2] * xs[0].z);
     }
     case K_ANCHOR: {  // springAnchorEnergy.cpp:21-26: the MODEL stiffness
         const double *a = e.anchor.data() + 3 * static_cast<size_t>(i);
@@ -943,7 +1008,7 @@ int ref_update_anchor(void *h, int e, int stencil, const double *anchor3)
 {
     return guarded([&] {
         auto &en = *static_cast<Group *>(h)->energies.at(e);
-        if (en.kind != K_ANCHOR) throw std::runtime_error("not an anchor energy");
+        if (en.kind != K_ANCHOR) throw std::runtime_error("not an anchor energy");  // (static loads share the field)
         std::copy(anchor3, anchor3 + 3, en.anchor.begin() + 3 * static_cast<size_t>(stencil));
     });
 }
@@ -1025,7 +1090,11 @@ int ref_rest_data(void *h, int e, int stencil, double *out, int *n)
         const Energy &en = *static_cast<Group *>(h)->energies.at(e);
         *n = 0;
         switch (en.kind) {
-        case K_DISCRETE_BENDING: out[(*n)++] = en.restTheta[stencil]; break;
+        case K_DISCRETE_BENDING:
+        case K_BENDING_BW: out[(*n)++] = en.restTheta[stencil]; break;
+        case K_STATIC_LOAD:
+            for (int c = 0; c < 3; ++c) out[(*n)++] = en.anchor[3 * static_cast<size_t>(stencil) + c];
+            break;
         case K_QUADRATIC_BENDING:
             for (int r = 0; r < 3; ++r)
                 for (int c = 0; c < 12; ++c) out[(*n)++] = (c % 3 == r) ? en.laplacian[4 * static_cast<size_t>(stencil) + c / 3] : 0.0;
@@ -1037,6 +1106,7 @@ int ref_rest_data(void *h, int e, int stencil, double *out, int *n)
             break;
         case K_TET_STVK:
         case K_TET_SNH:
+        case K_TET_SSNH:
             for (int k = 0; k < 9; ++k) out[(*n)++] = en.DmInv[9 * static_cast<size_t>(stencil) + k];
             if (en.kind == K_TET_SNH) out[(*n)++] = en.alpha[stencil];
             break;

@@ -37,7 +37,11 @@ static double modelRecordBytes(int kind)
     case K_MEMBRANE_BW: return 68;
     case K_TET_STVK:
     case K_TET_SNH: return 112;
-    case K_ANCHOR: return 36;
+    case K_ANCHOR:
+    case K_STATIC_LOAD: return 36;
+    case K_BENDING_BW: return 32;
+    case K_SPRING_SQUARED_CONTINUUM: return 24;
+    case K_TET_SSNH: return 112;
     default: return 0;
     }
 }

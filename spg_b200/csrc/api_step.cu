@@ -356,6 +356,8 @@ int spgx_xpbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, co
     return guarded([&] {
         requireFinalized(grp, false);
         if (iterations < 1) throw std::runtime_error("XPBD needs at least one iteration");
+        for (const auto &e : grp->energies)  // staticLoadEnergy.cpp:8-13: the reference throws from projectPosition
+            if (e.kind == K_STATIC_LOAD) throw std::runtime_error("Constraint-based load energy not implemented");
         runStep(grp, grp->solverKind, dt, nsubsteps, iterations, gravity, nFrames, sync);
     });
 }

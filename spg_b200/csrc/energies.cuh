@@ -25,7 +25,12 @@ enum Kind : int {
     K_TET_STVK = 7,
     K_TET_SNH = 8,
     K_ANCHOR = 9,
-    K_COUNT = 10
+    // the remaining particle energies (generic dual-number path in both solvers)
+    K_BENDING_BW = 10,
+    K_SPRING_SQUARED_CONTINUUM = 11,
+    K_TET_SSNH = 12,
+    K_STATIC_LOAD = 13,
+    K_COUNT = 14
 };
 
 template <int KIND>
@@ -402,6 +407,85 @@ struct EnergyKind<K_ANCHOR> {
     SPGX_HD static double alpha(const double *p, int, int) { return p[4]; }
 };
 
+// ---- BaraffWitkinBendingEnergy (baraffWitkinBendingEnergy.cpp:9-37): the dihedral angle with the three norms taken
+// as PASSIVE values (".val", :25-31: no derivative flows through them).  p = {theta0, k, 1/k}; the effective stiffness
+// is the model stiffness (no area factor, :68-69), theta0 is recomputed from the rest pose (:71-74)
+template <>
+struct EnergyKind<K_BENDING_BW> {
+    static constexpr int S = 4, NC = 1, NP = 3, NMODEL = 2;
+    static constexpr bool kDirectEnergy = false;
+    template <class T>
+    SPGX_HD static void constraints(const V3<T> *x, const double *p, T *C)
+    {
+        const V3<T> e0 = x[1] - x[0];
+        const V3<T> e3 = x[2] - x[1];
+        const V3<T> e4 = x[3] - x[1];
+        const double e0NormInv = 1.0 / value_of(norm(e0));
+        const V3<T> n1 = cross(e0, e3);
+        const double n1NormInv = 1.0 / value_of(norm(n1));
+        const V3<T> n2 = -cross(e0, e4);
+        const double n2NormInv = 1.0 / value_of(norm(n2));
+        const V3<T> a = n1 * n1NormInv, b = n2 * n2NormInv;
+        C[0] = datan2(dot(cross(a, b), e0 * e0NormInv), dot(a, b)) - p[0];
+    }
+    SPGX_HD static double K(const double *p, int, int) { return p[1]; }
+    SPGX_HD static double alpha(const double *p, int, int) { return p[2]; }
+};
+
+// ---- SpringSquaredContinuumEnergy (springSquaredContinuumEnergy.cpp:8-17): C = |x - y|^2 / L0^2 - 1.
+// p = {L0, k L0, 1/(k L0)}
+template <>
+struct EnergyKind<K_SPRING_SQUARED_CONTINUUM> {
+    static constexpr int S = 2, NC = 1, NP = 3, NMODEL = 2;
+    static constexpr bool kDirectEnergy = false;
+    template <class T>
+    SPGX_HD static void constraints(const V3<T> *x, const double *p, T *C)
+    {
+        C[0] = squaredNorm(x[0] - x[1]) / (p[0] * p[0]) - 1.0;
+    }
+    SPGX_HD static double K(const double *p, int, int) { return p[1]; }
+    SPGX_HD static double alpha(const double *p, int, int) { return p[2]; }
+};
+
+// ---- StableSquaredNeoHookeanEnergy (stableSquaredNeoHookeanEnergy.cpp:9-31): C = (det F - 1, tr(F^T F) - 3), energy
+// through the default 1/2 C^T K C.  p = {Dinv(9), lambda V, mu V, 1/(lambda V), 1/(mu V)} with the Lame lambda + 1e-20
+template <>
+struct EnergyKind<K_TET_SSNH> {
+    static constexpr int S = 4, NC = 2, NP = 13, NMODEL = 2;
+    static constexpr bool kDirectEnergy = false;
+    template <class T>
+    SPGX_HD static void constraints(const V3<T> *x, const double *p, T *C)
+    {
+        V3<T> F0, F1, F2;
+        tetF(x, p, F0, F1, F2);
+        C[0] = det3(F0, F1, F2) - 1.0;
+        C[1] = dot(F0, F0) + dot(F1, F1) + dot(F2, F2) - 3.0;
+    }
+    SPGX_HD static double K(const double *p, int i, int j) { return i == j ? p[9 + i] : 0.0; }
+    SPGX_HD static double alpha(const double *p, int i, int j) { return i == j ? p[11 + i] : 0.0; }
+};
+
+// ---- StaticLoadEnergy (staticLoadEnergy.cpp:15-20, staticLoadEnergy.h:11-19): E = -k (d . x), d normalised at
+// addStencil.  Energy only: its constraint form throws in the reference (:8-13), so XPBD rejects it (api_step.cu).
+// p = {dx, dy, dz, k, 1/k}
+template <>
+struct EnergyKind<K_STATIC_LOAD> {
+    static constexpr int S = 1, NC = 1, NP = 5, NMODEL = 4;
+    static constexpr bool kDirectEnergy = true;
+    template <class T>
+    SPGX_HD static void constraints(const V3<T> *, const double *, T *C)
+    {
+        C[0] = T(0.0);  // never reached: spgx_xpbd_step refuses groups that hold this kind
+    }
+    template <class T>
+    SPGX_HD static T energy(const V3<T> *x, const double *p)
+    {
+        return p[3] * -(p[0] * x[0].x + p[1] * x[0].y + p[2] * x[0].z);
+    }
+    SPGX_HD static double K(const double *p, int, int) { return p[3]; }
+    SPGX_HD static double alpha(const double *p, int, int) { return p[4]; }
+};
+
 // E(x) of one stencil for any scalar type: the direct energy when the kind has one, otherwise
 // 1/2 C^T K_eff C (energy.h:336-347)
 template <int KIND, class T>
@@ -440,11 +524,13 @@ SPGX_HD int kindStencilSize(int kind)
 {
     switch (kind) {
     case K_SPRING:
-    case K_SPRING_CONTINUUM: return 2;
+    case K_SPRING_CONTINUUM:
+    case K_SPRING_SQUARED_CONTINUUM: return 2;
     case K_MEMBRANE_STVK:
     case K_MEMBRANE_CHOI:
     case K_MEMBRANE_BW: return 3;
-    case K_ANCHOR: return 1;
+    case K_ANCHOR:
+    case K_STATIC_LOAD: return 1;
     default: return 4;
     }
 }

@@ -88,13 +88,13 @@ inline void membraneRest(const double *x0, const int *st, const char *name, doub
         throw std::runtime_error(std::string("Rest area of membrane ") + name + " triangle is not positive");
 }
 
-inline void tetRest(const double *x0, const int *st, double Dinv[9], double &volume)
+inline void tetRest(const double *x0, const int *st, double Dinv[9], double &volume, const char *name = "SNH")
 {
     const H3 a = at(x0, st[0]);
     const H3 u = sub(at(x0, st[1]), a), v = sub(at(x0, st[2]), a), w = sub(at(x0, st[3]), a);
     const double m[9] = {u.x, v.x, w.x, u.y, v.y, w.y, u.z, v.z, w.z};
     volume = 1. / 6. * det3rm(m);
-    if (volume <= 0) throw std::runtime_error("SNH tetrahedron rest volume is not positive");
+    if (volume <= 0) throw std::runtime_error(std::string(name) + " tetrahedron rest volume is not positive");
     double det;
     inverse3(m, Dinv, det);
 }
@@ -224,23 +224,64 @@ inline void prepareStencil(int kind, const int *st, const double *model, const d
         p[4] = 1.0 / model[3];
         break;
     }
+    case K_BENDING_BW: {  // baraffWitkinBendingEnergy.cpp:40-77: stiffness as given, rest angle from the rest pose
+        if (model[0] < -3.12 || model[0] > 3.12) throw std::runtime_error("Invalid restTheta");
+        const H3 x0p = at(x0, st[0]), x1p = at(x0, st[1]), x2p = at(x0, st[2]), x3p = at(x0, st[3]);
+        const H3 e0 = sub(x1p, x0p), e3 = sub(x2p, x1p), e4 = sub(x3p, x1p);
+        const H3 n1 = normalizedH(crossH(e0, e3));
+        const H3 c2 = normalizedH(crossH(e0, e4));
+        const H3 n2 = {-c2.x, -c2.y, -c2.z};
+        p[0] = std::atan2(dotH(crossH(n1, n2), normalizedH(e0)), dotH(n1, n2));
+        p[1] = model[1];
+        p[2] = 1.0 / model[1];
+        break;
+    }
+    case K_SPRING_SQUARED_CONTINUUM: {  // springSquaredContinuumEnergy.cpp:20-34
+        if (model[0] <= 0) throw std::runtime_error("Zero/negative rest length invalid");
+        p[0] = model[0];
+        p[1] = model[1] * model[0];
+        p[2] = 1.0 / p[1];
+        break;
+    }
+    case K_TET_SSNH: {  // stableSquaredNeoHookeanEnergy.cpp:34-78 (Lame parameters, lambda + 1e-20)
+        const double young = model[0], poisson = model[1];
+        const double mu = young / (2 * (1 + poisson));
+        const double lambda = young * poisson / ((1 + poisson) * (1 - 2 * poisson)) + 1e-20;
+        double volume;
+        tetRest(x0, st, p, volume, "SSNH");
+        const double invdet = 1.0 / (lambda * mu);
+        p[9] = lambda * volume;
+        p[10] = mu * volume;
+        p[11] = (mu * invdet) / volume;
+        p[12] = (lambda * invdet) / volume;
+        break;
+    }
+    case K_STATIC_LOAD: {  // staticLoadEnergy.h:11-19: the direction is normalised (Eigen normalized(): z > 0 guard)
+        const H3 d = normalizedH({model[0], model[1], model[2]});
+        p[0] = d.x;
+        p[1] = d.y;
+        p[2] = d.z;
+        p[3] = model[3];
+        p[4] = 1.0 / model[3];
+        break;
+    }
     default: throw std::runtime_error("unknown energy kind");
     }
 }
 
 inline int kindNumParams(int kind)
 {
-    static const int np[K_COUNT] = {3, 3, 3, 6, 10, 12, 10, 13, 14, 5};
+    static const int np[K_COUNT] = {3, 3, 3, 6, 10, 12, 10, 13, 14, 5, 3, 3, 13, 5};
     return (kind >= 0 && kind < K_COUNT) ? np[kind] : -1;
 }
 inline int kindNumModelParams(int kind)
 {
-    static const int nm[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4};
+    static const int nm[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4};
     return (kind >= 0 && kind < K_COUNT) ? nm[kind] : -1;
 }
 inline int kindNumConstraints(int kind)
 {
-    static const int nc[K_COUNT] = {1, 1, 1, 3, 3, 4, 3, 2, 2, 1};
+    static const int nc[K_COUNT] = {1, 1, 1, 3, 3, 4, 3, 2, 2, 1, 1, 1, 2, 1};
     return (kind >= 0 && kind < K_COUNT) ? nc[kind] : -1;
 }
 }  // namespace spgx

@@ -161,6 +161,10 @@ __global__ void evalVertexKernel(int kind, const double *x, const int32_t *ids, 
     case K_TET_STVK: evalOne<K_TET_STVK>(x, ids, rec, local, out12, fast); break;
     case K_TET_SNH: evalOne<K_TET_SNH>(x, ids, rec, local, out12, fast); break;
     case K_ANCHOR: evalOne<K_ANCHOR>(x, ids, rec, local, out12, fast); break;
+    case K_BENDING_BW: evalOne<K_BENDING_BW>(x, ids, rec, local, out12, fast); break;
+    case K_SPRING_SQUARED_CONTINUUM: evalOne<K_SPRING_SQUARED_CONTINUUM>(x, ids, rec, local, out12, fast); break;
+    case K_TET_SSNH: evalOne<K_TET_SSNH>(x, ids, rec, local, out12, fast); break;
+    case K_STATIC_LOAD: evalOne<K_STATIC_LOAD>(x, ids, rec, local, out12, fast); break;
     default: break;
     }
 }

@@ -103,6 +103,10 @@ __device__ __forceinline__ void accumulateCsrEnergies(const VbdArgs &a, int slot
         accumulateKindIfPresent<KMASK, K_TET_STVK>(en, a.x, slot, sub, G, g, H);
         accumulateKindIfPresent<KMASK, K_TET_SNH>(en, a.x, slot, sub, G, g, H);
         accumulateKindIfPresent<KMASK, K_ANCHOR>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_BENDING_BW>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_SPRING_SQUARED_CONTINUUM>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_TET_SSNH>(en, a.x, slot, sub, G, g, H);
+        accumulateKindIfPresent<KMASK, K_STATIC_LOAD>(en, a.x, slot, sub, G, g, H);
     }
 }
 

@@ -182,6 +182,9 @@ __global__ void evalConstraintsKernel(int kind, const double *x, const int32_t *
     case K_TET_STVK: evalConstraintsOne<K_TET_STVK>(x, ids, rec, outC, outGrad); break;
     case K_TET_SNH: evalConstraintsOne<K_TET_SNH>(x, ids, rec, outC, outGrad); break;
     case K_ANCHOR: evalConstraintsOne<K_ANCHOR>(x, ids, rec, outC, outGrad); break;
+    case K_BENDING_BW: evalConstraintsOne<K_BENDING_BW>(x, ids, rec, outC, outGrad); break;
+    case K_SPRING_SQUARED_CONTINUUM: evalConstraintsOne<K_SPRING_SQUARED_CONTINUUM>(x, ids, rec, outC, outGrad); break;
+    case K_TET_SSNH: evalConstraintsOne<K_TET_SSNH>(x, ids, rec, outC, outGrad); break;
     default: break;
     }
 }
@@ -213,6 +216,11 @@ void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *s
     case K_TET_STVK: launchKind<K_TET_STVK>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
     case K_TET_SNH: launchKind<K_TET_SNH>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
     case K_ANCHOR: launchKind<K_ANCHOR>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
+    case K_BENDING_BW: launchKind<K_BENDING_BW>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
+    case K_SPRING_SQUARED_CONTINUUM:
+        launchKind<K_SPRING_SQUARED_CONTINUUM>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
+        break;
+    case K_TET_SSNH: launchKind<K_TET_SSNH>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
     default: break;
     }
 }

@@ -18,10 +18,12 @@ import numpy as np
 
 K_SPRING, K_SPRING_CONTINUUM, K_DISCRETE_BENDING, K_QUADRATIC_BENDING = 0, 1, 2, 3
 K_MEMBRANE_STVK, K_MEMBRANE_CHOI, K_MEMBRANE_BW, K_TET_STVK, K_TET_SNH, K_ANCHOR = 4, 5, 6, 7, 8, 9
+K_BENDING_BW, K_SPRING_SQUARED_CONTINUUM, K_TET_SSNH, K_STATIC_LOAD = 10, 11, 12, 13
 KIND_NAMES = ["spring", "spring_continuum", "discrete_bending", "quadratic_bending", "membrane_stvk",
-              "membrane_choi", "membrane_bw", "tet_stvk", "tet_snh", "anchor"]
-STENCIL_SIZE = [2, 2, 4, 4, 3, 3, 3, 4, 4, 1]
-NUM_MODEL_PARAMS = [2, 2, 2, 2, 2, 3, 3, 2, 2, 4]
+              "membrane_choi", "membrane_bw", "tet_stvk", "tet_snh", "anchor", "bending_bw", "spring_squared_continuum",
+              "tet_ssnh", "static_load"]
+STENCIL_SIZE = [2, 2, 4, 4, 3, 3, 3, 4, 4, 1, 4, 2, 4, 1]
+NUM_MODEL_PARAMS = [2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4]
 
 
 @dataclass
@@ -100,7 +102,7 @@ def triangle_edges(faces: np.ndarray):
 def cloth(n_rows: int, n_cols: int, membrane: int = K_MEMBRANE_STVK, bending: int = K_DISCRETE_BENDING) -> Scene:
     """createCloth(mass=1, 1x1, n_rows x n_cols, membrane, bending) (apps/solverCompare.cpp:367-498).
 
-    `membrane` may also be K_SPRING / K_SPRING_CONTINUUM: a spring of stiffness 1e2 on every mesh edge with its
+    `membrane` may also be K_SPRING / K_SPRING_CONTINUUM / K_SPRING_SQUARED_CONTINUUM: a spring of stiffness 1e2 on every mesh edge with its
     rest length from the rest pose (the BASELINE config-2 scene, built through the public API as SURVEY 8d says).
     Energies in insertion order: bending, membrane, anchors (2 corner anchors, k = 1e5, at current positions)."""
     verts, verts0, faces = triangle_square_mesh(n_rows, n_cols)
@@ -120,7 +122,7 @@ def cloth(n_rows: int, n_cols: int, membrane: int = K_MEMBRANE_STVK, bending: in
     bend_p = np.tile(np.array([0.0, 1e-2]), (bend_st.shape[0], 1))
     scene = Scene(verts, verts0, mass, name=f"cloth{n_rows}x{n_cols}")
     scene.energies.append(SceneEnergy(bending, bend_st, bend_p))
-    if membrane in (K_SPRING, K_SPRING_CONTINUUM):
+    if membrane in (K_SPRING, K_SPRING_CONTINUUM, K_SPRING_SQUARED_CONTINUUM):
         d = verts0[edges[:, 0]] - verts0[edges[:, 1]]
         rest = np.sqrt(d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2])
         mem_p = np.stack([rest, np.full(rest.shape, 1e2)], 1)

@@ -29,12 +29,26 @@ def fixtures():
     for kind in (S.K_SPRING, S.K_SPRING_CONTINUUM):
         out.append((kind, x[:2], x0[:2], [0, 1], [0.9, 5.0]))
     out.append((S.K_ANCHOR, x[:1], x0[:1], [0], [0.2, -0.1, 0.3, 50.0]))
+    # SURVEY.md 8f rank 1 (appended: the indices of the fixtures above are part of the golden keys)
+    out.append((S.K_BENDING_BW, x, x0, [0, 1, 2, 3], [0.1, 0.7]))
+    out.append((S.K_SPRING_SQUARED_CONTINUUM, x[:2], x0[:2], [0, 1], [0.9, 5.0]))
+    out.append((S.K_TET_SSNH, t, t0, [0, 1, 2, 3], [10.0, 0.3]))
+    out.append((S.K_STATIC_LOAD, x[:1], x0[:1], [0], [0.3, -2.0, 0.5, 7.0]))
     return out
 
 
 def fixture_scene(kind, x, x0, st, p):
     sc = S.Scene(np.array(x, float).copy(), np.array(x0, float).copy(), np.ones(len(x)))
     sc.energies.append(S.SceneEnergy(kind, np.array([st], np.int32), np.array([p], float)))
+    return sc
+
+
+def beam_with_load(kind):
+    """a tet beam whose free end face is pulled sideways by a StaticLoadEnergy (energy-only kind: VBD)"""
+    sc = S.tet_beam(5, 3, 3, kind)
+    ids = np.arange(sc.n_vertices - 9, sc.n_vertices, dtype=np.int32)
+    p = np.tile(np.array([0.2, 0.0, 1.0, 0.05]), (ids.size, 1))
+    sc.energies.append(S.SceneEnergy(S.K_STATIC_LOAD, ids[:, None].copy(), p))
     return sc
 
 
@@ -46,6 +60,10 @@ STEP_CASES = {
     "vbd_snh_beam": (lambda: S.tet_beam(5, 3, 3, S.K_TET_SNH), 0, 1, 20, 1),
     "vbd_stvk_beam": (lambda: S.tet_beam(5, 3, 3, S.K_TET_STVK), 0, 1, 20, 1),
     "xpbd_snh_beam": (lambda: S.tet_beam(5, 3, 3, S.K_TET_SNH), 1, 10, 1, 1),
+    "vbd_cloth_bw": (lambda: S.cloth(11, 9, S.K_MEMBRANE_BW, S.K_BENDING_BW), 0, 1, 8, 1),
+    "xpbd_cloth_bw_sqspring": (lambda: S.cloth(11, 9, S.K_SPRING_SQUARED_CONTINUUM, S.K_BENDING_BW), 1, 10, 1, 1),
+    "vbd_ssnh_beam_load": (lambda: beam_with_load(S.K_TET_SSNH), 0, 1, 15, 1),
+    "xpbd_ssnh_beam": (lambda: S.tet_beam(5, 3, 3, S.K_TET_SSNH), 1, 10, 1, 1),
 }
 COLOR_CASES = {
     "cloth16": lambda: S.cloth(16, 16),
@@ -65,9 +83,10 @@ def main():
             f, h = og.vertex_force_hessian(0, 0, local)
             g[f"fix{i}_k{kind}_f{local}"] = f
             g[f"fix{i}_k{kind}_h{local}"] = h
-        c, gc = og.constraints(0, 0)
-        g[f"fix{i}_k{kind}_c"] = c
-        g[f"fix{i}_k{kind}_gc"] = gc
+        if kind != S.K_STATIC_LOAD:  # its constraint form throws (staticLoadEnergy.cpp:8-13)
+            c, gc = og.constraints(0, 0)
+            g[f"fix{i}_k{kind}_c"] = c
+            g[f"fix{i}_k{kind}_gc"] = gc
     for name, build in COLOR_CASES.items():
         sc = build()
         sets = [e.stencils for e in sc.energies]

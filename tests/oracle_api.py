@@ -22,8 +22,8 @@ _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
 _lp = C.POINTER(C.c_int64)
 
-STENCIL_SIZE = [2, 2, 4, 4, 3, 3, 3, 4, 4, 1]
-NUM_CONSTRAINTS = [1, 1, 1, 3, 3, 4, 3, 2, 2, 1]
+STENCIL_SIZE = [2, 2, 4, 4, 3, 3, 3, 4, 4, 1, 4, 2, 4, 1]
+NUM_CONSTRAINTS = [1, 1, 1, 3, 3, 4, 3, 2, 2, 1, 1, 1, 2, 1]
 
 
 def _f64(a):

@@ -50,14 +50,15 @@ def _compare_group(ctx, oracle, sc, solver_kind, n_samples=12):
                                               (S.K_SPRING, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_CHOI, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_BW, S.K_DISCRETE_BENDING),
-                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING)])
+                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING),
+                                              (S.K_SPRING_SQUARED_CONTINUUM, S.K_BENDING_BW)])
 @pytest.mark.parametrize("solver_kind", [api.SPGX_VBD, api.SPGX_XPBD])
 def test_cloth_elements(ctx, oracle, membrane, bending, solver_kind):
     sc = _perturb(S.cloth(8, 8, membrane, bending), 0.02)
     _compare_group(ctx, oracle, sc, solver_kind)
 
 
-@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK])
+@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK, S.K_TET_SSNH])
 def test_tet_elements(ctx, oracle, kind):
     sc = _perturb(S.tet_beam(5, 3, 3, kind), 0.03)
     _compare_group(ctx, oracle, sc, api.SPGX_VBD)

@@ -39,7 +39,9 @@ def test_vbd_structure_bit_exact(ctx, oracle, n):
                                               (S.K_MEMBRANE_CHOI, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_BW, S.K_DISCRETE_BENDING),
                                               (S.K_SPRING, S.K_QUADRATIC_BENDING),
-                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING)])
+                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING),
+                                              (S.K_SPRING_SQUARED_CONTINUUM, S.K_BENDING_BW),
+                                              (S.K_MEMBRANE_STVK, S.K_BENDING_BW)])
 def test_vbd_cloth_one_substep(ctx, oracle, membrane, bending):
     sc = S.cloth(12, 12, membrane, bending)
     g, og, osol = _vbd_pair(ctx, oracle, sc, 1, 10)
@@ -65,7 +67,7 @@ def test_vbd_config1_cloth64(ctx, oracle):
     assert drift[-1][0] <= 1e-7, drift   # bounded drift over N frames
 
 
-@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK])
+@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK, S.K_TET_SSNH])
 def test_vbd_tet_beam(ctx, oracle, kind):
     sc = S.tet_beam(9, 3, 3, kind)
     g, og, osol = _vbd_pair(ctx, oracle, sc, 2, 20)
@@ -129,7 +131,8 @@ def test_xpbd_structure_bit_exact(ctx, oracle, n):
                                               (S.K_MEMBRANE_STVK, S.K_DISCRETE_BENDING),
                                               (S.K_MEMBRANE_CHOI, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_BW, S.K_DISCRETE_BENDING),
-                                              (S.K_SPRING_CONTINUUM, S.K_QUADRATIC_BENDING)])
+                                              (S.K_SPRING_CONTINUUM, S.K_QUADRATIC_BENDING),
+                                              (S.K_SPRING_SQUARED_CONTINUUM, S.K_BENDING_BW)])
 def test_xpbd_cloth(ctx, oracle, membrane, bending):
     """config-2 style: 20 small steps per frame, one projection pass each."""
     sc = S.cloth(16, 16, membrane, bending)
@@ -141,7 +144,7 @@ def test_xpbd_cloth(ctx, oracle, membrane, bending):
     assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8
 
 
-@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK])
+@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK, S.K_TET_SSNH])
 def test_xpbd_tets(ctx, oracle, kind):
     sc = S.tet_beam(5, 3, 3, kind)
     g, og, osol = _xpbd_pair(ctx, oracle, sc, 10)
@@ -207,3 +210,25 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     for l in (1, 2, 4):  # persistent warps walk the same slices in the same per-vertex order: bit-identical
         assert np.array_equal(results[f"g{l}persist"][0], results[f"g{l}oneslice"][0]), l
         assert np.array_equal(results[f"g{l}persist"][1], results[f"g{l}oneslice"][1]), l
+
+
+def test_static_load_vbd_and_xpbd_refusal(ctx, oracle):
+    """StaticLoadEnergy is energy-only: VBD matches the reference, XPBD throws the reference's message
+    (staticLoadEnergy.cpp:8-13) through the C ABI."""
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent / "golden"))
+    import make_golden as MG
+    sc = MG.beam_with_load(S.K_TET_SSNH)
+    g, og, osol = _vbd_pair(ctx, oracle, sc, 1, 15)
+    g.vbd_step(0.01, 1, 15)
+    osol.step(1)
+    x, v = g.download()
+    xr, vr = osol.state()
+    assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8
+    g.close()
+    g2 = api.Group.from_scene(ctx, sc)
+    g2.finalize(api.SPGX_XPBD)
+    with pytest.raises(api.SpgxError, match="Constraint-based load energy not implemented"):
+        g2.xpbd_step(0.01, 4, 1)
+    g2.close()

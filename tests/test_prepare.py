@@ -23,9 +23,9 @@ def _check_energy(og, sc, e):
         rest = og.rest_data(e, i)
         r = rec[i]
         k = en.kind
-        if k in (S.K_SPRING, S.K_SPRING_CONTINUUM):
+        if k in (S.K_SPRING, S.K_SPRING_CONTINUUM, S.K_SPRING_SQUARED_CONTINUUM):
             _close(r, [en.params[i, 0], K[0, 0], A[0, 0]])
-        elif k == S.K_DISCRETE_BENDING:
+        elif k in (S.K_DISCRETE_BENDING, S.K_BENDING_BW):
             _close(r, [rest[0], K[0, 0], A[0, 0]])
         elif k == S.K_QUADRATIC_BENDING:
             L = rest.reshape(3, 12)
@@ -46,7 +46,7 @@ def _check_energy(og, sc, e):
             _close(r[:4], rest)
             _close(r[4:7], np.diag(K))
             _close(r[7:10], np.diag(A))
-        elif k == S.K_TET_STVK:
+        elif k in (S.K_TET_STVK, S.K_TET_SSNH):
             _close(r[:9], rest[:9])
             _close(r[9:11], np.diag(K))
             _close(r[11:13], np.diag(A))
@@ -57,13 +57,16 @@ def _check_energy(og, sc, e):
             _close(r[13], rest[9])
         elif k == S.K_ANCHOR:
             _close(r, list(en.params[i]) + [A[0, 0]])
+        elif k == S.K_STATIC_LOAD:
+            _close(r, list(rest[:3]) + [K[0, 0], A[0, 0]])
 
 
 @pytest.mark.parametrize("membrane,bending", [(S.K_MEMBRANE_STVK, S.K_DISCRETE_BENDING),
                                               (S.K_SPRING, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_CHOI, S.K_QUADRATIC_BENDING),
                                               (S.K_MEMBRANE_BW, S.K_DISCRETE_BENDING),
-                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING)])
+                                              (S.K_SPRING_CONTINUUM, S.K_DISCRETE_BENDING),
+                                              (S.K_SPRING_SQUARED_CONTINUUM, S.K_BENDING_BW)])
 def test_cloth_records(ref_oracle, membrane, bending):
     sc = S.cloth(9, 7, membrane, bending)
     og = oracle_api.OracleGroup(ref_oracle, sc)
@@ -78,12 +81,22 @@ def test_stvk_membrane_with_poisson(ref_oracle):
     _check_energy(og, sc, 1)
 
 
-@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK])
+@pytest.mark.parametrize("kind", [S.K_TET_SNH, S.K_TET_STVK, S.K_TET_SSNH])
 def test_beam_records(ref_oracle, kind):
     sc = S.tet_beam(5, 3, 3, kind)
     og = oracle_api.OracleGroup(ref_oracle, sc)
     for e in range(2):
         _check_energy(og, sc, e)
+
+
+def test_static_load_records(ref_oracle):
+    import sys
+    from pathlib import Path
+    sys.path.insert(0, str(Path(__file__).resolve().parent / "golden"))
+    import make_golden as MG
+    sc = MG.beam_with_load(S.K_TET_SSNH)
+    og = oracle_api.OracleGroup(ref_oracle, sc)
+    _check_energy(og, sc, 2)
 
 
 @pytest.mark.parametrize("kind,stencil,params,x0,msg", [
@@ -94,6 +107,9 @@ def test_beam_records(ref_oracle, kind):
     (S.K_MEMBRANE_STVK, [[0, 1, 2]], [[1.0, 0.0]], [[0, 0, 0], [1, 0, 0], [0, 1, 1]], "coordinate z=0"),
     (S.K_MEMBRANE_CHOI, [[0, 2, 1]], [[1.0, 1.0, 1.0]], [[0, 0, 0], [1, 0, 0], [0, 1, 0]], "not positive"),
     (S.K_TET_SNH, [[0, 2, 1, 3]], [[1.0, 0.3]], [[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], "not positive"),
+    (S.K_TET_SSNH, [[0, 2, 1, 3]], [[1.0, 0.3]], [[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], "SSNH tetrahedron"),
+    (S.K_BENDING_BW, [[0, 1, 2, 3]], [[-3.13, 1.0]], [[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, -1, 0]], "restTheta"),
+    (S.K_SPRING_SQUARED_CONTINUUM, [[0, 1]], [[0.0, 1.0]], [[0, 0, 0], [1, 0, 0]], "rest length"),
 ])
 def test_validation_errors_match_reference(ref_oracle, kind, stencil, params, x0, msg):
     """Same std::runtime_error conditions as the reference's addStencil / preparePrecomputations."""
