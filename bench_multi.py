@@ -14,6 +14,7 @@ from __future__ import annotations
 
 import json
 import os
+import sys
 import time
 
 import numpy as np
@@ -56,7 +57,11 @@ def run_multi(args):
     if halo == "p2p":
         # CUDA IPC handles all-gathered with torch.distributed; from here on the colour-pass kernel stores boundary
         # vertices straight into the neighbours' halo slots and synchronises through event counters in peer memory
-        g.connect_peers(dist)
+        try:
+            g.connect_peers(dist)
+        except api.SpgxError as e:  # raised on EVERY rank when any rank cannot connect: all keep the NCCL exchange
+            if rank == 0:
+                print(f"peer-memory exchange unavailable ({e}); using ncclSend/ncclRecv", file=sys.stderr, flush=True)
     halo_name = {api.SPGX_HALO_NCCL: "ncclSend/ncclRecv per colour, captured in the step graph",
                  api.SPGX_HALO_P2P: "peer-memory stores from the colour-pass kernel + event counters over NVLink (no NCCL on the data path)",
                  api.SPGX_HALO_NONE: "none"}[g.halo_mode()]

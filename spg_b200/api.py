@@ -273,7 +273,18 @@ class Group:
         """Collective: all-gather the export blobs over `dist` (torch.distributed) and connect; returns the halo mode."""
         blobs = [None] * dist.get_world_size()
         dist.all_gather_object(blobs, self.p2p_export())
-        self.p2p_connect(blobs)
+        err = None
+        try:
+            self.p2p_connect(blobs)
+        except SpgxError as e:  # keep the collectives below matched on every rank
+            err = str(e)
+        errs = [None] * dist.get_world_size()
+        dist.all_gather_object(errs, err)
+        if any(e is not None for e in errs):
+            # every rank must run the same exchange: one failure (e.g. CUDA IPC unavailable) sends all back to NCCL
+            check(lib.spgx_group_p2p_disconnect(self.handle))
+            dist.barrier()
+            raise SpgxError("peer-memory exchange unavailable: " + "; ".join(f"rank {r}: {e}" for r, e in enumerate(errs) if e))
         dist.barrier()
         return self.halo_mode()
 

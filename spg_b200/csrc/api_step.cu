@@ -114,6 +114,22 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const double invdt = 1 / dt;
     const bool serial = grp->solverKind == SPGX_XPBD_SERIAL;
     const bool useLambda = iters > 1;
+    // graph mode: the whole frame is one cooperative launch with grid barriers between the passes; plain-launch mode
+    // keeps one kernel per pass (and the per-phase events)
+    if (!serial && !timePhases && grp->graphMode && grp->xpbdFused && grp->d_xpbdPasses.count > 0) {
+        XpbdFusedArgs fa{};
+        fa.x = grp->d_x.ptr, fa.v = grp->d_v.ptr, fa.xOld = grp->d_xOld.ptr, fa.invMass = grp->d_invMass.ptr;
+        fa.n3 = 3LL * grp->nLocal;
+        fa.passes = grp->d_xpbdPasses.ptr;
+        fa.nPasses = static_cast<int>(grp->d_xpbdPasses.count);
+        fa.nsub = nsub, fa.iters = iters, fa.useLambda = useLambda ? 1 : 0;
+        fa.dt = dt, fa.invdt = invdt, fa.gx = grp->graphKey.g[0], fa.gy = grp->graphKey.g[1], fa.gz = grp->graphKey.g[2];
+        if (launchXpbdFused(fa, st)) {
+            grp->launchCounter++;
+            return;
+        }
+        cudaGetLastError();  // not co-schedulable here: fall through to one launch per pass
+    }
     for (int s = 0; s < nsub; ++s) {
         launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nLocal, dt, grp->graphKey.g, st);
         grp->launchCounter++;

@@ -202,6 +202,8 @@ struct spgx_group {
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)
     double uniqueNeighbourSum = 0;  // sum over vertices of the number of distinct stencil neighbours
 
+    spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
+    int xpbdFused = 0;
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
     spgx::DevBuf<int32_t> d_slot2vert;
     spgx::DevBuf<double> d_eval;

@@ -97,6 +97,27 @@ void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, 
 void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *stencils, const double *records,
                     double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream);
 
+// One (energy, colour) projection pass of a substep, as the fused XPBD kernel walks them (xpbd.cu)
+struct XpbdPassDev {
+    int kind, begin, end, nc;
+    const int32_t *stencils;
+    const double *records;
+    double *lambda;  // NC doubles per stencil of the energy (used when iterations > 1)
+};
+struct XpbdFusedArgs {
+    double *x, *v, *xOld;
+    const double *invMass;
+    long long n3;               // 3 * vertices
+    const XpbdPassDev *passes;  // device array, reference order: energies in insertion order, colours ascending
+    int nPasses, nsub, iters, useLambda;
+    double dt, invdt, gx, gy, gz;  // dt of one substep
+};
+// XPBD::step (xpbd.cpp:44-123) as ONE cooperative launch: predict, every (energy, colour) pass and finalize of every
+// substep, separated by grid-wide barriers instead of kernel boundaries (config 2 is launch-latency-bound: 27 passes of
+// 10-30 k stencils per substep).  Same per-stencil arithmetic as launchXpbdPass.  Returns false when the device cannot
+// co-schedule the grid (the caller falls back to one launch per pass).
+bool launchXpbdFused(const XpbdFusedArgs &args, cudaStream_t stream);
+
 // single-thread evaluators for the per-element parity tests
 void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
                                   double *out12, int handDerived, cudaStream_t stream);

@@ -7,6 +7,8 @@
 // in registers and scatters x_s += w_s gradC_s dlambda.  Stencils of one colour share no vertex, so the
 // scatter is race free.  With `lambda` the full XPBD right-hand side -C - alpha~ lambda is used and lambda is
 // accumulated on device; without it this is the reference's "small steps" form (dlambda = -A^-1 C).
+#include <cooperative_groups.h>
+
 #include "energies.cuh"
 #include "kernels.h"
 
@@ -134,6 +136,67 @@ __global__ void xpbdSerialKernel(double *x, const double *invMass, const int32_t
     }
 }
 
+// ---- fused frame: one cooperative launch, grid barriers between passes --------------------------------------------
+template <int KIND>
+__device__ __forceinline__ void fusedPass(const XpbdFusedArgs &a, const XpbdPassDev &p, long long tid, long long nthreads)
+{
+    for (long long i = p.begin + tid; i < p.end; i += nthreads)
+        projectStencil<KIND>(a.x, a.invMass, p.stencils, p.records, a.useLambda ? p.lambda : nullptr, static_cast<int>(i), a.dt);
+}
+
+constexpr int kFusedThreads = 256;
+__global__ void __launch_bounds__(kFusedThreads) xpbdFusedKernel(const XpbdFusedArgs a)
+{
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (int sub = 0; sub < a.nsub; ++sub) {
+        // predict (state.cu predictKernel, same arithmetic): xOld <- x; v += dt g; x += v dt
+        for (long long i = tid; i < a.n3; i += nthreads) {
+            const int c = static_cast<int>(i % 3);
+            const double dtg = a.dt * (c == 0 ? a.gx : (c == 1 ? a.gy : a.gz));
+            const double xo = a.x[i];
+            const double vn = a.v[i] + dtg;
+            const double xn = xo + vn * a.dt;
+            a.xOld[i] = xo;
+            a.v[i] = vn;
+            a.x[i] = xn;
+        }
+        if (a.useLambda)
+            for (int q = 0; q < a.nPasses; ++q) {
+                const XpbdPassDev p = a.passes[q];
+                for (long long i = static_cast<long long>(p.begin) * p.nc + tid; i < static_cast<long long>(p.end) * p.nc; i += nthreads)
+                    p.lambda[i] = 0.0;
+            }
+        grid.sync();
+        for (int it = 0; it < a.iters; ++it)
+            for (int q = 0; q < a.nPasses; ++q) {
+                const XpbdPassDev p = a.passes[q];
+                switch (p.kind) {
+                case K_SPRING: fusedPass<K_SPRING>(a, p, tid, nthreads); break;
+                case K_SPRING_CONTINUUM: fusedPass<K_SPRING_CONTINUUM>(a, p, tid, nthreads); break;
+                case K_DISCRETE_BENDING: fusedPass<K_DISCRETE_BENDING>(a, p, tid, nthreads); break;
+                case K_QUADRATIC_BENDING: fusedPass<K_QUADRATIC_BENDING>(a, p, tid, nthreads); break;
+                case K_MEMBRANE_STVK: fusedPass<K_MEMBRANE_STVK>(a, p, tid, nthreads); break;
+                case K_MEMBRANE_CHOI: fusedPass<K_MEMBRANE_CHOI>(a, p, tid, nthreads); break;
+                case K_MEMBRANE_BW: fusedPass<K_MEMBRANE_BW>(a, p, tid, nthreads); break;
+                case K_TET_STVK: fusedPass<K_TET_STVK>(a, p, tid, nthreads); break;
+                case K_TET_SNH: fusedPass<K_TET_SNH>(a, p, tid, nthreads); break;
+                case K_ANCHOR: fusedPass<K_ANCHOR>(a, p, tid, nthreads); break;
+                case K_BENDING_BW: fusedPass<K_BENDING_BW>(a, p, tid, nthreads); break;
+                case K_SPRING_SQUARED_CONTINUUM: fusedPass<K_SPRING_SQUARED_CONTINUUM>(a, p, tid, nthreads); break;
+                case K_TET_SSNH: fusedPass<K_TET_SSNH>(a, p, tid, nthreads); break;
+                default: break;
+                }
+                grid.sync();  // stencils of the next colour / energy read what this one wrote
+            }
+        // finalize (state.cu finalizeKernel): v <- (x - xOld) * invdt
+        for (long long i = tid; i < a.n3; i += nthreads) a.v[i] = (a.x[i] - a.xOld[i]) * a.invdt;
+        if (sub + 1 < a.nsub) grid.sync();
+    }
+}
+
 template <int KIND>
 void launchKind(double *x, const double *invMass, const int32_t *stencils, const double *records, double *lambda,
                 int begin, int end, double dt, bool serial, cudaStream_t stream)
@@ -223,6 +286,31 @@ void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *s
     case K_TET_SSNH: launchKind<K_TET_SSNH>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
     default: break;
     }
+}
+
+bool launchXpbdFused(const XpbdFusedArgs &args, cudaStream_t stream)
+{
+    static int blocks = -1;  // co-resident capacity, one block per SM at most (the barrier cost grows with the grid)
+    if (blocks < 0) {
+        int dev = 0, sms = 0, perSm = 0, coop = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, xpbdFusedKernel, kFusedThreads, 0);
+        blocks = (coop && perSm >= 1) ? sms : 0;
+    }
+    if (blocks <= 0) return false;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(kFusedThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, xpbdFusedKernel, args) == cudaSuccess;
 }
 
 void launchEvalConstraints(int kind, const double *x, const int32_t *stencil, const double *record, double *outC,
