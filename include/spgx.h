@@ -67,7 +67,16 @@ enum spgx_kind {
 enum spgx_solver_kind {
     SPGX_VBD = 0,        /* spg/source/sim/solver/vbd.cpp:12-195 */
     SPGX_XPBD = 1,       /* spg/source/sim/solver/xpbd.cpp:16-131, useParallelGaussSeidel = true */
-    SPGX_XPBD_SERIAL = 2 /* same with useParallelGaussSeidel = false (xpbd.cpp:96-102): stencils in index order */
+    SPGX_XPBD_SERIAL = 2, /* same with useParallelGaussSeidel = false (xpbd.cpp:96-102): stencils in index order */
+    SPGX_NEWTON = 3 /* the implicit-Euler family (implicitEulerBase.cpp) and symplectic Euler: spgx_implicit_step,
+                       spgx_symplectic_step, spgx_system_force, spgx_system_stiffness, spgx_linear_solve */
+};
+
+/* which member of the implicit-Euler family spgx_implicit_step runs (one linearised solve per substep each) */
+enum spgx_implicit_kind {
+    SPGX_IE_BARAFF_WITKIN = 0, /* spg/source/sim/solver/implicitEulerBaraffWitkin.cpp:11-59: (M - dt^2 K) dv = dt (f + dt K v0) */
+    SPGX_IE_NEWTON_DX = 1,     /* .../implicitEulerNewtonDx.cpp:11-64: (M / dt^2 - K) dx = f at the inertial guess */
+    SPGX_IE_NEWTON_DV = 2      /* .../implicitEulerNewtonDv.cpp:11-67: (M - dt^2 K) dv = dt f at the inertial guess */
 };
 
 typedef struct spgx_ctx spgx_ctx;     /* one CUDA device + stream (+ optional NCCL communicator) */
@@ -209,6 +218,33 @@ int spgx_xpbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, co
 int spgx_last_timings(spgx_group *grp, spgx_timings *out);
 /* 0: plain launches; 1 (default): the launch sequence of one step() is captured in a CUDA graph and replayed */
 int spgx_set_graph_mode(spgx_group *grp, int enabled);
+
+/* ---- implicit-Euler family and symplectic Euler (group finalized with SPGX_NEWTON) ------------ */
+/* ImplicitEulerBaraffWitkin / NewtonDx / NewtonDv ::step(): per substep the system force (getSystemForce,
+ * implicitEulerBase.cpp:102-143), the energy Hessian (getSystemStiffnessMatrix, :176-221; K = -Hessian) and one
+ * preconditioned conjugate-gradient solve (solveLinearSystem, :223-238: Eigen::ConjugateGradient, Jacobi preconditioner,
+ * zero initial guess, stop at |r| < cgTolerance |b|), all on the device.  The reference fixes cgTolerance = 1e-5 and
+ * cgMaxIterations = 300 (implicitEulerBase.h:22-23); pass those for parity.  The call synchronises with the device
+ * (the host polls the convergence flag between batches of iterations); `sync` is accepted for symmetry. */
+int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubsteps, const double *gravity,
+                       double cgTolerance, int cgMaxIterations, int nFrames, int sync);
+/* SimplecticEuler::step (simplecticEuler.cpp:12-62) with updateExplicitVelocities (energy.h:154-194) */
+int spgx_symplectic_step(spgx_group *grp, double dt, int nsubsteps, const double *gravity, int nFrames, int sync);
+/* CG iteration counts of the linear solves of the last spgx_implicit_step / spgx_linear_solve call (cg.iterations(),
+ * implicitEulerBase.cpp:235); *n = how many there are, at most `capacity` are written */
+int spgx_last_cg_iterations(spgx_group *grp, int32_t *out, int capacity, int *n);
+/* getSystemForce on the current device state: f = gravity * mass - dE/dx, 3 doubles per vertex */
+int spgx_system_force(spgx_group *grp, const double *gravity, double *f);
+/* getSystemStiffnessMatrix on the current device state as block-sparse rows (3 x 3 blocks, row-major, columns
+ * ascending within a row): K = -Hessian, with the duplicate triplets the reference hands to setFromTriplets already
+ * summed.  rowptr: nVerts + 1, cols: *nBlocks, vals: 9 * *nBlocks; pass NULL arrays to query *nBlocks. */
+int spgx_system_stiffness(spgx_group *grp, int64_t *nBlocks, int32_t *rowptr, int32_t *cols, double *vals);
+/* energyHessian of one stencil (energy.h:354-362) on the current device state: (3S)^2 doubles, row-major */
+int spgx_element_hessian(spgx_group *grp, int energyId, int stencil, double *hess);
+/* solveLinearSystem for A = cM * M + cH * Hessian, the Hessian being the one assembled by the last
+ * spgx_system_stiffness / spgx_implicit_step call: b, x 3 doubles per vertex */
+int spgx_linear_solve(spgx_group *grp, double cM, double cH, const double *b, double *x, double cgTolerance,
+                      int cgMaxIterations, int *iterations);
 
 /* ---- per-element evaluators (tests; reference: energy.h:240-258, :117-153, :289) -------------- */
 /* accumulateVertexForce + accumulateVertexHessian of (stencil, local) on the CURRENT device positions:

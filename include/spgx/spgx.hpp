@@ -405,5 +405,70 @@ protected:
     bool m_useParallelGaussSeidel;
     int m_iterations{1};
 };
+
+// The implicit-Euler family (implicitEulerBase.h:11-25): one linearised solve per substep, Eigen's Jacobi-preconditioned
+// conjugate gradient with m_cgThreshold 1e-5 and m_cgMaxIterations 300, all on the device.
+class ImplicitEulerBase : public BaseSolver
+{
+public:
+    using BaseSolver::BaseSolver;
+    void step() override { stepAll(); }
+    // cg.iterations() of every linear solve of the last step() of group `i` (the reference only prints it,
+    // implicitEulerBase.cpp:234-236)
+    std::vector<int> lastCgIterations(size_t i = 0) const
+    {
+        std::vector<int32_t> it(4096);
+        int n = 0;
+        if (i < m_slots.size() && m_slots[i].handle) spgx_last_cg_iterations(m_slots[i].handle, it.data(), 4096, &n);
+        return std::vector<int>(it.begin(), it.begin() + (n < 4096 ? n : 4096));
+    }
+
+protected:
+    int solverKind() const override { return SPGX_NEWTON; }
+    virtual int implicitKind() const = 0;
+    int stepGroup(spgx_group *g, const Real *gravity) override
+    {
+        return spgx_implicit_step(g, implicitKind(), m_dtStep, m_nsubsteps, gravity, m_cgThreshold, m_cgMaxIterations, 1, 1);
+    }
+    const Real m_cgThreshold{1e-5};
+    const int m_cgMaxIterations{300};
+};
+class ImplicitEulerBaraffWitkin : public ImplicitEulerBase  // implicitEulerBaraffWitkin.h
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_BARAFF_WITKIN; }
+};
+class ImplicitEulerNewtonDx : public ImplicitEulerBase  // implicitEulerNewtonDx.h
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_NEWTON_DX; }
+};
+class ImplicitEulerNewtonDv : public ImplicitEulerBase  // implicitEulerNewtonDv.h
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_NEWTON_DV; }
+};
+class SimplecticEuler : public BaseSolver  // simplecticEuler.h:12-16 (the reference's spelling)
+{
+public:
+    using BaseSolver::BaseSolver;
+    void step() override { stepAll(); }
+
+protected:
+    int solverKind() const override { return SPGX_NEWTON; }
+    int stepGroup(spgx_group *g, const Real *gravity) override
+    {
+        return spgx_symplectic_step(g, m_dtStep, m_nsubsteps, gravity, 1, 1);
+    }
+};
 }  // namespace solver
 }  // namespace spgx

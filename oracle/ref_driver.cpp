@@ -33,11 +33,16 @@
 #include <spg/sim/energy/staticLoadEnergy.h>
 #include <spg/sim/solver/vbd.h>
 #include <spg/sim/solver/xpbd.h>
+#include <spg/sim/solver/implicitEulerBaraffWitkin.h>
+#include <spg/sim/solver/implicitEulerNewtonDx.h>
+#include <spg/sim/solver/implicitEulerNewtonDv.h>
+#include <spg/sim/solver/simplecticEuler.h>
 #include <spg/utils/graphColoring.h>
 
 #include <omp.h>
 
 #include <algorithm>
+#include <functional>
 #include <cstdint>
 #include <cstring>
 #include <iostream>
@@ -122,11 +127,54 @@ struct OracleXPBD : spg::solver::XPBD {
     }
 };
 
+// The implicit-Euler family (implicitEulerBase.h:13-25): the protected system builders and the linear solve made
+// callable, nothing overridden.
+template <class B>
+struct OracleIE : B {
+    void sysForce(spg::VectorX &f) const { this->getSystemForce(f); }
+    void sysStiffness(spg::SparseMatrix &K) const { this->getSystemStiffnessMatrix(K); }
+    void sysMass(spg::SparseMatrix &M) const { this->getSystemMassMatrix(M); }
+    void linSolve(const spg::SparseMatrix &A, const spg::VectorX &b, spg::VectorX &x) const
+    {
+        this->solveLinearSystem(A, b, x);
+    }
+};
+
 struct RefSolver {
     std::unique_ptr<OracleVBD> vbd;
     std::unique_ptr<OracleXPBD> xpbd;
-    spg::solver::BaseSolver *base() { return vbd ? static_cast<spg::solver::BaseSolver *>(vbd.get()) : xpbd.get(); }
+    std::unique_ptr<spg::solver::BaseSolver> other;  // implicit-Euler family, symplectic Euler
+    std::function<void(spg::VectorX &)> sysForce;
+    std::function<void(spg::SparseMatrix &)> sysStiffness, sysMass;
+    std::function<void(const spg::SparseMatrix &, const spg::VectorX &, spg::VectorX &)> linSolve;
+    std::vector<int> cgIterations;  // of every linear solve of the last ref_solver_step call
+    spg::solver::BaseSolver *base()
+    {
+        if (other) return other.get();
+        return vbd ? static_cast<spg::solver::BaseSolver *>(vbd.get()) : xpbd.get();
+    }
 };
+
+template <class B>
+void makeImplicit(RefSolver &s)
+{
+    auto p = std::make_unique<OracleIE<B>>();
+    auto *raw = p.get();
+    s.sysForce = [raw](spg::VectorX &f) { raw->sysForce(f); };
+    s.sysStiffness = [raw](spg::SparseMatrix &K) { raw->sysStiffness(K); };
+    s.sysMass = [raw](spg::SparseMatrix &M) { raw->sysMass(M); };
+    s.linSolve = [raw](const spg::SparseMatrix &A, const spg::VectorX &b, spg::VectorX &x) { raw->linSolve(A, b, x); };
+    s.other = std::move(p);
+}
+
+// the reference reports the CG iteration count only through its Verbosity::Performance log line
+// (implicitEulerBase.cpp:234-236): collect the numbers that follow "CG iterations: "
+void parseCgIterations(const std::string &log, std::vector<int> &out)
+{
+    const std::string key = "CG iterations: ";
+    for (size_t p = log.find(key); p != std::string::npos; p = log.find(key, p + 1))
+        out.push_back(std::atoi(log.c_str() + p + key.size()));
+}
 
 template <class F>
 int guarded(F &&f)
@@ -558,7 +606,10 @@ int ref_color_stencils_flat(const int32_t *entries, int nEntries, int stencilSiz
 }
 
 // ---- solvers ----------------------------------------------------------------------------------
-// kind: 0 = VBD (vbd.cpp:12-195), 1 = XPBD parallel Gauss-Seidel (xpbd.cpp:16-131), 2 = XPBD serial.
+// kind: 0 = VBD (vbd.cpp:12-195), 1 = XPBD parallel Gauss-Seidel (xpbd.cpp:16-131), 2 = XPBD serial,
+// 3 = ImplicitEulerBaraffWitkin (implicitEulerBaraffWitkin.cpp:11-59), 4 = ImplicitEulerNewtonDx
+// (implicitEulerNewtonDx.cpp:11-64), 5 = ImplicitEulerNewtonDv (implicitEulerNewtonDv.cpp:11-67),
+// 6 = SimplecticEuler (simplecticEuler.cpp:12-62).
 void *ref_solver_create(int kind, void *group, double dt, int substeps, int iterations, const double *gravity)
 {
     auto *s = new RefSolver;
@@ -566,6 +617,14 @@ void *ref_solver_create(int kind, void *group, double dt, int substeps, int iter
     if (kind == 0) {
         s->vbd = std::make_unique<OracleVBD>();
         s->vbd->setIterations(iterations);
+    } else if (kind == 3) {
+        makeImplicit<spg::solver::ImplicitEulerBaraffWitkin>(*s);
+    } else if (kind == 4) {
+        makeImplicit<spg::solver::ImplicitEulerNewtonDx>(*s);
+    } else if (kind == 5) {
+        makeImplicit<spg::solver::ImplicitEulerNewtonDv>(*s);
+    } else if (kind == 6) {
+        s->other = std::make_unique<spg::solver::SimplecticEuler>();
     } else {
         s->xpbd = std::make_unique<OracleXPBD>(kind == 1);
     }
@@ -588,6 +647,7 @@ int ref_solver_step(void *h, int nFrames)
         // VBD::computeParallelVertexGroups prints unconditionally (vbd.cpp:228); silence it.
         std::ostringstream sink;
         auto *old = std::cout.rdbuf(sink.rdbuf());
+        if (s->linSolve) s->base()->setVerbosity(spg::Verbosity::Performance);  // the only way to learn the CG iteration count
         try {
             for (int f = 0; f < nFrames; ++f) s->base()->step();
         } catch (...) {
@@ -595,6 +655,82 @@ int ref_solver_step(void *h, int nFrames)
             throw;
         }
         std::cout.rdbuf(old);
+        s->base()->setVerbosity(spg::Verbosity::None);
+        s->cgIterations.clear();
+        if (s->linSolve) parseCgIterations(sink.str(), s->cgIterations);
+    });
+}
+
+// ---- implicit-Euler family probes (implicitEulerBase.cpp) ----------------------------------------
+// CG iteration counts of the linear solves of the last ref_solver_step call (one per substep and frame)
+int ref_solver_cg_iterations(void *h, int32_t *out, int capacity, int *n)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        *n = static_cast<int>(s->cgIterations.size());
+        for (int i = 0; i < *n && i < capacity; ++i) out[i] = s->cgIterations[i];
+    });
+}
+// getSystemForce (implicitEulerBase.cpp:102-143) on the solver's current state: 3V doubles
+int ref_system_force(void *h, double *f)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        if (!s->sysForce) throw std::runtime_error("not an implicit-Euler solver");
+        spg::VectorX fv(3 * s->base()->particleGroups()[0].size());
+        s->sysForce(fv);
+        std::copy(fv.data(), fv.data() + fv.size(), f);
+    });
+}
+// getSystemStiffnessMatrix (:176-221) or getSystemMassMatrix (:145-174) after setFromTriplets, as COO sorted by
+// (column, row) (the compressed column-major matrix walked in storage order). rows == NULL: only *nnz.
+int ref_system_matrix(void *h, int which, int64_t *nnz, int32_t *rows, int32_t *cols, double *vals)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        if (!s->sysStiffness) throw std::runtime_error("not an implicit-Euler solver");
+        const int n = 3 * s->base()->particleGroups()[0].size();
+        spg::SparseMatrix A(n, n);
+        if (which == 0)
+            s->sysStiffness(A);
+        else
+            s->sysMass(A);
+        int64_t k = 0;
+        for (int c = 0; c < A.outerSize(); ++c)
+            for (spg::SparseMatrix::InnerIterator it(A, c); it; ++it, ++k)
+                if (rows) rows[k] = static_cast<int32_t>(it.row()), cols[k] = static_cast<int32_t>(it.col()), vals[k] = it.value();
+        *nnz = k;
+    });
+}
+// solveLinearSystem (:223-238): Eigen::ConjugateGradient<SparseMatrix, Lower | Upper>, Jacobi preconditioner,
+// tolerance 1e-5, at most 300 iterations (implicitEulerBase.h:22-23), on a caller-supplied COO matrix
+int ref_linear_solve(void *h, int n, int64_t nnz, const int32_t *rows, const int32_t *cols, const double *vals,
+                     const double *b, double *x, int *iterations)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        if (!s->linSolve) throw std::runtime_error("not an implicit-Euler solver");
+        std::vector<spg::Triplet> trip;
+        trip.reserve(nnz);
+        for (int64_t k = 0; k < nnz; ++k) trip.emplace_back(rows[k], cols[k], vals[k]);
+        spg::SparseMatrix A(n, n);
+        A.setFromTriplets(trip.begin(), trip.end());
+        spg::VectorX bv = Eigen::Map<const spg::VectorX>(b, n), xv;
+        std::ostringstream sink;
+        auto *old = std::cout.rdbuf(sink.rdbuf());
+        s->base()->setVerbosity(spg::Verbosity::Performance);
+        try {
+            s->linSolve(A, bv, xv);
+        } catch (...) {
+            std::cout.rdbuf(old);
+            throw;
+        }
+        std::cout.rdbuf(old);
+        s->base()->setVerbosity(spg::Verbosity::None);
+        std::vector<int> it;
+        parseCgIterations(sink.str(), it);
+        if (iterations) *iterations = it.empty() ? -1 : it.back();
+        std::copy(xv.data(), xv.data() + n, x);
     });
 }
 

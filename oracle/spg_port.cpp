@@ -17,6 +17,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <stdexcept>
 #include <string>
@@ -812,7 +813,8 @@ inline std::vector<int> colorStencils(const int *ent, int64_t nEnt, int S)
 // Solvers.  BaseSolver::addObject copies the group (spg/source/sim/solver/baseSolver.cpp:10-14); energies stay shared.
 // ---------------------------------------------------------------------------------------------------------------------
 struct Solver {
-    int kind = 0;  // 0 VBD, 1 XPBD parallel Gauss-Seidel, 2 XPBD serial
+    int kind = 0;  // 0 VBD, 1 XPBD parallel Gauss-Seidel, 2 XPBD serial, 3 implicit Euler Baraff-Witkin, 4 Newton dx,
+                   // 5 Newton dv, 6 symplectic Euler
     Group g;
     double dt = 0.01, gravity[3] = {0, -9.8, 0};
     int substeps = 1, iterations = 1;
@@ -821,6 +823,7 @@ struct Solver {
     std::vector<std::vector<std::vector<std::array<int, 2>>>> incidence;  // [vertex][energy] -> (stencil, local), vbd.cpp:231-268
     std::vector<std::vector<std::vector<int>>> stencilGroups;           // per energy, xpbd.cpp:133-160
     std::vector<double> xOld, xInertial;
+    std::vector<int> cgIterations;  // implicit-Euler family: one entry per linear solve of the last step call
 };
 
 inline void groupBy(const std::vector<int> &colors, std::vector<std::vector<int>> &groups)
@@ -942,6 +945,227 @@ inline void xpbdStep(Solver &s)
                 }
             }
         finalizeVelocities(s, invdt);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The implicit-Euler family and symplectic Euler (spg/source/sim/solver/implicitEulerBase.cpp and friends).
+// ---------------------------------------------------------------------------------------------------------------------
+// A square sparse matrix as sorted COO -> CSR with duplicates summed (what SparseMatrix::setFromTriplets yields)
+struct Csr {
+    int n = 0;
+    std::vector<int64_t> rowptr;
+    std::vector<int> col;
+    std::vector<double> val;
+};
+struct Trip {
+    int r, c;
+    double v;
+};
+inline Csr fromTriplets(int n, std::vector<Trip> &t)
+{
+    std::stable_sort(t.begin(), t.end(), [](const Trip &a, const Trip &b) { return a.r != b.r ? a.r < b.r : a.c < b.c; });
+    Csr A;
+    A.n = n;
+    A.rowptr.assign(static_cast<size_t>(n) + 1, 0);
+    for (size_t k = 0; k < t.size(); ++k) {
+        if (k > 0 && t[k].r == t[k - 1].r && t[k].c == t[k - 1].c) {
+            A.val.back() += t[k].v;
+        } else {
+            A.col.push_back(t[k].c);
+            A.val.push_back(t[k].v);
+            A.rowptr[t[k].r + 1]++;
+        }
+    }
+    for (int r = 0; r < n; ++r) A.rowptr[r + 1] += A.rowptr[r];
+    return A;
+}
+inline void spmv(const Csr &A, const std::vector<double> &x, std::vector<double> &y)
+{
+    y.assign(static_cast<size_t>(A.n), 0.0);
+#pragma omp parallel for schedule(static)
+    for (int r = 0; r < A.n; ++r) {
+        double acc = 0;
+        for (int64_t k = A.rowptr[r]; k < A.rowptr[r + 1]; ++k) acc += A.val[k] * x[A.col[k]];
+        y[r] = acc;
+    }
+}
+inline double dotv(const std::vector<double> &a, const std::vector<double> &b)
+{
+    double acc = 0;
+    for (size_t i = 0; i < a.size(); ++i) acc += a[i] * b[i];
+    return acc;
+}
+
+// getSystemForce (implicitEulerBase.cpp:102-143): gravity * mass, then accumulateForces (energy.h:196-216) of every
+// stencil of every energy: f -= energyGradient
+inline void systemForce(const Solver &s, std::vector<double> &f)
+{
+    const Group &g = s.g;
+    f.assign(3 * static_cast<size_t>(g.n), 0.0);
+    for (int i = 0; i < g.n; ++i)
+        for (int c = 0; c < 3; ++c) f[3 * i + c] += s.gravity[c] * g.mass[i];
+    for (const auto &ep : g.energies) {
+        const Energy &e = *ep;
+        for (int i = 0; i < e.n; ++i) {
+            double grad[12];
+            energyDerivativesAny(e, i, g.x, nullptr, grad, nullptr);
+            for (int l = 0; l < e.S; ++l)
+                for (int c = 0; c < 3; ++c) f[3 * e.st(i)[l] + c] += -grad[3 * l + c];
+        }
+    }
+}
+// getSystemStiffnessMatrix (:176-221): K = sum of negativeHessianTriplets (energy.h:218-237), i.e. minus the assembled
+// energy Hessian
+inline Csr systemStiffness(const Solver &s)
+{
+    const Group &g = s.g;
+    std::vector<Trip> t;
+    for (const auto &ep : g.energies) {
+        const Energy &e = *ep;
+        const int K = 3 * e.S;
+        for (int i = 0; i < e.n; ++i) {
+            double hess[144];
+            energyDerivativesAny(e, i, g.x, nullptr, nullptr, hess);
+            for (int rs = 0; rs < e.S; ++rs)
+                for (int cs = 0; cs < e.S; ++cs)
+                    for (int rd = 0; rd < 3; ++rd)
+                        for (int cd = 0; cd < 3; ++cd)
+                            t.push_back({e.st(i)[rs] * 3 + rd, e.st(i)[cs] * 3 + cd, -hess[(rs * 3 + rd) * K + cs * 3 + cd]});
+        }
+    }
+    return fromTriplets(3 * g.n, t);
+}
+// getSystemMassMatrix (:145-174) for particles: diagonal
+inline Csr systemMass(const Solver &s)
+{
+    std::vector<Trip> t;
+    for (int i = 0; i < s.g.n; ++i)
+        for (int c = 0; c < 3; ++c) t.push_back({3 * i + c, 3 * i + c, s.g.mass[i]});
+    return fromTriplets(3 * s.g.n, t);
+}
+// alpha * A + beta * B over the union pattern
+inline Csr combine(double alpha, const Csr &A, double beta, const Csr &B)
+{
+    std::vector<Trip> t;
+    for (int r = 0; r < A.n; ++r) {
+        for (int64_t k = A.rowptr[r]; k < A.rowptr[r + 1]; ++k) t.push_back({r, A.col[k], alpha * A.val[k]});
+        for (int64_t k = B.rowptr[r]; k < B.rowptr[r + 1]; ++k) t.push_back({r, B.col[k], beta * B.val[k]});
+    }
+    return fromTriplets(A.n, t);
+}
+// solveLinearSystem (:223-238) = Eigen::ConjugateGradient with the default DiagonalPreconditioner
+// (external/eigen/Eigen/src/IterativeLinearSolvers/ConjugateGradient.h:29-87, BasicPreconditioners.h:62-73), zero initial
+// guess, tolerance 1e-5 on |r| / |b|, at most 300 iterations (implicitEulerBase.h:22-23).  Returns the iteration count.
+inline int conjugateGradient(const Csr &A, const std::vector<double> &b, std::vector<double> &x, double tol = 1e-5,
+                             int maxIters = 300)
+{
+    const size_t n = b.size();
+    x.assign(n, 0.0);
+    std::vector<double> invdiag(n, 1.0);
+    for (int r = 0; r < A.n; ++r)
+        for (int64_t k = A.rowptr[r]; k < A.rowptr[r + 1]; ++k)
+            if (A.col[k] == r && A.val[k] != 0) invdiag[r] = 1.0 / A.val[k];
+    std::vector<double> residual = b, p(n), z(n), tmp(n);
+    const double rhsNorm2 = dotv(b, b);
+    if (rhsNorm2 == 0) return 0;
+    const double threshold = std::max(tol * tol * rhsNorm2, std::numeric_limits<double>::min());
+    double residualNorm2 = dotv(residual, residual);
+    if (residualNorm2 < threshold) return 0;
+    for (size_t i = 0; i < n; ++i) p[i] = invdiag[i] * residual[i];
+    double absNew = dotv(residual, p);
+    int it = 0;
+    while (it < maxIters) {
+        spmv(A, p, tmp);
+        const double alpha = absNew / dotv(p, tmp);
+        for (size_t i = 0; i < n; ++i) x[i] += alpha * p[i];
+        for (size_t i = 0; i < n; ++i) residual[i] -= alpha * tmp[i];
+        residualNorm2 = dotv(residual, residual);
+        if (residualNorm2 < threshold) break;
+        for (size_t i = 0; i < n; ++i) z[i] = invdiag[i] * residual[i];
+        const double absOld = absNew;
+        absNew = dotv(residual, z);
+        const double beta = absNew / absOld;
+        for (size_t i = 0; i < n; ++i) p[i] = z[i] + beta * p[i];
+        ++it;
+    }
+    return it;
+}
+// particleGroup.cpp:57-63
+inline void integrateVelocities(Group &g, double dt)
+{
+    for (size_t k = 0; k < g.x.size(); ++k) g.x[k] += g.v[k] * dt;
+}
+// ImplicitEulerBaraffWitkin::step (implicitEulerBaraffWitkin.cpp:31-54), ImplicitEulerNewtonDx::step
+// (implicitEulerNewtonDx.cpp:31-59), ImplicitEulerNewtonDv::step (implicitEulerNewtonDv.cpp:30-62)
+inline void implicitStep(Solver &s)
+{
+    Group &g = s.g;
+    const double dt = s.dt / s.substeps;
+    const size_t n = g.x.size();
+    for (int sub = 0; sub < s.substeps; ++sub) {
+        std::vector<double> f, rhs(n), sol;
+        if (s.kind == 3) {
+            const std::vector<double> v0 = g.v;
+            systemForce(s, f);
+            const Csr M = systemMass(s), K = systemStiffness(s);
+            const Csr lhs = combine(1.0, M, -(dt * dt), K);
+            std::vector<double> Kv;
+            spmv(K, v0, Kv);
+            for (size_t i = 0; i < n; ++i) rhs[i] = dt * (f[i] + dt * Kv[i]);
+            s.cgIterations.push_back(conjugateGradient(lhs, rhs, sol));
+            for (size_t i = 0; i < n; ++i) g.v[i] = v0[i] + sol[i];
+            integrateVelocities(g, dt);
+        } else if (s.kind == 4) {
+            const std::vector<double> x0 = g.x;
+            const Csr M = systemMass(s);
+            integrateVelocities(g, dt);
+            systemForce(s, f);
+            const Csr K = systemStiffness(s);
+            const double invdt = 1. / dt;
+            const Csr lhs = combine(invdt * invdt, M, -1.0, K);
+            s.cgIterations.push_back(conjugateGradient(lhs, f, sol));
+            // integrateObjectsVelocitiesFromDx (implicitEulerBase.cpp:76-88): x += dx; v = (x - x0) * invdt
+            for (size_t i = 0; i < n; ++i) {
+                g.x[i] += sol[i];
+                g.v[i] = (g.x[i] - x0[i]) * invdt;
+            }
+        } else {
+            const std::vector<double> x0 = g.x, v0 = g.v;
+            const Csr M = systemMass(s);
+            integrateVelocities(g, dt);
+            systemForce(s, f);
+            const Csr K = systemStiffness(s);
+            const Csr lhs = combine(1.0, M, -(dt * dt), K);
+            for (size_t i = 0; i < n; ++i) rhs[i] = dt * f[i];
+            s.cgIterations.push_back(conjugateGradient(lhs, rhs, sol));
+            g.x = x0;
+            for (size_t i = 0; i < n; ++i) g.v[i] = v0[i] + sol[i];
+            integrateVelocities(g, dt);
+        }
+    }
+}
+// SimplecticEuler::step (simplecticEuler.cpp:12-62) with updateExplicitVelocities (energy.h:154-194):
+// v += dt g; per stencil v_s += w_s (-grad_s) dt; x += v dt
+inline void symplecticStep(Solver &s)
+{
+    Group &g = s.g;
+    const double dt = s.dt / s.substeps;
+    for (int sub = 0; sub < s.substeps; ++sub) {
+        for (int i = 0; i < g.n; ++i)
+            for (int c = 0; c < 3; ++c) g.v[3 * i + c] += dt * s.gravity[c];
+        for (const auto &ep : g.energies) {
+            const Energy &e = *ep;
+            for (int i = 0; i < e.n; ++i) {
+                double grad[12];
+                energyDerivativesAny(e, i, g.x, nullptr, grad, nullptr);
+                for (int l = 0; l < e.S; ++l) {
+                    const int v = e.st(i)[l];
+                    for (int c = 0; c < 3; ++c) g.v[3 * v + c] += g.invMass[v] * -grad[3 * l + c] * dt;
+                }
+            }
+        }
+        integrateVelocities(g, dt);
     }
 }
 
@@ -1171,12 +1395,57 @@ int ref_solver_step(void *h, int nFrames)
 {
     return guarded([&] {
         auto *s = static_cast<Solver *>(h);
+        s->cgIterations.clear();
         for (int f = 0; f < nFrames; ++f) {
             if (s->kind == 0)
                 vbdStep(*s);
+            else if (s->kind >= 3 && s->kind <= 5)
+                implicitStep(*s);
+            else if (s->kind == 6)
+                symplecticStep(*s);
             else
                 xpbdStep(*s);
         }
+    });
+}
+int ref_solver_cg_iterations(void *h, int32_t *out, int capacity, int *n)
+{
+    return guarded([&] {
+        auto *s = static_cast<Solver *>(h);
+        *n = static_cast<int>(s->cgIterations.size());
+        for (int i = 0; i < *n && i < capacity; ++i) out[i] = s->cgIterations[i];
+    });
+}
+int ref_system_force(void *h, double *f)
+{
+    return guarded([&] {
+        std::vector<double> fv;
+        systemForce(*static_cast<Solver *>(h), fv);
+        std::copy(fv.begin(), fv.end(), f);
+    });
+}
+int ref_system_matrix(void *h, int which, int64_t *nnz, int32_t *rows, int32_t *cols, double *vals)
+{
+    return guarded([&] {
+        auto *s = static_cast<Solver *>(h);
+        const Csr A = which == 0 ? systemStiffness(*s) : systemMass(*s);
+        *nnz = static_cast<int64_t>(A.val.size());
+        if (!rows) return;
+        for (int r = 0; r < A.n; ++r)
+            for (int64_t k = A.rowptr[r]; k < A.rowptr[r + 1]; ++k) rows[k] = r, cols[k] = A.col[k], vals[k] = A.val[k];
+    });
+}
+int ref_linear_solve(void *, int n, int64_t nnz, const int32_t *rows, const int32_t *cols, const double *vals,
+                     const double *b, double *x, int *iterations)
+{
+    return guarded([&] {
+        std::vector<Trip> t(static_cast<size_t>(nnz));
+        for (int64_t k = 0; k < nnz; ++k) t[k] = {rows[k], cols[k], vals[k]};
+        const Csr A = fromTriplets(n, t);
+        std::vector<double> bv(b, b + n), xv;
+        const int it = conjugateGradient(A, bv, xv);
+        if (iterations) *iterations = it;
+        std::copy(xv.begin(), xv.end(), x);
     });
 }
 int ref_solver_reset(void *h)  // ParticleGroup::reset, particleGroup.cpp:97-103

@@ -20,7 +20,8 @@ if not _LIB_PATH.exists():
                       "(__graft_entry__.build()). There is no CPU fallback.")
 lib = C.CDLL(str(_LIB_PATH))
 
-SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL = 0, 1, 2
+SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL, SPGX_NEWTON = 0, 1, 2, 3
+SPGX_IE_BARAFF_WITKIN, SPGX_IE_NEWTON_DX, SPGX_IE_NEWTON_DV = 0, 1, 2
 SPGX_HALO_NONE, SPGX_HALO_NCCL, SPGX_HALO_P2P = 0, 1, 2
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
@@ -81,6 +82,13 @@ SIGNATURES = {
     "spgx_eval_vertex_force_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]),
     "spgx_eval_constraints": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "spgx_model_bytes": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_implicit_step": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_int, _dp, C.c_double, C.c_int, C.c_int, C.c_int]),
+    "spgx_symplectic_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, _dp, C.c_int, C.c_int]),
+    "spgx_last_cg_iterations": (C.c_int, [C.c_void_p, _ip, C.c_int, C.POINTER(C.c_int)]),
+    "spgx_system_force": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_system_stiffness": (C.c_int, [C.c_void_p, _lp, _ip, _ip, _dp]),
+    "spgx_element_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp]),
+    "spgx_linear_solve": (C.c_int, [C.c_void_p, C.c_double, C.c_double, _dp, _dp, C.c_double, C.c_int, C.POINTER(C.c_int)]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -374,6 +382,51 @@ class Group:
         g = _f64(gravity)
         check(lib.spgx_xpbd_step(self.handle, dt, substeps, iterations, _d(g), frames, int(sync)))
 
+    # ---- implicit-Euler family / symplectic Euler (group finalized with SPGX_NEWTON) ----
+    def implicit_step(self, kind, dt, substeps=1, gravity=(0.0, -9.8, 0.0), cg_tolerance=1e-5, cg_max_iterations=300,
+                      frames=1, sync=True):
+        g = _f64(gravity)
+        check(lib.spgx_implicit_step(self.handle, kind, dt, substeps, _d(g), cg_tolerance, cg_max_iterations, frames, int(sync)))
+
+    def symplectic_step(self, dt, substeps=1, gravity=(0.0, -9.8, 0.0), frames=1, sync=True):
+        g = _f64(gravity)
+        check(lib.spgx_symplectic_step(self.handle, dt, substeps, _d(g), frames, int(sync)))
+
+    def cg_iterations(self) -> np.ndarray:
+        n = C.c_int(0)
+        check(lib.spgx_last_cg_iterations(self.handle, None, 0, C.byref(n)))
+        out = np.zeros(max(n.value, 1), dtype=np.int32)
+        check(lib.spgx_last_cg_iterations(self.handle, _i(out), out.size, C.byref(n)))
+        return out[: n.value].copy()
+
+    def system_force(self, gravity=(0.0, -9.8, 0.0)) -> np.ndarray:
+        g = _f64(gravity)
+        f = np.empty((self.n, 3))
+        check(lib.spgx_system_force(self.handle, _d(g), _d(f)))
+        return f
+
+    def system_stiffness(self):
+        """K = -Hessian as block-sparse rows: (rowptr [V + 1], cols [nb], blocks [nb, 3, 3])."""
+        nb = C.c_int64(0)
+        check(lib.spgx_system_stiffness(self.handle, C.byref(nb), None, None, None))
+        rowptr, cols = np.empty(self.n + 1, dtype=np.int32), np.empty(nb.value, dtype=np.int32)
+        vals = np.empty((nb.value, 3, 3))
+        check(lib.spgx_system_stiffness(self.handle, C.byref(nb), _i(rowptr), _i(cols), _d(vals)))
+        return rowptr, cols, vals
+
+    def element_hessian(self, eid: int, stencil: int) -> np.ndarray:
+        k = 3 * _scenes.STENCIL_SIZE[self.kinds[eid]]
+        h = np.empty((k, k))
+        check(lib.spgx_element_hessian(self.handle, eid, stencil, _d(h)))
+        return h
+
+    def linear_solve(self, c_mass, c_hessian, b, tolerance=1e-5, max_iterations=300):
+        b = _f64(b)
+        x = np.empty_like(b)
+        it = C.c_int(0)
+        check(lib.spgx_linear_solve(self.handle, c_mass, c_hessian, _d(b), _d(x), tolerance, max_iterations, C.byref(it)))
+        return x, it.value
+
     def timings(self) -> Timings:
         t = Timings()
         check(lib.spgx_last_timings(self.handle, C.byref(t)))
@@ -465,3 +518,36 @@ class XPBD(_BaseSolver):
     def step(self, frames: int = 1, sync: bool = True):
         for g in self.groups:
             g.xpbd_step(self._dt, self._substeps, self._iterations, self._gravity, frames, sync)
+
+
+class _ImplicitEuler(_BaseSolver):
+    """ImplicitEulerBase (implicitEulerBase.h:11-25): m_cgThreshold 1e-5, m_cgMaxIterations 300."""
+    kind = SPGX_NEWTON
+    implicit_kind = 0
+    cg_threshold, cg_max_iterations = 1e-5, 300
+
+    def step(self, frames: int = 1, sync: bool = True):
+        for g in self.groups:
+            g.implicit_step(self.implicit_kind, self._dt, self._substeps, self._gravity, self.cg_threshold,
+                            self.cg_max_iterations, frames, sync)
+
+
+class ImplicitEulerBaraffWitkin(_ImplicitEuler):
+    implicit_kind = SPGX_IE_BARAFF_WITKIN
+
+
+class ImplicitEulerNewtonDx(_ImplicitEuler):
+    implicit_kind = SPGX_IE_NEWTON_DX
+
+
+class ImplicitEulerNewtonDv(_ImplicitEuler):
+    implicit_kind = SPGX_IE_NEWTON_DV
+
+
+class SimplecticEuler(_BaseSolver):
+    """simplecticEuler.h:12 (the reference's spelling)."""
+    kind = SPGX_NEWTON
+
+    def step(self, frames: int = 1, sync: bool = True):
+        for g in self.groups:
+            g.symplectic_step(self._dt, self._substeps, self._gravity, frames, sync)

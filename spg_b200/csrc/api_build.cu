@@ -561,7 +561,7 @@ int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int of
 int spgx_group_finalize(spgx_group *grp, int solverKind)
 {
     return guarded([&] {
-        if (solverKind != SPGX_VBD && solverKind != SPGX_XPBD && solverKind != SPGX_XPBD_SERIAL)
+        if (solverKind != SPGX_VBD && solverKind != SPGX_XPBD && solverKind != SPGX_XPBD_SERIAL && solverKind != SPGX_NEWTON)
             throw std::runtime_error("unknown solver kind");
         SPGX_CUDA(cudaSetDevice(grp->ctx->device));
         cudaStream_t st = grp->ctx->stream;
@@ -721,6 +721,11 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             }
         } else {
             if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
+            {
+                CgState *pinned = grp->newton.hostState;
+                grp->newton = spgx_group::NewtonState{};
+                grp->newton.hostState = pinned;
+            }
             grp->nOwned = grp->nLocal = V;
             grp->peers.clear();
             for (int s = 0; s < V; ++s) grp->slot2vert[s] = grp->vert2slot[s] = s;
@@ -750,11 +755,12 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 }
                 e.d_stencils.upload(st2, st);
                 e.d_records.upload(rec2, st);
-                e.d_lambda.alloc(static_cast<size_t>(e.n) * e.NC);
+                e.d_lambda.alloc(solverKind == SPGX_NEWTON ? 0 : static_cast<size_t>(e.n) * e.NC);
                 e.d_rowptr.release();
                 e.d_entries.release();
                 SPGX_CUDA(cudaStreamSynchronize(st));
             }
+            if (solverKind == SPGX_NEWTON) newtonBuild(grp, st);
         }
         // pass table of the fused XPBD frame: energies in insertion order, colours ascending (xpbd.cpp:84-95)
         grp->d_xpbdPasses.release();

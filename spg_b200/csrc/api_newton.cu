@@ -1,0 +1,374 @@
+// C-ABI, part 3: the implicit-Euler family (ImplicitEulerBaraffWitkin, ImplicitEulerNewtonDx, ImplicitEulerNewtonDv) and
+// symplectic Euler on a group finalized with SPGX_NEWTON.
+//
+// Reference: spg/source/sim/solver/implicitEulerBase.cpp (system force / stiffness / mass, linear solve),
+// implicitEulerBaraffWitkin.cpp:31-54, implicitEulerNewtonDx.cpp:31-59, implicitEulerNewtonDv.cpp:30-62,
+// simplecticEuler.cpp:12-62.  The reference rebuilds a triplet list, two Eigen sparse matrices and a fresh CG object
+// every substep on the host; here the sparse pattern is fixed at finalize time and a substep is: element Hessians ->
+// block gather -> device-resident CG (newton.cu), with the host only polling the convergence flag.
+#include <algorithm>
+#include <cstring>
+
+#include "energies.cuh"
+#include "group.h"
+#include "host_build.h"
+
+using namespace spgx;
+
+namespace spgx
+{
+void newtonBuild(spgx_group *grp, cudaStream_t st)
+{
+    const int V = grp->nVerts;
+    auto &nw = grp->newton;
+    const size_t nE = grp->energies.size();
+    // vertex -> (stencil, local) incidence per energy, ascending flat index (the order vbd.cpp:231-268 keeps too)
+    std::vector<Incidence> inc;
+    for (auto &e : grp->energies) {
+        if (static_cast<uint64_t>(e.n) >= (1ull << 30)) throw std::runtime_error("too many stencils in one energy");
+        inc.push_back(buildIncidence(V, {e.stencils.data(), static_cast<int64_t>(e.stencils.size()), e.S}));
+    }
+    for (size_t ei = 0; ei < nE; ++ei) {
+        auto &e = grp->energies[ei];
+        std::vector<uint32_t> rowptr(static_cast<size_t>(V) + 1, 0), entries(inc[ei].flat.size());
+        for (int v = 0; v <= V; ++v) rowptr[v] = static_cast<uint32_t>(inc[ei].rowptr[v]);
+        for (size_t q = 0; q < entries.size(); ++q) {
+            const int64_t flat = inc[ei].flat[q];
+            entries[q] = (static_cast<uint32_t>(flat / e.S) << 2) | static_cast<uint32_t>(flat % e.S);
+        }
+        e.d_rowptr.upload(rowptr, st);
+        e.d_entries.upload(entries, st);
+        SPGX_CUDA(cudaStreamSynchronize(st));
+    }
+    // sparse pattern: block row v = v itself and every vertex sharing a stencil with it, ascending
+    nw.bsrRowptr.assign(static_cast<size_t>(V) + 1, 0);
+    nw.bsrCol.clear();
+    std::vector<int32_t> bsrRow, cols;
+    std::vector<uint32_t> diagPos(static_cast<size_t>(V), 0);
+    for (int v = 0; v < V; ++v) {
+        cols.clear();
+        cols.push_back(v);
+        for (size_t ei = 0; ei < nE; ++ei) {
+            const auto &e = grp->energies[ei];
+            for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                const int64_t base = (inc[ei].flat[q] / e.S) * e.S;
+                for (int l = 0; l < e.S; ++l) cols.push_back(e.stencils[base + l]);
+            }
+        }
+        std::sort(cols.begin(), cols.end());
+        cols.erase(std::unique(cols.begin(), cols.end()), cols.end());
+        for (int32_t c : cols) {
+            if (c == v) diagPos[v] = static_cast<uint32_t>(nw.bsrCol.size());
+            nw.bsrCol.push_back(c);
+            bsrRow.push_back(v);
+        }
+        if (nw.bsrCol.size() >= (1ull << 31)) throw std::runtime_error("sparse pattern too large");
+        nw.bsrRowptr[v + 1] = static_cast<uint32_t>(nw.bsrCol.size());
+    }
+    nw.nnzb = static_cast<int64_t>(nw.bsrCol.size());
+    nw.d_bsrRowptr.upload(nw.bsrRowptr, st);
+    nw.d_bsrCol.upload(nw.bsrCol, st);
+    nw.d_bsrRow.upload(bsrRow, st);
+    nw.d_diagPos.upload(diagPos, st);
+    SPGX_CUDA(cudaStreamSynchronize(st));
+    nw.d_bsrH.alloc(9 * static_cast<size_t>(nw.nnzb));
+    nw.d_elemH.clear();
+    nw.d_elemH.resize(nE);
+    nw.elemHessianBytes = 0;
+    for (size_t ei = 0; ei < nE; ++ei) {
+        const auto &e = grp->energies[ei];
+        nw.d_elemH[ei].alloc(static_cast<size_t>(e.n) * 9 * e.S * e.S);
+        nw.elemHessianBytes += 8.0 * e.n * 9 * e.S * e.S;
+    }
+    const size_t n3 = 3 * static_cast<size_t>(V);
+    for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0})
+        b->alloc(n3);
+    nw.d_partials.alloc(3 * kCgBlocks);
+    nw.d_state.alloc(2);
+    if (!nw.hostState) SPGX_CUDA(cudaMallocHost(&nw.hostState, sizeof(CgState)));
+    nw.assembled = false;
+    nw.cgIterations.clear();
+}
+}  // namespace spgx
+
+namespace
+{
+void requireNewton(spgx_group *grp)
+{
+    if (!grp || !grp->finalized) throw StateError("group is not finalized (call spgx_group_finalize first)");
+    if (grp->solverKind != SPGX_NEWTON) throw StateError("group was not finalized with SPGX_NEWTON");
+    if (cudaSetDevice(grp->ctx->device) != cudaSuccess) throw CudaError("cudaSetDevice failed");
+}
+
+NewtonArgs newtonArgs(spgx_group *grp)
+{
+    NewtonArgs a{};
+    auto &nw = grp->newton;
+    a.x = grp->d_x.ptr;
+    a.mass = grp->d_mass.ptr;
+    a.nVerts = grp->nVerts;
+    a.nEnergies = static_cast<int>(grp->energies.size());
+    if (a.nEnergies > kMaxEnergies) throw std::runtime_error("too many energies in one group");
+    for (int e = 0; e < a.nEnergies; ++e) {
+        const auto &en = grp->energies[e];
+        a.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr, nw.d_elemH[e].ptr};
+    }
+    a.bsrRowptr = nw.d_bsrRowptr.ptr;
+    a.bsrCol = nw.d_bsrCol.ptr;
+    a.bsrRow = nw.d_bsrRow.ptr;
+    a.diagPos = nw.d_diagPos.ptr;
+    a.bsrH = nw.d_bsrH.ptr;
+    a.nnzb = nw.nnzb;
+    return a;
+}
+
+CgArgs cgArgs(spgx_group *grp, double cM, double cH)
+{
+    auto &nw = grp->newton;
+    CgArgs c{};
+    c.bsrRowptr = nw.d_bsrRowptr.ptr;
+    c.bsrCol = nw.d_bsrCol.ptr;
+    c.bsrH = nw.d_bsrH.ptr;
+    c.diagPos = nw.d_diagPos.ptr;
+    c.mass = grp->d_mass.ptr;
+    c.cM = cM;
+    c.cH = cH;
+    c.nVerts = grp->nVerts;
+    c.x = nw.d_sol.ptr;
+    c.r = nw.d_r.ptr;
+    c.p = nw.d_p.ptr;
+    c.z = nw.d_z.ptr;
+    c.tmp = nw.d_tmp.ptr;
+    c.invdiag = nw.d_invdiag.ptr;
+    c.partials = nw.d_partials.ptr;
+    c.state = nw.d_state.ptr;
+    return c;
+}
+
+// element Hessians + block gather of the current positions
+void assembleHessian(spgx_group *grp, cudaStream_t st)
+{
+    const NewtonArgs a = newtonArgs(grp);
+    launchElementHessians(a, st);
+    launchBsrAssemble(a, st);
+    grp->launchCounter += a.nEnergies + 1;
+    grp->newton.assembled = true;
+}
+
+// solve (cM M + cH H) sol = b on the device; returns the iteration count (cg.iterations())
+int conjugateGradient(spgx_group *grp, double cM, double cH, const double *b, double tol, int maxIters, cudaStream_t st)
+{
+    auto &nw = grp->newton;
+    const CgArgs c = cgArgs(grp, cM, cH);
+    launchCgInit(c, b, tol, st);
+    grp->launchCounter += 3;
+    constexpr int kChunk = 8;  // iterations enqueued between two looks at the convergence flag
+    int it = 0;
+    for (;;) {
+        SPGX_CUDA(cudaMemcpyAsync(nw.hostState, nw.d_state.ptr + (it & 1), sizeof(CgState), cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        if (nw.hostState->done || it >= maxIters) break;
+        const int n = std::min(kChunk, maxIters - it);
+        for (int k = 0; k < n; ++k) launchCgIteration(c, it + k, st);
+        grp->launchCounter += 3 * n;
+        it += n;
+    }
+    SPGX_CUDA(cudaGetLastError());
+    return nw.hostState->iters;
+}
+
+void copyD2D(double *dst, const double *src, size_t n, cudaStream_t st)
+{
+    if (n) SPGX_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
+}
+}  // namespace
+
+extern "C" {
+
+int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubsteps, const double *gravity,
+                       double cgTolerance, int cgMaxIterations, int nFrames, int /*sync*/)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        if (implicitKind < SPGX_IE_BARAFF_WITKIN || implicitKind > SPGX_IE_NEWTON_DV) throw std::runtime_error("unknown implicit solver kind");
+        if (nsubsteps < 1 || nFrames < 0 || cgMaxIterations < 0) throw std::runtime_error("invalid step parameters");
+        cudaStream_t st = grp->ctx->stream;
+        auto &nw = grp->newton;
+        const double g[3] = {gravity ? gravity[0] : 0.0, gravity ? gravity[1] : -9.8, gravity ? gravity[2] : 0.0};
+        const double h = dt / nsubsteps, invh = 1. / h;
+        const long long n3 = 3LL * grp->nVerts;
+        double *x = grp->d_x.ptr, *v = grp->d_v.ptr;
+        nw.cgIterations.clear();
+        grp->launchCounter = 0;
+        SPGX_CUDA(cudaEventRecord(grp->evStart, st));
+        for (int f = 0; f < nFrames; ++f)
+            for (int s = 0; s < nsubsteps; ++s) {
+                if (implicitKind == SPGX_IE_BARAFF_WITKIN) {
+                    // f, K at the current state; (M - h^2 K) dv = h (f + h K v0); v = v0 + dv; x += v h
+                    const NewtonArgs a = newtonArgs(grp);
+                    launchSystemForce(a, g, nw.d_f.ptr, st);
+                    assembleHessian(grp, st);
+                    launchBsrSpmv(cgArgs(grp, 0.0, 1.0), v, nw.d_tmp.ptr, st);  // H v0 = -K v0
+                    launchAxpby(nw.d_rhs.ptr, h, nw.d_f.ptr, -h * h, nw.d_tmp.ptr, n3, st);
+                    grp->launchCounter += 3;
+                    nw.cgIterations.push_back(conjugateGradient(grp, 1.0, h * h, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st));
+                    launchAxpby(v, 1.0, v, 1.0, nw.d_sol.ptr, n3, st);
+                    launchAxpby(x, 1.0, x, h, v, n3, st);
+                    grp->launchCounter += 2;
+                } else if (implicitKind == SPGX_IE_NEWTON_DX) {
+                    // x0 = x; x += v h; f, K there; (M / h^2 - K) dx = f; x += dx; v = (x - x0) / h
+                    copyD2D(nw.d_x0.ptr, x, n3, st);
+                    launchAxpby(x, 1.0, x, h, v, n3, st);
+                    const NewtonArgs a = newtonArgs(grp);
+                    launchSystemForce(a, g, nw.d_f.ptr, st);
+                    assembleHessian(grp, st);
+                    grp->launchCounter += 2;
+                    nw.cgIterations.push_back(conjugateGradient(grp, invh * invh, 1.0, nw.d_f.ptr, cgTolerance, cgMaxIterations, st));
+                    launchApplyDx(x, v, nw.d_sol.ptr, nw.d_x0.ptr, invh, n3, st);
+                    grp->launchCounter += 1;
+                } else {
+                    // x0, v0; x += v h; f, K there; (M - h^2 K) dv = h f; x = x0; v = v0 + dv; x += v h
+                    copyD2D(nw.d_x0.ptr, x, n3, st);
+                    launchAxpby(x, 1.0, x, h, v, n3, st);
+                    const NewtonArgs a = newtonArgs(grp);
+                    launchSystemForce(a, g, nw.d_f.ptr, st);
+                    assembleHessian(grp, st);
+                    launchAxpby(nw.d_rhs.ptr, h, nw.d_f.ptr, 0.0, nw.d_f.ptr, n3, st);
+                    grp->launchCounter += 3;
+                    nw.cgIterations.push_back(conjugateGradient(grp, 1.0, h * h, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st));
+                    launchAxpby(v, 1.0, v, 1.0, nw.d_sol.ptr, n3, st);
+                    launchAxpby(x, 1.0, nw.d_x0.ptr, h, v, n3, st);
+                    grp->launchCounter += 2;
+                }
+            }
+        SPGX_CUDA(cudaEventRecord(grp->evStop, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+        float ms = 0;
+        SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
+        grp->timings = spgx_timings{};
+        grp->timings.total_ms = ms;
+        grp->timings.kernel_launches = grp->launchCounter;
+    });
+}
+
+int spgx_symplectic_step(spgx_group *grp, double dt, int nsubsteps, const double *gravity, int nFrames, int sync)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        if (nsubsteps < 1 || nFrames < 0) throw std::runtime_error("invalid step parameters");
+        cudaStream_t st = grp->ctx->stream;
+        auto &nw = grp->newton;
+        const double g[3] = {gravity ? gravity[0] : 0.0, gravity ? gravity[1] : -9.8, gravity ? gravity[2] : 0.0};
+        const double zero[3] = {0.0, 0.0, 0.0};
+        const double h = dt / nsubsteps;
+        grp->launchCounter = 0;
+        SPGX_CUDA(cudaEventRecord(grp->evStart, st));
+        const NewtonArgs a = newtonArgs(grp);
+        for (int f = 0; f < nFrames; ++f)
+            for (int s = 0; s < nsubsteps; ++s) {
+                launchSystemForce(a, zero, nw.d_f.ptr, st);  // internal forces only: gravity acts on v directly
+                launchSymplecticUpdate(grp->d_x.ptr, grp->d_v.ptr, nw.d_f.ptr, grp->d_invMass.ptr, grp->nVerts, h, g, st);
+                grp->launchCounter += 2;
+            }
+        SPGX_CUDA(cudaEventRecord(grp->evStop, st));
+        if (sync) {
+            SPGX_CUDA(cudaStreamSynchronize(st));
+            SPGX_CUDA(cudaGetLastError());
+            float ms = 0;
+            SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
+            grp->timings = spgx_timings{};
+            grp->timings.total_ms = ms;
+            grp->timings.kernel_launches = grp->launchCounter;
+        }
+    });
+}
+
+int spgx_last_cg_iterations(spgx_group *grp, int32_t *out, int capacity, int *n)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        const auto &it = grp->newton.cgIterations;
+        if (n) *n = static_cast<int>(it.size());
+        for (int i = 0; i < static_cast<int>(it.size()) && i < capacity; ++i) out[i] = it[i];
+    });
+}
+
+int spgx_system_force(spgx_group *grp, const double *gravity, double *f)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        cudaStream_t st = grp->ctx->stream;
+        const double g[3] = {gravity ? gravity[0] : 0.0, gravity ? gravity[1] : -9.8, gravity ? gravity[2] : 0.0};
+        launchSystemForce(newtonArgs(grp), g, grp->newton.d_f.ptr, st);
+        SPGX_CUDA(cudaMemcpyAsync(f, grp->newton.d_f.ptr, 3 * static_cast<size_t>(grp->nVerts) * sizeof(double),
+                                  cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+    });
+}
+
+int spgx_system_stiffness(spgx_group *grp, int64_t *nBlocks, int32_t *rowptr, int32_t *cols, double *vals)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        auto &nw = grp->newton;
+        if (nBlocks) *nBlocks = nw.nnzb;
+        if (!rowptr && !cols && !vals) return;
+        cudaStream_t st = grp->ctx->stream;
+        assembleHessian(grp, st);
+        if (rowptr)
+            for (int v = 0; v <= grp->nVerts; ++v) rowptr[v] = static_cast<int32_t>(nw.bsrRowptr[v]);
+        if (cols) std::copy(nw.bsrCol.begin(), nw.bsrCol.end(), cols);
+        if (vals) {
+            SPGX_CUDA(cudaMemcpyAsync(vals, nw.d_bsrH.ptr, 9 * static_cast<size_t>(nw.nnzb) * sizeof(double), cudaMemcpyDeviceToHost, st));
+            SPGX_CUDA(cudaStreamSynchronize(st));
+            for (size_t k = 0; k < 9 * static_cast<size_t>(nw.nnzb); ++k) vals[k] = -vals[k];  // K = -Hessian (energy.h:223)
+        }
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+    });
+}
+
+int spgx_element_hessian(spgx_group *grp, int energyId, int stencil, double *hess)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        if (energyId < 0 || energyId >= static_cast<int>(grp->energies.size())) throw std::runtime_error("energy id out of range");
+        const auto &e = grp->energies[energyId];
+        if (stencil < 0 || stencil >= e.n) throw std::runtime_error("stencil index out of range");
+        cudaStream_t st = grp->ctx->stream;
+        launchElementHessians(newtonArgs(grp), st);
+        const int S = e.S, K = 3 * S;
+        std::vector<double> blocks(static_cast<size_t>(9) * S * S);
+        SPGX_CUDA(cudaMemcpyAsync(blocks.data(), grp->newton.d_elemH[energyId].ptr + static_cast<size_t>(stencil) * blocks.size(),
+                                  blocks.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+        for (int la = 0; la < S; ++la)
+            for (int lb = 0; lb < S; ++lb)
+                for (int i = 0; i < 3; ++i)
+                    for (int j = 0; j < 3; ++j) hess[(3 * la + i) * K + 3 * lb + j] = blocks[(la * S + lb) * 9 + 3 * i + j];
+    });
+}
+
+int spgx_linear_solve(spgx_group *grp, double cM, double cH, const double *b, double *x, double cgTolerance,
+                      int cgMaxIterations, int *iterations)
+{
+    return guarded([&] {
+        requireNewton(grp);
+        auto &nw = grp->newton;
+        if (!nw.assembled) throw StateError("no Hessian assembled yet (call spgx_system_stiffness or spgx_implicit_step first)");
+        cudaStream_t st = grp->ctx->stream;
+        const size_t bytes = 3 * static_cast<size_t>(grp->nVerts) * sizeof(double);
+        SPGX_CUDA(cudaMemcpyAsync(nw.d_rhs.ptr, b, bytes, cudaMemcpyHostToDevice, st));
+        const int it = conjugateGradient(grp, cM, cH, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st);
+        nw.cgIterations.assign(1, it);
+        if (iterations) *iterations = it;
+        SPGX_CUDA(cudaMemcpyAsync(x, nw.d_sol.ptr, bytes, cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+    });
+}
+
+}  // extern "C"

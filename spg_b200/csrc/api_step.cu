@@ -16,6 +16,7 @@ void requireFinalized(spgx_group *grp, bool vbd)
     if (!grp || !grp->finalized) throw StateError("group is not finalized (call spgx_group_finalize first)");
     if (vbd && grp->solverKind != SPGX_VBD) throw StateError("group was finalized for XPBD, not VBD");
     if (!vbd && grp->solverKind == SPGX_VBD) throw StateError("group was finalized for VBD, not XPBD");
+    if (!vbd && grp->solverKind == SPGX_NEWTON) throw StateError("group was finalized for the implicit-Euler family, not XPBD");
 }
 
 unsigned kindMaskOf(const spgx_group *grp)

@@ -202,6 +202,23 @@ struct spgx_group {
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)
     double uniqueNeighbourSum = 0;  // sum over vertices of the number of distinct stencil neighbours
 
+    // implicit-Euler family (api_newton.cu, newton.cu): sparse pattern, element Hessians, CG work vectors
+    struct NewtonState {
+        std::vector<uint32_t> bsrRowptr;  // nVerts + 1 (host copies serve spgx_system_stiffness)
+        std::vector<int32_t> bsrCol;
+        int64_t nnzb = 0;
+        spgx::DevBuf<uint32_t> d_bsrRowptr, d_diagPos;
+        spgx::DevBuf<int32_t> d_bsrCol, d_bsrRow;
+        spgx::DevBuf<double> d_bsrH;
+        std::vector<spgx::DevBuf<double>> d_elemH;  // per energy
+        spgx::DevBuf<double> d_f, d_rhs, d_sol, d_r, d_p, d_z, d_tmp, d_invdiag, d_x0, d_v0;
+        spgx::DevBuf<double> d_partials;
+        spgx::DevBuf<spgx::CgState> d_state;
+        spgx::CgState *hostState = nullptr;  // pinned
+        bool assembled = false;              // d_bsrH holds the Hessian of some state
+        std::vector<int32_t> cgIterations;   // of every linear solve of the last step call
+        double elemHessianBytes = 0;
+    } newton;
     spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
     int xpbdFused = 0;
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
@@ -244,6 +261,7 @@ struct spgx_group {
         if (graphExec) cudaGraphExecDestroy(graphExec);
         if (evStart) cudaEventDestroy(evStart);
         if (evStop) cudaEventDestroy(evStop);
+        if (newton.hostState) cudaFreeHost(newton.hostState);
         spgx::p2pRelease(this);
     }
 };
@@ -251,6 +269,8 @@ struct spgx_group {
 namespace spgx
 {
 int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
+// api_newton.cu: incidence tables, sparse pattern and work buffers of a group finalized with SPGX_NEWTON
+void newtonBuild(spgx_group *grp, cudaStream_t st);
 // peer-memory exchange (comm.cu)
 void p2pPrepare(spgx_group *grp, cudaStream_t st);   // after finalize: sync words, error word; closes old mappings
 void p2pRelease(spgx_group *grp);

@@ -118,6 +118,74 @@ struct XpbdFusedArgs {
 // co-schedule the grid (the caller falls back to one launch per pass).
 bool launchXpbdFused(const XpbdFusedArgs &args, cudaStream_t stream);
 
+// ---- implicit-Euler family and symplectic Euler (newton.cu; reference: spg/source/sim/solver/implicitEulerBase.cpp) ----
+struct NewtonEnergyDev {
+    int kind;
+    int nStencils;
+    const int32_t *stencils;  // S vertex ids per stencil (identity ordering: slot == vertex)
+    const double *records;    // NP doubles per stencil
+    const uint32_t *rowptr;   // nVerts + 1
+    const uint32_t *entries;  // (stencil << 2) | local, ascending per vertex
+    double *elemH;            // per stencil S x S blocks of 3 x 3, block (la, lb) at ((la * S + lb) * 9), row-major inside
+};
+struct NewtonArgs {
+    const double *x;
+    const double *mass;
+    int nVerts;
+    int nEnergies;
+    NewtonEnergyDev e[kMaxEnergies];
+    // block-sparse rows of the assembled Hessian: row v holds the blocks of v and of every vertex sharing a stencil
+    // with it, columns ascending
+    const uint32_t *bsrRowptr;  // nVerts + 1
+    const int32_t *bsrCol;      // per block
+    const int32_t *bsrRow;      // per block
+    const uint32_t *diagPos;    // per vertex: its diagonal block
+    double *bsrH;               // 9 doubles per block, row-major
+    long long nnzb;
+};
+// getSystemForce (implicitEulerBase.cpp:102-143): f_v = g * m_v - sum over the incident stencils of dE/dx_v (owner-centric
+// gather over the vertex incidence table: no atomics, fixed summation order). g3: host pointer, 3 doubles.
+void launchSystemForce(const NewtonArgs &a, const double *g3, double *f, cudaStream_t stream);
+// energyHessian of every stencil of every energy (energy.h:354-362) into e[].elemH
+void launchElementHessians(const NewtonArgs &a, cudaStream_t stream);
+// getSystemStiffnessMatrix (:176-221) without the triplet list: every block of the sparse Hessian gathers its
+// contributions from the element Hessians in a fixed order (energies in insertion order, stencils ascending)
+void launchBsrAssemble(const NewtonArgs &a, cudaStream_t stream);
+
+constexpr int kCgBlocks = 592;   // 148 SMs x 4: fixed grid of the reductions, so partial sums have a fixed order
+constexpr int kCgThreads = 256;
+struct CgState {
+    double absNew, rhsNorm2, threshold, residualNorm2;
+    int done, iters;
+};
+struct CgArgs {
+    // A = cM * diag(mass) + cH * H (H: the assembled block-sparse Hessian)
+    const uint32_t *bsrRowptr;
+    const int32_t *bsrCol;
+    const double *bsrH;
+    const uint32_t *diagPos;
+    const double *mass;
+    double cM, cH;
+    int nVerts;
+    double *x, *r, *p, *z, *tmp, *invdiag;  // 3 * nVerts each
+    double *partials;                       // 3 * kCgBlocks: [p . Ap | r . z | r . r]
+    CgState *state;                         // 2 entries (read [it & 1], written [(it + 1) & 1])
+};
+// y = (cM diag(mass) + cH H) x
+void launchBsrSpmv(const CgArgs &a, const double *x, double *y, cudaStream_t stream);
+// Eigen::ConjugateGradient with the Jacobi preconditioner (ConjugateGradient.h:29-87), device-resident:
+// launchCgInit: invdiag, x = 0, r = b, p = invdiag r, state[0]; launchCgIteration: iteration `it` (3 kernels; a no-op
+// once state.done is set)
+void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t stream);
+void launchCgIteration(const CgArgs &a, int it, cudaStream_t stream);
+// out = alpha * a + beta * b over n doubles (out may alias a or b)
+void launchAxpby(double *out, double alpha, const double *a, double beta, const double *b, long long n, cudaStream_t stream);
+// x += dx; v = (x - x0) * invdt  (integrateObjectsVelocitiesFromDx, implicitEulerBase.cpp:76-88)
+void launchApplyDx(double *x, double *v, const double *dx, const double *x0, double invdt, long long n, cudaStream_t stream);
+// SimplecticEuler::step velocity update (simplecticEuler.cpp:23-48): v += dt g; v += w * fInternal * dt; then x += v dt
+void launchSymplecticUpdate(double *x, double *v, const double *fInternal, const double *invMass, int nVerts, double dt,
+                            const double *g3, cudaStream_t stream);
+
 // single-thread evaluators for the per-element parity tests
 void launchEvalVertexForceHessian(int kind, const double *x, const int32_t *stencil, const double *record, int local,
                                   double *out12, int handDerived, cudaStream_t stream);

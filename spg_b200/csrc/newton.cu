@@ -1,0 +1,532 @@
+// Device side of the implicit-Euler family: system force vector, element Hessians, block-sparse
+// Hessian assembly, and a device-resident preconditioned conjugate gradient.
+//
+// Reference: spg/source/sim/solver/implicitEulerBase.cpp:102-143 (getSystemForce), :176-221 (getSystemStiffnessMatrix),
+// :223-238 (solveLinearSystem = Eigen::ConjugateGradient, external/eigen/Eigen/src/IterativeLinearSolvers/
+// ConjugateGradient.h:29-87 with the DiagonalPreconditioner of BasicPreconditioners.h:62-73);
+// spg/include/spg/sim/energy/energy.h:196-237 (accumulateForces, negativeHessianTriplets), :348-362 (energyGradient /
+// energyHessian by autodiff).
+//
+// What changes on the GPU:
+//  * forces are gathered per vertex over its incidence table with first-order duals seeded on the owner (no atomics,
+//    fixed order) instead of scattered per stencil under `omp atomic`;
+//  * the k x k element Hessian (k = 3S) is not produced by one 1 + k + k^2 scalar per operation: one thread per
+//    (stencil, vertex pair) runs second-order duals seeded on the SIX coordinates of the pair (1 + 6 + 21 doubles) and
+//    writes the 3 x 3 blocks it owns;
+//  * there is no triplet list and no sort: the sparse pattern (one block row per vertex) is built once at finalize and
+//    every block gathers its element contributions in a fixed order, so the assembled matrix is reproducible bit for bit;
+//  * the CG loop never leaves the device: reductions go through a fixed grid of partial sums that every block re-reduces
+//    in the same order, the scalars (alpha, beta, convergence flag, iteration count) live in a two-entry state ring, and
+//    iterations launched after convergence are no-ops.
+#include <cfloat>
+
+#include "energies.cuh"
+#include "kernels.h"
+
+namespace spgx
+{
+namespace
+{
+// ---------------------------------------------------------------------------------------------------------------------
+// system force
+// ---------------------------------------------------------------------------------------------------------------------
+using D1 = Dual<3, false>;
+
+template <int KIND>
+__device__ __forceinline__ void forceKind(const NewtonEnergyDev &en, const double *__restrict__ x, int v, int sub, int G,
+                                          V3d &g)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int S = EK::S;
+    const uint32_t rb = en.rowptr[v], re = en.rowptr[v + 1];
+    for (uint32_t q = rb + sub; q < re; q += G) {
+        const uint32_t ent = en.entries[q];
+        const uint32_t st = ent >> 2;
+        const int local = ent & 3u;
+        const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
+        const double *rec = en.records + static_cast<size_t>(st) * EK::NP;
+        V3<D1> xs[S];
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            const size_t o = 3 * static_cast<size_t>(ids[s]);
+            const bool own = (s == local);
+            xs[s] = V3<D1>(D1(x[o], own ? 0 : -1), D1(x[o + 1], own ? 1 : -1), D1(x[o + 2], own ? 2 : -1));
+        }
+        const D1 E = stencilEnergy<KIND, D1>(xs, rec);
+        g.x += E.g[0];
+        g.y += E.g[1];
+        g.z += E.g[2];
+    }
+}
+
+#define SPGX_FOR_EACH_KIND(X)                                                                                          \
+    X(K_SPRING)                                                                                                        \
+    X(K_SPRING_CONTINUUM)                                                                                              \
+    X(K_DISCRETE_BENDING)                                                                                              \
+    X(K_QUADRATIC_BENDING)                                                                                             \
+    X(K_MEMBRANE_STVK)                                                                                                 \
+    X(K_MEMBRANE_CHOI)                                                                                                 \
+    X(K_MEMBRANE_BW)                                                                                                   \
+    X(K_TET_STVK)                                                                                                      \
+    X(K_TET_SNH)                                                                                                       \
+    X(K_ANCHOR)                                                                                                        \
+    X(K_BENDING_BW)                                                                                                    \
+    X(K_SPRING_SQUARED_CONTINUUM)                                                                                      \
+    X(K_TET_SSNH)                                                                                                      \
+    X(K_STATIC_LOAD)
+
+constexpr int kForceLanes = 4;  // lanes per vertex
+
+__global__ void __launch_bounds__(128) systemForceKernel(const NewtonArgs a, double gx, double gy, double gz,
+                                                         double *__restrict__ f)
+{
+    constexpr int G = kForceLanes, VW = 32 / G;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    const int sub = lane / VW;
+    const int v = warp * VW + (lane % VW);
+    if (warp * VW >= a.nVerts) return;
+    const bool valid = v < a.nVerts;
+    V3d g(0.0, 0.0, 0.0);
+    if (valid) {
+        for (int e = 0; e < a.nEnergies; ++e) {
+            const NewtonEnergyDev &en = a.e[e];
+            switch (en.kind) {
+#define X(KIND)                                                                                                        \
+    case KIND: forceKind<KIND>(en, a.x, v, sub, G, g); break;
+                SPGX_FOR_EACH_KIND(X)
+#undef X
+            default: break;
+            }
+        }
+    }
+#pragma unroll
+    for (int o = VW; o < 32; o <<= 1) {
+        g.x += __shfl_xor_sync(0xffffffffu, g.x, o);
+        g.y += __shfl_xor_sync(0xffffffffu, g.y, o);
+        g.z += __shfl_xor_sync(0xffffffffu, g.z, o);
+    }
+    if (valid && sub == 0) {
+        const double m = a.mass[v];
+        const size_t o = 3 * static_cast<size_t>(v);
+        f[o] = gx * m - g.x;
+        f[o + 1] = gy * m - g.y;
+        f[o + 2] = gz * m - g.z;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// element Hessians: one thread per (stencil, pair of stencil vertices)
+// ---------------------------------------------------------------------------------------------------------------------
+template <int S>
+struct Pairs;
+template <>
+struct Pairs<1> {
+    static constexpr int N = 1;
+    __device__ static void get(int, int &a, int &b) { a = 0, b = -1; }
+};
+template <>
+struct Pairs<2> {
+    static constexpr int N = 1;
+    __device__ static void get(int, int &a, int &b) { a = 0, b = 1; }
+};
+template <>
+struct Pairs<3> {
+    static constexpr int N = 3;
+    __device__ static void get(int p, int &a, int &b)
+    {
+        a = p == 2 ? 1 : 0;
+        b = p == 0 ? 1 : 2;
+    }
+};
+template <>
+struct Pairs<4> {
+    static constexpr int N = 6;
+    __device__ static void get(int p, int &a, int &b)
+    {
+        // (0,1) (0,2) (0,3) (1,2) (1,3) (2,3)
+        a = p < 3 ? 0 : (p < 5 ? 1 : 2);
+        b = p < 3 ? p + 1 : (p < 5 ? p - 1 : 3);
+    }
+};
+
+template <int KIND>
+__global__ void __launch_bounds__(128) elementHessianKernel(const NewtonEnergyDev en, const double *__restrict__ x)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int S = EK::S;
+    using P = Pairs<S>;
+    constexpr int KD = S > 1 ? 6 : 3;
+    using D = Dual<KD, true>;
+    const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    const long long st = t / P::N;
+    if (st >= en.nStencils) return;
+    int a, b;
+    P::get(static_cast<int>(t % P::N), a, b);
+    const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
+    const double *rec = en.records + static_cast<size_t>(st) * EK::NP;
+    V3<D> xs[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        const size_t o = 3 * static_cast<size_t>(ids[s]);
+        const int base = s == a ? 0 : (s == b ? 3 : -4);  // negative seeds are passive
+        xs[s] = V3<D>(D(x[o], base), D(x[o + 1], base + 1), D(x[o + 2], base + 2));
+    }
+    const D E = stencilEnergy<KIND, D>(xs, rec);
+    double *out = en.elemH + static_cast<size_t>(st) * (9 * S * S);
+    if constexpr (S == 1) {
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) out[3 * i + j] = E.hess(i, j);
+    } else {
+        double *bab = out + (a * S + b) * 9, *bba = out + (b * S + a) * 9;
+#pragma unroll
+        for (int i = 0; i < 3; ++i)
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const double h = E.hess(i, 3 + j);
+                bab[3 * i + j] = h;
+                bba[3 * j + i] = h;
+            }
+        if (b == a + 1) {  // the pair (a, a + 1) owns the diagonal block of a
+            double *baa = out + (a * S + a) * 9;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) baa[3 * i + j] = E.hess(i, j);
+        }
+        if (a == S - 2 && b == S - 1) {  // and the last pair the one of the last vertex
+            double *bbb = out + (b * S + b) * 9;
+#pragma unroll
+            for (int i = 0; i < 3; ++i)
+#pragma unroll
+                for (int j = 0; j < 3; ++j) bbb[3 * i + j] = E.hess(3 + i, 3 + j);
+        }
+    }
+}
+
+template <int KIND>
+void launchElementHessianKind(const NewtonEnergyDev &en, const double *x, cudaStream_t stream)
+{
+    const long long threads = static_cast<long long>(en.nStencils) * Pairs<EnergyKind<KIND>::S>::N;
+    if (threads == 0) return;
+    elementHessianKernel<KIND><<<static_cast<unsigned>((threads + 127) / 128), 128, 0, stream>>>(en, x);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// block-sparse assembly: one thread per block (row, col)
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) bsrAssembleKernel(const NewtonArgs a)
+{
+    const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= a.nnzb) return;
+    const int row = a.bsrRow[t], col = a.bsrCol[t];
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    for (int e = 0; e < a.nEnergies; ++e) {
+        const NewtonEnergyDev &en = a.e[e];
+        const int S = kindStencilSize(en.kind);
+        const uint32_t rb = en.rowptr[row], re = en.rowptr[row + 1];
+        for (uint32_t q = rb; q < re; ++q) {
+            const uint32_t ent = en.entries[q];
+            const uint32_t st = ent >> 2;
+            const int la = ent & 3u;
+            const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
+            for (int lb = 0; lb < S; ++lb) {
+                if (ids[lb] != col) continue;
+                const double *blk = en.elemH + static_cast<size_t>(st) * (9 * S * S) + (la * S + lb) * 9;
+#pragma unroll
+                for (int k = 0; k < 9; ++k) acc[k] += blk[k];
+            }
+        }
+    }
+    double *out = a.bsrH + 9 * t;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) out[k] = acc[k];
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// conjugate gradient
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int kRowLanes = 8;  // lanes per block row in the sparse product
+
+// sum over the block, result valid in thread 0 (fixed tree: deterministic)
+__device__ __forceinline__ double blockSum(double v, double *smem)
+{
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    double s = 0.0;
+    if (threadIdx.x == 0)
+        for (int w = 0; w < kCgThreads / 32; ++w) s += smem[w];
+    return s;
+}
+// every block reduces the kCgBlocks partial sums itself, in the same order: result in every thread
+__device__ __forceinline__ double reducePartials(const double *__restrict__ partials, double *smem)
+{
+    double v = 0.0;
+    for (int i = threadIdx.x; i < kCgBlocks; i += kCgThreads) v += partials[i];
+    const double s = blockSum(v, smem);
+    __shared__ double bcast;
+    if (threadIdx.x == 0) bcast = s;
+    __syncthreads();
+    const double r = bcast;
+    __syncthreads();
+    return r;
+}
+
+// y = (cM diag(mass) + cH H) x over block rows; partial sums of x . y when `partials` is given
+__global__ void __launch_bounds__(kCgThreads) bsrSpmvKernel(const CgArgs a, const double *__restrict__ x,
+                                                           double *__restrict__ y, double *__restrict__ partials,
+                                                           const CgState *__restrict__ state)
+{
+    __shared__ double smem[kCgThreads / 32];
+    if (state && state->done) return;
+    constexpr int RPB = kCgThreads / kRowLanes;  // rows per block per sweep
+    const int sub = threadIdx.x % kRowLanes;
+    const int rowInBlock = threadIdx.x / kRowLanes;
+    double dotAcc = 0.0;
+    for (long long base = static_cast<long long>(blockIdx.x) * RPB; base < a.nVerts; base += static_cast<long long>(gridDim.x) * RPB) {
+        const long long row = base + rowInBlock;
+        double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+        if (row < a.nVerts) {
+            const uint32_t rb = a.bsrRowptr[row], re = a.bsrRowptr[row + 1];
+            for (uint32_t k = rb + sub; k < re; k += kRowLanes) {
+                const double *h = a.bsrH + 9 * static_cast<size_t>(k);
+                const size_t c = 3 * static_cast<size_t>(a.bsrCol[k]);
+                const double x0 = x[c], x1 = x[c + 1], x2 = x[c + 2];
+                y0 += h[0] * x0 + h[1] * x1 + h[2] * x2;
+                y1 += h[3] * x0 + h[4] * x1 + h[5] * x2;
+                y2 += h[6] * x0 + h[7] * x1 + h[8] * x2;
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < kRowLanes; o <<= 1) {
+            y0 += __shfl_xor_sync(0xffffffffu, y0, o);
+            y1 += __shfl_xor_sync(0xffffffffu, y1, o);
+            y2 += __shfl_xor_sync(0xffffffffu, y2, o);
+        }
+        if (row < a.nVerts && sub == 0) {
+            const size_t o = 3 * static_cast<size_t>(row);
+            const double m = a.cM * a.mass[row];
+            const double x0 = x[o], x1 = x[o + 1], x2 = x[o + 2];
+            y0 = a.cH * y0 + m * x0;
+            y1 = a.cH * y1 + m * x1;
+            y2 = a.cH * y2 + m * x2;
+            y[o] = y0, y[o + 1] = y1, y[o + 2] = y2;
+            dotAcc += x0 * y0 + x1 * y1 + x2 * y2;
+        }
+    }
+    if (partials) {
+        const double s = blockSum(dotAcc, smem);
+        if (threadIdx.x == 0) partials[blockIdx.x] = s;
+    }
+}
+
+// Jacobi preconditioner (BasicPreconditioners.h:62-73): 1 / diagonal, 1 where the diagonal is zero
+__global__ void invDiagKernel(const CgArgs a)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= 3LL * a.nVerts) return;
+    const long long v = i / 3;
+    const int c = static_cast<int>(i % 3);
+    const double d = a.cM * a.mass[v] + a.cH * a.bsrH[9 * static_cast<size_t>(a.diagPos[v]) + 4 * c];
+    a.invdiag[i] = d != 0.0 ? 1.0 / d : 1.0;
+}
+
+// x = 0, r = b, p = invdiag r; partial sums of b . b and r . p
+__global__ void __launch_bounds__(kCgThreads) cgInitKernel(const CgArgs a, const double *__restrict__ b)
+{
+    __shared__ double smem[kCgThreads / 32];
+    const long long n = 3LL * a.nVerts;
+    double bb = 0.0, rp = 0.0;
+    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * kCgThreads) {
+        const double bi = b[i];
+        const double pi = a.invdiag[i] * bi;
+        a.x[i] = 0.0;
+        a.r[i] = bi;
+        a.p[i] = pi;
+        bb += bi * bi;
+        rp += bi * pi;
+    }
+    const double s0 = blockSum(bb, smem);
+    const double s1 = blockSum(rp, smem);
+    if (threadIdx.x == 0) {
+        a.partials[blockIdx.x] = s0;
+        a.partials[kCgBlocks + blockIdx.x] = s1;
+    }
+}
+__global__ void __launch_bounds__(kCgThreads) cgInitFinishKernel(const CgArgs a, double tol)
+{
+    __shared__ double smem[kCgThreads / 32];
+    const double rhsNorm2 = reducePartials(a.partials, smem);
+    const double absNew = reducePartials(a.partials + kCgBlocks, smem);
+    if (threadIdx.x == 0) {
+        CgState s;
+        s.absNew = absNew;
+        s.rhsNorm2 = rhsNorm2;
+        s.threshold = fmax(tol * tol * rhsNorm2, DBL_MIN);
+        s.residualNorm2 = rhsNorm2;
+        // rhs == 0: x = 0 and no iteration (ConjugateGradient.h:44-49); r = b, so the initial-residual test of :52 can
+        // only pass when tol >= 1
+        s.done = (rhsNorm2 == 0.0 || rhsNorm2 < s.threshold) ? 1 : 0;
+        s.iters = 0;
+        a.state[0] = s;
+    }
+}
+// alpha = absNew / p . tmp; x += alpha p; r -= alpha tmp; z = invdiag r; partial sums of r . r and r . z
+__global__ void __launch_bounds__(kCgThreads) cgUpdateKernel(const CgArgs a, int it)
+{
+    __shared__ double smem[kCgThreads / 32];
+    const CgState st = a.state[it & 1];
+    if (st.done) return;
+    const double pAp = reducePartials(a.partials, smem);
+    const double alpha = st.absNew / pAp;
+    const long long n = 3LL * a.nVerts;
+    double rr = 0.0, rz = 0.0;
+    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * kCgThreads) {
+        a.x[i] += alpha * a.p[i];
+        const double ri = a.r[i] - alpha * a.tmp[i];
+        const double zi = a.invdiag[i] * ri;
+        a.r[i] = ri;
+        a.z[i] = zi;
+        rr += ri * ri;
+        rz += ri * zi;
+    }
+    const double s0 = blockSum(rr, smem);
+    const double s1 = blockSum(rz, smem);
+    if (threadIdx.x == 0) {
+        a.partials[kCgBlocks + blockIdx.x] = s1;
+        // r . r goes to a third range so that the p . tmp partials stay intact for blocks still reducing them
+        a.partials[2 * kCgBlocks + blockIdx.x] = s0;
+    }
+}
+// convergence test, beta = absNew' / absNew, p = z + beta p; block 0 writes the next state
+__global__ void __launch_bounds__(kCgThreads) cgDirectionKernel(const CgArgs a, int it)
+{
+    __shared__ double smem[kCgThreads / 32];
+    const CgState st = a.state[it & 1];
+    if (st.done) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) a.state[(it + 1) & 1] = st;
+        return;
+    }
+    const double rr = reducePartials(a.partials + 2 * kCgBlocks, smem);
+    const double rz = reducePartials(a.partials + kCgBlocks, smem);
+    const bool converged = rr < st.threshold;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        CgState nx = st;
+        nx.residualNorm2 = rr;
+        nx.done = converged ? 1 : 0;
+        if (!converged) {
+            nx.absNew = rz;
+            nx.iters = st.iters + 1;
+        }
+        a.state[(it + 1) & 1] = nx;
+    }
+    if (converged) return;
+    const double beta = rz / st.absNew;
+    const long long n = 3LL * a.nVerts;
+    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * kCgThreads)
+        a.p[i] = a.z[i] + beta * a.p[i];
+}
+
+__global__ void axpbyKernel(double *out, double alpha, const double *a, double beta, const double *b, long long n)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = alpha * a[i] + beta * b[i];
+}
+__global__ void applyDxKernel(double *__restrict__ x, double *__restrict__ v, const double *__restrict__ dx,
+                              const double *__restrict__ x0, double invdt, long long n)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double xn = x[i] + dx[i];
+    x[i] = xn;
+    v[i] = (xn - x0[i]) * invdt;
+}
+__global__ void symplecticKernel(double *__restrict__ x, double *__restrict__ v, const double *__restrict__ f,
+                                 const double *__restrict__ invMass, long long n3, double dt, double gx, double gy, double gz)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    const int c = static_cast<int>(i % 3);
+    double vn = v[i] + dt * (c == 0 ? gx : (c == 1 ? gy : gz));
+    vn += invMass[i / 3] * f[i] * dt;
+    v[i] = vn;
+    x[i] += vn * dt;
+}
+}  // namespace
+
+void launchSystemForce(const NewtonArgs &a, const double *g3, double *f, cudaStream_t stream)
+{
+    if (a.nVerts == 0) return;
+    constexpr int VW = 32 / kForceLanes;
+    const int warps = (a.nVerts + VW - 1) / VW;
+    const int blocks = (warps * 32 + 127) / 128;
+    systemForceKernel<<<blocks, 128, 0, stream>>>(a, g3[0], g3[1], g3[2], f);
+}
+
+void launchElementHessians(const NewtonArgs &a, cudaStream_t stream)
+{
+    for (int e = 0; e < a.nEnergies; ++e) {
+        switch (a.e[e].kind) {
+#define X(KIND)                                                                                                        \
+    case KIND: launchElementHessianKind<KIND>(a.e[e], a.x, stream); break;
+            SPGX_FOR_EACH_KIND(X)
+#undef X
+        default: break;
+        }
+    }
+}
+
+void launchBsrAssemble(const NewtonArgs &a, cudaStream_t stream)
+{
+    if (a.nnzb == 0) return;
+    bsrAssembleKernel<<<static_cast<unsigned>((a.nnzb + 127) / 128), 128, 0, stream>>>(a);
+}
+
+void launchBsrSpmv(const CgArgs &a, const double *x, double *y, cudaStream_t stream)
+{
+    if (a.nVerts == 0) return;
+    bsrSpmvKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, nullptr, nullptr);
+}
+
+void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t stream)
+{
+    const long long n = 3LL * a.nVerts;
+    invDiagKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(a);
+    cgInitKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, b);
+    cgInitFinishKernel<<<1, kCgThreads, 0, stream>>>(a, tol);
+}
+
+void launchCgIteration(const CgArgs &a, int it, cudaStream_t stream)
+{
+    bsrSpmvKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, a.p, a.tmp, a.partials, a.state + (it & 1));
+    cgUpdateKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, it);
+    cgDirectionKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, it);
+}
+
+void launchAxpby(double *out, double alpha, const double *a, double beta, const double *b, long long n, cudaStream_t stream)
+{
+    if (n == 0) return;
+    axpbyKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(out, alpha, a, beta, b, n);
+}
+
+void launchApplyDx(double *x, double *v, const double *dx, const double *x0, double invdt, long long n, cudaStream_t stream)
+{
+    if (n == 0) return;
+    applyDxKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(x, v, dx, x0, invdt, n);
+}
+
+void launchSymplecticUpdate(double *x, double *v, const double *fInternal, const double *invMass, int nVerts, double dt,
+                            const double *g3, cudaStream_t stream)
+{
+    const long long n3 = 3LL * nVerts;
+    if (n3 == 0) return;
+    symplecticKernel<<<static_cast<unsigned>((n3 + 255) / 256), 256, 0, stream>>>(x, v, fInternal, invMass, n3, dt, g3[0],
+                                                                                  g3[1], g3[2]);
+}
+}  // namespace spgx

@@ -85,6 +85,11 @@ class Oracle:
         L.ref_xpbd_stencil_colors.argtypes = [C.c_void_p, C.c_int, _ip, C.POINTER(C.c_int)]
         L.ref_xpbd_inject_colors.argtypes = [C.c_void_p, C.c_int, _ip, C.c_int]
         L.ref_omp_max_threads.restype = C.c_int
+        # implicit-Euler family probes (both oracles export them)
+        L.ref_solver_cg_iterations.argtypes = [C.c_void_p, _ip, C.c_int, C.POINTER(C.c_int)]
+        L.ref_system_force.argtypes = [C.c_void_p, _dp]
+        L.ref_system_matrix.argtypes = [C.c_void_p, C.c_int, _lp, _ip, _ip, _dp]
+        L.ref_linear_solve.argtypes = [C.c_void_p, C.c_int, C.c_int64, _ip, _ip, _dp, _dp, _dp, C.POINTER(C.c_int)]
         L.ref_omp_set_threads.argtypes = [C.c_int]
         if kind == "reference":
             L.ref_scene_cloth.restype = C.c_void_p
@@ -239,7 +244,8 @@ class OracleGroup:
 
 
 class OracleSolver:
-    """kind: 0 = VBD, 1 = XPBD parallel Gauss-Seidel, 2 = XPBD serial."""
+    """kind: 0 = VBD, 1 = XPBD parallel Gauss-Seidel, 2 = XPBD serial, 3 = ImplicitEulerBaraffWitkin,
+    4 = ImplicitEulerNewtonDx, 5 = ImplicitEulerNewtonDv, 6 = SimplecticEuler."""
 
     def __init__(self, group: OracleGroup, kind: int, dt=0.01, substeps=1, iterations=1, gravity=(0.0, -9.8, 0.0)):
         self.g = group
@@ -273,6 +279,36 @@ class OracleSolver:
         x = None if x is None else _f64(x)
         v = None if v is None else _f64(v)
         self.o.lib.ref_solver_set_state(self.h, _d(x), _d(v))
+
+    # ---- implicit-Euler family (kinds 3-5) ----
+    def cg_iterations(self):
+        out = np.zeros(4096, dtype=np.int32)
+        n = C.c_int(0)
+        self.o.check(self.o.lib.ref_solver_cg_iterations(self.h, _i(out), out.size, C.byref(n)))
+        return out[: n.value].copy()
+
+    def system_force(self):
+        f = np.empty((self.g.n, 3))
+        self.o.check(self.o.lib.ref_system_force(self.h, _d(f)))
+        return f
+
+    def system_matrix(self, which=0):
+        """which = 0: stiffness K = -Hessian (getSystemStiffnessMatrix), 1: mass. Returns a scipy CSR matrix."""
+        import scipy.sparse as sp
+        nnz = C.c_int64(0)
+        self.o.check(self.o.lib.ref_system_matrix(self.h, which, C.byref(nnz), None, None, None))
+        r, c, v = np.empty(nnz.value, dtype=np.int32), np.empty(nnz.value, dtype=np.int32), np.empty(nnz.value)
+        self.o.check(self.o.lib.ref_system_matrix(self.h, which, C.byref(nnz), _i(r), _i(c), _d(v)))
+        return sp.csr_matrix((v, (r, c)), shape=(3 * self.g.n, 3 * self.g.n))
+
+    def linear_solve(self, A, b):
+        """solveLinearSystem on a scipy sparse matrix: returns (x, CG iterations)."""
+        A = A.tocoo()
+        r, c, v, b = _i32(A.row), _i32(A.col), _f64(A.data), _f64(b)
+        x = np.empty(b.size)
+        it = C.c_int(0)
+        self.o.check(self.o.lib.ref_linear_solve(self.h, b.size, v.size, _i(r), _i(c), _d(v), _d(b), _d(x), C.byref(it)))
+        return x, it.value
 
     def vbd_colors(self):
         c = np.empty(self.g.n, dtype=np.int32)
