@@ -626,7 +626,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->vbdOcc = 4;
             if (const char *env = getenv("SPGX_VBD_OCC")) {
                 const int o = atoi(env);
-                if (o >= 3 && o <= 5) grp->vbdOcc = o;
+                if ((o >= 3 && o <= 5) || (o >= 17 && o <= 19)) grp->vbdOcc = o;
             }
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {

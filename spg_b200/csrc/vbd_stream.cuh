@@ -347,20 +347,24 @@ __device__ __forceinline__ void prefetchStreamIfPresent(const VbdArgs &a, const 
 
 constexpr int kStreamBlockThreads = 128;
 
-template <unsigned SMASK, unsigned KMASK, int G, int OCC>
-__global__ void __launch_bounds__(kStreamBlockThreads, OCC)
-    vbdStreamKernel(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
+// The body of the colour pass; BT = threads per block.  Warps never synchronise with each other (each has its own tile),
+// so the block size only sets the granularity of the occupancy / register trade-off: vbdStreamKernel bounds registers by
+// resident 128-thread blocks (OCC), vbdStreamKernelR runs one-warp blocks under an explicit register cap.
+template <unsigned SMASK, unsigned KMASK, int G, int BT>
+__device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
     extern __shared__ double tile[];
     const int warpInBlock = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int warp = blockIdx.x * (kStreamBlockThreads / 32) + warpInBlock;
+    const int warp = blockIdx.x * (BT / 32) + warpInBlock;
     asm volatile("griddepcontrol.launch_dependents;");  // the next colour pass may start its prologue
     if (warp >= nSlicesOfColour) return;  // whole warp past the colour
     const int v = lane % VW, sub = lane / VW;
     const int slice = sliceBase + warp;
-    double *P = tile + static_cast<size_t>(warpInBlock) * (a.maxNbr * 3 * VW) + v;
+    // per warp: maxNbr neighbour rows + one row for the vertices' own positions
+    double *P = tile + static_cast<size_t>(warpInBlock) * ((a.maxNbr + 1) * 3 * VW) + v;
+    double *Pown = P + a.maxNbr * (3 * VW);
 
     SliceDesc d, n;
     d.load(a.sliceDesc, slice);
@@ -440,14 +444,19 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
         cpAsync8(dst + VW, src + 1);
         cpAsync8(dst + 2 * VW, src + 2);
     }
-    cpAsyncCommit();
-    V3d xo(0.0, 0.0, 0.0);
-    if (valid) {
-        const size_t o = 3 * static_cast<size_t>(slot);
-        xo = V3d(a.x[o], a.x[o + 1], a.x[o + 2]);
+    // the vertex's own position rides in the same asynchronous batch (a plain load here gets scheduled BEHIND the wait
+    // for the gather and costs a second, fully exposed L2 round trip: profiles/r1f_*)
+    if (valid && sub == 0) {
+        const double *src = a.x + 3 * static_cast<size_t>(slot);
+        cpAsync8(Pown, src);
+        cpAsync8(Pown + VW, src + 1);
+        cpAsync8(Pown + 2 * VW, src + 2);
     }
+    cpAsyncCommit();
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
+    V3d xo(0.0, 0.0, 0.0);
+    if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
 
     // 3. incidence streams.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
     // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
@@ -476,18 +485,68 @@ __global__ void __launch_bounds__(kStreamBlockThreads, OCC)
     }
 }
 
-template <unsigned SMASK, unsigned KMASK, int G, int OCC>
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
+__global__ void __launch_bounds__(BT, OCC)
+    vbdStreamKernel(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
+{
+    vbdStreamBody<SMASK, KMASK, G, BT>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
+}
+// one-warp blocks with an explicit register cap: resident warps per SM = 65536 / (32 REGS), any integer
+template <unsigned SMASK, unsigned KMASK, int G, int REGS>
+__global__ void __maxnreg__(REGS)
+    vbdStreamKernelR(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
+{
+    vbdStreamBody<SMASK, KMASK, G, 32>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
+}
+
+template <class Kernel>
+void launchStreamKernel(Kernel kernel, size_t &configured, int BT, const VbdArgs &args, int begin, int end, int sliceBase,
+                        double invdtSquared, int VW, cudaStream_t stream)
+{
+    const int n = end - begin;
+    if (n <= 0) return;
+    const int warps = (n + VW - 1) / VW;
+    if ((args.maxNbr + 1) * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
+    const int warpsPerBlock = BT / 32;
+    const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
+    const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
+    if (smem > configured) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        configured = smem;
+    }
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(blocks);
+    cfg.blockDim = dim3(BT);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = args.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
+}
+template <unsigned SMASK, unsigned KMASK, int G, int REGS>
+void launchStreamGR(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
+{
+    static size_t configured = 0;  // per instantiation
+    launchStreamKernel(vbdStreamKernelR<SMASK, KMASK, G, REGS>, configured, 32, args, begin, end, sliceBase, invdtSquared, 32 / G,
+                       stream);
+}
+
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
 void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
 {
     constexpr int VW = 32 / G;
     const int n = end - begin;
     if (n <= 0) return;
     const int warps = (n + VW - 1) / VW;
-    if (args.maxNbr * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
-    constexpr int warpsPerBlock = kStreamBlockThreads / 32;
+    if ((args.maxNbr + 1) * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
+    constexpr int warpsPerBlock = BT / 32;
     const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
-    const size_t smem = static_cast<size_t>(warpsPerBlock) * args.maxNbr * 3 * VW * sizeof(double);
-    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC>;
+    const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
+    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC, BT>;
     static size_t configured = 0;  // per instantiation
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -496,7 +555,7 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(blocks);
-    cfg.blockDim = dim3(kStreamBlockThreads);
+    cfg.blockDim = dim3(BT);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr[1];
@@ -522,6 +581,10 @@ void launchStreamG(const VbdArgs &args, int occ, int begin, int end, int sliceBa
     switch (occ) {
     case 3: launchStreamGO<SMASK, KMASK, G, 3>(args, begin, end, sliceBase, invdtSquared, stream); break;
     case 5: launchStreamGO<SMASK, KMASK, G, 5>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    // finer steps of the occupancy / register trade-off: occ = resident warps per SM
+    case 17: launchStreamGR<SMASK, KMASK, G, 120>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    case 18: launchStreamGR<SMASK, KMASK, G, 112>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    case 19: launchStreamGR<SMASK, KMASK, G, 104>(args, begin, end, sliceBase, invdtSquared, stream); break;
     default: launchStreamGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream); break;
     }
 }

@@ -192,7 +192,7 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     xr, vr = osol.state()
     results = {}
     for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [
-            (f"g{l}o{o}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_OCC": str(o)}) for l in (1, 2, 4) for o in (3, 4, 5)] + [
+            (f"g{l}o{o}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_OCC": str(o)}) for l in (1, 2, 4) for o in (3, 4, 5, 17, 18, 19)] + [
             (f"g{l}{p}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_PERSIST": "1" if p == "persist" else "0"})
             for l in (1, 2, 4) for p in ("persist", "oneslice")]:
         for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_OCC", "SPGX_VBD_PERSIST"):
