@@ -688,6 +688,10 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (const char *env = getenv("SPGX_VBD_PDL")) grp->vbdPdl = atoi(env) != 0;
             grp->vbdPersist = 0;
             if (const char *env = getenv("SPGX_VBD_PERSIST")) grp->vbdPersist = atoi(env) != 0;
+            grp->vbdL1pf = 0;
+            if (const char *env = getenv("SPGX_VBD_L1PF")) grp->vbdL1pf = atoi(env) != 0;
+            grp->vbdCarveout = -1;
+            if (const char *env = getenv("SPGX_VBD_CARVEOUT")) grp->vbdCarveout = std::min(100, std::max(-1, atoi(env)));
             {
                 unsigned smask = 0, kmask = 0;
                 for (auto &e : grp->energies) {

@@ -12,6 +12,7 @@
 //   4. the G partial sums are reduced with warp shuffles; lane group 0 adds the inertia term, applies the
 //      det(H) > 1e-10 gate (vbd.cpp:139) and the cofactor solve, and writes the vertex.
 #pragma once
+#include <algorithm>
 #include "halo.cuh"
 #include "kernels.h"
 #include "streams.cuh"
@@ -298,6 +299,25 @@ struct StreamPipe {
             loadFrom<ST + 1>(a, r, s, lane);
         }
     }
+    // pull the 128-byte lines of the record of step s into L1: lane 0 the index line, lanes 1 .. 2 NQ the parameter lines
+    template <int ST>
+    __device__ __forceinline__ void prefetchL1From(const VbdArgs &a, uint32_t s, int lane) const
+    {
+        if constexpr (ST < kNumStreamTypes) {
+            if constexpr ((SMASK >> ST) & 1u) {
+                if (s < cum[ST]) {
+                    const uint32_t t = base[ST] + s;
+                    constexpr int NQ = Stream<ST>::NQ;
+                    const char *line = lane == 0 ? reinterpret_cast<const char *>(a.s[ST].idx + static_cast<size_t>(t) * 32)
+                                                 : reinterpret_cast<const char *>(a.s[ST].params + static_cast<size_t>(t) * (NQ * 32)) +
+                                                       static_cast<size_t>(lane - 1) * 128;
+                    if (lane <= 2 * NQ) asm volatile("prefetch.global.L1 [%0];" ::"l"(line));
+                    return;
+                }
+            }
+            prefetchL1From<ST + 1>(a, s, lane);
+        }
+    }
     template <int ST>
     __device__ __forceinline__ void evalFrom(const StreamRec<SMASK> &r, uint32_t s, const double *P, const V3d &xo, V3d &g,
                                              Sym3 &H) const
@@ -379,6 +399,7 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     StreamRec<SMASK> r0, r1;
     r0.idx = r1.idx = 0xFFFFFFFFu;
     if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
+    if (a.l1pf && pipe.total > 1) pipe.template prefetchL1From<0>(a, 1, lane);
     constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
     const uint32_t nb = d.lo.y, ne = n.lo.y;
     uint32_t nid[PRE];
@@ -468,10 +489,12 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
         int l = orderAfter(lane, r0.idx);
         if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
+        if (a.l1pf && s + 2 < pipe.total) pipe.template prefetchL1From<0>(a, s + 2, lane);
         pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
         if (s + 1 >= pipe.total) break;
         l = orderAfter(lane, r1.idx);
         if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
+        if (a.l1pf && s + 3 < pipe.total) pipe.template prefetchL1From<0>(a, s + 3, lane);
         pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
@@ -512,7 +535,8 @@ void launchStreamKernel(Kernel kernel, size_t &configured, int BT, const VbdArgs
     const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                             args.carveout >= 0 ? args.carveout : static_cast<int>(cudaSharedmemCarveoutMaxShared));
         configured = smem;
     }
     cudaLaunchConfig_t cfg{};
@@ -550,7 +574,12 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     static size_t configured = 0;  // per instantiation
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        // shared memory for exactly OCC resident blocks (+ 1 KB per block the runtime reserves), the rest of the 228 KB
+        // stays L1: the neighbour gather and the record streams go through it (measured on config 3: 3.08 -> 2.95 ms per
+        // frame against the maximum-shared carveout)
+        int pct = args.carveout;
+        if (pct < 0) pct = static_cast<int>(std::min<size_t>(100, (OCC * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024) + 2));
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         configured = smem;
     }
     cudaLaunchConfig_t cfg{};
