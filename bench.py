@@ -39,6 +39,8 @@ CONFIGS = {
     3: ("cloth", (1024, 1024), "vbd", 1, 10),
     4: ("beam", (149, 38, 38), "vbd", 1, 20),
     5: ("cloth", (4096, 4096), "vbd", 1, 10),
+    # SURVEY 8f rank 2 (not a BASELINE config): ImplicitEulerNewtonDx, one linearised solve per substep
+    6: ("cloth", (1024, 1024), "newton_dx", 1, 1),
 }
 
 
@@ -54,6 +56,9 @@ def build_scene(builder, args):
 
 
 def workload_name(builder, args, solver, substeps, iterations):
+    if solver == "newton_dx":
+        return (f"cloth {args[0]}x{args[1]} StVK membrane + discrete bending + 2 anchors, ImplicitEulerNewtonDx, {substeps} substep, "
+                f"dt {DT}, CG tolerance 1e-5, <= 300 iterations")
     if builder == "cloth":
         return (f"cloth {args[0]}x{args[1]} StVK membrane + discrete bending + 2 anchors, VBD {iterations} iters/substep, "
                 f"{substeps} substep, dt {DT}")
@@ -135,12 +140,13 @@ def time_oracle(cfg_id, frames, warmup, threads=None):
     cores = threads or oracle.max_threads()
     sc = build_scene(builder, args)
     og = oracle_api.OracleGroup(oracle, sc)
-    osol = oracle_api.OracleSolver(og, 0 if solver == "vbd" else 1, DT, substeps, iterations)
+    osol = oracle_api.OracleSolver(og, {"vbd": 0, "xpbd": 1, "newton_dx": 4}[solver], DT, substeps, iterations)
     osol.step(max(warmup, 1))  # first frame includes the (quadratic) colouring
     t = time.perf_counter()
     osol.step(frames)
     el = time.perf_counter() - t
-    units = sc.n_vertices * iterations * substeps * frames if solver == "vbd" else \
+    units = sc.n_vertices * int(osol.cg_iterations().sum()) if solver == "newton_dx" else \
+        sc.n_vertices * iterations * substeps * frames if solver == "vbd" else \
         sum(e.stencils.shape[0] for e in sc.energies) * iterations * substeps * frames
     return units / el, 1e3 * el / frames, {"kind": oracle.kind, "cores": cores,
                                             "sample": f"{workload_name(*CONFIGS[cfg_id])}, {frames} frames after "
@@ -154,6 +160,9 @@ def run_reference(args):
     builder, a, solver, substeps, iterations = CONFIGS[args.config]
     # bounded sample of the workload: same scene family at the reference's own CPU-runnable size (config 1 / 2 at 64^2)
     sample_cfg = 1 if solver == "vbd" and builder == "cloth" else args.config
+    if solver == "newton_dx":
+        CONFIGS[60] = ("cloth", (64, 64), "newton_dx", substeps, iterations)
+        sample_cfg = 60
     if builder == "beam":
         CONFIGS[40] = ("beam", (17, 5, 5), "vbd", substeps, iterations)
         sample_cfg = 40
@@ -161,7 +170,7 @@ def run_reference(args):
         CONFIGS[20] = ("cloth_xpbd", (64, 64), "xpbd", substeps, iterations)
         sample_cfg = 20
     value, ms, info = time_oracle(sample_cfg, args.steps, args.warmup)
-    unit = "vertex-iters/s" if solver == "vbd" else "constraint-projections/s"
+    unit = "vertex-iters/s" if solver == "vbd" else ("vertex-cg-iters/s" if solver == "newton_dx" else "constraint-projections/s")
     line = {"impl": "reference", "metric": metric_name(solver), "value": value, "unit": unit, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -175,7 +184,111 @@ def run_reference(args):
 
 
 def metric_name(solver):
+    if solver == "newton_dx":
+        return "implicit_euler_newton_dx_cg_vertex_iters_per_sec"
     return "vbd_vertex_iters_per_sec" if solver == "vbd" else "xpbd_constraint_projections_per_sec"
+
+
+def run_implicit(args):
+    """config 6: ImplicitEulerNewtonDx (implicitEulerNewtonDx.cpp:11-64) on the config-3 cloth.  A "step" is one frame =
+    system force + Hessian assembly + one Jacobi-PCG solve (tolerance 1e-5, <= 300 iterations, the reference's constants).
+    metric = vertices x CG iterations per second (the CG iteration is the unit of work: its count is data dependent and
+    equal to the reference's); the roofline is quoted on the CG iteration (block-sparse product + two vector passes)."""
+    from spg_b200 import api
+    builder, a, solver, substeps, iterations = CONFIGS[args.config]
+    if args.rows:
+        a = (args.rows, a[1])
+    sc = build_scene(builder, a)
+    ctx = api.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    g = api.Group.from_scene(ctx, sc)
+    g.finalize(api.SPGX_NEWTON)
+    V = sc.n_vertices
+    # every frame starts from the scene's initial state (flat cloth at rest, falling): at this resolution the reference's
+    # formulation (no PSD projection, CG capped at 300 iterations) does not survive more than three consecutive frames
+    class T:  # accumulated spgx_timings
+        total_ms = solve_ms = inertial_ms = update_ms = 0.0
+        kernel_launches = 0
+    t = T()
+    cg_list = []
+
+    def frame(timed):
+        g.reset()
+        g.implicit_step(api.SPGX_IE_NEWTON_DX, DT, substeps, frames=1)
+        if timed:
+            tt = g.timings()
+            for k in ("total_ms", "solve_ms", "inertial_ms", "update_ms", "kernel_launches"):
+                setattr(t, k, getattr(t, k) + getattr(tt, k))
+            cg_list.extend(g.cg_iterations().tolist())
+
+    for _ in range(max(args.warmup, 3)):
+        frame(False)
+    sampler = ClockSampler(ctx.device)
+    sampler.start()
+    time.sleep(0.3)
+    for _ in range(args.steps):
+        frame(True)
+    cg = np.array(cg_list)
+    time.sleep(0.2)
+    clocks = sampler.stop()
+    rowptr, cols, _ = g.system_stiffness()
+    nnzb = int(cols.size)
+    cg_total = int(cg.sum())
+    # per CG iteration: blocks (72 B) + column ids (4 B) + row bounds, p gathered once per row + 13 vector passes of 24 B
+    # per vertex (product: p in, tmp out; update: p, tmp, r, invdiag, x in, x, r, z out; direction: z, p in, p out)
+    bytes_cg = nnzb * 76.0 + (V + 1) * 4.0 + 13 * 24.0 * V
+    peak, peak_src = peaks()
+    achieved = bytes_cg * cg_total / (t.solve_ms * 1e-3) / 1e9
+    value = V * cg_total / (t.total_ms * 1e-3)
+    xh, vh = api.pinned_empty((V, 3)), api.pinned_empty((V, 3))
+    x0h, v0h = api.pinned_empty((V, 3)), api.pinned_empty((V, 3))
+    g.reset()
+    g.download_into(x0h, v0h)
+    ef = max(min(args.steps, 5), 1)
+    t0 = time.perf_counter()
+    cg_e2e = 0
+    for _ in range(ef):
+        g.upload(x0h, v0h)
+        g.implicit_step(api.SPGX_IE_NEWTON_DX, DT, substeps, frames=1)
+        cg_e2e += int(g.cg_iterations().sum())
+        g.download_into(xh, vh)
+    e2e_s = time.perf_counter() - t0
+    assert np.isfinite(xh).all()
+    cpu = None
+    if not args.no_cpu_baseline:
+        import oracle_api
+        oracle = oracle_api.load()
+        scs = build_scene("cloth", (64, 64))
+        osol = oracle_api.OracleSolver(oracle_api.OracleGroup(oracle, scs), 4, DT, 1, 1)
+        osol.step(1)
+        t1 = time.perf_counter()
+        osol.step(3)
+        el = time.perf_counter() - t1
+        cpu = {"value": scs.n_vertices * int(osol.cg_iterations().sum()) / el, "unit": "vertex-cg-iters/s",
+               "ms_per_frame_on_sample": 1e3 * el / 3, "kind": oracle.kind, "cores": oracle.max_threads(),
+               "sample": "cloth 64x64, ImplicitEulerNewtonDx, 3 frames after 1 warm-up"}
+    line = {"metric": metric_name(solver), "value": value, "unit": "vertex-cg-iters/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": t.total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"cloth {a[0]}x{a[1]} StVK membrane + discrete bending + 2 anchors, ImplicitEulerNewtonDx, "
+                                   f"{substeps} substep, dt {DT}, CG tolerance 1e-5, <= 300 iterations",
+                       "vertices": V, "blocks_3x3": nnzb, "cg_iterations_per_frame": cg_total / args.steps,
+                       "l2": "inputs larger than L2 (0.9 GB of matrix blocks per CG iteration vs 126 MB L2)",
+                       "launch": "plain launches, the host polls the convergence flag every 8 iterations",
+                       "state": "every frame starts from the scene's initial state", "parallelism": "1 GPU"},
+            "clocks": clocks,
+            "phases_ms_per_step": {"force_and_hessian_assembly": t.inertial_ms / args.steps, "cg_solve": t.solve_ms / args.steps,
+                                   "update": t.update_ms / args.steps},
+            "e2e": {"value": V * cg_e2e / e2e_s, "unit": "vertex-cg-iters/s", "h2d_bytes_per_step": int(xh.nbytes + vh.nbytes),
+                    "d2h_bytes_per_step": int(xh.nbytes + vh.nbytes), "ms_per_step": 1e3 * e2e_s / ef, "steps": ef},
+            "gpu_launches": int(t.kernel_launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                         "kernel": "bsrSpmvKernel + cgUpdateKernel + cgDirectionKernel (one CG iteration)",
+                         "launches_per_step": 3 * cg_total / args.steps, "avg_launch_us": 1e3 * t.solve_ms / max(3 * cg_total, 1),
+                         "algorithmic_bytes_per_launch": bytes_cg / 3, "algorithmic_bytes_per_unit": bytes_cg / V,
+                         "kernel_share_of_step": t.solve_ms / t.total_ms, "peak_source": peak_src},
+            "cpu_baseline": cpu}
+    print(json.dumps(line), flush=True)
+    return 0
 
 
 def run_single(args):
@@ -307,6 +420,8 @@ def main():
     if args.gpus > 1 or world > 1:
         from bench_multi import run_multi
         return run_multi(args)
+    if CONFIGS[args.config][2] == "newton_dx":
+        return run_implicit(args)
     return run_single(args)
 
 

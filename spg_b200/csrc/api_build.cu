@@ -727,8 +727,10 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
             {
                 CgState *pinned = grp->newton.hostState;
+                cudaEvent_t ev[3] = {grp->newton.ev[0], grp->newton.ev[1], grp->newton.ev[2]};
                 grp->newton = spgx_group::NewtonState{};
                 grp->newton.hostState = pinned;
+                for (int k = 0; k < 3; ++k) grp->newton.ev[k] = ev[k];
             }
             grp->nOwned = grp->nLocal = V;
             grp->peers.clear();

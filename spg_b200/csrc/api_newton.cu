@@ -86,6 +86,8 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
     nw.d_partials.alloc(3 * kCgBlocks);
     nw.d_state.alloc(2);
     if (!nw.hostState) SPGX_CUDA(cudaMallocHost(&nw.hostState, sizeof(CgState)));
+    for (auto &e : nw.ev)
+        if (!e) SPGX_CUDA(cudaEventCreate(&e));
     nw.assembled = false;
     nw.cgIterations.clear();
 }
@@ -129,6 +131,7 @@ CgArgs cgArgs(spgx_group *grp, double cM, double cH)
     c.bsrRowptr = nw.d_bsrRowptr.ptr;
     c.bsrCol = nw.d_bsrCol.ptr;
     c.bsrH = nw.d_bsrH.ptr;
+    c.nnzb = nw.nnzb;
     c.diagPos = nw.d_diagPos.ptr;
     c.mass = grp->d_mass.ptr;
     c.cM = cM;
@@ -200,9 +203,23 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
         double *x = grp->d_x.ptr, *v = grp->d_v.ptr;
         nw.cgIterations.clear();
         grp->launchCounter = 0;
+        double assembleMs = 0, solveMs = 0;
+        // the CG loop synchronises with the stream anyway, so per-phase times cost nothing extra: inertial_ms = system
+        // force + Hessian assembly ("f computation" + "H computation / assembly" of implicitEulerBase.cpp:139, :215-219),
+        // solve_ms = the linear solve (:233-236)
+        auto phase = [&](int k) { SPGX_CUDA(cudaEventRecord(nw.ev[k], st)); };
+        auto collect = [&] {
+            float a = 0, b = 0;
+            SPGX_CUDA(cudaEventSynchronize(nw.ev[2]));
+            SPGX_CUDA(cudaEventElapsedTime(&a, nw.ev[0], nw.ev[1]));
+            SPGX_CUDA(cudaEventElapsedTime(&b, nw.ev[1], nw.ev[2]));
+            assembleMs += a;
+            solveMs += b;
+        };
         SPGX_CUDA(cudaEventRecord(grp->evStart, st));
         for (int f = 0; f < nFrames; ++f)
             for (int s = 0; s < nsubsteps; ++s) {
+                phase(0);
                 if (implicitKind == SPGX_IE_BARAFF_WITKIN) {
                     // f, K at the current state; (M - h^2 K) dv = h (f + h K v0); v = v0 + dv; x += v h
                     const NewtonArgs a = newtonArgs(grp);
@@ -211,7 +228,10 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
                     launchBsrSpmv(cgArgs(grp, 0.0, 1.0), v, nw.d_tmp.ptr, st);  // H v0 = -K v0
                     launchAxpby(nw.d_rhs.ptr, h, nw.d_f.ptr, -h * h, nw.d_tmp.ptr, n3, st);
                     grp->launchCounter += 3;
+                    phase(1);
                     nw.cgIterations.push_back(conjugateGradient(grp, 1.0, h * h, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st));
+                    phase(2);
+                    collect();
                     launchAxpby(v, 1.0, v, 1.0, nw.d_sol.ptr, n3, st);
                     launchAxpby(x, 1.0, x, h, v, n3, st);
                     grp->launchCounter += 2;
@@ -223,7 +243,10 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
                     launchSystemForce(a, g, nw.d_f.ptr, st);
                     assembleHessian(grp, st);
                     grp->launchCounter += 2;
+                    phase(1);
                     nw.cgIterations.push_back(conjugateGradient(grp, invh * invh, 1.0, nw.d_f.ptr, cgTolerance, cgMaxIterations, st));
+                    phase(2);
+                    collect();
                     launchApplyDx(x, v, nw.d_sol.ptr, nw.d_x0.ptr, invh, n3, st);
                     grp->launchCounter += 1;
                 } else {
@@ -235,7 +258,10 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
                     assembleHessian(grp, st);
                     launchAxpby(nw.d_rhs.ptr, h, nw.d_f.ptr, 0.0, nw.d_f.ptr, n3, st);
                     grp->launchCounter += 3;
+                    phase(1);
                     nw.cgIterations.push_back(conjugateGradient(grp, 1.0, h * h, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st));
+                    phase(2);
+                    collect();
                     launchAxpby(v, 1.0, v, 1.0, nw.d_sol.ptr, n3, st);
                     launchAxpby(x, 1.0, nw.d_x0.ptr, h, v, n3, st);
                     grp->launchCounter += 2;
@@ -247,6 +273,9 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
         float ms = 0;
         SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
         grp->timings = spgx_timings{};
+        grp->timings.inertial_ms = assembleMs;
+        grp->timings.solve_ms = solveMs;
+        grp->timings.update_ms = ms - assembleMs - solveMs;
         grp->timings.total_ms = ms;
         grp->timings.kernel_launches = grp->launchCounter;
     });
@@ -321,9 +350,13 @@ int spgx_system_stiffness(spgx_group *grp, int64_t *nBlocks, int32_t *rowptr, in
             for (int v = 0; v <= grp->nVerts; ++v) rowptr[v] = static_cast<int32_t>(nw.bsrRowptr[v]);
         if (cols) std::copy(nw.bsrCol.begin(), nw.bsrCol.end(), cols);
         if (vals) {
-            SPGX_CUDA(cudaMemcpyAsync(vals, nw.d_bsrH.ptr, 9 * static_cast<size_t>(nw.nnzb) * sizeof(double), cudaMemcpyDeviceToHost, st));
+            // device storage is component-major; the caller gets block-major 3 x 3 blocks of K = -Hessian (energy.h:223)
+            std::vector<double> soa(9 * static_cast<size_t>(nw.nnzb));
+            SPGX_CUDA(cudaMemcpyAsync(soa.data(), nw.d_bsrH.ptr, soa.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
             SPGX_CUDA(cudaStreamSynchronize(st));
-            for (size_t k = 0; k < 9 * static_cast<size_t>(nw.nnzb); ++k) vals[k] = -vals[k];  // K = -Hessian (energy.h:223)
+            const size_t nb = static_cast<size_t>(nw.nnzb);
+            for (size_t t = 0; t < nb; ++t)
+                for (int k = 0; k < 9; ++k) vals[9 * t + k] = -soa[k * nb + t];
         }
         SPGX_CUDA(cudaStreamSynchronize(st));
         SPGX_CUDA(cudaGetLastError());

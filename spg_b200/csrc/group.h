@@ -218,6 +218,7 @@ struct spgx_group {
         bool assembled = false;              // d_bsrH holds the Hessian of some state
         std::vector<int32_t> cgIterations;   // of every linear solve of the last step call
         double elemHessianBytes = 0;
+        cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // substep start, system assembled, linear system solved
     } newton;
     spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
     int xpbdFused = 0;
@@ -262,6 +263,8 @@ struct spgx_group {
         if (evStart) cudaEventDestroy(evStart);
         if (evStop) cudaEventDestroy(evStop);
         if (newton.hostState) cudaFreeHost(newton.hostState);
+        for (auto e : newton.ev)
+            if (e) cudaEventDestroy(e);
         spgx::p2pRelease(this);
     }
 };

@@ -142,7 +142,7 @@ struct NewtonArgs {
     const int32_t *bsrCol;      // per block
     const int32_t *bsrRow;      // per block
     const uint32_t *diagPos;    // per vertex: its diagonal block
-    double *bsrH;               // 9 doubles per block, row-major
+    double *bsrH;               // 9 x nnzb doubles, component-major: entry (i, j) of block t at bsrH[(3 i + j) * nnzb + t]
     long long nnzb;
 };
 // getSystemForce (implicitEulerBase.cpp:102-143): f_v = g * m_v - sum over the incident stencils of dE/dx_v (owner-centric
@@ -164,7 +164,8 @@ struct CgArgs {
     // A = cM * diag(mass) + cH * H (H: the assembled block-sparse Hessian)
     const uint32_t *bsrRowptr;
     const int32_t *bsrCol;
-    const double *bsrH;
+    const double *bsrH;  // component-major (NewtonArgs::bsrH)
+    long long nnzb;
     const uint32_t *diagPos;
     const double *mass;
     double cM, cH;

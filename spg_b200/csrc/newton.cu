@@ -11,8 +11,9 @@
 //  * forces are gathered per vertex over its incidence table with first-order duals seeded on the owner (no atomics,
 //    fixed order) instead of scattered per stencil under `omp atomic`;
 //  * the k x k element Hessian (k = 3S) is not produced by one 1 + k + k^2 scalar per operation: one thread per
-//    (stencil, vertex pair) runs second-order duals seeded on the SIX coordinates of the pair (1 + 6 + 21 doubles) and
-//    writes the 3 x 3 blocks it owns;
+//    (stencil, vertex pair) runs MIXED second-order duals (value, two 3-gradients, the 3 x 3 mixed partials: 16 doubles,
+//    dual.cuh DualMixed) for the off-diagonal blocks, one thread per (stencil, vertex) second-order duals seeded on that
+//    vertex (10 doubles) for the diagonal blocks;
 //  * there is no triplet list and no sort: the sparse pattern (one block row per vertex) is built once at finalize and
 //    every block gathers its element contributions in a fixed order, so the assembled matrix is reproducible bit for bit;
 //  * the CG loop never leaves the device: reductions go through a fixed grid of partial sums that every block re-reduces
@@ -150,66 +151,66 @@ struct Pairs<4> {
     }
 };
 
+// Work items of one stencil: its S (S - 1) / 2 vertex pairs (a < b), each evaluated with mixed second-order duals (16
+// doubles per scalar) for the off-diagonal blocks (a, b) and (b, a) = transpose, then its S vertices, each evaluated with
+// second-order duals seeded on that vertex alone (10 doubles per scalar) for the diagonal block.
 template <int KIND>
 __global__ void __launch_bounds__(128) elementHessianKernel(const NewtonEnergyDev en, const double *__restrict__ x)
 {
     using EK = EnergyKind<KIND>;
     constexpr int S = EK::S;
     using P = Pairs<S>;
-    constexpr int KD = S > 1 ? 6 : 3;
-    using D = Dual<KD, true>;
+    constexpr int NP = S > 1 ? P::N : 0, NW = NP + S;
     const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-    const long long st = t / P::N;
+    const long long st = t / NW;
     if (st >= en.nStencils) return;
-    int a, b;
-    P::get(static_cast<int>(t % P::N), a, b);
+    const int item = static_cast<int>(t % NW);
     const int32_t *ids = en.stencils + static_cast<size_t>(st) * S;
     const double *rec = en.records + static_cast<size_t>(st) * EK::NP;
-    V3<D> xs[S];
-#pragma unroll
-    for (int s = 0; s < S; ++s) {
-        const size_t o = 3 * static_cast<size_t>(ids[s]);
-        const int base = s == a ? 0 : (s == b ? 3 : -4);  // negative seeds are passive
-        xs[s] = V3<D>(D(x[o], base), D(x[o + 1], base + 1), D(x[o + 2], base + 2));
-    }
-    const D E = stencilEnergy<KIND, D>(xs, rec);
     double *out = en.elemH + static_cast<size_t>(st) * (9 * S * S);
-    if constexpr (S == 1) {
+    if (item < NP) {
+        int a, b;
+        P::get(item, a, b);
+        V3<DualMixed> xs[S];
 #pragma unroll
-        for (int i = 0; i < 3; ++i)
-#pragma unroll
-            for (int j = 0; j < 3; ++j) out[3 * i + j] = E.hess(i, j);
-    } else {
+        for (int s = 0; s < S; ++s) {
+            const size_t o = 3 * static_cast<size_t>(ids[s]);
+            const int base = s == a ? 0 : (s == b ? 3 : -4);  // negative seeds are passive
+            xs[s] = V3<DualMixed>(DualMixed(x[o], base), DualMixed(x[o + 1], base + 1), DualMixed(x[o + 2], base + 2));
+        }
+        const DualMixed E = stencilEnergy<KIND, DualMixed>(xs, rec);
         double *bab = out + (a * S + b) * 9, *bba = out + (b * S + a) * 9;
 #pragma unroll
         for (int i = 0; i < 3; ++i)
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
-                const double h = E.hess(i, 3 + j);
-                bab[3 * i + j] = h;
-                bba[3 * j + i] = h;
+                bab[3 * i + j] = E.h[3 * i + j];
+                bba[3 * j + i] = E.h[3 * i + j];
             }
-        if (b == a + 1) {  // the pair (a, a + 1) owns the diagonal block of a
-            double *baa = out + (a * S + a) * 9;
+    } else {
+        const int a = item - NP;
+        using D = Dual<3, true>;
+        V3<D> xs[S];
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
-#pragma unroll
-                for (int j = 0; j < 3; ++j) baa[3 * i + j] = E.hess(i, j);
+        for (int s = 0; s < S; ++s) {
+            const size_t o = 3 * static_cast<size_t>(ids[s]);
+            const int base = s == a ? 0 : -4;
+            xs[s] = V3<D>(D(x[o], base), D(x[o + 1], base + 1), D(x[o + 2], base + 2));
         }
-        if (a == S - 2 && b == S - 1) {  // and the last pair the one of the last vertex
-            double *bbb = out + (b * S + b) * 9;
+        const D E = stencilEnergy<KIND, D>(xs, rec);
+        double *baa = out + (a * S + a) * 9;
 #pragma unroll
-            for (int i = 0; i < 3; ++i)
+        for (int i = 0; i < 3; ++i)
 #pragma unroll
-                for (int j = 0; j < 3; ++j) bbb[3 * i + j] = E.hess(3 + i, 3 + j);
-        }
+            for (int j = 0; j < 3; ++j) baa[3 * i + j] = E.hess(i, j);
     }
 }
 
 template <int KIND>
 void launchElementHessianKind(const NewtonEnergyDev &en, const double *x, cudaStream_t stream)
 {
-    const long long threads = static_cast<long long>(en.nStencils) * Pairs<EnergyKind<KIND>::S>::N;
+    constexpr int S = EnergyKind<KIND>::S;
+    const long long threads = static_cast<long long>(en.nStencils) * ((S > 1 ? Pairs<S>::N : 0) + S);
     if (threads == 0) return;
     elementHessianKernel<KIND><<<static_cast<unsigned>((threads + 127) / 128), 128, 0, stream>>>(en, x);
 }
@@ -240,9 +241,10 @@ __global__ void __launch_bounds__(128) bsrAssembleKernel(const NewtonArgs a)
             }
         }
     }
-    double *out = a.bsrH + 9 * t;
+    // component-major storage (component k of block t at bsrH[k * nnzb + t]): the write here and the reads of the sparse
+    // product are unit-stride across the lanes that own consecutive blocks
 #pragma unroll
-    for (int k = 0; k < 9; ++k) out[k] = acc[k];
+    for (int k = 0; k < 9; ++k) a.bsrH[k * a.nnzb + t] = acc[k];
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -294,13 +296,19 @@ __global__ void __launch_bounds__(kCgThreads) bsrSpmvKernel(const CgArgs a, cons
         double y0 = 0.0, y1 = 0.0, y2 = 0.0;
         if (row < a.nVerts) {
             const uint32_t rb = a.bsrRowptr[row], re = a.bsrRowptr[row + 1];
+            const size_t nb = static_cast<size_t>(a.nnzb);
+            // (two blocks per lane and trip with the column ids hoisted, and a 148 x 8 grid, measured slower: 90.8 vs 81.1
+            // ms per 300 iterations at 1 M vertices)
             for (uint32_t k = rb + sub; k < re; k += kRowLanes) {
-                const double *h = a.bsrH + 9 * static_cast<size_t>(k);
+                const double *h = a.bsrH + k;
                 const size_t c = 3 * static_cast<size_t>(a.bsrCol[k]);
+                const double h0 = __ldg(h), h1 = __ldg(h + nb), h2 = __ldg(h + 2 * nb), h3 = __ldg(h + 3 * nb),
+                             h4 = __ldg(h + 4 * nb), h5 = __ldg(h + 5 * nb), h6 = __ldg(h + 6 * nb), h7 = __ldg(h + 7 * nb),
+                             h8 = __ldg(h + 8 * nb);
                 const double x0 = x[c], x1 = x[c + 1], x2 = x[c + 2];
-                y0 += h[0] * x0 + h[1] * x1 + h[2] * x2;
-                y1 += h[3] * x0 + h[4] * x1 + h[5] * x2;
-                y2 += h[6] * x0 + h[7] * x1 + h[8] * x2;
+                y0 += h0 * x0 + h1 * x1 + h2 * x2;
+                y1 += h3 * x0 + h4 * x1 + h5 * x2;
+                y2 += h6 * x0 + h7 * x1 + h8 * x2;
             }
         }
 #pragma unroll
@@ -333,7 +341,7 @@ __global__ void invDiagKernel(const CgArgs a)
     if (i >= 3LL * a.nVerts) return;
     const long long v = i / 3;
     const int c = static_cast<int>(i % 3);
-    const double d = a.cM * a.mass[v] + a.cH * a.bsrH[9 * static_cast<size_t>(a.diagPos[v]) + 4 * c];
+    const double d = a.cM * a.mass[v] + a.cH * a.bsrH[static_cast<size_t>(4 * c) * a.nnzb + a.diagPos[v]];
     a.invdiag[i] = d != 0.0 ? 1.0 / d : 1.0;
 }
 
@@ -387,14 +395,29 @@ __global__ void __launch_bounds__(kCgThreads) cgUpdateKernel(const CgArgs a, int
     const double alpha = st.absNew / pAp;
     const long long n = 3LL * a.nVerts;
     double rr = 0.0, rz = 0.0;
-    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * kCgThreads) {
-        a.x[i] += alpha * a.p[i];
-        const double ri = a.r[i] - alpha * a.tmp[i];
-        const double zi = a.invdiag[i] * ri;
-        a.r[i] = ri;
-        a.z[i] = zi;
-        rr += ri * ri;
-        rz += ri * zi;
+    // four independent elements per trip: 20 loads in flight per thread (the loop is pure latency otherwise)
+    constexpr int U = 4;
+    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
+    for (long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i0 < n; i0 += U * stride) {
+        double xv[U], pv[U], rv[U], tv[U], dv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n) xv[u] = a.x[i], pv[u] = a.p[i], rv[u] = a.r[i], tv[u] = a.tmp[i], dv[u] = a.invdiag[i];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n) {
+                a.x[i] = xv[u] + alpha * pv[u];
+                const double ri = rv[u] - alpha * tv[u];
+                const double zi = dv[u] * ri;
+                a.r[i] = ri;
+                a.z[i] = zi;
+                rr += ri * ri;
+                rz += ri * zi;
+            }
+        }
     }
     const double s0 = blockSum(rr, smem);
     const double s1 = blockSum(rz, smem);
@@ -429,8 +452,21 @@ __global__ void __launch_bounds__(kCgThreads) cgDirectionKernel(const CgArgs a, 
     if (converged) return;
     const double beta = rz / st.absNew;
     const long long n = 3LL * a.nVerts;
-    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n; i += static_cast<long long>(gridDim.x) * kCgThreads)
-        a.p[i] = a.z[i] + beta * a.p[i];
+    constexpr int U = 4;
+    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
+    for (long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i0 < n; i0 += U * stride) {
+        double zv[U], pv[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n) zv[u] = a.z[i], pv[u] = a.p[i];
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = i0 + u * stride;
+            if (i < n) a.p[i] = zv[u] + beta * pv[u];
+        }
+    }
 }
 
 __global__ void axpbyKernel(double *out, double alpha, const double *a, double beta, const double *b, long long n)
