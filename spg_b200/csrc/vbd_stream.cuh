@@ -241,11 +241,14 @@ struct StreamRec {
         for (int k = 0; k < SK::NQ; ++k) q[k] = __ldg(qp + k * 32);
     }
     // P: the warp's neighbour tile, already offset to this lane's vertex column; element (k, c) at P[(3 k + c) * VW]
+    // ownOff >= 0: the owner's position is re-read from its tile row (element offset ownOff from P) instead of being
+    // held in registers across the whole incidence loop (6 registers less in the register-capped variants)
     template <int ST, int VW>
-    __device__ __forceinline__ void eval(const double *P, const V3d &xo, V3d &g, Sym3 &H) const
+    __device__ __forceinline__ void eval(const double *P, const V3d &xoReg, V3d &g, Sym3 &H, int ownOff = -1) const
     {
         using SK = Stream<ST>;
         if (idx == 0xFFFFFFFFu) return;
+        const V3d xo = ownOff >= 0 ? V3d(P[ownOff], P[ownOff + VW], P[ownOff + 2 * VW]) : xoReg;
         V3d xn[SK::NI];
 #pragma unroll
         for (int k = 0; k < SK::NI; ++k) {
@@ -320,16 +323,16 @@ struct StreamPipe {
     }
     template <int ST>
     __device__ __forceinline__ void evalFrom(const StreamRec<SMASK> &r, uint32_t s, const double *P, const V3d &xo, V3d &g,
-                                             Sym3 &H) const
+                                             Sym3 &H, int ownOff = -1) const
     {
         if constexpr (ST < kNumStreamTypes) {
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < cum[ST]) {
-                    r.template eval<ST, VW>(P, xo, g, H);
+                    r.template eval<ST, VW>(P, xo, g, H, ownOff);
                     return;
                 }
             }
-            evalFrom<ST + 1>(r, s, P, xo, g, H);
+            evalFrom<ST + 1>(r, s, P, xo, g, H, ownOff);
         }
     }
 };
@@ -370,7 +373,7 @@ constexpr int kStreamBlockThreads = 128;
 // The body of the colour pass; BT = threads per block.  Warps never synchronise with each other (each has its own tile),
 // so the block size only sets the granularity of the occupancy / register trade-off: vbdStreamKernel bounds registers by
 // resident 128-thread blocks (OCC), vbdStreamKernelR runs one-warp blocks under an explicit register cap.
-template <unsigned SMASK, unsigned KMASK, int G, int BT>
+template <unsigned SMASK, unsigned KMASK, int G, int BT, bool XS = false>
 __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
@@ -477,7 +480,10 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
     V3d xo(0.0, 0.0, 0.0);
-    if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
+    if constexpr (!XS) {
+        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
+    }
+    const int ownOff = XS ? a.maxNbr * (3 * VW) : -1;
 
     // 3. incidence streams.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
     // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
@@ -490,16 +496,19 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         int l = orderAfter(lane, r0.idx);
         if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
         if (a.l1pf && s + 2 < pipe.total) pipe.template prefetchL1From<0>(a, s + 2, lane);
-        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
+        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H, ownOff);
         if (s + 1 >= pipe.total) break;
         l = orderAfter(lane, r1.idx);
         if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
         if (a.l1pf && s + 3 < pipe.total) pipe.template prefetchL1From<0>(a, s + 3, lane);
-        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
+        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H, ownOff);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
     // 5. reduce, solve, write
+    if constexpr (XS) {
+        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
+    }
     const V3d xn = reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
     // 6. multi-GPU: boundary vertices of the slice go to the neighbours' halo slots over NVLink
     if (a.halo.nPeers) {
@@ -519,12 +528,12 @@ template <unsigned SMASK, unsigned KMASK, int G, int REGS>
 __global__ void __maxnreg__(REGS)
     vbdStreamKernelR(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
-    vbdStreamBody<SMASK, KMASK, G, 32>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
+    vbdStreamBody<SMASK, KMASK, G, 32, true>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
 }
 
 template <class Kernel>
-void launchStreamKernel(Kernel kernel, size_t &configured, int BT, const VbdArgs &args, int begin, int end, int sliceBase,
-                        double invdtSquared, int VW, cudaStream_t stream)
+void launchStreamKernel(Kernel kernel, size_t &configured, int BT, int occBlocks, const VbdArgs &args, int begin, int end,
+                        int sliceBase, double invdtSquared, int VW, cudaStream_t stream)
 {
     const int n = end - begin;
     if (n <= 0) return;
@@ -535,8 +544,9 @@ void launchStreamKernel(Kernel kernel, size_t &configured, int BT, const VbdArgs
     const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
-                             args.carveout >= 0 ? args.carveout : static_cast<int>(cudaSharedmemCarveoutMaxShared));
+        int pct = args.carveout;  // as in launchStreamGO: shared memory for the resident blocks, the rest stays L1
+        if (pct < 0) pct = static_cast<int>(std::min<size_t>(100, (occBlocks * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024) + 2));
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         configured = smem;
     }
     cudaLaunchConfig_t cfg{};
@@ -555,8 +565,8 @@ template <unsigned SMASK, unsigned KMASK, int G, int REGS>
 void launchStreamGR(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
 {
     static size_t configured = 0;  // per instantiation
-    launchStreamKernel(vbdStreamKernelR<SMASK, KMASK, G, REGS>, configured, 32, args, begin, end, sliceBase, invdtSquared, 32 / G,
-                       stream);
+    launchStreamKernel(vbdStreamKernelR<SMASK, KMASK, G, REGS>, configured, 32, 65536 / (32 * REGS), args, begin, end, sliceBase,
+                       invdtSquared, 32 / G, stream);
 }
 
 template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
