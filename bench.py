@@ -135,9 +135,10 @@ def time_oracle(cfg_id, frames, warmup, threads=None):
     import oracle_api
     builder, args, solver, substeps, iterations = CONFIGS[cfg_id]
     oracle = oracle_api.load()
-    if threads:
-        oracle.set_threads(threads)
-    cores = threads or oracle.max_threads()
+    # all the host threads this process may use (torchrun exports OMP_NUM_THREADS=1 to its workers: override it)
+    threads = threads or len(os.sched_getaffinity(0))
+    oracle.set_threads(threads)
+    cores = threads
     sc = build_scene(builder, args)
     og = oracle_api.OracleGroup(oracle, sc)
     osol = oracle_api.OracleSolver(og, {"vbd": 0, "xpbd": 1, "newton_dx": 4}[solver], DT, substeps, iterations)
@@ -257,6 +258,7 @@ def run_implicit(args):
     if not args.no_cpu_baseline:
         import oracle_api
         oracle = oracle_api.load()
+        oracle.set_threads(len(os.sched_getaffinity(0)))
         scs = build_scene("cloth", (64, 64))
         osol = oracle_api.OracleSolver(oracle_api.OracleGroup(oracle, scs), 4, DT, 1, 1)
         osol.step(1)
