@@ -782,7 +782,8 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             // opt-in: measured on B200 at config 2 the grid barrier (~4 us with 148 co-resident blocks) costs more than
             // the kernel boundary it replaces (~3 us per pass in a replayed graph): 2.43 vs 1.75 ms per frame
             grp->xpbdFused = 0;
-            if (const char *env = getenv("SPGX_XPBD_FUSED")) grp->xpbdFused = atoi(env) != 0;
+            if (const char *env = getenv("SPGX_XPBD_FUSED")) grp->xpbdFused = std::min(2, std::max(0, atoi(env)));
+            grp->d_xpbdBarrier.alloc(1);
         }
         // state: local vertices (owned + halo) on the device; the staging buffer spans the global index range
         const int nLocalAll = grp->nLocal;

@@ -127,6 +127,7 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
         fa.nPasses = static_cast<int>(grp->d_xpbdPasses.count);
         fa.nsub = nsub, fa.iters = iters, fa.useLambda = useLambda ? 1 : 0;
         fa.dt = dt, fa.invdt = invdt, fa.gx = grp->graphKey.g[0], fa.gy = grp->graphKey.g[1], fa.gz = grp->graphKey.g[2];
+        fa.barrier = grp->xpbdFused == 2 ? grp->d_xpbdBarrier.ptr : nullptr;
         if (launchXpbdFused(fa, st)) {
             grp->launchCounter++;
             return;

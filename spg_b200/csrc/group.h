@@ -221,7 +221,8 @@ struct spgx_group {
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // substep start, system assembled, linear system solved
     } newton;
     spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
-    int xpbdFused = 0;
+    int xpbdFused = 0;  // 0: one launch per pass, 1: cooperative kernel + cooperative-groups sync, 2: + hand-rolled barrier
+    spgx::DevBuf<unsigned> d_xpbdBarrier;
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
     spgx::DevBuf<int32_t> d_slot2vert;
     spgx::DevBuf<double> d_eval;

@@ -113,6 +113,7 @@ struct XpbdFusedArgs {
     const XpbdPassDev *passes;  // device array, reference order: energies in insertion order, colours ascending
     int nPasses, nsub, iters, useLambda;
     double dt, invdt, gx, gy, gz;  // dt of one substep
+    unsigned *barrier;             // one zeroed device word: arrival counter of the hand-rolled grid barrier (null: cooperative-groups sync)
 };
 // XPBD::step (xpbd.cpp:44-123) as ONE cooperative launch: predict, every (energy, colour) pass and finalize of every
 // substep, separated by grid-wide barriers instead of kernel boundaries (config 2 is launch-latency-bound: 27 passes of

@@ -240,15 +240,16 @@ def test_xpbd_fused_frame_equals_per_pass_launches(ctx, iters, monkeypatch):
     (energy, colour) pass, CUDA-graph replay and plain launches: the same per-stencil arithmetic, bit-identical."""
     sc = S.cloth(24, 19, S.K_SPRING, S.K_QUADRATIC_BENDING)
     results = {}
-    for name, fused, graph in (("fused", "1", True), ("passes_graph", "0", True), ("passes_plain", "0", False)):
+    for name, fused, graph in (("fused", "1", True), ("fused_barrier", "2", True), ("passes_graph", "0", True),
+                               ("passes_plain", "0", False)):
         monkeypatch.setenv("SPGX_XPBD_FUSED", fused)
         g = api.Group.from_scene(ctx, sc)
         g.finalize(api.SPGX_XPBD)
         g.set_graph_mode(graph)
         g.xpbd_step(0.01, 5, iters, frames=3)
         results[name] = g.download()
-        assert g.timings().kernel_launches == (3 if name == "fused" else g.timings().kernel_launches)
+        assert g.timings().kernel_launches == (3 if name.startswith("fused") else g.timings().kernel_launches)
         g.close()
-    for name in ("passes_graph", "passes_plain"):
+    for name in ("passes_graph", "passes_plain", "fused_barrier"):
         assert np.array_equal(results["fused"][0], results[name][0]), name
         assert np.array_equal(results["fused"][1], results[name][1]), name
