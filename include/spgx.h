@@ -76,7 +76,11 @@ enum spgx_solver_kind {
 enum spgx_implicit_kind {
     SPGX_IE_BARAFF_WITKIN = 0, /* spg/source/sim/solver/implicitEulerBaraffWitkin.cpp:11-59: (M - dt^2 K) dv = dt (f + dt K v0) */
     SPGX_IE_NEWTON_DX = 1,     /* .../implicitEulerNewtonDx.cpp:11-64: (M / dt^2 - K) dx = f at the inertial guess */
-    SPGX_IE_NEWTON_DV = 2      /* .../implicitEulerNewtonDv.cpp:11-67: (M - dt^2 K) dv = dt f at the inertial guess */
+    SPGX_IE_NEWTON_DV = 2,     /* .../implicitEulerNewtonDv.cpp:11-67: (M - dt^2 K) dv = dt f at the inertial guess */
+    SPGX_IE_BDF2 = 3,          /* .../bdf2.cpp:10-76: (M - 4/9 dt^2 K) dv = 1/3 M (v0 - v-1) + 2/3 dt (f + 1/3 K (x0 - x-1 + 2 dt v0));
+                                  the previous state (x-1, v-1) lives with the group, spgx_reset forgets it (bdf2.cpp:78-83) */
+    SPGX_IE_STATIC_NEWTON = 4, /* .../staticNewton.cpp:10-51: K dx = -f, positions only */
+    SPGX_IE_QUASI_STATIC_NEWTON = 5 /* .../quasiStaticNewton.cpp:10-55: (M - dt^2 K) dx = dt^2 f, positions only */
 };
 
 typedef struct spgx_ctx spgx_ctx;     /* one CUDA device + stream (+ optional NCCL communicator) */

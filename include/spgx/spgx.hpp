@@ -457,6 +457,30 @@ public:
 protected:
     int implicitKind() const override { return SPGX_IE_NEWTON_DV; }
 };
+class BDF2 : public ImplicitEulerBase  // bdf2.h:12-21 (reset() forgets the previous state: spgx_reset does)
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_BDF2; }
+};
+class StaticNewton : public ImplicitEulerBase  // staticNewton.h:12
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_STATIC_NEWTON; }
+};
+class QuasiStaticNewton : public ImplicitEulerBase  // quasiStaticNewton.h:11
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_QUASI_STATIC_NEWTON; }
+};
 class SimplecticEuler : public BaseSolver  // simplecticEuler.h:12-16 (the reference's spelling)
 {
 public:

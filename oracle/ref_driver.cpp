@@ -37,6 +37,9 @@
 #include <spg/sim/solver/implicitEulerNewtonDx.h>
 #include <spg/sim/solver/implicitEulerNewtonDv.h>
 #include <spg/sim/solver/simplecticEuler.h>
+#include <spg/sim/solver/bdf2.h>
+#include <spg/sim/solver/staticNewton.h>
+#include <spg/sim/solver/quasiStaticNewton.h>
 #include <spg/utils/graphColoring.h>
 
 #include <omp.h>
@@ -609,7 +612,8 @@ int ref_color_stencils_flat(const int32_t *entries, int nEntries, int stencilSiz
 // kind: 0 = VBD (vbd.cpp:12-195), 1 = XPBD parallel Gauss-Seidel (xpbd.cpp:16-131), 2 = XPBD serial,
 // 3 = ImplicitEulerBaraffWitkin (implicitEulerBaraffWitkin.cpp:11-59), 4 = ImplicitEulerNewtonDx
 // (implicitEulerNewtonDx.cpp:11-64), 5 = ImplicitEulerNewtonDv (implicitEulerNewtonDv.cpp:11-67),
-// 6 = SimplecticEuler (simplecticEuler.cpp:12-62).
+// 6 = SimplecticEuler (simplecticEuler.cpp:12-62), 7 = BDF2 (bdf2.cpp:10-76), 8 = StaticNewton (staticNewton.cpp:10-51),
+// 9 = QuasiStaticNewton (quasiStaticNewton.cpp:10-55).
 void *ref_solver_create(int kind, void *group, double dt, int substeps, int iterations, const double *gravity)
 {
     auto *s = new RefSolver;
@@ -625,6 +629,12 @@ void *ref_solver_create(int kind, void *group, double dt, int substeps, int iter
         makeImplicit<spg::solver::ImplicitEulerNewtonDv>(*s);
     } else if (kind == 6) {
         s->other = std::make_unique<spg::solver::SimplecticEuler>();
+    } else if (kind == 7) {
+        makeImplicit<spg::solver::BDF2>(*s);
+    } else if (kind == 8) {
+        makeImplicit<spg::solver::StaticNewton>(*s);
+    } else if (kind == 9) {
+        makeImplicit<spg::solver::QuasiStaticNewton>(*s);
     } else {
         s->xpbd = std::make_unique<OracleXPBD>(kind == 1);
     }

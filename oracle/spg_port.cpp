@@ -814,7 +814,7 @@ inline std::vector<int> colorStencils(const int *ent, int64_t nEnt, int S)
 // ---------------------------------------------------------------------------------------------------------------------
 struct Solver {
     int kind = 0;  // 0 VBD, 1 XPBD parallel Gauss-Seidel, 2 XPBD serial, 3 implicit Euler Baraff-Witkin, 4 Newton dx,
-                   // 5 Newton dv, 6 symplectic Euler
+                   // 5 Newton dv, 6 symplectic Euler, 7 BDF2, 8 static Newton, 9 quasi-static Newton
     Group g;
     double dt = 0.01, gravity[3] = {0, -9.8, 0};
     int substeps = 1, iterations = 1;
@@ -824,6 +824,7 @@ struct Solver {
     std::vector<std::vector<std::vector<int>>> stencilGroups;           // per energy, xpbd.cpp:133-160
     std::vector<double> xOld, xInertial;
     std::vector<int> cgIterations;  // implicit-Euler family: one entry per linear solve of the last step call
+    std::vector<double> xMinusOne, vMinusOne;  // BDF2 (bdf2.h:19-20)
 };
 
 inline void groupBy(const std::vector<int> &colors, std::vector<std::vector<int>> &groups)
@@ -1130,6 +1131,38 @@ inline void implicitStep(Solver &s)
                 g.x[i] += sol[i];
                 g.v[i] = (g.x[i] - x0[i]) * invdt;
             }
+        } else if (s.kind == 7) {  // BDF2::step, bdf2.cpp:31-70
+            const std::vector<double> x0 = g.x, v0 = g.v;
+            if (s.xMinusOne.size() != n || s.vMinusOne.size() != n) s.xMinusOne = x0, s.vMinusOne = v0;
+            systemForce(s, f);
+            const Csr M = systemMass(s), K = systemStiffness(s);
+            const Csr lhs = combine(1.0, M, -(4.0 / 9.0 * (dt * dt)), K);
+            std::vector<double> w(n), Kw, dvm(n), Mdv;
+            for (size_t i = 0; i < n; ++i) w[i] = x0[i] - s.xMinusOne[i] + 2 * dt * v0[i];
+            spmv(K, w, Kw);
+            for (size_t i = 0; i < n; ++i) dvm[i] = v0[i] - s.vMinusOne[i];
+            spmv(M, dvm, Mdv);
+            for (size_t i = 0; i < n; ++i) rhs[i] = 1.0 / 3.0 * Mdv[i] + 2.0 / 3.0 * dt * (f[i] + 1.0 / 3.0 * Kw[i]);
+            s.cgIterations.push_back(conjugateGradient(lhs, rhs, sol));
+            for (size_t i = 0; i < n; ++i) {
+                g.v[i] = v0[i] + sol[i];
+                g.x[i] = 4.0 / 3.0 * x0[i] - 1.0 / 3.0 * s.xMinusOne[i] + 2.0 / 3.0 * g.v[i] * dt;
+            }
+            s.xMinusOne = x0;
+            s.vMinusOne = v0;
+        } else if (s.kind == 8) {  // StaticNewton::step, staticNewton.cpp:29-45: K dx = -f
+            systemForce(s, f);
+            const Csr K = systemStiffness(s);
+            for (size_t i = 0; i < n; ++i) rhs[i] = -f[i];
+            s.cgIterations.push_back(conjugateGradient(K, rhs, sol));
+            for (size_t i = 0; i < n; ++i) g.x[i] += sol[i];
+        } else if (s.kind == 9) {  // QuasiStaticNewton::step, quasiStaticNewton.cpp:31-49: (M - dt^2 K) dx = dt^2 f
+            systemForce(s, f);
+            const Csr M = systemMass(s), K = systemStiffness(s);
+            const Csr lhs = combine(1.0, M, -(dt * dt), K);
+            for (size_t i = 0; i < n; ++i) rhs[i] = dt * dt * f[i];
+            s.cgIterations.push_back(conjugateGradient(lhs, rhs, sol));
+            for (size_t i = 0; i < n; ++i) g.x[i] += sol[i];
         } else {
             const std::vector<double> x0 = g.x, v0 = g.v;
             const Csr M = systemMass(s);
@@ -1399,7 +1432,7 @@ int ref_solver_step(void *h, int nFrames)
         for (int f = 0; f < nFrames; ++f) {
             if (s->kind == 0)
                 vbdStep(*s);
-            else if (s->kind >= 3 && s->kind <= 5)
+            else if ((s->kind >= 3 && s->kind <= 5) || (s->kind >= 7 && s->kind <= 9))
                 implicitStep(*s);
             else if (s->kind == 6)
                 symplecticStep(*s);
@@ -1454,6 +1487,8 @@ int ref_solver_reset(void *h)  // ParticleGroup::reset, particleGroup.cpp:97-103
         auto *s = static_cast<Solver *>(h);
         s->g.x = s->g.xInitial;
         std::fill(s->g.v.begin(), s->g.v.end(), 0.0);
+        s->xMinusOne.clear();  // BDF2::reset, bdf2.cpp:78-83
+        s->vMinusOne.clear();
     });
 }
 void ref_solver_get_state(void *h, double *x, double *v) { ref_group_get_state(&static_cast<Solver *>(h)->g, x, v); }

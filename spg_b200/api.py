@@ -21,7 +21,7 @@ if not _LIB_PATH.exists():
 lib = C.CDLL(str(_LIB_PATH))
 
 SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL, SPGX_NEWTON = 0, 1, 2, 3
-SPGX_IE_BARAFF_WITKIN, SPGX_IE_NEWTON_DX, SPGX_IE_NEWTON_DV = 0, 1, 2
+SPGX_IE_BARAFF_WITKIN, SPGX_IE_NEWTON_DX, SPGX_IE_NEWTON_DV, SPGX_IE_BDF2, SPGX_IE_STATIC_NEWTON, SPGX_IE_QUASI_STATIC_NEWTON = range(6)
 SPGX_HALO_NONE, SPGX_HALO_NCCL, SPGX_HALO_P2P = 0, 1, 2
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
@@ -542,6 +542,18 @@ class ImplicitEulerNewtonDx(_ImplicitEuler):
 
 class ImplicitEulerNewtonDv(_ImplicitEuler):
     implicit_kind = SPGX_IE_NEWTON_DV
+
+
+class BDF2(_ImplicitEuler):
+    implicit_kind = SPGX_IE_BDF2
+
+
+class StaticNewton(_ImplicitEuler):
+    implicit_kind = SPGX_IE_STATIC_NEWTON
+
+
+class QuasiStaticNewton(_ImplicitEuler):
+    implicit_kind = SPGX_IE_QUASI_STATIC_NEWTON
 
 
 class SimplecticEuler(_BaseSolver):

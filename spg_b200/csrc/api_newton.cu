@@ -1,9 +1,9 @@
-// C-ABI, part 3: the implicit-Euler family (ImplicitEulerBaraffWitkin, ImplicitEulerNewtonDx, ImplicitEulerNewtonDv) and
-// symplectic Euler on a group finalized with SPGX_NEWTON.
+// C-ABI, part 3: the implicit-Euler family (ImplicitEulerBaraffWitkin, ImplicitEulerNewtonDx, ImplicitEulerNewtonDv, BDF2,
+// StaticNewton, QuasiStaticNewton) and symplectic Euler on a group finalized with SPGX_NEWTON.
 //
 // Reference: spg/source/sim/solver/implicitEulerBase.cpp (system force / stiffness / mass, linear solve),
-// implicitEulerBaraffWitkin.cpp:31-54, implicitEulerNewtonDx.cpp:31-59, implicitEulerNewtonDv.cpp:30-62,
-// simplecticEuler.cpp:12-62.  The reference rebuilds a triplet list, two Eigen sparse matrices and a fresh CG object
+// implicitEulerBaraffWitkin.cpp:31-54, implicitEulerNewtonDx.cpp:31-59, implicitEulerNewtonDv.cpp:30-62, bdf2.cpp:31-70,
+// staticNewton.cpp:29-45, quasiStaticNewton.cpp:31-49, simplecticEuler.cpp:12-62.  The reference rebuilds a triplet list, two Eigen sparse matrices and a fresh CG object
 // every substep on the host; here the sparse pattern is fixed at finalize time and a substep is: element Hessians ->
 // block gather -> device-resident CG (newton.cu), with the host only polling the convergence flag.
 #include <algorithm>
@@ -81,7 +81,7 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
         nw.elemHessianBytes += 8.0 * e.n * 9 * e.S * e.S;
     }
     const size_t n3 = 3 * static_cast<size_t>(V);
-    for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0})
+    for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0, &nw.d_xm1, &nw.d_vm1})
         b->alloc(n3);
     nw.d_partials.alloc(3 * kCgBlocks);
     nw.d_state.alloc(2);
@@ -89,6 +89,7 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
     for (auto &e : nw.ev)
         if (!e) SPGX_CUDA(cudaEventCreate(&e));
     nw.assembled = false;
+    nw.bdf2Init = false;
     nw.cgIterations.clear();
 }
 }  // namespace spgx
@@ -193,7 +194,7 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
 {
     return guarded([&] {
         requireNewton(grp);
-        if (implicitKind < SPGX_IE_BARAFF_WITKIN || implicitKind > SPGX_IE_NEWTON_DV) throw std::runtime_error("unknown implicit solver kind");
+        if (implicitKind < SPGX_IE_BARAFF_WITKIN || implicitKind > SPGX_IE_QUASI_STATIC_NEWTON) throw std::runtime_error("unknown implicit solver kind");
         if (nsubsteps < 1 || nFrames < 0 || cgMaxIterations < 0) throw std::runtime_error("invalid step parameters");
         cudaStream_t st = grp->ctx->stream;
         auto &nw = grp->newton;
@@ -248,6 +249,49 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
                     phase(2);
                     collect();
                     launchApplyDx(x, v, nw.d_sol.ptr, nw.d_x0.ptr, invh, n3, st);
+                    grp->launchCounter += 1;
+                } else if (implicitKind == SPGX_IE_BDF2) {
+                    // (M - 4/9 h^2 K) dv = 1/3 M (v0 - v-1) + 2/3 h (f + 1/3 K (x0 - x-1 + 2 h v0));
+                    // v = v0 + dv; x = 4/3 x0 - 1/3 x-1 + 2/3 h v   (K = -H)
+                    if (!nw.bdf2Init) {
+                        copyD2D(nw.d_xm1.ptr, x, n3, st);
+                        copyD2D(nw.d_vm1.ptr, v, n3, st);
+                        nw.bdf2Init = true;
+                    }
+                    const NewtonArgs a = newtonArgs(grp);
+                    launchSystemForce(a, g, nw.d_f.ptr, st);
+                    assembleHessian(grp, st);
+                    launchAxpby(nw.d_x0.ptr, 1.0, x, -1.0, nw.d_xm1.ptr, n3, st);             // w = x0 - x-1
+                    launchAxpby(nw.d_x0.ptr, 1.0, nw.d_x0.ptr, 2.0 * h, v, n3, st);           //     + 2 h v0
+                    launchBsrSpmv(cgArgs(grp, 0.0, 1.0), nw.d_x0.ptr, nw.d_tmp.ptr, st);       // H w = -K w
+                    launchAxpby(nw.d_rhs.ptr, 2.0 / 3.0 * h, nw.d_f.ptr, -2.0 / 9.0 * h, nw.d_tmp.ptr, n3, st);
+                    launchAddMassDiff(nw.d_rhs.ptr, 1.0 / 3.0, grp->d_mass.ptr, v, nw.d_vm1.ptr, grp->nVerts, st);
+                    grp->launchCounter += 6;
+                    phase(1);
+                    nw.cgIterations.push_back(conjugateGradient(grp, 1.0, 4.0 / 9.0 * h * h, nw.d_rhs.ptr, cgTolerance, cgMaxIterations, st));
+                    phase(2);
+                    collect();
+                    copyD2D(nw.d_vm1.ptr, v, n3, st);                                          // v-1 <- v0
+                    launchAxpby(v, 1.0, v, 1.0, nw.d_sol.ptr, n3, st);                         // v = v0 + dv
+                    copyD2D(nw.d_x0.ptr, x, n3, st);                                           // x0
+                    launchAxpby(x, 4.0 / 3.0, nw.d_x0.ptr, -1.0 / 3.0, nw.d_xm1.ptr, n3, st);
+                    launchAxpby(x, 1.0, x, 2.0 / 3.0 * h, v, n3, st);
+                    copyD2D(nw.d_xm1.ptr, nw.d_x0.ptr, n3, st);                                // x-1 <- x0
+                    grp->launchCounter += 3;
+                } else if (implicitKind == SPGX_IE_STATIC_NEWTON || implicitKind == SPGX_IE_QUASI_STATIC_NEWTON) {
+                    // static: K dx = -f, i.e. (0 M - 1 H) dx = -f; quasi-static: (M - h^2 K) dx = h^2 f; x += dx
+                    const bool quasi = implicitKind == SPGX_IE_QUASI_STATIC_NEWTON;
+                    const NewtonArgs a = newtonArgs(grp);
+                    launchSystemForce(a, g, nw.d_f.ptr, st);
+                    assembleHessian(grp, st);
+                    launchAxpby(nw.d_rhs.ptr, quasi ? h * h : -1.0, nw.d_f.ptr, 0.0, nw.d_f.ptr, n3, st);
+                    grp->launchCounter += 2;
+                    phase(1);
+                    nw.cgIterations.push_back(conjugateGradient(grp, quasi ? 1.0 : 0.0, quasi ? h * h : -1.0, nw.d_rhs.ptr, cgTolerance,
+                                                                cgMaxIterations, st));
+                    phase(2);
+                    collect();
+                    launchAxpby(x, 1.0, x, 1.0, nw.d_sol.ptr, n3, st);  // updateObjectsPositionsFromDx (implicitEulerBase.cpp:90-100)
                     grp->launchCounter += 1;
                 } else {
                     // x0, v0; x += v h; f, K there; (M - h^2 K) dv = h f; x = x0; v = v0 + dv; x += v h

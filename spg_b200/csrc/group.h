@@ -212,6 +212,8 @@ struct spgx_group {
         spgx::DevBuf<double> d_bsrH;
         std::vector<spgx::DevBuf<double>> d_elemH;  // per energy
         spgx::DevBuf<double> d_f, d_rhs, d_sol, d_r, d_p, d_z, d_tmp, d_invdiag, d_x0, d_v0;
+        spgx::DevBuf<double> d_xm1, d_vm1;   // BDF2: the state before the previous substep (bdf2.h:19-20)
+        bool bdf2Init = false;
         spgx::DevBuf<double> d_partials;
         spgx::DevBuf<spgx::CgState> d_state;
         spgx::CgState *hostState = nullptr;  // pinned

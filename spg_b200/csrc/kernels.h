@@ -184,6 +184,8 @@ void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t str
 void launchCgIteration(const CgArgs &a, int it, cudaStream_t stream);
 // out = alpha * a + beta * b over n doubles (out may alias a or b)
 void launchAxpby(double *out, double alpha, const double *a, double beta, const double *b, long long n, cudaStream_t stream);
+// out += c * mass[vertex] * (a - b): the M (v0 - v-1) term of BDF2 (bdf2.cpp:53) without a mass matrix
+void launchAddMassDiff(double *out, double c, const double *mass, const double *a, const double *b, int nVerts, cudaStream_t stream);
 // x += dx; v = (x - x0) * invdt  (integrateObjectsVelocitiesFromDx, implicitEulerBase.cpp:76-88)
 void launchApplyDx(double *x, double *v, const double *dx, const double *x0, double invdt, long long n, cudaStream_t stream);
 // SimplecticEuler::step velocity update (simplecticEuler.cpp:23-48): v += dt g; v += w * fInternal * dt; then x += v dt

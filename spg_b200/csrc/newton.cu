@@ -474,6 +474,12 @@ __global__ void axpbyKernel(double *out, double alpha, const double *a, double b
     const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) out[i] = alpha * a[i] + beta * b[i];
 }
+__global__ void addMassDiffKernel(double *__restrict__ out, double c, const double *__restrict__ mass, const double *__restrict__ a,
+                                  const double *__restrict__ b, long long n3)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n3) out[i] += c * (mass[i / 3] * (a[i] - b[i]));
+}
 __global__ void applyDxKernel(double *__restrict__ x, double *__restrict__ v, const double *__restrict__ dx,
                               const double *__restrict__ x0, double invdt, long long n)
 {
@@ -549,6 +555,13 @@ void launchAxpby(double *out, double alpha, const double *a, double beta, const 
 {
     if (n == 0) return;
     axpbyKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(out, alpha, a, beta, b, n);
+}
+
+void launchAddMassDiff(double *out, double c, const double *mass, const double *a, const double *b, int nVerts, cudaStream_t stream)
+{
+    const long long n3 = 3LL * nVerts;
+    if (n3 == 0) return;
+    addMassDiffKernel<<<static_cast<unsigned>((n3 + 255) / 256), 256, 0, stream>>>(out, c, mass, a, b, n3);
 }
 
 void launchApplyDx(double *x, double *v, const double *dx, const double *x0, double invdt, long long n, cudaStream_t stream)

@@ -16,7 +16,7 @@ import make_golden as MG  # noqa: E402
 from spg_b200 import scenes as S  # noqa: E402
 
 # oracle solver kinds (oracle/ref_driver.cpp: ref_solver_create)
-BW, NDX, NDV, SYMPLECTIC = 3, 4, 5, 6
+BW, NDX, NDV, SYMPLECTIC, BDF2, STATIC, QUASI = 3, 4, 5, 6, 7, 8, 9
 SCENES = {
     "cloth12": lambda: S.cloth(12, 12),
     "cloth10_quad": lambda: S.cloth(10, 10, S.K_SPRING, S.K_QUADRATIC_BENDING),
@@ -30,6 +30,13 @@ for _sc in SCENES:
     for _k, _kn in ((BW, "bw"), (NDX, "ndx"), (NDV, "ndv")):
         STEP_CASES[f"{_kn}_{_sc}"] = (_sc, _k, 1, 2)
 STEP_CASES["ndx_cloth12_3sub"] = ("cloth12", NDX, 3, 1)
+# BDF2 (keeps the previous state across substeps and frames), quasi-static and static Newton (the static solve needs a
+# scene without zero-energy modes: the anchored beams)
+for _sc in ("cloth12", "cloth10_quad", "beam_snh"):
+    STEP_CASES[f"bdf2_{_sc}"] = (_sc, BDF2, 2, 2)
+    STEP_CASES[f"quasi_{_sc}"] = (_sc, QUASI, 1, 3)
+for _sc in ("beam_snh", "beam_stvk"):
+    STEP_CASES[f"static_{_sc}"] = (_sc, STATIC, 1, 3)
 STEP_CASES["symplectic_cloth10_quad"] = ("cloth10_quad", SYMPLECTIC, 200, 1)
 STEP_CASES["symplectic_beam_snh"] = ("beam_snh", SYMPLECTIC, 400, 1)
 

@@ -175,7 +175,7 @@ def test_gpu_linear_solve_vs_oracle(ctx, oracle, name):
     g.close()
 
 
-_GPU_KIND = {MI.BW: 0, MI.NDX: 1, MI.NDV: 2}
+_GPU_KIND = {MI.BW: 0, MI.NDX: 1, MI.NDV: 2, MI.BDF2: 3, MI.STATIC: 4, MI.QUASI: 5}
 
 
 @pytest.mark.gpu
@@ -236,4 +236,19 @@ def test_gpu_newton_state_errors(ctx):
     g.implicit_step(1, 0.01)
     x, _ = g.download()
     assert np.isfinite(x).all()
+    g.close()
+
+
+@pytest.mark.gpu
+def test_gpu_bdf2_reset_forgets_previous_state(ctx):
+    """BDF2::reset (bdf2.cpp:78-83) drops x-1 / v-1: a run after reset repeats the first run bit for bit"""
+    from spg_b200 import api
+    g = api.Group.from_scene(ctx, S.cloth(9, 9))
+    g.finalize(api.SPGX_NEWTON)
+    g.implicit_step(api.SPGX_IE_BDF2, 0.01, 2, frames=2)
+    first = g.download()
+    g.reset()
+    g.implicit_step(api.SPGX_IE_BDF2, 0.01, 2, frames=2)
+    second = g.download()
+    assert np.array_equal(first[0], second[0]) and np.array_equal(first[1], second[1])
     g.close()
