@@ -80,7 +80,12 @@ enum spgx_implicit_kind {
     SPGX_IE_BDF2 = 3,          /* .../bdf2.cpp:10-76: (M - 4/9 dt^2 K) dv = 1/3 M (v0 - v-1) + 2/3 dt (f + 1/3 K (x0 - x-1 + 2 dt v0));
                                   the previous state (x-1, v-1) lives with the group, spgx_reset forgets it (bdf2.cpp:78-83) */
     SPGX_IE_STATIC_NEWTON = 4, /* .../staticNewton.cpp:10-51: K dx = -f, positions only */
-    SPGX_IE_QUASI_STATIC_NEWTON = 5 /* .../quasiStaticNewton.cpp:10-55: (M - dt^2 K) dx = dt^2 f, positions only */
+    SPGX_IE_QUASI_STATIC_NEWTON = 5, /* .../quasiStaticNewton.cpp:10-55: (M - dt^2 K) dx = dt^2 f, positions only */
+    /* the two adaptive solvers: up to 5 Newton iterations per substep, each with a halving line search (up to 5 trials)
+     * on the residual norm; a substep that does not reach the residual threshold is rolled back and the solver's own time
+     * step shrinks by 0.75, five good substeps in a row let it grow back (state kept with the group, cleared by spgx_reset) */
+    SPGX_IE_NEWTON_ROBUST = 6,             /* .../implicitEulerNewtonRobust.cpp:11-130, threshold 1e-5 on |dt f - M (v - v0)| */
+    SPGX_IE_QUASI_STATIC_NEWTON_ROBUST = 7 /* .../quasiStaticNewtonRobust.cpp:11-128, threshold 1e-2 on |f - M (x - x0) / dt^2| */
 };
 
 typedef struct spgx_ctx spgx_ctx;     /* one CUDA device + stream (+ optional NCCL communicator) */

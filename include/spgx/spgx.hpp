@@ -481,6 +481,22 @@ public:
 protected:
     int implicitKind() const override { return SPGX_IE_QUASI_STATIC_NEWTON; }
 };
+class ImplicitEulerNewtonRobust : public ImplicitEulerBase  // implicitEulerNewtonRobust.h:12-28
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_NEWTON_ROBUST; }
+};
+class QuasiStaticNewtonRobust : public ImplicitEulerBase  // quasiStaticNewtonRobust.h:12-31
+{
+public:
+    using ImplicitEulerBase::ImplicitEulerBase;
+
+protected:
+    int implicitKind() const override { return SPGX_IE_QUASI_STATIC_NEWTON_ROBUST; }
+};
 class SimplecticEuler : public BaseSolver  // simplecticEuler.h:12-16 (the reference's spelling)
 {
 public:

@@ -40,6 +40,8 @@
 #include <spg/sim/solver/bdf2.h>
 #include <spg/sim/solver/staticNewton.h>
 #include <spg/sim/solver/quasiStaticNewton.h>
+#include <spg/sim/solver/implicitEulerNewtonRobust.h>
+#include <spg/sim/solver/quasiStaticNewtonRobust.h>
 #include <spg/utils/graphColoring.h>
 
 #include <omp.h>
@@ -613,7 +615,8 @@ int ref_color_stencils_flat(const int32_t *entries, int nEntries, int stencilSiz
 // 3 = ImplicitEulerBaraffWitkin (implicitEulerBaraffWitkin.cpp:11-59), 4 = ImplicitEulerNewtonDx
 // (implicitEulerNewtonDx.cpp:11-64), 5 = ImplicitEulerNewtonDv (implicitEulerNewtonDv.cpp:11-67),
 // 6 = SimplecticEuler (simplecticEuler.cpp:12-62), 7 = BDF2 (bdf2.cpp:10-76), 8 = StaticNewton (staticNewton.cpp:10-51),
-// 9 = QuasiStaticNewton (quasiStaticNewton.cpp:10-55).
+// 9 = QuasiStaticNewton (quasiStaticNewton.cpp:10-55), 10 = ImplicitEulerNewtonRobust (implicitEulerNewtonRobust.cpp:11-137),
+// 11 = QuasiStaticNewtonRobust (quasiStaticNewtonRobust.cpp:11-151).
 void *ref_solver_create(int kind, void *group, double dt, int substeps, int iterations, const double *gravity)
 {
     auto *s = new RefSolver;
@@ -635,6 +638,10 @@ void *ref_solver_create(int kind, void *group, double dt, int substeps, int iter
         makeImplicit<spg::solver::StaticNewton>(*s);
     } else if (kind == 9) {
         makeImplicit<spg::solver::QuasiStaticNewton>(*s);
+    } else if (kind == 10) {
+        makeImplicit<spg::solver::ImplicitEulerNewtonRobust>(*s);
+    } else if (kind == 11) {
+        makeImplicit<spg::solver::QuasiStaticNewtonRobust>(*s);
     } else {
         s->xpbd = std::make_unique<OracleXPBD>(kind == 1);
     }

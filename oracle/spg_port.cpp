@@ -814,7 +814,8 @@ inline std::vector<int> colorStencils(const int *ent, int64_t nEnt, int S)
 // ---------------------------------------------------------------------------------------------------------------------
 struct Solver {
     int kind = 0;  // 0 VBD, 1 XPBD parallel Gauss-Seidel, 2 XPBD serial, 3 implicit Euler Baraff-Witkin, 4 Newton dx,
-                   // 5 Newton dv, 6 symplectic Euler, 7 BDF2, 8 static Newton, 9 quasi-static Newton
+                   // 5 Newton dv, 6 symplectic Euler, 7 BDF2, 8 static Newton, 9 quasi-static Newton, 10 Newton robust,
+                   // 11 quasi-static Newton robust
     Group g;
     double dt = 0.01, gravity[3] = {0, -9.8, 0};
     int substeps = 1, iterations = 1;
@@ -825,6 +826,8 @@ struct Solver {
     std::vector<double> xOld, xInertial;
     std::vector<int> cgIterations;  // implicit-Euler family: one entry per linear solve of the last step call
     std::vector<double> xMinusOne, vMinusOne;  // BDF2 (bdf2.h:19-20)
+    double currentDt = -1.;                    // the adaptive solvers (implicitEulerNewtonRobust.h:21-22)
+    int consecutiveSuccessfulSteps = 0;
 };
 
 inline void groupBy(const std::vector<int> &colors, std::vector<std::vector<int>> &groups)
@@ -1178,6 +1181,90 @@ inline void implicitStep(Solver &s)
         }
     }
 }
+// ImplicitEulerNewtonRobust::step (implicitEulerNewtonRobust.cpp:31-127) and QuasiStaticNewtonRobust::step
+// (quasiStaticNewtonRobust.cpp:33-125): up to 5 Newton iterations per substep, each followed by a halving line search on
+// the residual norm; failed substeps are rolled back and shrink the solver's own time step.
+inline void robustStep(Solver &s)
+{
+    Group &g = s.g;
+    const bool quasi = s.kind == 11;
+    const size_t n = g.x.size();
+    const double threshold = quasi ? 1e-2 : 1e-5;
+    for (int sub = 0; sub < s.substeps; ++sub) {
+        bool successful = true;
+        const double maxDt = s.dt / s.substeps;
+        if (s.currentDt == -1. || s.currentDt > maxDt) s.currentDt = maxDt;
+        const double dt = s.currentDt, invdt = 1 / dt, invdtSquared = invdt * invdt;
+        const std::vector<double> x0 = g.x, v0 = g.v;
+        if (!quasi) integrateVelocities(g, dt);
+        std::vector<double> it = quasi ? x0 : v0;  // xi / vi
+        std::vector<double> f, rhs(n), sol;
+        auto residual = [&](std::vector<double> *out) {
+            double acc = 0;
+            for (size_t i = 0; i < n; ++i) {
+                const double r = quasi ? f[i] - invdt * (g.mass[i / 3] * g.v[i]) : dt * f[i] - g.mass[i / 3] * (g.v[i] - v0[i]);
+                if (out) (*out)[i] = r;
+                acc += r * r;
+            }
+            return std::sqrt(acc);
+        };
+        double stepResidual = 0;
+        int newton = 0;
+        do {
+            systemForce(s, f);
+            const Csr M = systemMass(s), K = systemStiffness(s);
+            double initialResidual;
+            Csr lhs;
+            if (quasi) {
+                lhs = combine(invdtSquared, M, -1.0, K);
+                for (size_t i = 0; i < n; ++i) g.v[i] = (g.x[i] - x0[i]) * invdt;  // computeSystemIntegratedVelocities
+                initialResidual = residual(&rhs);
+            } else {
+                lhs = combine(1.0, M, -(dt * dt), K);
+                double acc = 0;  // RHS uses the accepted iterate vi, not the state's velocities (:66)
+                for (size_t i = 0; i < n; ++i) {
+                    rhs[i] = dt * f[i] - g.mass[i / 3] * (it[i] - v0[i]);
+                    acc += rhs[i] * rhs[i];
+                }
+                initialResidual = std::sqrt(acc);
+            }
+            s.cgIterations.push_back(conjugateGradient(lhs, rhs, sol));
+            stepResidual = initialResidual;
+            int ls = 0;
+            double alpha = 1.;
+            while (stepResidual >= initialResidual && ls < 5) {
+                if (quasi) {
+                    for (size_t i = 0; i < n; ++i) {
+                        g.x[i] = it[i] + sol[i] * alpha;
+                        g.v[i] = (g.x[i] - x0[i]) * invdt;
+                    }
+                } else {
+                    for (size_t i = 0; i < n; ++i) {
+                        g.v[i] = it[i] + sol[i] * alpha;
+                        g.x[i] = x0[i] + g.v[i] * dt;
+                    }
+                }
+                systemForce(s, f);
+                stepResidual = residual(nullptr);
+                if (stepResidual < initialResidual) it = quasi ? g.x : g.v;
+                alpha *= 0.5;
+                ++ls;
+            }
+            if (stepResidual >= initialResidual && stepResidual > threshold) successful = false;
+            ++newton;
+        } while (stepResidual > threshold && successful && newton < 5);
+        if (stepResidual > threshold) successful = false;
+        if (!successful) {
+            g.x = x0;
+            if (!quasi) g.v = v0;
+            s.currentDt *= 0.75;
+            s.consecutiveSuccessfulSteps = 0;
+        } else {
+            s.consecutiveSuccessfulSteps++;
+            if (s.consecutiveSuccessfulSteps > 5 && s.currentDt < maxDt) s.currentDt /= 0.75;
+        }
+    }
+}
 // SimplecticEuler::step (simplecticEuler.cpp:12-62) with updateExplicitVelocities (energy.h:154-194):
 // v += dt g; per stencil v_s += w_s (-grad_s) dt; x += v dt
 inline void symplecticStep(Solver &s)
@@ -1436,6 +1523,8 @@ int ref_solver_step(void *h, int nFrames)
                 implicitStep(*s);
             else if (s->kind == 6)
                 symplecticStep(*s);
+            else if (s->kind == 10 || s->kind == 11)
+                robustStep(*s);
             else
                 xpbdStep(*s);
         }
@@ -1489,6 +1578,8 @@ int ref_solver_reset(void *h)  // ParticleGroup::reset, particleGroup.cpp:97-103
         std::fill(s->g.v.begin(), s->g.v.end(), 0.0);
         s->xMinusOne.clear();  // BDF2::reset, bdf2.cpp:78-83
         s->vMinusOne.clear();
+        s->currentDt = -1.;    // ImplicitEulerNewtonRobust::reset, implicitEulerNewtonRobust.cpp:132-137
+        s->consecutiveSuccessfulSteps = 0;
     });
 }
 void ref_solver_get_state(void *h, double *x, double *v) { ref_group_get_state(&static_cast<Solver *>(h)->g, x, v); }

@@ -21,7 +21,8 @@ if not _LIB_PATH.exists():
 lib = C.CDLL(str(_LIB_PATH))
 
 SPGX_VBD, SPGX_XPBD, SPGX_XPBD_SERIAL, SPGX_NEWTON = 0, 1, 2, 3
-SPGX_IE_BARAFF_WITKIN, SPGX_IE_NEWTON_DX, SPGX_IE_NEWTON_DV, SPGX_IE_BDF2, SPGX_IE_STATIC_NEWTON, SPGX_IE_QUASI_STATIC_NEWTON = range(6)
+(SPGX_IE_BARAFF_WITKIN, SPGX_IE_NEWTON_DX, SPGX_IE_NEWTON_DV, SPGX_IE_BDF2, SPGX_IE_STATIC_NEWTON, SPGX_IE_QUASI_STATIC_NEWTON,
+ SPGX_IE_NEWTON_ROBUST, SPGX_IE_QUASI_STATIC_NEWTON_ROBUST) = range(8)
 SPGX_HALO_NONE, SPGX_HALO_NCCL, SPGX_HALO_P2P = 0, 1, 2
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
@@ -554,6 +555,14 @@ class StaticNewton(_ImplicitEuler):
 
 class QuasiStaticNewton(_ImplicitEuler):
     implicit_kind = SPGX_IE_QUASI_STATIC_NEWTON
+
+
+class ImplicitEulerNewtonRobust(_ImplicitEuler):
+    implicit_kind = SPGX_IE_NEWTON_ROBUST
+
+
+class QuasiStaticNewtonRobust(_ImplicitEuler):
+    implicit_kind = SPGX_IE_QUASI_STATIC_NEWTON_ROBUST
 
 
 class SimplecticEuler(_BaseSolver):

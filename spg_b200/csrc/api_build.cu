@@ -727,9 +727,11 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
             {
                 CgState *pinned = grp->newton.hostState;
+                double *pinnedScalar = grp->newton.hostScalar;
                 cudaEvent_t ev[3] = {grp->newton.ev[0], grp->newton.ev[1], grp->newton.ev[2]};
                 grp->newton = spgx_group::NewtonState{};
                 grp->newton.hostState = pinned;
+                grp->newton.hostScalar = pinnedScalar;
                 for (int k = 0; k < 3; ++k) grp->newton.ev[k] = ev[k];
             }
             grp->nOwned = grp->nLocal = V;

@@ -81,11 +81,16 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
         nw.elemHessianBytes += 8.0 * e.n * 9 * e.S * e.S;
     }
     const size_t n3 = 3 * static_cast<size_t>(V);
-    for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0, &nw.d_xm1, &nw.d_vm1})
+    for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0, &nw.d_xm1, &nw.d_vm1,
+                    &nw.d_xi})
         b->alloc(n3);
     nw.d_partials.alloc(3 * kCgBlocks);
     nw.d_state.alloc(2);
     if (!nw.hostState) SPGX_CUDA(cudaMallocHost(&nw.hostState, sizeof(CgState)));
+    if (!nw.hostScalar) SPGX_CUDA(cudaMallocHost(&nw.hostScalar, sizeof(double)));
+    nw.d_scalar.alloc(1);
+    nw.currentDt = -1.0;
+    nw.consecutiveSuccessfulSteps = 0;
     for (auto &e : nw.ev)
         if (!e) SPGX_CUDA(cudaEventCreate(&e));
     nw.assembled = false;
@@ -185,6 +190,89 @@ void copyD2D(double *dst, const double *src, size_t n, cudaStream_t st)
 {
     if (n) SPGX_CUDA(cudaMemcpyAsync(dst, src, n * sizeof(double), cudaMemcpyDeviceToDevice, st));
 }
+
+// out = c1 f - c2 M (a - b), returns |out| (one stream synchronisation: the line search branches on it)
+double residualNorm(spgx_group *grp, double *out, double c1, double c2, const double *a, const double *b, cudaStream_t st)
+{
+    auto &nw = grp->newton;
+    launchResidualNorm(out, c1, nw.d_f.ptr, c2, grp->d_mass.ptr, a, b, grp->nVerts, nw.d_partials.ptr, nw.d_scalar.ptr, st);
+    grp->launchCounter += 2;
+    SPGX_CUDA(cudaMemcpyAsync(nw.hostScalar, nw.d_scalar.ptr, sizeof(double), cudaMemcpyDeviceToHost, st));
+    SPGX_CUDA(cudaStreamSynchronize(st));
+    return *nw.hostScalar;
+}
+
+// One substep of ImplicitEulerNewtonRobust::step (implicitEulerNewtonRobust.cpp:31-127) or QuasiStaticNewtonRobust::step
+// (quasiStaticNewtonRobust.cpp:33-125): the reference's control flow on the host, every vector on the device.
+void robustSubstep(spgx_group *grp, bool quasi, double maxDt, const double *g, double cgTol, int cgMaxIters, cudaStream_t st)
+{
+    auto &nw = grp->newton;
+    const long long n3 = 3LL * grp->nVerts;
+    double *x = grp->d_x.ptr, *v = grp->d_v.ptr;
+    const double newtonThreshold = quasi ? 1e-2 : 1e-5;  // quasiStaticNewtonRobust.h:20 / implicitEulerNewtonRobust.h:19
+    constexpr int kMaxNewton = 5, kMaxLineSearch = 5, kRequiredGoodSteps = 5;
+    constexpr double kSplit = 0.75;
+    bool successful = true;
+    if (nw.currentDt == -1. || nw.currentDt > maxDt) nw.currentDt = maxDt;
+    const double dt = nw.currentDt, invdt = 1 / dt, invdtSquared = invdt * invdt;
+    copyD2D(nw.d_x0.ptr, x, n3, st);
+    if (!quasi) {
+        copyD2D(nw.d_v0.ptr, v, n3, st);
+        launchAxpby(x, 1.0, x, dt, v, n3, st);  // initial guess: the inertial position
+        grp->launchCounter++;
+    }
+    // the accepted iterate: velocities vi (Newton) / positions xi (quasi-static)
+    copyD2D(nw.d_xi.ptr, quasi ? nw.d_x0.ptr : nw.d_v0.ptr, n3, st);
+    double stepResidual = 0;
+    int newtonIterations = 0;
+    do {
+        const NewtonArgs a = newtonArgs(grp);
+        launchSystemForce(a, g, nw.d_f.ptr, st);
+        assembleHessian(grp, st);
+        grp->launchCounter++;
+        double initialResidual;
+        if (quasi) {
+            launchAxpby(v, invdt, x, -invdt, nw.d_x0.ptr, n3, st);  // computeSystemIntegratedVelocities
+            grp->launchCounter++;
+            initialResidual = residualNorm(grp, nw.d_rhs.ptr, 1.0, invdtSquared, x, nw.d_x0.ptr, st);
+            nw.cgIterations.push_back(conjugateGradient(grp, invdtSquared, 1.0, nw.d_rhs.ptr, cgTol, cgMaxIters, st));
+        } else {
+            initialResidual = residualNorm(grp, nw.d_rhs.ptr, dt, 1.0, nw.d_xi.ptr, nw.d_v0.ptr, st);
+            nw.cgIterations.push_back(conjugateGradient(grp, 1.0, dt * dt, nw.d_rhs.ptr, cgTol, cgMaxIters, st));
+        }
+        stepResidual = initialResidual;
+        int lineSearch = 0;
+        double alpha = 1.;
+        while (stepResidual >= initialResidual && lineSearch < kMaxLineSearch) {
+            if (quasi) {
+                launchAxpby(x, 1.0, nw.d_xi.ptr, alpha, nw.d_sol.ptr, n3, st);   // x = xi + alpha dx
+                launchAxpby(v, invdt, x, -invdt, nw.d_x0.ptr, n3, st);          // v = (x - x0) / dt
+            } else {
+                launchAxpby(v, 1.0, nw.d_xi.ptr, alpha, nw.d_sol.ptr, n3, st);   // v = vi + alpha dv
+                launchAxpby(x, 1.0, nw.d_x0.ptr, dt, v, n3, st);                // x = x0 + v dt
+            }
+            launchSystemForce(newtonArgs(grp), g, nw.d_f.ptr, st);
+            grp->launchCounter += 3;
+            stepResidual = quasi ? residualNorm(grp, nw.d_tmp.ptr, 1.0, invdtSquared, x, nw.d_x0.ptr, st)
+                                 : residualNorm(grp, nw.d_tmp.ptr, dt, 1.0, v, nw.d_v0.ptr, st);
+            if (stepResidual < initialResidual) copyD2D(nw.d_xi.ptr, quasi ? x : v, n3, st);
+            alpha *= 0.5;
+            lineSearch++;
+        }
+        if (stepResidual >= initialResidual && stepResidual > newtonThreshold) successful = false;
+        newtonIterations++;
+    } while (stepResidual > newtonThreshold && successful && newtonIterations < kMaxNewton);
+    if (stepResidual > newtonThreshold) successful = false;
+    if (!successful) {
+        copyD2D(x, nw.d_x0.ptr, n3, st);
+        if (!quasi) copyD2D(v, nw.d_v0.ptr, n3, st);
+        nw.currentDt *= kSplit;
+        nw.consecutiveSuccessfulSteps = 0;
+    } else {
+        nw.consecutiveSuccessfulSteps++;
+        if (nw.consecutiveSuccessfulSteps > kRequiredGoodSteps && nw.currentDt < maxDt) nw.currentDt /= kSplit;
+    }
+}
 }  // namespace
 
 extern "C" {
@@ -194,7 +282,7 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
 {
     return guarded([&] {
         requireNewton(grp);
-        if (implicitKind < SPGX_IE_BARAFF_WITKIN || implicitKind > SPGX_IE_QUASI_STATIC_NEWTON) throw std::runtime_error("unknown implicit solver kind");
+        if (implicitKind < SPGX_IE_BARAFF_WITKIN || implicitKind > SPGX_IE_QUASI_STATIC_NEWTON_ROBUST) throw std::runtime_error("unknown implicit solver kind");
         if (nsubsteps < 1 || nFrames < 0 || cgMaxIterations < 0) throw std::runtime_error("invalid step parameters");
         cudaStream_t st = grp->ctx->stream;
         auto &nw = grp->newton;
@@ -221,7 +309,12 @@ int spgx_implicit_step(spgx_group *grp, int implicitKind, double dt, int nsubste
         for (int f = 0; f < nFrames; ++f)
             for (int s = 0; s < nsubsteps; ++s) {
                 phase(0);
-                if (implicitKind == SPGX_IE_BARAFF_WITKIN) {
+                if (implicitKind == SPGX_IE_NEWTON_ROBUST || implicitKind == SPGX_IE_QUASI_STATIC_NEWTON_ROBUST) {
+                    robustSubstep(grp, implicitKind == SPGX_IE_QUASI_STATIC_NEWTON_ROBUST, h, g, cgTolerance, cgMaxIterations, st);
+                    phase(1);
+                    phase(2);
+                    collect();
+                } else if (implicitKind == SPGX_IE_BARAFF_WITKIN) {
                     // f, K at the current state; (M - h^2 K) dv = h (f + h K v0); v = v0 + dv; x += v h
                     const NewtonArgs a = newtonArgs(grp);
                     launchSystemForce(a, g, nw.d_f.ptr, st);

@@ -335,6 +335,8 @@ int spgx_reset(spgx_group *grp)
     return guarded([&] {
         std::vector<double> zeros(3 * static_cast<size_t>(grp->nVerts), 0.0);
         grp->newton.bdf2Init = false;  // BDF2::reset (bdf2.cpp:78-83)
+        grp->newton.currentDt = -1.0;  // ImplicitEulerNewtonRobust::reset (implicitEulerNewtonRobust.cpp:132-137)
+        grp->newton.consecutiveSuccessfulSteps = 0;
         if (spgx_upload(grp, grp->xInitial.data(), zeros.data()) != SPGX_OK) throw CudaError(spgx_last_error());
     });
 }

@@ -212,6 +212,10 @@ struct spgx_group {
         spgx::DevBuf<double> d_bsrH;
         std::vector<spgx::DevBuf<double>> d_elemH;  // per energy
         spgx::DevBuf<double> d_f, d_rhs, d_sol, d_r, d_p, d_z, d_tmp, d_invdiag, d_x0, d_v0;
+        spgx::DevBuf<double> d_xi, d_scalar;  // adaptive solvers: the accepted Newton iterate (x or v), a norm
+        double *hostScalar = nullptr;         // pinned
+        double currentDt = -1.0;              // implicitEulerNewtonRobust.h:21-22 / quasiStaticNewtonRobust.h:24-25
+        int consecutiveSuccessfulSteps = 0;
         spgx::DevBuf<double> d_xm1, d_vm1;   // BDF2: the state before the previous substep (bdf2.h:19-20)
         bool bdf2Init = false;
         spgx::DevBuf<double> d_partials;
@@ -266,6 +270,7 @@ struct spgx_group {
         if (evStart) cudaEventDestroy(evStart);
         if (evStop) cudaEventDestroy(evStop);
         if (newton.hostState) cudaFreeHost(newton.hostState);
+        if (newton.hostScalar) cudaFreeHost(newton.hostScalar);
         for (auto e : newton.ev)
             if (e) cudaEventDestroy(e);
         spgx::p2pRelease(this);

@@ -184,6 +184,11 @@ void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t str
 void launchCgIteration(const CgArgs &a, int it, cudaStream_t stream);
 // out = alpha * a + beta * b over n doubles (out may alias a or b)
 void launchAxpby(double *out, double alpha, const double *a, double beta, const double *b, long long n, cudaStream_t stream);
+// out = c1 * f - c2 * mass[vertex] * (a - b) and its Euclidean norm (deterministic two-stage reduction through `partials`,
+// kCgBlocks doubles) into *normOut: the Newton residuals dt f - M (v - v0) (implicitEulerNewtonRobust.cpp:66, :88) and
+// f - M (x - x0) / dt^2 (quasiStaticNewtonRobust.cpp:67, :86)
+void launchResidualNorm(double *out, double c1, const double *f, double c2, const double *mass, const double *a, const double *b,
+                        int nVerts, double *partials, double *normOut, cudaStream_t stream);
 // out += c * mass[vertex] * (a - b): the M (v0 - v-1) term of BDF2 (bdf2.cpp:53) without a mass matrix
 void launchAddMassDiff(double *out, double c, const double *mass, const double *a, const double *b, int nVerts, cudaStream_t stream);
 // x += dx; v = (x - x0) * invdt  (integrateObjectsVelocitiesFromDx, implicitEulerBase.cpp:76-88)

@@ -474,6 +474,26 @@ __global__ void axpbyKernel(double *out, double alpha, const double *a, double b
     const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) out[i] = alpha * a[i] + beta * b[i];
 }
+__global__ void __launch_bounds__(kCgThreads) residualKernel(double *__restrict__ out, double c1, const double *__restrict__ f, double c2,
+                                                            const double *__restrict__ mass, const double *__restrict__ a,
+                                                            const double *__restrict__ b, long long n3, double *__restrict__ partials)
+{
+    __shared__ double smem[kCgThreads / 32];
+    double acc = 0.0;
+    for (long long i = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i < n3; i += static_cast<long long>(gridDim.x) * kCgThreads) {
+        const double r = c1 * f[i] - c2 * (mass[i / 3] * (a[i] - b[i]));
+        out[i] = r;
+        acc += r * r;
+    }
+    const double s = blockSum(acc, smem);
+    if (threadIdx.x == 0) partials[blockIdx.x] = s;
+}
+__global__ void __launch_bounds__(kCgThreads) normFinishKernel(const double *__restrict__ partials, double *__restrict__ normOut)
+{
+    __shared__ double smem[kCgThreads / 32];
+    const double s = reducePartials(partials, smem);
+    if (threadIdx.x == 0) *normOut = ::sqrt(s);
+}
 __global__ void addMassDiffKernel(double *__restrict__ out, double c, const double *__restrict__ mass, const double *__restrict__ a,
                                   const double *__restrict__ b, long long n3)
 {
@@ -555,6 +575,13 @@ void launchAxpby(double *out, double alpha, const double *a, double beta, const 
 {
     if (n == 0) return;
     axpbyKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(out, alpha, a, beta, b, n);
+}
+
+void launchResidualNorm(double *out, double c1, const double *f, double c2, const double *mass, const double *a, const double *b,
+                        int nVerts, double *partials, double *normOut, cudaStream_t stream)
+{
+    residualKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(out, c1, f, c2, mass, a, b, 3LL * nVerts, partials);
+    normFinishKernel<<<1, kCgThreads, 0, stream>>>(partials, normOut);
 }
 
 void launchAddMassDiff(double *out, double c, const double *mass, const double *a, const double *b, int nVerts, cudaStream_t stream)

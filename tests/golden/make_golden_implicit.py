@@ -16,7 +16,7 @@ import make_golden as MG  # noqa: E402
 from spg_b200 import scenes as S  # noqa: E402
 
 # oracle solver kinds (oracle/ref_driver.cpp: ref_solver_create)
-BW, NDX, NDV, SYMPLECTIC, BDF2, STATIC, QUASI = 3, 4, 5, 6, 7, 8, 9
+BW, NDX, NDV, SYMPLECTIC, BDF2, STATIC, QUASI, NROBUST, QROBUST = 3, 4, 5, 6, 7, 8, 9, 10, 11
 SCENES = {
     "cloth12": lambda: S.cloth(12, 12),
     "cloth10_quad": lambda: S.cloth(10, 10, S.K_SPRING, S.K_QUADRATIC_BENDING),
@@ -37,6 +37,10 @@ for _sc in ("cloth12", "cloth10_quad", "beam_snh"):
     STEP_CASES[f"quasi_{_sc}"] = (_sc, QUASI, 1, 3)
 for _sc in ("beam_snh", "beam_stvk"):
     STEP_CASES[f"static_{_sc}"] = (_sc, STATIC, 1, 3)
+# the adaptive solvers: 7 frames so that the "five good substeps in a row" branch is reached
+for _sc in ("cloth12", "cloth10_quad", "beam_snh"):
+    STEP_CASES[f"nrobust_{_sc}"] = (_sc, NROBUST, 1, 7)
+    STEP_CASES[f"qrobust_{_sc}"] = (_sc, QROBUST, 2, 4)
 STEP_CASES["symplectic_cloth10_quad"] = ("cloth10_quad", SYMPLECTIC, 200, 1)
 STEP_CASES["symplectic_beam_snh"] = ("beam_snh", SYMPLECTIC, 400, 1)
 

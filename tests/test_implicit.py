@@ -175,7 +175,7 @@ def test_gpu_linear_solve_vs_oracle(ctx, oracle, name):
     g.close()
 
 
-_GPU_KIND = {MI.BW: 0, MI.NDX: 1, MI.NDV: 2, MI.BDF2: 3, MI.STATIC: 4, MI.QUASI: 5}
+_GPU_KIND = {MI.BW: 0, MI.NDX: 1, MI.NDV: 2, MI.BDF2: 3, MI.STATIC: 4, MI.QUASI: 5, MI.NROBUST: 6, MI.QROBUST: 7}
 
 
 @pytest.mark.gpu
@@ -232,7 +232,7 @@ def test_gpu_newton_state_errors(ctx):
     with pytest.raises(api.SpgxError):
         g.linear_solve(1.0, 1.0, np.zeros(75))  # nothing assembled yet
     with pytest.raises(api.SpgxError):
-        g.implicit_step(7, 0.01)
+        g.implicit_step(99, 0.01)
     g.implicit_step(1, 0.01)
     x, _ = g.download()
     assert np.isfinite(x).all()
