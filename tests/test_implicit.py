@@ -252,3 +252,29 @@ def test_gpu_bdf2_reset_forgets_previous_state(ctx):
     second = g.download()
     assert np.array_equal(first[0], second[0]) and np.array_equal(first[1], second[1])
     g.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("scene", ["cloth", "beam"])
+@pytest.mark.parametrize("kind", [MI.NROBUST, MI.QROBUST])
+def test_gpu_robust_newton_iterations_vs_oracle(ctx, oracle, scene, kind):
+    """a state that needs several Newton iterations per substep (random velocities, dt = 0.03): same number of linear
+    solves as the reference (i.e. the same Newton / line-search / roll-back decisions), CG counts within 2"""
+    from spg_b200 import api
+    sc = S.cloth(12, 12) if scene == "cloth" else S.tet_beam(5, 3, 3, S.K_TET_SNH)
+    v0 = 0.5 * np.random.default_rng(3).standard_normal(sc.x.shape)
+    g = api.Group.from_scene(ctx, sc)
+    g.finalize(api.SPGX_NEWTON)
+    g.upload(sc.x, v0)
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, kind, 0.03, 1, 1)
+    osol.set_state(sc.x, v0)
+    g.implicit_step(_GPU_KIND[kind], 0.03, 1, frames=5)
+    osol.step(5)
+    cg, cgr = g.cg_iterations(), osol.cg_iterations()
+    assert cg.size == cgr.size and cg.size > 5, (cg, cgr)
+    assert np.abs(cg - cgr).max() <= 2, (cg, cgr)
+    x, v = g.download()
+    xr, vr = osol.state()
+    assert _rel(x, xr) <= 1e-6 and _rel(v, vr) <= 1e-4, (_rel(x, xr), _rel(v, vr))
+    g.close()
