@@ -145,6 +145,11 @@ void spgx_group_destroy(spgx_group *grp);
  * Energies are processed in the order they were added (vbd.cpp:128, xpbd.cpp:84). */
 int spgx_group_add_energy(spgx_group *grp, int kind, int nStencils, const int32_t *stencils,
                           const double *modelParams, int *energyId);
+/* ParticleGroup::removeEnergy (particleGroup.cpp:89-95; picking release, apps/solverCompare.cpp:1499-1502). The ids of
+ * the energies added after it shift down by one, as their positions in the reference's energy vector do. The group
+ * must be finalized again before the next step (requirePrecomputationUpdate, vbd.h:26 / xpbd.h:20); positions and
+ * velocities are kept across it. */
+int spgx_group_remove_energy(spgx_group *grp, int energyId);
 /* SpringAnchorEnergy::updateAnchor (springAnchorEnergy.h:13) and friends: overwrite `count` doubles of
  * the precomputed record of one stencil starting at `offset`. Takes effect at the next step. */
 int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int offset, const double *values,

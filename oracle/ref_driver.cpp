@@ -678,6 +678,44 @@ int ref_solver_step(void *h, int nFrames)
     });
 }
 
+// ---- live topology edits (picking: apps/solverCompare.cpp:717-726, :1446-1455, :1471-1473, :1499-1502) ----------
+// The application adds / removes an energy on the SOLVER's copy of the group and flags the solver
+// (VBD::requirePrecomputationUpdate, vbd.h:26; XPBD has the same hook, xpbd.h:20).
+int ref_solver_add_energy(void *h, int kind, int nStencils, const int32_t *stencils, const double *params)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        auto &pg = s->base()->particleGroups()[0];
+        auto e = makeEnergy(kind, nStencils, stencils, params);
+        pg.addEnergy(e);
+        e->preparePrecomputations(pg);
+        if (s->vbd) s->vbd->requirePrecomputationUpdate();
+        if (s->xpbd) s->xpbd->requirePrecomputationUpdate();
+    });
+}
+
+int ref_solver_remove_energy(void *h, int e)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        auto &pg = s->base()->particleGroups()[0];
+        auto victim = pg.energies().at(e);  // (a copy: removeEnergy compares against it while erasing)
+        pg.removeEnergy(victim);
+        if (s->vbd) s->vbd->requirePrecomputationUpdate();
+        if (s->xpbd) s->xpbd->requirePrecomputationUpdate();
+    });
+}
+
+int ref_solver_update_anchor(void *h, int e, int stencil, const double *anchor3)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefSolver *>(h);
+        auto a = std::dynamic_pointer_cast<spg::SpringAnchorEnergy>(s->base()->particleGroups()[0].energies().at(e));
+        if (!a) throw std::runtime_error("energy is not a SpringAnchorEnergy");
+        a->updateAnchor(stencil, spg::Vector3(anchor3[0], anchor3[1], anchor3[2]));
+    });
+}
+
 // ---- implicit-Euler family probes (implicitEulerBase.cpp) ----------------------------------------
 // CG iteration counts of the linear solves of the last ref_solver_step call (one per substep and frame)
 int ref_solver_cg_iterations(void *h, int32_t *out, int capacity, int *n)

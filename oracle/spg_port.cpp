@@ -1511,6 +1511,45 @@ void *ref_solver_create(int kind, void *group, double dt, int substeps, int iter
     return s;
 }
 void ref_solver_destroy(void *h) { delete static_cast<Solver *>(h); }
+// live topology edits (picking: apps/solverCompare.cpp:717-726, :1446-1455, :1471-1473, :1499-1502) on the solver's copy
+// of the group, with requirePrecomputationUpdate (vbd.h:26, xpbd.h:20): colours and incidence are rebuilt on the next step
+int ref_solver_add_energy(void *h, int kind, int nStencils, const int32_t *stencils, const double *params)
+{
+    return guarded([&] {
+        auto *s = static_cast<Solver *>(h);
+        if (kind < 0 || kind >= K_COUNT) throw std::runtime_error("unknown energy kind");
+        auto e = std::make_shared<Energy>();
+        e->kind = kind;
+        e->S = kStencilSize[kind];
+        e->NC = kNumConstraints[kind];
+        for (int i = 0; i < nStencils; ++i)
+            addStencil(*e, stencils + static_cast<size_t>(i) * e->S, params + static_cast<size_t>(i) * kNumModelParams[kind]);
+        prepare(*e, s->g);
+        s->g.energies.push_back(e);
+        s->vertexGroups.clear();
+        s->stencilGroups.clear();
+        s->dirty = true;
+    });
+}
+int ref_solver_remove_energy(void *h, int e)
+{
+    return guarded([&] {
+        auto *s = static_cast<Solver *>(h);
+        if (e < 0 || e >= static_cast<int>(s->g.energies.size())) throw std::out_of_range("energy index");
+        s->g.energies.erase(s->g.energies.begin() + e);
+        s->vertexGroups.clear();
+        s->stencilGroups.clear();
+        s->dirty = true;
+    });
+}
+int ref_solver_update_anchor(void *h, int e, int stencil, const double *anchor3)
+{
+    return guarded([&] {
+        auto &en = *static_cast<Solver *>(h)->g.energies.at(e);
+        if (en.kind != K_ANCHOR) throw std::runtime_error("not an anchor energy");
+        std::copy(anchor3, anchor3 + 3, en.anchor.begin() + 3 * static_cast<size_t>(stencil));
+    });
+}
 int ref_solver_step(void *h, int nFrames)
 {
     return guarded([&] {

@@ -65,6 +65,7 @@ SIGNATURES = {
     "spgx_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
     "spgx_group_destroy": (None, [C.c_void_p]),
     "spgx_group_add_energy": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip, _dp, C.POINTER(C.c_int)]),
+    "spgx_group_remove_energy": (C.c_int, [C.c_void_p, C.c_int]),
     "spgx_energy_update_record": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, C.c_int]),
     "spgx_energy_get_records": (C.c_int, [C.c_void_p, C.c_int, _dp]),
     "spgx_group_finalize": (C.c_int, [C.c_void_p, C.c_int]),
@@ -247,6 +248,12 @@ class Group:
         self.kinds.append(kind)
         self.n_stencils.append(n)
         return eid.value
+
+    def remove_energy(self, eid: int):
+        """ParticleGroup::removeEnergy (particleGroup.cpp:89-95); finalize again before the next step."""
+        check(lib.spgx_group_remove_energy(self.handle, eid))
+        del self.kinds[eid]
+        del self.n_stencils[eid]
 
     def set_partition(self, rank: int, nranks: int, owner=None):
         """Domain decomposition (before finalize): this rank owns the vertices with owner[v] == rank (None: equal

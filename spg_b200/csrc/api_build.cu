@@ -531,6 +531,17 @@ int spgx_group_add_energy(spgx_group *grp, int kind, int nStencils, const int32_
     });
 }
 
+int spgx_group_remove_energy(spgx_group *grp, int energyId)
+{
+    return guarded([&] {
+        if (energyId < 0 || energyId >= static_cast<int>(grp->energies.size())) throw std::runtime_error("energy id out of range");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));  // a step still in flight reads the energy's device buffers
+        grp->energies.erase(grp->energies.begin() + energyId);
+        grp->finalized = false;
+    });
+}
+
 int spgx_energy_get_records(spgx_group *grp, int energyId, double *records)
 {
     return guarded([&] {

@@ -240,7 +240,9 @@ void launchStreamPersistGO(const VbdArgs &args, int begin, int end, int sliceBas
     static int blocksPerSm = 0, smCount = 0;
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+        int pct = args.carveout;  // as in launchStreamGO: shared memory for the resident blocks, the rest stays L1
+        if (pct < 0) pct = static_cast<int>(std::min<size_t>(100, (OCC * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024) + 2));
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
         configured = smem;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocksPerSm, kernel, kStreamBlockThreads, smem);
         int dev = 0;

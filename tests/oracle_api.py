@@ -91,6 +91,10 @@ class Oracle:
         L.ref_system_matrix.argtypes = [C.c_void_p, C.c_int, _lp, _ip, _ip, _dp]
         L.ref_linear_solve.argtypes = [C.c_void_p, C.c_int, C.c_int64, _ip, _ip, _dp, _dp, _dp, C.POINTER(C.c_int)]
         L.ref_omp_set_threads.argtypes = [C.c_int]
+        # live topology edits on the solver's copy of the group (picking)
+        L.ref_solver_add_energy.argtypes = [C.c_void_p, C.c_int, C.c_int, _ip, _dp]
+        L.ref_solver_remove_energy.argtypes = [C.c_void_p, C.c_int]
+        L.ref_solver_update_anchor.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
         if kind == "reference":
             L.ref_scene_cloth.restype = C.c_void_p
             L.ref_scene_cloth.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
@@ -279,6 +283,19 @@ class OracleSolver:
         x = None if x is None else _f64(x)
         v = None if v is None else _f64(v)
         self.o.lib.ref_solver_set_state(self.h, _d(x), _d(v))
+
+    # ---- live topology edits (apps/solverCompare.cpp:717-726, :1446-1455): the energy joins / leaves the solver's own
+    # copy of the group and the solver is flagged with requirePrecomputationUpdate ----
+    def add_energy(self, kind, stencils, params):
+        st, pr = _i32(stencils), _f64(params)
+        self.o.check(self.o.lib.ref_solver_add_energy(self.h, kind, st.shape[0], _i(st), _d(pr)))
+
+    def remove_energy(self, e):
+        self.o.check(self.o.lib.ref_solver_remove_energy(self.h, e))
+
+    def update_anchor(self, e, stencil, anchor):
+        a = _f64(anchor)
+        self.o.check(self.o.lib.ref_solver_update_anchor(self.h, e, stencil, _d(a)))
 
     # ---- implicit-Euler family (kinds 3-5) ----
     def cg_iterations(self):

@@ -43,3 +43,34 @@ def test_rope_facade_matches_oracle(tmp_path, oracle, solver, substeps, iters):
     osol.step(frames - frames // 2)
     xr, _ = osol.state()
     assert np.abs(x - xr).max() <= 1e-9 * np.abs(xr).max()
+
+
+@pytest.mark.parametrize("solver,substeps,iters", [("vbd", 2, 8), ("xpbd", 10, 1)])
+def test_rope_facade_picking_matches_oracle(tmp_path, oracle, solver, substeps, iters):
+    """Picking through the facade (addEnergy / removeEnergy on the solver's copy of the group + requirePrecomputationUpdate:
+    apps/solverCompare.cpp:717-726, :1446-1455, :1499-1502) against the same edits on the reference solver."""
+    exe = tmp_path / "rope_facade"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", str(ROOT / "include"), str(ROOT / "examples" / "rope_facade.cpp"),
+                    "-L", str(ROOT / "spg_b200" / "lib"), "-lspgx", f"-Wl,-rpath,{ROOT / 'spg_b200' / 'lib'}", "-o", str(exe)],
+                   check=True)
+    n, frames = 24, 9
+    res = subprocess.run([str(exe), solver, str(n), str(frames), str(substeps), str(iters), "pick"], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    x = np.array([[float(a) for a in l.split()] for l in res.stdout.strip().splitlines()])
+    sc = _rope_scene(n)
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, 0 if solver == "vbd" else 1, 0.01, substeps, iters)
+    picked = False
+    for f in range(frames):
+        if f == frames // 3:
+            xs, _ = osol.state()
+            osol.add_energy(S.K_ANCHOR, np.array([[n - 1]], np.int32), np.array([[*xs[n - 1], 1e4]]))
+            picked = True
+        if picked and f > frames // 3:
+            osol.update_anchor(2, 0, [1.0, 0.01 * f, 0.02])
+        if f == 2 * frames // 3:
+            osol.remove_energy(2)
+            picked = False
+        osol.step(1)
+    xr, _ = osol.state()
+    assert np.abs(x - xr).max() <= 1e-8 * np.abs(xr).max()
