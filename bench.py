@@ -289,6 +289,13 @@ def run_implicit(args):
                          "algorithmic_bytes_per_launch": bytes_cg / 3, "algorithmic_bytes_per_unit": bytes_cg / V,
                          "kernel_share_of_step": t.solve_ms / t.total_ms, "peak_source": peak_src},
             "cpu_baseline": cpu}
+    prof = ROOT / "profiles" / "traffic.json"
+    if prof.exists():
+        try:
+            line["roofline"]["traffic"] = json.loads(prof.read_text()).get(str(args.config))
+        except Exception:
+            pass
+    line["roofline"]["kernel"] = "bsrSpmvPipelinedKernel + cgUpdateKernel + cgDirectionKernel (one CG iteration)"
     print(json.dumps(line), flush=True)
     return 0
 

@@ -280,7 +280,43 @@ __device__ __forceinline__ double reducePartials(const double *__restrict__ part
     return r;
 }
 
-// y = (cM diag(mass) + cH H) x over block rows; partial sums of x . y when `partials` is given
+// y = (cM diag(mass) + cH H) x over block rows; partial sums of x . y when `partials` is given.
+// VARIANT 0: one block per lane and trip.  1: the row pointers of the next sweep are requested before this sweep's blocks
+// (takes one dependent round trip out of every sweep).  2: as 1, and the first two trips of a row (up to 16 blocks: every
+// row of a triangle mesh) are requested together.  The per-lane summation order is the same in all three: results are
+// bit-identical.
+struct SpmvBlock {
+    double h0, h1, h2, h3, h4, h5, h6, h7, h8;
+    size_t c;
+};
+__device__ __forceinline__ SpmvBlock spmvLoad(const CgArgs &a, uint32_t k)
+{
+    const size_t nb = static_cast<size_t>(a.nnzb);
+    const double *h = a.bsrH + k;
+    SpmvBlock b;
+    b.c = 3 * static_cast<size_t>(a.bsrCol[k]);
+    b.h0 = __ldg(h), b.h1 = __ldg(h + nb), b.h2 = __ldg(h + 2 * nb), b.h3 = __ldg(h + 3 * nb), b.h4 = __ldg(h + 4 * nb);
+    b.h5 = __ldg(h + 5 * nb), b.h6 = __ldg(h + 6 * nb), b.h7 = __ldg(h + 7 * nb), b.h8 = __ldg(h + 8 * nb);
+    return b;
+}
+__device__ __forceinline__ SpmvBlock spmvLoadH(const CgArgs &a, uint32_t k, int32_t col)
+{
+    const size_t nb = static_cast<size_t>(a.nnzb);
+    const double *h = a.bsrH + k;
+    SpmvBlock b;
+    b.c = 3 * static_cast<size_t>(col);
+    b.h0 = __ldg(h), b.h1 = __ldg(h + nb), b.h2 = __ldg(h + 2 * nb), b.h3 = __ldg(h + 3 * nb), b.h4 = __ldg(h + 4 * nb);
+    b.h5 = __ldg(h + 5 * nb), b.h6 = __ldg(h + 6 * nb), b.h7 = __ldg(h + 7 * nb), b.h8 = __ldg(h + 8 * nb);
+    return b;
+}
+__device__ __forceinline__ void spmvAccumulate(const SpmvBlock &b, double x0, double x1, double x2, double &y0, double &y1, double &y2)
+{
+    y0 += b.h0 * x0 + b.h1 * x1 + b.h2 * x2;
+    y1 += b.h3 * x0 + b.h4 * x1 + b.h5 * x2;
+    y2 += b.h6 * x0 + b.h7 * x1 + b.h8 * x2;
+}
+
+template <int VARIANT>
 __global__ void __launch_bounds__(kCgThreads) bsrSpmvKernel(const CgArgs a, const double *__restrict__ x,
                                                            double *__restrict__ y, double *__restrict__ partials,
                                                            const CgState *__restrict__ state)
@@ -290,25 +326,42 @@ __global__ void __launch_bounds__(kCgThreads) bsrSpmvKernel(const CgArgs a, cons
     constexpr int RPB = kCgThreads / kRowLanes;  // rows per block per sweep
     const int sub = threadIdx.x % kRowLanes;
     const int rowInBlock = threadIdx.x / kRowLanes;
+    const long long stride = static_cast<long long>(gridDim.x) * RPB;
     double dotAcc = 0.0;
-    for (long long base = static_cast<long long>(blockIdx.x) * RPB; base < a.nVerts; base += static_cast<long long>(gridDim.x) * RPB) {
+    uint32_t rbNext = 0, reNext = 0;
+    if (VARIANT >= 1) {
+        const long long row = static_cast<long long>(blockIdx.x) * RPB + rowInBlock;
+        if (row < a.nVerts) rbNext = a.bsrRowptr[row], reNext = a.bsrRowptr[row + 1];
+    }
+    for (long long base = static_cast<long long>(blockIdx.x) * RPB; base < a.nVerts; base += stride) {
         const long long row = base + rowInBlock;
         double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+        uint32_t rb = rbNext, re = reNext;
+        if (VARIANT >= 1) {
+            rbNext = reNext = 0;
+            if (row + stride < a.nVerts) rbNext = a.bsrRowptr[row + stride], reNext = a.bsrRowptr[row + stride + 1];
+        } else if (row < a.nVerts) {
+            rb = a.bsrRowptr[row], re = a.bsrRowptr[row + 1];
+        }
         if (row < a.nVerts) {
-            const uint32_t rb = a.bsrRowptr[row], re = a.bsrRowptr[row + 1];
-            const size_t nb = static_cast<size_t>(a.nnzb);
-            // (two blocks per lane and trip with the column ids hoisted, and a 148 x 8 grid, measured slower: 90.8 vs 81.1
-            // ms per 300 iterations at 1 M vertices)
-            for (uint32_t k = rb + sub; k < re; k += kRowLanes) {
-                const double *h = a.bsrH + k;
-                const size_t c = 3 * static_cast<size_t>(a.bsrCol[k]);
-                const double h0 = __ldg(h), h1 = __ldg(h + nb), h2 = __ldg(h + 2 * nb), h3 = __ldg(h + 3 * nb),
-                             h4 = __ldg(h + 4 * nb), h5 = __ldg(h + 5 * nb), h6 = __ldg(h + 6 * nb), h7 = __ldg(h + 7 * nb),
-                             h8 = __ldg(h + 8 * nb);
-                const double x0 = x[c], x1 = x[c + 1], x2 = x[c + 2];
-                y0 += h0 * x0 + h1 * x1 + h2 * x2;
-                y1 += h3 * x0 + h4 * x1 + h5 * x2;
-                y2 += h6 * x0 + h7 * x1 + h8 * x2;
+            // (two blocks per lane and trip together with a 148 x 8 grid measured slower: 90.8 vs 81.1 ms per 300
+            // iterations at 1 M vertices)
+            uint32_t k = rb + sub;
+            if (VARIANT >= 2) {
+                const bool p1 = k < re, p2 = k + kRowLanes < re;
+                if (p1) {
+                    const SpmvBlock b1 = spmvLoad(a, k);
+                    const SpmvBlock b2 = spmvLoad(a, p2 ? k + kRowLanes : k);
+                    const double u0 = x[b1.c], u1 = x[b1.c + 1], u2 = x[b1.c + 2];
+                    const double w0 = x[b2.c], w1 = x[b2.c + 1], w2 = x[b2.c + 2];
+                    spmvAccumulate(b1, u0, u1, u2, y0, y1, y2);
+                    if (p2) spmvAccumulate(b2, w0, w1, w2, y0, y1, y2);
+                }
+                k += 2 * kRowLanes;
+            }
+            for (; k < re; k += kRowLanes) {
+                const SpmvBlock b = spmvLoad(a, k);
+                spmvAccumulate(b, x[b.c], x[b.c + 1], x[b.c + 2], y0, y1, y2);
             }
         }
 #pragma unroll
@@ -332,6 +385,94 @@ __global__ void __launch_bounds__(kCgThreads) bsrSpmvKernel(const CgArgs a, cons
         const double s = blockSum(dotAcc, smem);
         if (threadIdx.x == 0) partials[blockIdx.x] = s;
     }
+}
+
+// VARIANT 3: software pipeline over the sweeps of a block: the row pointers are requested two sweeps ahead and the column
+// ids one sweep ahead, so a sweep's matrix blocks and its gathered x entries are requested together (one exposed memory
+// round trip per sweep instead of three).  Same lanes, same per-lane order: bit-identical to the other variants.
+__global__ void __launch_bounds__(kCgThreads, 4) bsrSpmvPipelinedKernel(const CgArgs a, const double *__restrict__ x,
+                                                                    double *__restrict__ y, double *__restrict__ partials,
+                                                                    const CgState *__restrict__ state)
+{
+    __shared__ double smem[kCgThreads / 32];
+    if (state && state->done) return;
+    constexpr int RPB = kCgThreads / kRowLanes;
+    const int sub = threadIdx.x % kRowLanes;
+    const int rowInBlock = threadIdx.x / kRowLanes;
+    const long long stride = static_cast<long long>(gridDim.x) * RPB;
+    const long long n = a.nVerts;
+    double dotAcc = 0.0;
+    long long row = static_cast<long long>(blockIdx.x) * RPB + rowInBlock;
+    uint32_t rb = 0, re = 0, rbN = 0, reN = 0;
+    if (row < n) rb = a.bsrRowptr[row], re = a.bsrRowptr[row + 1];
+    if (row + stride < n) rbN = a.bsrRowptr[row + stride], reN = a.bsrRowptr[row + stride + 1];
+    int32_t c1 = 0, c2 = 0;
+    if (rb + sub < re) c1 = a.bsrCol[rb + sub];
+    if (rb + sub + kRowLanes < re) c2 = a.bsrCol[rb + sub + kRowLanes];
+    for (long long base = static_cast<long long>(blockIdx.x) * RPB; base < n; base += stride, row += stride) {
+        // requests for the sweeps to come
+        uint32_t rbNN = 0, reNN = 0;
+        if (row + 2 * stride < n) rbNN = a.bsrRowptr[row + 2 * stride], reNN = a.bsrRowptr[row + 2 * stride + 1];
+        int32_t c1N = 0, c2N = 0;
+        if (rbN + sub < reN) c1N = a.bsrCol[rbN + sub];
+        if (rbN + sub + kRowLanes < reN) c2N = a.bsrCol[rbN + sub + kRowLanes];
+        // this sweep (the row's own x entries and mass are requested up front too: after the lane reduction they would be
+        // one more exposed round trip)
+        double y0 = 0.0, y1 = 0.0, y2 = 0.0;
+        double xr0 = 0.0, xr1 = 0.0, xr2 = 0.0, mr = 0.0;
+        if (row < n && sub == 0) {
+            const size_t o = 3 * static_cast<size_t>(row);
+            xr0 = x[o], xr1 = x[o + 1], xr2 = x[o + 2], mr = a.mass[row];
+        }
+        uint32_t k = rb + sub;
+        if (k < re) {
+            const bool p2 = k + kRowLanes < re;
+            const SpmvBlock b1 = spmvLoadH(a, k, c1);
+            const SpmvBlock b2 = spmvLoadH(a, p2 ? k + kRowLanes : k, p2 ? c2 : c1);
+            const double u0 = x[b1.c], u1 = x[b1.c + 1], u2 = x[b1.c + 2];
+            const double w0 = x[b2.c], w1 = x[b2.c + 1], w2 = x[b2.c + 2];
+            spmvAccumulate(b1, u0, u1, u2, y0, y1, y2);
+            if (p2) spmvAccumulate(b2, w0, w1, w2, y0, y1, y2);
+            for (k += 2 * kRowLanes; k < re; k += kRowLanes) {
+                const SpmvBlock b = spmvLoad(a, k);
+                spmvAccumulate(b, x[b.c], x[b.c + 1], x[b.c + 2], y0, y1, y2);
+            }
+        }
+#pragma unroll
+        for (int o = 1; o < kRowLanes; o <<= 1) {
+            y0 += __shfl_xor_sync(0xffffffffu, y0, o);
+            y1 += __shfl_xor_sync(0xffffffffu, y1, o);
+            y2 += __shfl_xor_sync(0xffffffffu, y2, o);
+        }
+        if (row < n && sub == 0) {
+            const size_t o = 3 * static_cast<size_t>(row);
+            const double m = a.cM * mr;
+            const double x0 = xr0, x1 = xr1, x2 = xr2;
+            y0 = a.cH * y0 + m * x0;
+            y1 = a.cH * y1 + m * x1;
+            y2 = a.cH * y2 + m * x2;
+            y[o] = y0, y[o + 1] = y1, y[o + 2] = y2;
+            dotAcc += x0 * y0 + x1 * y1 + x2 * y2;
+        }
+        rb = rbN, re = reN, rbN = rbNN, reN = reNN, c1 = c1N, c2 = c2N;
+    }
+    if (partials) {
+        const double s = blockSum(dotAcc, smem);
+        if (threadIdx.x == 0) partials[blockIdx.x] = s;
+    }
+}
+
+void launchSpmvVariant(const CgArgs &a, const double *x, double *y, double *partials, const CgState *state, cudaStream_t stream)
+{
+    static const int variant = getenv("SPGX_SPMV_VARIANT") ? atoi(getenv("SPGX_SPMV_VARIANT")) : 3;
+    if (variant == 3)
+        bsrSpmvPipelinedKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, partials, state);
+    else if (variant == 1)
+        bsrSpmvKernel<1><<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, partials, state);
+    else if (variant == 2)
+        bsrSpmvKernel<2><<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, partials, state);
+    else
+        bsrSpmvKernel<0><<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, partials, state);
 }
 
 // Jacobi preconditioner (BasicPreconditioners.h:62-73): 1 / diagonal, 1 where the diagonal is zero
@@ -553,7 +694,7 @@ void launchBsrAssemble(const NewtonArgs &a, cudaStream_t stream)
 void launchBsrSpmv(const CgArgs &a, const double *x, double *y, cudaStream_t stream)
 {
     if (a.nVerts == 0) return;
-    bsrSpmvKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, x, y, nullptr, nullptr);
+    launchSpmvVariant(a, x, y, nullptr, nullptr, stream);
 }
 
 void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t stream)
@@ -566,7 +707,7 @@ void launchCgInit(const CgArgs &a, const double *b, double tol, cudaStream_t str
 
 void launchCgIteration(const CgArgs &a, int it, cudaStream_t stream)
 {
-    bsrSpmvKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, a.p, a.tmp, a.partials, a.state + (it & 1));
+    launchSpmvVariant(a, a.p, a.tmp, a.partials, a.state + (it & 1), stream);
     cgUpdateKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, it);
     cgDirectionKernel<<<kCgBlocks, kCgThreads, 0, stream>>>(a, it);
 }
