@@ -530,22 +530,27 @@ __global__ void __launch_bounds__(kCgThreads) cgInitFinishKernel(const CgArgs a,
 __global__ void __launch_bounds__(kCgThreads) cgUpdateKernel(const CgArgs a, int it)
 {
     __shared__ double smem[kCgThreads / 32];
+    const long long n = 3LL * a.nVerts;
+    double rr = 0.0, rz = 0.0;
+    // four independent elements per trip: 20 loads in flight per thread (the loop is pure latency otherwise); the first
+    // trip is requested BEFORE the reduction of the p . tmp partials, which does not depend on it
+    constexpr int U = 4;
+    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
+    long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x;
+    double xv[U], pv[U], rv[U], tv[U], dv[U];
+    auto request = [&](long long at) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = at + u * stride;
+            if (i < n) xv[u] = a.x[i], pv[u] = a.p[i], rv[u] = a.r[i], tv[u] = a.tmp[i], dv[u] = a.invdiag[i];
+        }
+    };
+    request(i0);
     const CgState st = a.state[it & 1];
     if (st.done) return;
     const double pAp = reducePartials(a.partials, smem);
     const double alpha = st.absNew / pAp;
-    const long long n = 3LL * a.nVerts;
-    double rr = 0.0, rz = 0.0;
-    // four independent elements per trip: 20 loads in flight per thread (the loop is pure latency otherwise)
-    constexpr int U = 4;
-    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
-    for (long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i0 < n; i0 += U * stride) {
-        double xv[U], pv[U], rv[U], tv[U], dv[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const long long i = i0 + u * stride;
-            if (i < n) xv[u] = a.x[i], pv[u] = a.p[i], rv[u] = a.r[i], tv[u] = a.tmp[i], dv[u] = a.invdiag[i];
-        }
+    while (i0 < n) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const long long i = i0 + u * stride;
@@ -559,6 +564,8 @@ __global__ void __launch_bounds__(kCgThreads) cgUpdateKernel(const CgArgs a, int
                 rz += ri * zi;
             }
         }
+        i0 += U * stride;
+        request(i0);
     }
     const double s0 = blockSum(rr, smem);
     const double s1 = blockSum(rz, smem);
@@ -572,6 +579,19 @@ __global__ void __launch_bounds__(kCgThreads) cgUpdateKernel(const CgArgs a, int
 __global__ void __launch_bounds__(kCgThreads) cgDirectionKernel(const CgArgs a, int it)
 {
     __shared__ double smem[kCgThreads / 32];
+    const long long n = 3LL * a.nVerts;
+    constexpr int U = 4;
+    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
+    long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x;
+    double zv[U], pv[U];
+    auto request = [&](long long at) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const long long i = at + u * stride;
+            if (i < n) zv[u] = a.z[i], pv[u] = a.p[i];
+        }
+    };
+    request(i0);  // before the state and the two reductions, which do not depend on it
     const CgState st = a.state[it & 1];
     if (st.done) {
         if (blockIdx.x == 0 && threadIdx.x == 0) a.state[(it + 1) & 1] = st;
@@ -592,21 +612,14 @@ __global__ void __launch_bounds__(kCgThreads) cgDirectionKernel(const CgArgs a, 
     }
     if (converged) return;
     const double beta = rz / st.absNew;
-    const long long n = 3LL * a.nVerts;
-    constexpr int U = 4;
-    const long long stride = static_cast<long long>(gridDim.x) * kCgThreads;
-    for (long long i0 = static_cast<long long>(blockIdx.x) * kCgThreads + threadIdx.x; i0 < n; i0 += U * stride) {
-        double zv[U], pv[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const long long i = i0 + u * stride;
-            if (i < n) zv[u] = a.z[i], pv[u] = a.p[i];
-        }
+    while (i0 < n) {
 #pragma unroll
         for (int u = 0; u < U; ++u) {
             const long long i = i0 + u * stride;
             if (i < n) a.p[i] = zv[u] + beta * pv[u];
         }
+        i0 += U * stride;
+        request(i0);
     }
 }
 
