@@ -19,6 +19,12 @@
 
 namespace spgx
 {
+// prefetch.global.L1 of the record two steps ahead (VbdArgs::l1pf, SPGX_VBD_L1PF=1) measured slower (3.22 vs 2.95 ms per
+// frame at config 3, profiles/r1g_l1pf_carveout_sweep.txt): compiled out of the incidence loop unless this is set.
+#ifndef SPGX_VBD_L1PF_BUILD
+#define SPGX_VBD_L1PF_BUILD 0
+#endif
+constexpr bool kVbdL1Prefetch = SPGX_VBD_L1PF_BUILD != 0;
 using D2 = Dual<3, true>;
 
 __device__ __forceinline__ void cpAsync8(double *smemDst, const double *gmemSrc)
@@ -402,7 +408,8 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     StreamRec<SMASK> r0, r1;
     r0.idx = r1.idx = 0xFFFFFFFFu;
     if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
-    if (a.l1pf && pipe.total > 1) pipe.template prefetchL1From<0>(a, 1, lane);
+    if constexpr (kVbdL1Prefetch)
+        if (a.l1pf && pipe.total > 1) pipe.template prefetchL1From<0>(a, 1, lane);
     constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
     const uint32_t nb = d.lo.y, ne = n.lo.y;
     uint32_t nid[PRE];
@@ -495,12 +502,14 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
         int l = orderAfter(lane, r0.idx);
         if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
-        if (a.l1pf && s + 2 < pipe.total) pipe.template prefetchL1From<0>(a, s + 2, lane);
+        if constexpr (kVbdL1Prefetch)
+            if (a.l1pf && s + 2 < pipe.total) pipe.template prefetchL1From<0>(a, s + 2, lane);
         pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H, ownOff);
         if (s + 1 >= pipe.total) break;
         l = orderAfter(lane, r1.idx);
         if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
-        if (a.l1pf && s + 3 < pipe.total) pipe.template prefetchL1From<0>(a, s + 3, lane);
+        if constexpr (kVbdL1Prefetch)
+            if (a.l1pf && s + 3 < pipe.total) pipe.template prefetchL1From<0>(a, s + 3, lane);
         pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H, ownOff);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
