@@ -72,13 +72,50 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
     nw.d_diagPos.upload(diagPos, st);
     SPGX_CUDA(cudaStreamSynchronize(st));
     nw.d_bsrH.alloc(9 * static_cast<size_t>(nw.nnzb));
-    nw.d_elemH.clear();
-    nw.d_elemH.resize(nE);
+    // element Hessians: one arena, energy ei owning the blocks [baseBlk[ei], baseBlk[ei + 1]) (a block = 9 doubles)
+    std::vector<uint64_t> baseBlk(nE + 1, 0);
     nw.elemHessianBytes = 0;
     for (size_t ei = 0; ei < nE; ++ei) {
         const auto &e = grp->energies[ei];
-        nw.d_elemH[ei].alloc(static_cast<size_t>(e.n) * 9 * e.S * e.S);
+        baseBlk[ei + 1] = baseBlk[ei] + static_cast<uint64_t>(e.n) * e.S * e.S;
         nw.elemHessianBytes += 8.0 * e.n * 9 * e.S * e.S;
+    }
+    if (baseBlk[nE] >= (1ull << 32)) throw std::runtime_error("too many element Hessian blocks for 32-bit gather lists");
+    nw.d_elemArena.alloc(9 * static_cast<size_t>(baseBlk[nE]));
+    nw.d_elemH.assign(nE, nullptr);
+    for (size_t ei = 0; ei < nE; ++ei) nw.d_elemH[ei] = nw.d_elemArena.ptr + 9 * static_cast<size_t>(baseBlk[ei]);
+    // gather lists: block (v, c) of the sparse Hessian sums, energies in insertion order and the row vertex's incidences
+    // ascending (the order getSystemStiffnessMatrix's triplets are summed in is not defined; this one is fixed), the
+    // element blocks (la, lb) of the stencils of v whose vertex lb is c
+    {
+        std::vector<uint32_t> asmPtr(static_cast<size_t>(nw.nnzb) + 1, 0), asmSrc;
+        asmSrc.reserve(static_cast<size_t>(baseBlk[nE]));
+        std::vector<std::vector<uint32_t>> perCol;  // of the current row, indexed by position in the row
+        for (int v = 0; v < V; ++v) {
+            const uint32_t rb = nw.bsrRowptr[v], re = nw.bsrRowptr[v + 1];
+            perCol.assign(re - rb, {});
+            for (size_t ei = 0; ei < nE; ++ei) {
+                const auto &e = grp->energies[ei];
+                for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                    const int64_t flat = inc[ei].flat[q];
+                    const int64_t stl = flat / e.S;
+                    const int la = static_cast<int>(flat % e.S);
+                    for (int lb = 0; lb < e.S; ++lb) {
+                        const int32_t c = e.stencils[stl * e.S + lb];
+                        const auto it = std::lower_bound(nw.bsrCol.begin() + rb, nw.bsrCol.begin() + re, c);
+                        perCol[static_cast<size_t>(it - (nw.bsrCol.begin() + rb))].push_back(
+                            static_cast<uint32_t>(baseBlk[ei] + static_cast<uint64_t>(stl) * e.S * e.S + la * e.S + lb));
+                    }
+                }
+            }
+            for (uint32_t t = rb; t < re; ++t) {
+                asmSrc.insert(asmSrc.end(), perCol[t - rb].begin(), perCol[t - rb].end());
+                asmPtr[t + 1] = static_cast<uint32_t>(asmSrc.size());
+            }
+        }
+        nw.d_asmPtr.upload(asmPtr, st);
+        nw.d_asmSrc.upload(asmSrc, st);
+        SPGX_CUDA(cudaStreamSynchronize(st));
     }
     const size_t n3 = 3 * static_cast<size_t>(V);
     for (auto *b : {&nw.d_f, &nw.d_rhs, &nw.d_sol, &nw.d_r, &nw.d_p, &nw.d_z, &nw.d_tmp, &nw.d_invdiag, &nw.d_x0, &nw.d_v0, &nw.d_xm1, &nw.d_vm1,
@@ -119,7 +156,7 @@ NewtonArgs newtonArgs(spgx_group *grp)
     if (a.nEnergies > kMaxEnergies) throw std::runtime_error("too many energies in one group");
     for (int e = 0; e < a.nEnergies; ++e) {
         const auto &en = grp->energies[e];
-        a.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr, nw.d_elemH[e].ptr};
+        a.e[e] = {en.kind, en.n, en.d_stencils.ptr, en.d_records.ptr, en.d_rowptr.ptr, en.d_entries.ptr, nw.d_elemH[e]};
     }
     a.bsrRowptr = nw.d_bsrRowptr.ptr;
     a.bsrCol = nw.d_bsrCol.ptr;
@@ -127,6 +164,9 @@ NewtonArgs newtonArgs(spgx_group *grp)
     a.diagPos = nw.d_diagPos.ptr;
     a.bsrH = nw.d_bsrH.ptr;
     a.nnzb = nw.nnzb;
+    a.asmPtr = nw.d_asmPtr.ptr;
+    a.asmSrc = nw.d_asmSrc.ptr;
+    a.elemArena = nw.d_elemArena.ptr;
     return a;
 }
 
@@ -511,7 +551,7 @@ int spgx_element_hessian(spgx_group *grp, int energyId, int stencil, double *hes
         launchElementHessians(newtonArgs(grp), st);
         const int S = e.S, K = 3 * S;
         std::vector<double> blocks(static_cast<size_t>(9) * S * S);
-        SPGX_CUDA(cudaMemcpyAsync(blocks.data(), grp->newton.d_elemH[energyId].ptr + static_cast<size_t>(stencil) * blocks.size(),
+        SPGX_CUDA(cudaMemcpyAsync(blocks.data(), grp->newton.d_elemH[energyId] + static_cast<size_t>(stencil) * blocks.size(),
                                   blocks.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
         SPGX_CUDA(cudaStreamSynchronize(st));
         SPGX_CUDA(cudaGetLastError());

@@ -210,7 +210,10 @@ struct spgx_group {
         spgx::DevBuf<uint32_t> d_bsrRowptr, d_diagPos;
         spgx::DevBuf<int32_t> d_bsrCol, d_bsrRow;
         spgx::DevBuf<double> d_bsrH;
-        std::vector<spgx::DevBuf<double>> d_elemH;  // per energy
+        spgx::DevBuf<double> d_elemArena;   // the element Hessians of all energies, one allocation
+        std::vector<double *> d_elemH;      // per energy: its range of the arena
+        spgx::DevBuf<uint32_t> d_asmPtr;    // nnzb + 1: the sources of every block of the sparse Hessian ...
+        spgx::DevBuf<uint32_t> d_asmSrc;    // ... as 3x3-block indices into the arena, in summation order
         spgx::DevBuf<double> d_f, d_rhs, d_sol, d_r, d_p, d_z, d_tmp, d_invdiag, d_x0, d_v0;
         spgx::DevBuf<double> d_xi, d_scalar;  // adaptive solvers: the accepted Newton iterate (x or v), a norm
         double *hostScalar = nullptr;         // pinned

@@ -145,6 +145,10 @@ struct NewtonArgs {
     const uint32_t *diagPos;    // per vertex: its diagonal block
     double *bsrH;               // 9 x nnzb doubles, component-major: entry (i, j) of block t at bsrH[(3 i + j) * nnzb + t]
     long long nnzb;
+    // gather lists of the assembly (built once with the pattern): block t sums the arena blocks asmSrc[asmPtr[t] .. asmPtr[t + 1])
+    const uint32_t *asmPtr;
+    const uint32_t *asmSrc;
+    const double *elemArena;
 };
 // getSystemForce (implicitEulerBase.cpp:102-143): f_v = g * m_v - sum over the incident stencils of dE/dx_v (owner-centric
 // gather over the vertex incidence table: no atomics, fixed summation order). g3: host pointer, 3 doubles.

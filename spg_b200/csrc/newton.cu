@@ -290,6 +290,36 @@ __global__ void __launch_bounds__(128) bsrAssembleKernel(const NewtonArgs a)
     for (int k = 0; k < 9; ++k) a.bsrH[k * a.nnzb + t] = acc[k];
 }
 
+// the same sums from the precomputed gather lists (api_newton.cu newtonBuild): no incidence walk, no stencil-id
+// compares, four element blocks requested per trip; the order of the additions is the one above, bit for bit
+__global__ void __launch_bounds__(128) bsrAssembleGatherKernel(const NewtonArgs a)
+{
+    const long long t = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (t >= a.nnzb) return;
+    const uint32_t b = a.asmPtr[t], e = a.asmPtr[t + 1];
+    double acc[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    uint32_t k = b;
+    for (; k + 4 <= e; k += 4) {
+        const double *p0 = a.elemArena + 9 * static_cast<size_t>(a.asmSrc[k]);
+        const double *p1 = a.elemArena + 9 * static_cast<size_t>(a.asmSrc[k + 1]);
+        const double *p2 = a.elemArena + 9 * static_cast<size_t>(a.asmSrc[k + 2]);
+        const double *p3 = a.elemArena + 9 * static_cast<size_t>(a.asmSrc[k + 3]);
+        double v0[9], v1[9], v2[9], v3[9];
+#pragma unroll
+        for (int c = 0; c < 9; ++c) v0[c] = p0[c], v1[c] = p1[c], v2[c] = p2[c], v3[c] = p3[c];  // (plain loads: the barrier below orders them)
+        asm volatile("" ::: "memory");  // all 36 loads are requested before the first addition waits for one
+#pragma unroll
+        for (int c = 0; c < 9; ++c) acc[c] = ((acc[c] + v0[c]) + v1[c]) + v2[c] + v3[c];
+    }
+    for (; k < e; ++k) {
+        const double *p0 = a.elemArena + 9 * static_cast<size_t>(a.asmSrc[k]);
+#pragma unroll
+        for (int c = 0; c < 9; ++c) acc[c] += p0[c];
+    }
+#pragma unroll
+    for (int c = 0; c < 9; ++c) a.bsrH[c * a.nnzb + t] = acc[c];
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // conjugate gradient
 // ---------------------------------------------------------------------------------------------------------------------
@@ -744,7 +774,12 @@ void launchElementHessians(const NewtonArgs &a, cudaStream_t stream)
 void launchBsrAssemble(const NewtonArgs &a, cudaStream_t stream)
 {
     if (a.nnzb == 0) return;
-    bsrAssembleKernel<<<static_cast<unsigned>((a.nnzb + 127) / 128), 128, 0, stream>>>(a);
+    // SPGX_ASM_GATHER=0: the incidence-walking kernel (3.8 ms at config 6)
+    static const bool gather = !(getenv("SPGX_ASM_GATHER") && atoi(getenv("SPGX_ASM_GATHER")) == 0);
+    if (gather && a.asmPtr)
+        bsrAssembleGatherKernel<<<static_cast<unsigned>((a.nnzb + 127) / 128), 128, 0, stream>>>(a);
+    else
+        bsrAssembleKernel<<<static_cast<unsigned>((a.nnzb + 127) / 128), 128, 0, stream>>>(a);
 }
 
 void launchBsrSpmv(const CgArgs &a, const double *x, double *y, cudaStream_t stream)
