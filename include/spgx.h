@@ -181,6 +181,20 @@ int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, co
                         int32_t *slot2vert, int32_t *peers, int64_t *sendOffsets, int32_t *sendVerts, int64_t *recvSlot,
                         int64_t *recvCount);
 
+/* pure host: the XPBD counterpart (spg_b200/csrc/xpbd_partition.h; SURVEY.md section 8e "next"): what rank `rank` holds and
+ * exchanges when XPBD::step (xpbd.cpp:16-131) is split between ranks. A pass = one stencil colour of one energy
+ * (xpbd.cpp:133-160), numbered energy-major; a rank executes every stencil touching a vertex it owns (cut stencils run on
+ * every rank holding them, with identical results), and after a pass the owner of a moved vertex sends it to the ranks
+ * that keep it as halo without holding the stencil that moved it. The stencil colours are computed here
+ * (colorStencils) exactly as spgx_group_finalize does. sizes: [nOwned, nHalo, nPeers, nPasses, nHeld, nSend, nRecv] out; the
+ * arrays may be NULL to query the sizes first. halo: nHalo global ids; peers: nPeers ranks; heldOffsets: nPasses + 1 into
+ * held (stencil ids within their energy); sendOffsets / recvOffsets: nPasses * nPeers + 1 into sendVerts / recvVerts
+ * (global ids, ascending, (pass, peer)-major). The device path is not built yet: XPBD groups run on one GPU. */
+int spgx_xpbd_partition_plan(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                             const int32_t *stencilSizes, const int32_t *owner, int rank, int nranks, int64_t *sizes,
+                             int32_t *halo, int32_t *peers, int64_t *heldOffsets, int32_t *held, int64_t *sendOffsets,
+                             int32_t *sendVerts, int64_t *recvOffsets, int32_t *recvVerts);
+
 /* Peer-memory halo exchange (replaces the ncclSend / ncclRecv schedule once connected; the reference is single-process,
  * the dependency it serves is the colour order of vbd.cpp:151-157).  After spgx_group_finalize every rank exports a
  * blob (CUDA IPC handles of its position array and flag array + its halo layout), the caller all-gathers the blobs

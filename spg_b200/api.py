@@ -52,6 +52,8 @@ SIGNATURES = {
     "spgx_ctx_init_comm": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "spgx_group_set_partition": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip]),
     "spgx_group_partition_info": (C.c_int, [C.c_void_p, _lp]),
+    "spgx_xpbd_partition_plan": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.c_int, C.c_int, _lp, _ip, _ip, _lp, _ip,
+                                           _lp, _ip, _lp, _ip]),
     "spgx_partition_plan": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.c_int, C.c_int, _lp, _ip, _ip, _lp, _ip,
                                       _lp, _lp]),
     "spgx_group_p2p_export": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, _lp]),
@@ -185,6 +187,30 @@ def partition_plan(n_verts: int, stencil_sets, rank: int, nranks: int, owner=Non
                                   _i(slot2vert), _i(peers), lp(send_off), _i(send_verts), lp(recv_slot), lp(recv_count)))
     return {"n_owned": n_owned, "n_local": n_local, "n_colors": n_colors, "peers": peers, "slot2vert": slot2vert,
             "send_offsets": send_off, "send_verts": send_verts, "recv_slot": recv_slot, "recv_count": recv_count}
+
+
+def xpbd_partition_plan(n_verts: int, stencil_sets, rank: int, nranks: int, owner=None) -> dict:
+    """Pure host: what rank `rank` of `nranks` holds and exchanges when the XPBD passes are split between ranks
+    (spg_b200/csrc/xpbd_partition.h). A pass is one stencil colour of one energy, numbered energy-major."""
+    sets = [_i32(s) for s in stencil_sets]
+    ptrs = (_ip * len(sets))(*[_i(s) for s in sets])
+    n_entries = np.array([s.size for s in sets], dtype=np.int64)
+    sizes_s = np.array([s.shape[1] for s in sets], dtype=np.int32)
+    own = None if owner is None else _i32(owner)
+    op = None if own is None else _i(own)
+    sizes = np.zeros(7, dtype=np.int64)
+    lp = lambda a: a.ctypes.data_as(_lp)
+    check(lib.spgx_xpbd_partition_plan(n_verts, len(sets), ptrs, lp(n_entries), _i(sizes_s), op, rank, nranks, lp(sizes),
+                                       None, None, None, None, None, None, None, None))
+    n_owned, n_halo, n_peers, n_passes, n_held, n_send, n_recv = (int(a) for a in sizes)
+    halo, peers = np.empty(n_halo, np.int32), np.empty(n_peers, np.int32)
+    held_off, held = np.empty(n_passes + 1, np.int64), np.empty(n_held, np.int32)
+    send_off, send = np.empty(n_passes * n_peers + 1, np.int64), np.empty(n_send, np.int32)
+    recv_off, recv = np.empty(n_passes * n_peers + 1, np.int64), np.empty(n_recv, np.int32)
+    check(lib.spgx_xpbd_partition_plan(n_verts, len(sets), ptrs, lp(n_entries), _i(sizes_s), op, rank, nranks, lp(sizes),
+                                       _i(halo), _i(peers), lp(held_off), _i(held), lp(send_off), _i(send), lp(recv_off), _i(recv)))
+    return {"n_owned": n_owned, "halo": halo, "peers": peers, "n_passes": n_passes, "held_offsets": held_off, "held": held,
+            "send_offsets": send_off, "send_verts": send, "recv_offsets": recv_off, "recv_verts": recv}
 
 
 def pinned_empty(shape, dtype=np.float64) -> np.ndarray:

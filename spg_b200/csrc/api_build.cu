@@ -9,6 +9,7 @@
 #include "group.h"
 #include "host_build.h"
 #include "partition.h"
+#include "xpbd_partition.h"
 #include "streams.cuh"
 
 namespace spgx
@@ -451,6 +452,41 @@ int spgx_partition_plan(int nVerts, int nSets, const int32_t *const *entries, co
             for (size_t i = 0; i < lv.sendSlots.size(); ++i) sendVerts[i] = lv.slot2vert[lv.sendSlots[i]];
         if (recvSlot) std::copy(lv.recvSlot.begin(), lv.recvSlot.end(), recvSlot);
         if (recvCount) std::copy(lv.recvCount.begin(), lv.recvCount.end(), recvCount);
+    });
+}
+
+int spgx_xpbd_partition_plan(int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                             const int32_t *stencilSizes, const int32_t *owner, int rank, int nranks, int64_t *sizes,
+                             int32_t *halo, int32_t *peers, int64_t *heldOffsets, int32_t *held, int64_t *sendOffsets,
+                             int32_t *sendVerts, int64_t *recvOffsets, int32_t *recvVerts)
+{
+    return guarded([&] {
+        std::vector<FlatStencilsView> sets;
+        std::vector<std::vector<int32_t>> colors;
+        std::vector<const int32_t *> colorPtrs;
+        std::vector<int32_t> nColors;
+        for (int s = 0; s < nSets; ++s) {
+            sets.push_back({entries[s], nEntries[s], stencilSizes[s]});
+            colors.push_back(colorStencils(sets.back()));  // xpbd.cpp:133-160
+            int32_t nc = 0;
+            for (int32_t c : colors.back()) nc = std::max(nc, c + 1);
+            nColors.push_back(nc);
+        }
+        for (auto &c : colors) colorPtrs.push_back(c.data());
+        const XpbdPlan plan = buildXpbdPlan(nVerts, sets, colorPtrs, nColors, owner, rank, nranks);
+        if (sizes) {
+            sizes[0] = plan.nOwned, sizes[1] = static_cast<int64_t>(plan.halo.size()), sizes[2] = static_cast<int64_t>(plan.peers.size());
+            sizes[3] = plan.nPasses, sizes[4] = static_cast<int64_t>(plan.held.size());
+            sizes[5] = static_cast<int64_t>(plan.sendVerts.size()), sizes[6] = static_cast<int64_t>(plan.recvVerts.size());
+        }
+        if (halo) std::copy(plan.halo.begin(), plan.halo.end(), halo);
+        if (peers) std::copy(plan.peers.begin(), plan.peers.end(), peers);
+        if (heldOffsets) std::copy(plan.heldOffsets.begin(), plan.heldOffsets.end(), heldOffsets);
+        if (held) std::copy(plan.held.begin(), plan.held.end(), held);
+        if (sendOffsets) std::copy(plan.sendOffsets.begin(), plan.sendOffsets.end(), sendOffsets);
+        if (sendVerts) std::copy(plan.sendVerts.begin(), plan.sendVerts.end(), sendVerts);
+        if (recvOffsets) std::copy(plan.recvOffsets.begin(), plan.recvOffsets.end(), recvOffsets);
+        if (recvVerts) std::copy(plan.recvVerts.begin(), plan.recvVerts.end(), recvVerts);
     });
 }
 

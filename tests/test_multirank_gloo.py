@@ -97,3 +97,78 @@ def test_two_rank_halo_exchange_matches_single_domain(tmp_path):
     for r in range(world):
         got[np.load(tmp_path / f"v{r}.npy")] = np.load(tmp_path / f"x{r}.npy")
     assert np.array_equal(got, x.numpy())
+
+
+# ---- the XPBD schedule (spg_b200/csrc/xpbd_partition.h): one exchange per (energy, colour) pass ----------------------------
+def _xpbd_worker(rank, world, port, out_dir):
+    sys.path.insert(0, str(ROOT))
+    sys.path.insert(0, str(ROOT / "tests"))
+    import torch
+    import torch.distributed as dist
+    import oracle_api
+    from spg_b200 import api, scenes as S
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sc = S.cloth(9, 9, S.K_SPRING, S.K_QUADRATIC_BENDING)
+    sets = [e.stencils for e in sc.energies]
+    pl = api.xpbd_partition_plan(sc.n_vertices, sets, rank, world)
+    og = oracle_api.OracleGroup(oracle_api.load(), sc)   # the projection of one stencil: test infrastructure
+    pass_energy = []
+    for e, st in enumerate(sets):
+        col = api.color_stencils(st)
+        pass_energy += [e] * (int(col.max()) + 1)
+    dt, substeps, g = 0.01 / 4, 4, np.array([0.0, -9.8, 0.0])
+    x, v = sc.x.copy(), np.zeros_like(sc.x)
+    npeers = len(pl["peers"])
+    for _ in range(substeps):
+        x_old = x.copy()
+        v += dt * g
+        x += v * dt
+        for p, e in enumerate(pass_energy):
+            og.set_state(x, v)
+            for st in pl["held"][pl["held_offsets"][p]:pl["held_offsets"][p + 1]]:
+                og.project(e, int(st), dt)
+            x = og.state()[0]
+            reqs, bufs = [], []
+            for i, peer in enumerate(pl["peers"]):
+                cell = p * npeers + i
+                sent = pl["send_verts"][pl["send_offsets"][cell]:pl["send_offsets"][cell + 1]]
+                want = pl["recv_verts"][pl["recv_offsets"][cell]:pl["recv_offsets"][cell + 1]]
+                if len(sent):
+                    reqs.append(dist.isend(torch.from_numpy(x[sent].copy()), int(peer)))
+                if len(want):
+                    rb = torch.empty((len(want), 3), dtype=torch.float64)
+                    bufs.append((want, rb))
+                    reqs.append(dist.irecv(rb, int(peer)))
+            for r in reqs:
+                r.wait()
+            for want, rb in bufs:
+                x[want] = rb.numpy()
+        v = (x - x_old) * (1.0 / dt)
+    own = (np.arange(sc.n_vertices, dtype=np.int64) * world // sc.n_vertices) == rank
+    np.save(Path(out_dir) / f"xp{rank}.npy", x[own])
+    np.save(Path(out_dir) / f"xv{rank}.npy", np.flatnonzero(own))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_xpbd_schedule_matches_reference_step(tmp_path):
+    import torch.multiprocessing as mp
+    sys.path.insert(0, str(ROOT / "tests"))
+    import oracle_api
+    from spg_b200 import scenes as S
+    try:
+        oracle = oracle_api.load()
+    except oracle_api.OracleError as e:
+        pytest.skip(str(e))
+    world, port = 2, _free_port()
+    mp.spawn(_xpbd_worker, args=(world, port, str(tmp_path)), nprocs=world, join=True)
+    sc = S.cloth(9, 9, S.K_SPRING, S.K_QUADRATIC_BENDING)
+    sol = oracle_api.OracleSolver(oracle_api.OracleGroup(oracle, sc), 1, 0.01, 4, 1)
+    sol.step(1)
+    xr, _ = sol.state()
+    got = np.full_like(xr, np.nan)
+    for r in range(world):
+        got[np.load(tmp_path / f"xv{r}.npy")] = np.load(tmp_path / f"xp{r}.npy")
+    assert np.array_equal(got, xr)
