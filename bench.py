@@ -130,8 +130,9 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def time_oracle(cfg_id, frames, warmup, threads=None):
-    """The reference's OpenMP path (or the CPU port) on the host cores: returns (units/s, ms/frame, info)."""
+def time_oracle(cfg_id, frames, warmup, threads=None, min_seconds=0.0):
+    """The reference's OpenMP path (or the CPU port) on the host cores: returns (units/s, ms/frame, info).
+    min_seconds > 0: keep stepping (whole frames) until about that much CPU time has been measured."""
     import oracle_api
     builder, args, solver, substeps, iterations = CONFIGS[cfg_id]
     oracle = oracle_api.load()
@@ -146,7 +147,15 @@ def time_oracle(cfg_id, frames, warmup, threads=None):
     t = time.perf_counter()
     osol.step(frames)
     el = time.perf_counter() - t
-    units = sc.n_vertices * int(osol.cg_iterations().sum()) if solver == "newton_dx" else \
+    cg_total = int(osol.cg_iterations().sum()) if solver == "newton_dx" else 0
+    if el < min_seconds:  # a sample of about min_seconds of CPU work (the same work every frame: no adaptive counts)
+        extra = min(int((min_seconds - el) / (el / frames)) + 1, 400)
+        t = time.perf_counter()
+        osol.step(extra)
+        el += time.perf_counter() - t
+        frames += extra
+        cg_total += int(osol.cg_iterations().sum()) if solver == "newton_dx" else 0
+    units = sc.n_vertices * cg_total if solver == "newton_dx" else \
         sc.n_vertices * iterations * substeps * frames if solver == "vbd" else \
         sum(e.stencils.shape[0] for e in sc.energies) * iterations * substeps * frames
     return units / el, 1e3 * el / frames, {"kind": oracle.kind, "cores": cores,
@@ -395,7 +404,7 @@ def run_single(args):
             if builder == "cloth_xpbd":
                 CONFIGS[20] = ("cloth_xpbd", (64, 64), "xpbd", substeps, iterations)
                 sample_cfg = 20
-            v_cpu, ms_cpu, info = time_oracle(sample_cfg, 3, 1)
+            v_cpu, ms_cpu, info = time_oracle(sample_cfg, 3, 1, min_seconds=10.0)
             cpu = {"value": v_cpu, "unit": unit, "ms_per_frame_on_sample": ms_cpu, **info}
         except Exception as e:  # the oracle is test infrastructure; its absence must not hide the GPU number
             cpu = {"value": None, "unit": unit, "error": str(e)}
