@@ -78,3 +78,44 @@ def test_colouring_is_linear_time():
     c = api.color_vertices(sc.n_vertices, _sets(sc))
     assert time.time() - t < 2.0
     assert c.max() + 1 == 7
+
+
+# ---- edge cases of the two colourings, against the compiled reference where it can run them ----
+@pytest.mark.parametrize("n,sets", [
+    (6, [np.array([[0, 1], [1, 2]], np.int32)]),                                   # isolated vertices 3..5
+    (6, [np.array([[0, 1], [1, 2]], np.int32), np.empty((0, 2), np.int32)]),       # an energy without stencils
+    (5, [np.empty((0, 2), np.int32)]),                                             # no stencil at all
+    (1, [np.array([[0]], np.int32)]),                                              # one vertex, one anchor
+    (3, [np.array([[0, 1, 2], [2, 1, 0]], np.int32)]),                             # the same triangle twice
+    (4, [np.array([[0, 1], [0, 1], [1, 0], [2, 3]], np.int32)]),                   # duplicate and reversed springs
+])
+def test_vertex_colouring_edge_cases_match_reference(n, sets):
+    import oracle_api
+    from spg_b200 import api
+    if not oracle_api.available("reference"):
+        pytest.skip("needs the compiled reference")
+    ref = oracle_api.load("reference").color_vertices(n, sets)
+    assert np.array_equal(api.color_vertices(n, sets), ref)
+
+
+@pytest.mark.parametrize("stencils", [
+    np.array([[0, 1], [1, 2]], np.int32),
+    np.array([[0, 1], [0, 1], [1, 0]], np.int32),          # three stencils on the same two vertices: three colours
+    np.array([[0], [1], [2]], np.int32),                   # anchors never conflict: one colour
+    np.array([[0, 1, 2, 3]], np.int32),
+])
+def test_stencil_colouring_edge_cases_match_reference(stencils):
+    import oracle_api
+    from spg_b200 import api
+    if not oracle_api.available("reference"):
+        pytest.skip("needs the compiled reference")
+    ref = oracle_api.load("reference").color_stencils(stencils)
+    assert np.array_equal(api.color_stencils(stencils), ref)
+
+
+def test_empty_stencil_set_is_defined_here():
+    """Graph::greedyColoring writes result[0] unconditionally (graphColoring.cpp:26): on an energy without stencils the
+    reference's colorStencils is undefined behaviour (it crashes in this container). Here it is an empty colouring."""
+    from spg_b200 import api
+    assert api.color_stencils(np.empty((0, 2), np.int32)).size == 0
+    assert api.color_vertices(0, [np.empty((0, 2), np.int32)]).size == 0
