@@ -78,6 +78,7 @@ void newtonBuild(spgx_group *grp, cudaStream_t st)
     for (size_t ei = 0; ei < nE; ++ei) {
         const auto &e = grp->energies[ei];
         baseBlk[ei + 1] = baseBlk[ei] + static_cast<uint64_t>(e.n) * e.S * e.S;
+        baseBlk[ei + 1] += baseBlk[ei + 1] & 1ull;  // every energy starts on 16 bytes (a block is 72): hingeHessianKernel stores double2
         nw.elemHessianBytes += 8.0 * e.n * 9 * e.S * e.S;
     }
     if (baseBlk[nE] >= (1ull << 32)) throw std::runtime_error("too many element Hessian blocks for 32-bit gather lists");
