@@ -18,9 +18,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-#include <map>
 
-#include "spgx/io.hpp"
+#include "spgx/geom.hpp"
 
 using namespace spgx;
 
@@ -75,16 +74,12 @@ int main(int argc, char **argv)
             std::vector<Vector3> flat(verts.size());
             for (size_t i = 0; i < verts.size(); ++i) flat[i] = {verts[i].x, 0.0, -verts[i].y};
             for (size_t i = 0; i < verts.size(); ++i) object.addParticle(flat[i], verts[i], particleArea[i] * (1.0 / total));
-            // edge table: (min, max) -> opposing vertices in face order
-            std::map<std::pair<int, int>, std::vector<int>> edges;
-            for (const auto &f : faces)
-                for (int k = 0; k < 3; ++k) {
-                    const int a = f[k], b = f[(k + 1) % 3], o = f[(k + 2) % 3];
-                    edges[{std::min(a, b), std::max(a, b)}].push_back(o);
-                }
+            const TriangleMesh mesh(flat, verts, faces);  // edges in (min, max) order, opposing vertices in face order
             auto bending = std::make_shared<DiscreteBendingEnergy>();
-            for (const auto &[e, opp] : edges)
-                if (opp.size() == 2) bending->addStencil({e.first, e.second, opp[0], opp[1]}, 0.0, 1e-2);
+            for (size_t e = 0; e < mesh.edges().size(); ++e) {
+                const auto &opp = mesh.opposingVerticesPerEdge()[e];
+                if (opp.size() == 2) bending->addStencil({mesh.edges()[e][0], mesh.edges()[e][1], opp[0].vertexId, opp[1].vertexId}, 0.0, 1e-2);
+            }
             auto membrane = std::make_shared<MembraneStvkEnergy>();
             for (const auto &f : faces) membrane->addStencil({f[0], f[1], f[2]}, 1e2, 0.0);
             auto pins = std::make_shared<SpringAnchorEnergy>();

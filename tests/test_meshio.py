@@ -124,6 +124,34 @@ def test_load_msh_ascii_41_and_22(tmp_path):
         _dump(exe, s)
 
 
+def test_triangle_and_tetrahedral_mesh_tables(tmp_path):
+    """spgx::TriangleMesh / TetrahedralMesh (include/spgx/geom.hpp): edge order and opposing vertices as the reference's
+    classes give them (triangleMesh.h:36-50, tetrahedralMesh.h:32-46); scenes.triangle_edges is the same table, checked
+    against the compiled reference's createCloth stencils in test_scenes.py."""
+    exe = _compile(tmp_path, ROOT / "tests" / "native" / "geom_dump.cpp", "geom_dump")
+    res = subprocess.run([str(exe), "selftest"], capture_output=True, text=True)
+    assert res.returncode == 0 and res.stdout.strip() == "ok", res.stdout + res.stderr
+    _, verts0, faces = S.triangle_square_mesh(5, 7)
+    obj = tmp_path / "grid.obj"
+    _write_obj(obj, verts0, faces)
+    lines = subprocess.run([str(exe), str(obj)], capture_output=True, text=True, check=True).stdout.strip().splitlines()
+    edges, count, opps = S.triangle_edges(faces)
+    assert int(lines[0].split()[1]) == len(edges)
+    for row, e, c, o in zip(lines[1:], edges, count, opps):
+        t = [int(a) for a in row.split()]
+        assert t[0] == e[0] and t[1] == e[1] and t[2] == c
+        assert [t[4 + 2 * k] for k in range(c)] == [int(a) for a in o[:c]]
+        for k in range(c):   # the triangle named really holds the edge and the opposite vertex
+            assert set(faces[t[3 + 2 * k]]) == {e[0], e[1], t[4 + 2 * k]}
+    verts, tets = S.tet_beam_mesh(3, 2, 3)
+    msh = tmp_path / "beam.msh"
+    _write_msh41(msh, verts, tets.astype(np.int32))
+    lines = subprocess.run([str(exe), str(msh)], capture_output=True, text=True, check=True).stdout.strip().splitlines()
+    got = np.array([[int(a) for a in l.split()] for l in lines[1:]])
+    pairs = np.concatenate([np.sort(tets[:, [i, j]], axis=1) for i in range(3) for j in range(i + 1, 4)])
+    assert np.array_equal(got, np.unique(pairs, axis=0))
+
+
 # ---------------------------------------------------------------- GPU: a loaded mesh through the facade vs the oracle
 def _run_headless(exe, *args):
     res = subprocess.run([str(exe), *map(str, args)], capture_output=True, text=True)
