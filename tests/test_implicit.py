@@ -279,29 +279,3 @@ def test_gpu_robust_newton_iterations_vs_oracle(ctx, oracle, scene, kind):
     assert _rel(x, xr) <= 1e-6 and _rel(v, vr) <= 1e-4, (_rel(x, xr), _rel(v, vr))
     g.close()
 
-
-@pytest.mark.gpu
-def test_gpu_energy_order_does_not_matter_to_the_arena(ctx, oracle):
-    """The element Hessians of all energies share one arena (api_newton.cu): with the anchors first (an odd number of
-    72-byte blocks) and the membrane second (another odd number) the discrete-bending range used to start off a
-    16-byte boundary, which the hinge kernel's double2 stores need.  Same scene as the others, energies reordered on
-    both sides."""
-    from spg_b200 import api
-    base = S.cloth(9, 9)   # 2 * 8 * 8 = 128 faces; + 3 anchors below = odd block counts before the bending energy
-    sc = S.Scene(base.x.copy(), base.x0.copy(), base.mass.copy())
-    bend, membrane, anchors = base.energies
-    ids = np.array([0, 8, 40], np.int32)
-    anchors3 = S.SceneEnergy(S.K_ANCHOR, ids[:, None].copy(), np.concatenate([base.x[ids], np.full((3, 1), 1e5)], axis=1))
-    sc.energies = [anchors3, membrane, bend]
-    assert (3 * 1 + membrane.stencils.shape[0] * 9) % 2 == 1
-    g = api.Group.from_scene(ctx, sc)
-    g.finalize(api.SPGX_NEWTON)
-    og = oracle_api.OracleGroup(oracle, sc)
-    osol = oracle_api.OracleSolver(og, MI.NDX, 0.01, 1, 1)
-    g.implicit_step(_GPU_KIND[MI.NDX], 0.01, 1, frames=2)
-    osol.step(2)
-    x, v = g.download()
-    xr, vr = osol.state()
-    assert np.abs(g.cg_iterations() - osol.cg_iterations()).max() <= 1
-    assert _rel(x, xr) <= 1e-6 and _rel(v, vr) <= 1e-4
-    g.close()

@@ -6,11 +6,19 @@ to the oracle (tests/test_gpu_step.py):
     where all three are within 1e-9 of the reference;
   * a frame is a pure function of the state: two runs from the initial state, and 2 frames in one call against 1 + 1, are
     bit-identical (no atomics, no run-to-run reduction order anywhere in the path);
-  * the physics the scene fixes: the two pinned corners stay put, everything else falls."""
+  * the physics the scene fixes: the two pinned corners stay put, everything else falls.
+(This file sorts last on purpose: it is the newest and the heaviest of the GPU suite.)  It also holds the regression test of
+the element-Hessian arena's alignment (api_newton.cu)."""
+import sys
+from pathlib import Path
+
 import numpy as np
 import pytest
 
-from spg_b200 import api, scenes as S
+sys.path.insert(0, str(Path(__file__).resolve().parent / "golden"))
+import make_golden_implicit as MI  # noqa: E402
+import oracle_api  # noqa: E402
+from spg_b200 import api, scenes as S  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 N = 1024
@@ -81,4 +89,29 @@ def test_config3_scene_invariants_after_a_frame(ctx, scene, monkeypatch):
     far.reshape(N, N)[:200, :] = False
     assert np.allclose(dy[far], -9.8 * 0.01 * 0.01, rtol=1e-5, atol=1e-12)
     assert np.abs(x[far][:, [0, 2]] - scene.x[far][:, [0, 2]]).max() <= 1e-8
+    g.close()
+
+
+def test_gpu_energy_order_does_not_matter_to_the_arena(ctx, oracle):
+    """The element Hessians of all energies share one arena (api_newton.cu): with the anchors first (an odd number of
+    72-byte blocks) and the membrane second (another odd number) the discrete-bending range used to start off a
+    16-byte boundary, which the hinge kernel's double2 stores need.  Same scene as the others, energies reordered on
+    both sides."""
+    base = S.cloth(9, 9)   # 2 * 8 * 8 = 128 faces; + 3 anchors below = odd block counts before the bending energy
+    sc = S.Scene(base.x.copy(), base.x0.copy(), base.mass.copy())
+    bend, membrane, anchors = base.energies
+    ids = np.array([0, 8, 40], np.int32)
+    anchors3 = S.SceneEnergy(S.K_ANCHOR, ids[:, None].copy(), np.concatenate([base.x[ids], np.full((3, 1), 1e5)], axis=1))
+    sc.energies = [anchors3, membrane, bend]
+    assert (3 * 1 + membrane.stencils.shape[0] * 9) % 2 == 1
+    g = api.Group.from_scene(ctx, sc)
+    g.finalize(api.SPGX_NEWTON)
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, MI.NDX, 0.01, 1, 1)
+    g.implicit_step(api.SPGX_IE_NEWTON_DX, 0.01, 1, frames=2)
+    osol.step(2)
+    x, v = g.download()
+    xr, vr = osol.state()
+    assert np.abs(g.cg_iterations() - osol.cg_iterations()).max() <= 1
+    assert np.abs(x - xr).max() <= 1e-6 * np.abs(xr).max() and np.abs(v - vr).max() <= 1e-4 * np.abs(vr).max()
     g.close()
