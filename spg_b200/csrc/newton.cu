@@ -23,6 +23,7 @@
 
 #include "energies.cuh"
 #include "hinge_hessian.cuh"
+#include "membrane_hessian.cuh"
 #include "kernels.h"
 
 namespace spgx
@@ -240,9 +241,45 @@ __global__ void __launch_bounds__(32) hingeHessianKernel(const NewtonEnergyDev e
     }
 }
 
+// StVK membrane: the hand-derived 9 x 9 Hessian (membrane_hessian.cuh), one thread per triangle, staged like the hinge
+// kernel (a triangle's 9 blocks are 648 bytes: 8-byte coalesced stores, the stage stride 81 is odd: conflict-free).
+// Opt-in (SPGX_MEMBRANE_HAND=1) until it has been measured and parity-checked on the device; the arithmetic is checked on
+// the host against Dual<9, true> (tests/native/host_membrane_hessian.cpp).
+__global__ void __launch_bounds__(32) membraneStvkHessianKernel(const NewtonEnergyDev en, const double *__restrict__ x)
+{
+    extern __shared__ double stage[];
+    const int lane = threadIdx.x;
+    const long long base = static_cast<long long>(blockIdx.x) * 32;
+    const long long st = base + lane;
+    if (st < en.nStencils) {
+        const int32_t *ids = en.stencils + static_cast<size_t>(st) * 3;
+        V3d xs[3];
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+            const size_t o = 3 * static_cast<size_t>(ids[s]);
+            xs[s] = V3d(x[o], x[o + 1], x[o + 2]);
+        }
+        membraneStvkElementHessian(xs, en.records + static_cast<size_t>(st) * EnergyKind<K_MEMBRANE_STVK>::NP, stage + lane * 81);
+    }
+    __syncwarp();
+    const long long left = en.nStencils - base;
+    const int total = static_cast<int>(left < 32 ? left : 32) * 81;
+    double *dst = en.elemH + static_cast<size_t>(base) * 81;
+    for (int q = lane; q < total; q += 32) dst[q] = stage[q];  // (stage rows are contiguous at stride 81: a flat copy)
+}
+
 template <int KIND>
 void launchElementHessianKind(const NewtonEnergyDev &en, const double *x, cudaStream_t stream)
 {
+    if (KIND == K_MEMBRANE_STVK) {
+        const char *env = getenv("SPGX_MEMBRANE_HAND");  // read per launch: a test can switch it inside one process
+        const bool hand = env && atoi(env) != 0;
+        if (hand) {
+            if (en.nStencils > 0)
+                membraneStvkHessianKernel<<<static_cast<unsigned>((en.nStencils + 31) / 32), 32, 32 * 81 * sizeof(double), stream>>>(en, x);
+            return;
+        }
+    }
     if (KIND == K_DISCRETE_BENDING) {
         // SPGX_HINGE_HAND=0: the generic mixed-dual evaluation (what the hand-derived blocks are tested against)
         static const bool hand = !(getenv("SPGX_HINGE_HAND") && atoi(getenv("SPGX_HINGE_HAND")) == 0);
