@@ -62,3 +62,14 @@ def test_facade_example_compiles(tmp_path):
     if not torch.cuda.is_available():
         res = subprocess.run([str(exe), "vbd", "8", "2", "1", "5"], capture_output=True, text=True)
         assert res.returncode == 1 and "no CUDA device" in res.stderr  # std::runtime_error from the facade
+
+
+def test_integration_notes_name_every_entry_point():
+    """INTEGRATION.md section C is the map from the C ABI to what it replaces in the reference: no declared entry point
+    may be missing from it."""
+    import re
+    from pathlib import Path
+    root = Path(__file__).resolve().parent.parent
+    names = set(re.findall(r"\b(spgx_[a-z0-9_]+)\s*\(", (root / "include" / "spgx.h").read_text()))
+    doc = (root / "INTEGRATION.md").read_text()
+    assert not [n for n in sorted(names) if n not in doc]
