@@ -21,7 +21,7 @@ OBJDIR = ROOT / "build" / "obj"
 LIB = LIBDIR / "libspgx.so"
 
 CU_SOURCES = ["api_build.cu", "api_step.cu", "vbd.cu", "vbd_stream_cloth.cu", "vbd_stream_tets.cu", "xpbd.cu", "state.cu", "comm.cu", "newton.cu", "api_newton.cu"]
-HEADERS = ["dual.cuh", "halo.cuh", "vbd_stream_persist.cuh", "linalg.cuh", "energies.cuh", "streams.cuh", "vbd_stream.cuh", "energy_prepare.h", "host_build.h", "partition.h",
+HEADERS = ["dual.cuh", "halo.cuh", "linalg.cuh", "energies.cuh", "streams.cuh", "vbd_stream.cuh", "energy_prepare.h", "host_build.h", "partition.h",
            "kernels.h", "group.h"]
 
 NVCC_FLAGS = [

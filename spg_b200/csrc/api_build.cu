@@ -671,10 +671,6 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 if (l == 1 || l == 2 || l == 4) grp->vbdLanes = l;
             }
             grp->vbdOcc = 4;
-            if (const char *env = getenv("SPGX_VBD_OCC")) {
-                const int o = atoi(env);
-                if ((o >= 3 && o <= 5) || (o >= 17 && o <= 19)) grp->vbdOcc = o;
-            }
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
                 const int64_t n = grp->colorOffsets[c + 1] - grp->colorOffsets[c];
@@ -733,10 +729,6 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (const char *env = getenv("SPGX_VBD_LOOKAHEAD")) grp->vbdLookahead = std::max(0, atoi(env));
             grp->vbdPdl = 1;
             if (const char *env = getenv("SPGX_VBD_PDL")) grp->vbdPdl = atoi(env) != 0;
-            grp->vbdPersist = 0;
-            if (const char *env = getenv("SPGX_VBD_PERSIST")) grp->vbdPersist = atoi(env) != 0;
-            grp->vbdL1pf = 0;
-            if (const char *env = getenv("SPGX_VBD_L1PF")) grp->vbdL1pf = atoi(env) != 0;
             grp->vbdCarveout = -1;
             if (const char *env = getenv("SPGX_VBD_CARVEOUT")) grp->vbdCarveout = std::min(100, std::max(-1, atoi(env)));
             {

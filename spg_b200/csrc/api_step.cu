@@ -56,8 +56,6 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.nSlices = grp->nSlices;
     args.lookahead = std::min(grp->vbdLookahead, std::max(grp->nSlices - 1, 0));
     args.pdl = grp->vbdPdl;
-    args.persist = grp->vbdPersist;
-    args.l1pf = grp->vbdL1pf;
     args.carveout = grp->vbdCarveout;
     const unsigned mask = kindMaskOf(grp);
     const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;

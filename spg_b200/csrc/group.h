@@ -196,7 +196,7 @@ struct spgx_group {
     };
     std::vector<StreamState> streams;  // indexed by stream type when non-empty
     spgx::DevBuf<uint32_t> d_sliceDesc, d_nbrIds;
-    int maxNbr = 0, nSlices = 0, vbdLookahead = 512, vbdPdl = 1, vbdPersist = 0, vbdL1pf = 0, vbdCarveout = -1;
+    int maxNbr = 0, nSlices = 0, vbdLookahead = 512, vbdPdl = 1, vbdCarveout = -1;
     unsigned streamMask = 0;
     double streamBytes = 0;  // bytes of stream + neighbour tables one full sweep reads (reported)
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)

@@ -68,8 +68,6 @@ struct VbdArgs {
     int nSlices;             // all colours
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
     int pdl;                 // 1: launch colour passes with programmatic stream serialization
-    int persist;             // 1: persistent warps that prefetch their next slice (vbd_stream_persist.cuh)
-    int l1pf;                // 1: the record two steps ahead is pulled into L1 (prefetch.global.L1: no registers held)
     int carveout;            // preferred shared-memory carveout of the streaming kernel in percent (-1: maximum shared)
     VbdHaloDev halo;
 };

@@ -19,12 +19,6 @@
 
 namespace spgx
 {
-// prefetch.global.L1 of the record two steps ahead (VbdArgs::l1pf, SPGX_VBD_L1PF=1) measured slower (3.22 vs 2.95 ms per
-// frame at config 3, profiles/r1g_l1pf_carveout_sweep.txt): compiled out of the incidence loop unless this is set.
-#ifndef SPGX_VBD_L1PF_BUILD
-#define SPGX_VBD_L1PF_BUILD 0
-#endif
-constexpr bool kVbdL1Prefetch = SPGX_VBD_L1PF_BUILD != 0;
 using D2 = Dual<3, true>;
 
 __device__ __forceinline__ void cpAsync8(double *smemDst, const double *gmemSrc)
@@ -247,14 +241,11 @@ struct StreamRec {
         for (int k = 0; k < SK::NQ; ++k) q[k] = __ldg(qp + k * 32);
     }
     // P: the warp's neighbour tile, already offset to this lane's vertex column; element (k, c) at P[(3 k + c) * VW]
-    // ownOff >= 0: the owner's position is re-read from its tile row (element offset ownOff from P) instead of being
-    // held in registers across the whole incidence loop (6 registers less in the register-capped variants)
     template <int ST, int VW>
-    __device__ __forceinline__ void eval(const double *P, const V3d &xoReg, V3d &g, Sym3 &H, int ownOff = -1) const
+    __device__ __forceinline__ void eval(const double *P, const V3d &xo, V3d &g, Sym3 &H) const
     {
         using SK = Stream<ST>;
         if (idx == 0xFFFFFFFFu) return;
-        const V3d xo = ownOff >= 0 ? V3d(P[ownOff], P[ownOff + VW], P[ownOff + 2 * VW]) : xoReg;
         V3d xn[SK::NI];
 #pragma unroll
         for (int k = 0; k < SK::NI; ++k) {
@@ -308,37 +299,18 @@ struct StreamPipe {
             loadFrom<ST + 1>(a, r, s, lane);
         }
     }
-    // pull the 128-byte lines of the record of step s into L1: lane 0 the index line, lanes 1 .. 2 NQ the parameter lines
-    template <int ST>
-    __device__ __forceinline__ void prefetchL1From(const VbdArgs &a, uint32_t s, int lane) const
-    {
-        if constexpr (ST < kNumStreamTypes) {
-            if constexpr ((SMASK >> ST) & 1u) {
-                if (s < cum[ST]) {
-                    const uint32_t t = base[ST] + s;
-                    constexpr int NQ = Stream<ST>::NQ;
-                    const char *line = lane == 0 ? reinterpret_cast<const char *>(a.s[ST].idx + static_cast<size_t>(t) * 32)
-                                                 : reinterpret_cast<const char *>(a.s[ST].params + static_cast<size_t>(t) * (NQ * 32)) +
-                                                       static_cast<size_t>(lane - 1) * 128;
-                    if (lane <= 2 * NQ) asm volatile("prefetch.global.L1 [%0];" ::"l"(line));
-                    return;
-                }
-            }
-            prefetchL1From<ST + 1>(a, s, lane);
-        }
-    }
     template <int ST>
     __device__ __forceinline__ void evalFrom(const StreamRec<SMASK> &r, uint32_t s, const double *P, const V3d &xo, V3d &g,
-                                             Sym3 &H, int ownOff = -1) const
+                                             Sym3 &H) const
     {
         if constexpr (ST < kNumStreamTypes) {
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < cum[ST]) {
-                    r.template eval<ST, VW>(P, xo, g, H, ownOff);
+                    r.template eval<ST, VW>(P, xo, g, H);
                     return;
                 }
             }
-            evalFrom<ST + 1>(r, s, P, xo, g, H, ownOff);
+            evalFrom<ST + 1>(r, s, P, xo, g, H);
         }
     }
 };
@@ -377,9 +349,9 @@ __device__ __forceinline__ void prefetchStreamIfPresent(const VbdArgs &a, const 
 constexpr int kStreamBlockThreads = 128;
 
 // The body of the colour pass; BT = threads per block.  Warps never synchronise with each other (each has its own tile),
-// so the block size only sets the granularity of the occupancy / register trade-off: vbdStreamKernel bounds registers by
-// resident 128-thread blocks (OCC), vbdStreamKernelR runs one-warp blocks under an explicit register cap.
-template <unsigned SMASK, unsigned KMASK, int G, int BT, bool XS = false>
+// so the block size only sets the granularity of the occupancy / register trade-off (registers are bounded by OCC resident
+// blocks of BT threads).
+template <unsigned SMASK, unsigned KMASK, int G, int BT>
 __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
@@ -408,8 +380,6 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     StreamRec<SMASK> r0, r1;
     r0.idx = r1.idx = 0xFFFFFFFFu;
     if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
-    if constexpr (kVbdL1Prefetch)
-        if (a.l1pf && pipe.total > 1) pipe.template prefetchL1From<0>(a, 1, lane);
     constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
     const uint32_t nb = d.lo.y, ne = n.lo.y;
     uint32_t nid[PRE];
@@ -487,10 +457,7 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     cpAsyncWaitAll();
     if constexpr (G > 1) __syncwarp();
     V3d xo(0.0, 0.0, 0.0);
-    if constexpr (!XS) {
-        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
-    }
-    const int ownOff = XS ? a.maxNbr * (3 * VW) : -1;
+    if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
 
     // 3. incidence streams.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
     // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
@@ -502,22 +469,15 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
         int l = orderAfter(lane, r0.idx);
         if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
-        if constexpr (kVbdL1Prefetch)
-            if (a.l1pf && s + 2 < pipe.total) pipe.template prefetchL1From<0>(a, s + 2, lane);
-        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H, ownOff);
+        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
         if (s + 1 >= pipe.total) break;
         l = orderAfter(lane, r1.idx);
         if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
-        if constexpr (kVbdL1Prefetch)
-            if (a.l1pf && s + 3 < pipe.total) pipe.template prefetchL1From<0>(a, s + 3, lane);
-        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H, ownOff);
+        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
     // 5. reduce, solve, write
-    if constexpr (XS) {
-        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
-    }
     const V3d xn = reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
     // 6. multi-GPU: boundary vertices of the slice go to the neighbours' halo slots over NVLink
     if (a.halo.nPeers) {
@@ -532,52 +492,6 @@ __global__ void __launch_bounds__(BT, OCC)
 {
     vbdStreamBody<SMASK, KMASK, G, BT>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
 }
-// one-warp blocks with an explicit register cap: resident warps per SM = 65536 / (32 REGS), any integer
-template <unsigned SMASK, unsigned KMASK, int G, int REGS>
-__global__ void __maxnreg__(REGS)
-    vbdStreamKernelR(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
-{
-    vbdStreamBody<SMASK, KMASK, G, 32, true>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
-}
-
-template <class Kernel>
-void launchStreamKernel(Kernel kernel, size_t &configured, int BT, int occBlocks, const VbdArgs &args, int begin, int end,
-                        int sliceBase, double invdtSquared, int VW, cudaStream_t stream)
-{
-    const int n = end - begin;
-    if (n <= 0) return;
-    const int warps = (n + VW - 1) / VW;
-    if ((args.maxNbr + 1) * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
-    const int warpsPerBlock = BT / 32;
-    const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
-    const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
-    if (smem > configured) {
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        int pct = args.carveout;  // as in launchStreamGO: shared memory for the resident blocks, the rest stays L1
-        if (pct < 0) pct = static_cast<int>(std::min<size_t>(100, (occBlocks * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024) + 2));
-        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
-        configured = smem;
-    }
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(blocks);
-    cfg.blockDim = dim3(BT);
-    cfg.dynamicSmemBytes = smem;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = args.pdl ? 1 : 0;
-    cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
-}
-template <unsigned SMASK, unsigned KMASK, int G, int REGS>
-void launchStreamGR(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
-{
-    static size_t configured = 0;  // per instantiation
-    launchStreamKernel(vbdStreamKernelR<SMASK, KMASK, G, REGS>, configured, 32, 65536 / (32 * REGS), args, begin, end, sliceBase,
-                       invdtSquared, 32 / G, stream);
-}
-
 template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
 void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
 {
@@ -614,27 +528,15 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
 }
 
-// vbd_stream_persist.cuh (included by the translation units that instantiate the launchers)
-template <unsigned SMASK, unsigned KMASK, int G, int OCC>
-void launchStreamPersistGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream);
-
 template <unsigned SMASK, unsigned KMASK, int G>
 void launchStreamG(const VbdArgs &args, int occ, int begin, int end, int sliceBase, double invdtSquared,
                    cudaStream_t stream)
 {
-    if (args.persist) {  // persistent warps with next-slice prefetch (one occupancy variant)
-        launchStreamPersistGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream);
-        return;
-    }
-    switch (occ) {
-    case 3: launchStreamGO<SMASK, KMASK, G, 3>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    case 5: launchStreamGO<SMASK, KMASK, G, 5>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    // finer steps of the occupancy / register trade-off: occ = resident warps per SM
-    case 17: launchStreamGR<SMASK, KMASK, G, 120>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    case 18: launchStreamGR<SMASK, KMASK, G, 112>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    case 19: launchStreamGR<SMASK, KMASK, G, 104>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    default: launchStreamGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    }
+    // one occupancy point is compiled: 4 resident blocks of 128 threads (<= 128 registers).  Measured and rejected in
+    // round 1 (profiles/r1f_regcap_sweep_config3.txt, r1f_knob_sweep_config3.txt): 3 / 5 blocks, register caps at
+    // 120 / 112 / 104, persistent warps, prefetch.global.L1 of the record two steps ahead.
+    (void)occ;
+    launchStreamGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream);
 }
 
 template <unsigned SMASK, unsigned KMASK>

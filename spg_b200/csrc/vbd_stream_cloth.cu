@@ -1,6 +1,6 @@
 // Streaming VBD colour pass instantiated for cloth: discrete bending (two canonical streams) + StVK membrane streams,
 // anchors through the CSR path.
-#include "vbd_stream_persist.cuh"
+#include "vbd_stream.cuh"
 
 namespace spgx
 {

@@ -1,6 +1,6 @@
 // Streaming VBD colour pass instantiated for tetrahedral meshes: stable Neo-Hookean / StVK tet streams, anchors through
 // the CSR path.
-#include "vbd_stream_persist.cuh"
+#include "vbd_stream.cuh"
 
 namespace spgx
 {

@@ -2,11 +2,12 @@
 VBD 10 iterations): the reference cannot run there in test time (100 s per frame and a quadratic colouring, SURVEY.md
 section 8c), so parity at this size rests on properties that do not depend on the size and that the small-scene tests tie
 to the oracle (tests/test_gpu_step.py):
-  * the streaming kernel, its persistent-warp form and the generic dual-number kernel agree here as they do at 23 x 17,
-    where all three are within 1e-9 of the reference;
+  * the streaming kernel and the generic dual-number kernel agree here as they do at 23 x 17, where both are within
+    1e-9 of the reference;
   * a frame is a pure function of the state: two runs from the initial state, and 2 frames in one call against 1 + 1, are
     bit-identical (no atomics, no run-to-run reduction order anywhere in the path);
-  * the physics the scene fixes: the two pinned corners stay put, everything else falls.
+  * the physics the scene fixes: far from the anchors one frame is a rigid free fall.
+The direct comparison with the reference at this size is tests/test_gpu_atsize.py (golden vectors of the reference run).
 (This file sorts last on purpose: it is the newest and the heaviest of the GPU suite.)  It also holds the regression test of
 the element-Hessian arena's alignment (api_newton.cu)."""
 import sys
@@ -22,7 +23,7 @@ from spg_b200 import api, scenes as S  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 N = 1024
-KNOBS = ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_OCC", "SPGX_VBD_PERSIST")
+KNOBS = ("SPGX_NO_STREAMS", "SPGX_VBD_LANES")
 
 
 @pytest.fixture(scope="module")
@@ -60,10 +61,6 @@ def test_config3_kernel_forms_agree_and_are_deterministic(ctx, scene, monkeypatc
     assert np.array_equal(xa, xb) and np.array_equal(va, vb)
     g.close()
 
-    gp, (xp, vp) = _frame(ctx, scene, monkeypatch, {"SPGX_VBD_PERSIST": "1"})
-    assert np.array_equal(x, xp) and np.array_equal(v, vp)   # persistent warps: same slices, same per-vertex order
-    gp.close()
-
     gc, (xc, vc) = _frame(ctx, scene, monkeypatch, {"SPGX_NO_STREAMS": "1"})
     assert not gc.streamed()
     scale = np.abs(xc).max()
@@ -74,12 +71,11 @@ def test_config3_kernel_forms_agree_and_are_deterministic(ctx, scene, monkeypatc
 
 def test_config3_scene_invariants_after_a_frame(ctx, scene, monkeypatch):
     g, (x, v) = _frame(ctx, scene, monkeypatch, {})
-    pinned = np.array([0, N - 1])
     free = np.ones(scene.n_vertices, bool)
-    free[pinned] = False
-    # anchors of stiffness 1e5 on particles of mass ~1e-6: the pinned corners hold against a fall of g dt^2 = 9.8e-4
-    # (the reference moves them by 3.4e-6 at 96 x 96, where the particles are a hundred times heavier)
-    assert np.abs(x[pinned] - scene.x[pinned]).max() <= 1e-4
+    free[[0, N - 1]] = False
+    # (the pinned corners are NOT expected to hold at this resolution: one frame of gravity, g dt^2 = 9.8e-4, is a whole
+    # edge length, and ten unconverged sweeps leave the corner elements stretched -- the reference itself moves them by
+    # 7.3e-4; tests/test_gpu_atsize.py pins those two vertices, and every other one, to the reference's values)
     # one frame of free fall from rest: a rigid translation stores no elastic energy, so far from the anchors the
     # inertial guess x + dt^2 g already is the minimiser: dy = -g dt^2, nothing sideways
     dy = x[:, 1] - scene.x[:, 1]
