@@ -70,20 +70,25 @@ def workload_name(builder, args, solver, substeps, iterations):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe).  Only samples taken
+    UNDER LOAD count (GPU utilisation above 50 %, or power at least 100 W above the idle draw seen first): a 60 ms timed
+    region inside a one-second sampling window used to report the idle clock (120 MHz) as the median.  `hold()` keeps the
+    same workload running until enough loaded samples exist when the timed region itself is too short to be sampled."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,utilization.gpu,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, period_ms=50):
         self.device = device
+        self.period_ms = period_ms
         self.proc = None
         self.lines = []
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", str(self.period_ms), "-i", str(self.device)], stdout=subprocess.PIPE, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
         except Exception:
@@ -93,6 +98,33 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
+    def _parse(self):
+        rows = []
+        for ln in list(self.lines):
+            f = [a.strip() for a in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                rows.append((float(f[1]), float(f[2]), float(f[3]), float(f[4]), f[5:9]))
+            except ValueError:
+                continue
+        return rows
+
+    @staticmethod
+    def _loaded(rows):
+        if not rows:
+            return []
+        idle_w = min(r[2] for r in rows)
+        return [r for r in rows if r[3] > 50.0 or r[2] > idle_w + 100.0]
+
+    def hold(self, work, min_samples=8, max_seconds=3.0):
+        """keep calling work() (the timed workload, results discarded) until min_samples loaded samples exist"""
+        if not self.proc:
+            return
+        t0 = time.perf_counter()
+        while len(self._loaded(self._parse())) < min_samples and time.perf_counter() - t0 < max_seconds:
+            work()
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -101,23 +133,18 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, smax, reasons, power = [], None, set(), []
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
-            f = [a.strip() for a in ln.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                sm.append(float(f[1]))
-                smax = float(f[2])
-                power.append(float(f[3]))
-            except ValueError:
-                continue
-            for name, val in zip(names, f[4:8]):
+        rows = self._parse()
+        loaded = self._loaded(rows)
+        reasons = set()
+        for r in loaded:
+            for name, val in zip(self.NAMES, r[4]):
                 if val.lower().startswith("active"):
                     reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "reasons": sorted(reasons),
-                "power_w_max": max(power) if power else None, "samples": len(sm)}
+        return {"sm_mhz": float(np.median([r[0] for r in loaded])) if loaded else None,
+                "sm_max_mhz": rows[-1][1] if rows else None, "reasons": sorted(reasons),
+                "power_w_max": max(r[2] for r in loaded) if loaded else None,
+                "samples": len(rows), "samples_under_load": len(loaded),
+                "note": "median over the samples taken under load (utilisation > 50 % or power > idle + 100 W)"}
 
 
 def peaks():
@@ -298,26 +325,114 @@ def run_implicit(args):
                          "algorithmic_bytes_per_launch": bytes_cg / 3, "algorithmic_bytes_per_unit": bytes_cg / V,
                          "kernel_share_of_step": t.solve_ms / t.total_ms, "peak_source": peak_src},
             "cpu_baseline": cpu}
-    prof = ROOT / "profiles" / "traffic.json"
-    if prof.exists():
-        try:
-            line["roofline"]["traffic"] = json.loads(prof.read_text()).get(str(args.config))
-        except Exception:
-            pass
+    traffic, _, tsrc = ncu_traffic(args.config)
+    line["roofline"]["traffic"] = traffic
+    line["roofline"]["traffic_source"] = tsrc
     line["roofline"]["kernel"] = "bsrSpmvPipelinedKernel + cgUpdateKernel + cgDirectionKernel (one CG iteration)"
     print(json.dumps(line), flush=True)
     return 0
 
 
-def run_single(args):
+def kernel_source_hash():
+    """sha256 over the CUDA sources the library is built from: ties an ncu capture (profiles/traffic.json) to a build"""
+    import hashlib
+    h = hashlib.sha256()
+    for f in sorted((ROOT / "spg_b200" / "csrc").glob("*")):
+        if f.suffix in (".cu", ".cuh", ".h"):
+            h.update(f.name.encode())
+            h.update(f.read_bytes())
+    return h.hexdigest()[:16]
+
+
+def ncu_traffic(cfg_id):
+    """(traffic bytes per launch, FP64 pipe %, provenance) of the dominant kernel from the committed ncu capture -- only
+    when that capture was taken on THIS build of the kernels (same source hash); otherwise null with the reason."""
+    prof = ROOT / "profiles" / "traffic.json"
+    here = kernel_source_hash()
+    if not prof.exists():
+        return None, None, {"csrc_sha256": here, "note": "no ncu capture committed"}
+    try:
+        tj = json.loads(prof.read_text())
+    except Exception as e:
+        return None, None, {"csrc_sha256": here, "note": f"profiles/traffic.json unreadable: {e}"}
+    src = {"csrc_sha256": here, "ncu_csrc_sha256": tj.get("_csrc_sha256"), "ncu_capture": tj.get(f"_source_{cfg_id}", tj.get("_source"))}
+    if tj.get("_csrc_sha256") != here:
+        src["note"] = "the committed ncu capture is of another build of the kernels: traffic omitted"
+        return None, None, src
+    return tj.get(str(cfg_id)), tj.get(f"fp64_pipe_pct_{cfg_id}"), src
+
+
+def measure_e2e(api, ctx, g, step, x_init, units_per_frame, unit, steps, lo=0, hi=None, olo=0, ohi=None, sync_all=None):
+    """End to end through the C ABI with pinned host buffers: every frame uploads its inputs (x, v), steps, and reads its
+    result (x, v) back.  Headline = the pipelined frame loop (spgx_upload_async / spgx_vbd_step(sync = 0) /
+    spgx_download_async): frames take their inputs from the host independently of each other (a frame queue), so the
+    upload of frame k + 1 and the read-back of frame k - 1 run on their own streams while frame k is solved.  The serial
+    loop (blocking upload -> step -> blocking download) is reported beside it.  Every frame's input is the scene's initial
+    state held in pinned host memory (x_init, zero velocities), so every frame does the same work and returns the same
+    result (checked).  [lo, hi) / [olo, ohi): index ranges a partitioned rank uploads / downloads."""
+    V = x_init.shape[0]
+    hi = V if hi is None else hi
+    ohi = V if ohi is None else ohi
+    xin, vin = api.pinned_empty((V, 3)), api.pinned_empty((V, 3))
+    xout = [api.pinned_empty((V, 3)), api.pinned_empty((V, 3))]
+    vout = [api.pinned_empty((V, 3)), api.pinned_empty((V, 3))]
+    xin[lo:hi] = x_init[lo:hi]
+    vin[lo:hi] = 0.0
+    ef = max(min(steps, 10), 1)
+    sync_all = sync_all or (lambda: None)
+
+    def serial():
+        g.upload(xin, vin)
+        step(1)
+        g.download_into(xout[0], vout[0])
+    for _ in range(2):
+        serial()
+    sync_all()
+    t0 = time.perf_counter()
+    for _ in range(ef):
+        serial()
+    sync_all()
+    serial_s = time.perf_counter() - t0
+    assert np.isfinite(xout[0][olo:ohi]).all()
+    x_serial = xout[0][olo:ohi].copy()
+
+    # pipelined: inputs of every frame come from pinned host memory, results go to alternating pinned buffers
+    def pipelined(n):
+        for k in range(n):
+            g.upload_async(xin, vin)
+            step(1, sync=False)
+            g.download_async(xout[k & 1], vout[k & 1])
+        ctx.sync()
+    pipelined(2)
+    sync_all()
+    t0 = time.perf_counter()
+    pipelined(ef)
+    sync_all()
+    pipe_s = time.perf_counter() - t0
+    # the pipelined loop returns, frame after frame, what the serial loop returns (same inputs, same arithmetic)
+    assert np.array_equal(xout[(ef - 1) & 1][olo:ohi], x_serial) and np.array_equal(xout[ef & 1][olo:ohi], x_serial)
+    nb_in, nb_out = 2 * 24 * (hi - lo), 2 * 24 * (ohi - olo)
+    return {"value": units_per_frame * ef / pipe_s, "unit": unit, "h2d_bytes_per_step": int(nb_in), "d2h_bytes_per_step": int(nb_out),
+            "ms_per_step": 1e3 * pipe_s / ef, "steps": ef,
+            "pipeline": "frame queue: H2D of frame k+1 and D2H of frame k-1 on their own streams while frame k is solved "
+                        "(spgx_upload_async / step(sync=0) / spgx_download_async); every frame's x, v come from and return to pinned host memory",
+            "serial_ms_per_step": 1e3 * serial_s / ef, "serial_value": units_per_frame * ef / serial_s}
+
+
+def measure_single(ctx, cfg_id, steps, warmup, rows=0, e2e=True, cpu=True, clocks=True):
+    """One config on one GPU: device-resident value (CUDA-graph replays, CUDA events on the library's stream), the
+    colour-pass / projection-pass roofline (plain launches, per-phase events), end to end through the C ABI, CPU baseline."""
     from spg_b200 import api
-    builder, a, solver, substeps, iterations = CONFIGS[args.config]
-    if args.rows and builder.startswith("cloth"):
-        a = (args.rows, a[1])
+    builder, a, solver, substeps, iterations = CONFIGS[cfg_id]
+    if rows and builder.startswith("cloth"):
+        a = (rows, a[1])
+    t0 = time.perf_counter()
     sc = build_scene(builder, a)
-    ctx = api.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    scene_s = time.perf_counter() - t0
     g = api.Group.from_scene(ctx, sc)
+    t0 = time.perf_counter()
     g.finalize(api.SPGX_VBD if solver == "vbd" else api.SPGX_XPBD)
+    finalize_s = time.perf_counter() - t0   # host colouring + incidence + stream build + upload (blocking call)
     V = sc.n_vertices
     n_stencils = sum(e.stencils.shape[0] for e in sc.energies)
 
@@ -332,70 +447,61 @@ def run_single(args):
     bytes_iter, bytes_lower = g.model_bytes()  # per VBD iteration (all colours) / per XPBD substep
 
     # ---- device-resident value: CUDA-graph replay of K frames, timed with CUDA events on the library's stream ----
-    step(max(args.warmup, 3))
-    sampler = ClockSampler(ctx.device)
-    sampler.start()
-    time.sleep(0.3)
-    step(args.steps)
+    step(max(warmup, 3))
+    sampler = ClockSampler(ctx.device) if clocks else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.15)
+    step(steps)
     t = g.timings()
     total_ms = t.total_ms
     launches = int(t.kernel_launches)
-    time.sleep(0.2)
-    clocks = sampler.stop()
-    value = units_per_frame * args.steps / (total_ms * 1e-3)
+    clk = None
+    if sampler:
+        sampler.hold(lambda: step(steps))   # same workload, results discarded: enough loaded samples for a median
+        clk = sampler.stop()
+    value = units_per_frame * steps / (total_ms * 1e-3)
 
     # ---- dominant kernel (the colour pass): plain launches with per-phase events over the same region ----
     g.set_graph_mode(False)
     step(1)
-    rf = max(min(args.steps, 5), 1)
+    rf = max(min(steps, 5), 1)
     step(rf)
     tp = g.timings()
     g.set_graph_mode(True)
-    passes_per_frame = substeps * iterations * (g.num_colors() if solver == "vbd" else
-                                                sum(g.num_colors(e) for e in range(len(sc.energies))))
+    ncol = g.num_colors() if solver == "vbd" else None
+    passes_per_frame = substeps * iterations * (ncol if solver == "vbd" else sum(g.num_colors(e) for e in range(len(sc.energies))))
     solve_ms_per_frame = tp.solve_ms / rf
     sweeps = iterations * substeps if solver == "vbd" else substeps
     achieved = bytes_iter * sweeps / (solve_ms_per_frame * 1e-3) / 1e9
     peak, peak_src = peaks()
+    info = g.kernel_info()
+    kernel = (("vbdStreamKernel" if g.streamed() else "vbdPassKernel") if solver == "vbd"
+              else ("xpbdClusterKernel" if info.get("xpbd_cluster") else "xpbdPassKernel"))
+    traffic, fp64, tsrc = ncu_traffic(cfg_id)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "kernel": ("vbdStreamKernel" if g.streamed() else "vbdPassKernel") if solver == "vbd" else "xpbdPassKernel",
+                "traffic": traffic, "traffic_source": tsrc, "kernel": kernel,
                 "launches_per_step": passes_per_frame,
                 "avg_launch_us": 1e3 * solve_ms_per_frame / max(passes_per_frame, 1),
                 "algorithmic_bytes_per_launch": bytes_iter * sweeps / max(passes_per_frame, 1),
                 "algorithmic_bytes_per_unit": bytes_iter * sweeps / units_per_frame,
                 "lower_bound_frac": bytes_lower * sweeps / (solve_ms_per_frame * 1e-3) / 1e9 / peak,
                 "kernel_share_of_step": solve_ms_per_frame / (tp.total_ms / rf), "peak_source": peak_src}
-    prof = ROOT / "profiles" / "traffic.json"
-    if prof.exists():
-        try:
-            tj = json.loads(prof.read_text())
-            roofline["traffic"] = tj.get(str(args.config))
-            # the FP64 pipe co-binds this kernel: its utilisation from the same ncu capture rides along
-            roofline["fp64_pipe_pct_ncu"] = tj.get(f"fp64_pipe_pct_{args.config}")
-        except Exception:
-            pass
+    if fp64 is not None:
+        roofline["fp64_pipe_pct_ncu"] = fp64   # the FP64 pipe co-binds this kernel
+    if traffic:
+        roofline["dram_frac_of_peak"] = traffic / (roofline["avg_launch_us"] * 1e-6) / 1e9 / peak
+
+    out = {"value": value, "unit": unit, "ms_per_step": total_ms / steps, "launches": launches, "clocks": clk,
+           "roofline": roofline, "vertices": V, "stencils": n_stencils, "colours": ncol, "finalize_s": finalize_s,
+           "scene_build_s": scene_s, "workload": workload_name(builder, a, solver, substeps, iterations), "solver": solver}
 
     # ---- end to end through the public API: pinned host buffers, H2D + step + D2H every frame ----
-    xh, vh = api.pinned_empty((V, 3)), api.pinned_empty((V, 3))
-    g.download_into(xh, vh)
-    ef = max(min(args.steps, 10), 1)
-    for _ in range(2):
-        g.upload(xh, vh)
-        step(1)
-        g.download_into(xh, vh)
-    t0 = time.perf_counter()
-    for _ in range(ef):
-        g.upload(xh, vh)
-        step(1)
-        g.download_into(xh, vh)
-    e2e_s = time.perf_counter() - t0
-    e2e = {"value": units_per_frame * ef / e2e_s, "unit": unit, "h2d_bytes_per_step": int(xh.nbytes + vh.nbytes),
-           "d2h_bytes_per_step": int(xh.nbytes + vh.nbytes), "ms_per_step": 1e3 * e2e_s / ef, "steps": ef}
-    assert np.isfinite(xh).all()
+    if e2e:
+        out["e2e"] = measure_e2e(api, ctx, g, step, sc.x, units_per_frame, unit, steps)
 
     # ---- CPU baseline on the host cores, bounded sample ----
-    cpu = None
-    if not args.no_cpu_baseline:
+    if cpu:
         try:
             sample_cfg = 1 if (solver == "vbd" and builder == "cloth") else None
             if builder == "beam":
@@ -404,19 +510,42 @@ def run_single(args):
             if builder == "cloth_xpbd":
                 CONFIGS[20] = ("cloth_xpbd", (64, 64), "xpbd", substeps, iterations)
                 sample_cfg = 20
-            v_cpu, ms_cpu, info = time_oracle(sample_cfg, 3, 1, min_seconds=10.0)
-            cpu = {"value": v_cpu, "unit": unit, "ms_per_frame_on_sample": ms_cpu, **info}
+            v_cpu, ms_cpu, cinfo = time_oracle(sample_cfg, 3, 1, min_seconds=10.0)
+            out["cpu_baseline"] = {"value": v_cpu, "unit": unit, "ms_per_frame_on_sample": ms_cpu, **cinfo}
         except Exception as e:  # the oracle is test infrastructure; its absence must not hide the GPU number
-            cpu = {"value": None, "unit": unit, "error": str(e)}
+            out["cpu_baseline"] = {"value": None, "unit": unit, "error": str(e)}
+    g.close()
+    return out
 
-    line = {"metric": metric_name(solver), "value": value, "unit": unit, "n_gpus": 1, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+
+def run_single(args):
+    from spg_b200 import api
+    ctx = api.Context(int(os.environ.get("LOCAL_RANK", "0")))
+    m = measure_single(ctx, args.config, args.steps, args.warmup, rows=args.rows, cpu=not args.no_cpu_baseline)
+    solver = m["solver"]
+    line = {"metric": metric_name(solver), "value": m["value"], "unit": m["unit"], "n_gpus": 1, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": m["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(builder, a, solver, substeps, iterations), "vertices": V,
-                       "stencils": n_stencils, "colours": g.num_colors() if solver == "vbd" else None,
+            "config": {"workload": m["workload"], "vertices": m["vertices"], "stencils": m["stencils"], "colours": m["colours"],
                        "l2": "inputs larger than L2 (element records + incidence ~0.4 GB per iteration vs 126 MB L2)",
                        "launch": "CUDA graph replay of one step()", "parallelism": "1 GPU"},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu}
+            "clocks": m["clocks"], "e2e": m.get("e2e"), "gpu_launches": m["launches"], "roofline": m["roofline"],
+            "cpu_baseline": m.get("cpu_baseline"), "finalize_s": m["finalize_s"], "scene_build_s": m["scene_build_s"]}
+    # the other single-GPU BASELINE configs ride along (they cost milliseconds of device time): config 2 (XPBD cloth
+    # 256 x 256) and config 4 (stable Neo-Hookean beam, ~1 M tets) -- parity-gated at full size by tests/test_gpu_atsize.py
+    if args.config == 3 and not args.rows and not args.no_other_configs:
+        others = {}
+        for cid in (2, 4):
+            try:
+                o = measure_single(ctx, cid, min(args.steps, 10), args.warmup, e2e=True, cpu=False, clocks=False)
+                others[f"config{cid}"] = {k: o[k] for k in ("workload", "value", "unit", "ms_per_step", "launches", "vertices", "stencils",
+                                                             "colours", "finalize_s", "e2e")}
+                others[f"config{cid}"]["roofline"] = {k: o["roofline"][k] for k in ("frac", "achieved", "peak", "kernel", "launches_per_step",
+                                                                                    "avg_launch_us", "algorithmic_bytes_per_unit",
+                                                                                    "lower_bound_frac", "kernel_share_of_step")}
+            except Exception as e:
+                others[f"config{cid}"] = {"error": str(e)}
+        line["other_configs"] = others
     print(json.dumps(line), flush=True)
     return 0
 
@@ -429,7 +558,10 @@ def main():
     ap.add_argument("--impl", default="spgx", choices=["spgx", "reference"])
     ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true", help="N = 1: skip the config 2 / config 4 blocks")
     ap.add_argument("--rows", type=int, default=0, help="diagnostics: override the first grid dimension of a cloth config")
+    ap.add_argument("--no-identity", action="store_true", help="N > 1: skip the N-GPU == 1-GPU bit-identity check")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the config-5 strong-scaling block")
     ap.add_argument("--halo", default="p2p", choices=["p2p", "nccl"], help="multi-GPU halo exchange (bench_multi.py)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -134,6 +134,10 @@ int spgx_ctx_init_comm(spgx_ctx *ctx, int rank, int nranks, const void *id128);
 /* page-lock / unlock a caller-owned host buffer so spgx_upload / spgx_download run at full PCIe rate */
 int spgx_host_register(void *ptr, uint64_t bytes);
 int spgx_host_unregister(void *ptr);
+/* page-locked host memory owned by the library (cudaHostAlloc / cudaFreeHost): what a caller without storage of its own
+ * (a frame queue, a binding's staging arrays) hands to spgx_upload / spgx_download and their asynchronous forms */
+int spgx_host_alloc(uint64_t bytes, void **ptr);
+int spgx_host_free(void *ptr);
 
 /* ---- particle group (BaseSolver::addObject copies the group: baseSolver.cpp:10-14) ----------- */
 /* ParticleGroup::addParticle for nVerts particles (particleGroup.cpp:74-82): x current, x0 rest
@@ -151,13 +155,18 @@ int spgx_group_add_energy(spgx_group *grp, int kind, int nStencils, const int32_
  * velocities are kept across it. */
 int spgx_group_remove_energy(spgx_group *grp, int energyId);
 /* SpringAnchorEnergy::updateAnchor (springAnchorEnergy.h:13) and friends: overwrite `count` doubles of
- * the precomputed record of one stencil starting at `offset`. Takes effect at the next step. */
+ * the precomputed record of one stencil starting at `offset`. Takes effect at the next step, for every solver and
+ * every kind: on a group finalized for VBD whose kind runs through the streaming colour pass (discrete bending, StVK
+ * membrane, tetrahedra) the stencil's canonical per-incidence records are rebuilt and patched in place as well. */
 int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int offset, const double *values,
                               int count);
 int spgx_energy_get_records(spgx_group *grp, int energyId, double *records);
 /* VBD::computeParallelVertexGroups + computeStencilInfoPerVertex (vbd.cpp:203-268) or
  * XPBD::computeParallelStencilGroups (xpbd.cpp:133-160), then upload. Must be called once before stepping;
- * calling it again re-does the precomputation (requirePrecomputationUpdate). */
+ * calling it again re-does the precomputation (requirePrecomputationUpdate) and keeps positions and velocities of
+ * every vertex the rank held before, owned and halo alike. (A vertex that only the NEW layout holds -- the partition
+ * changed, or a new energy reaches further -- starts from the state last uploaded for it: after such a change upload
+ * the global state on every rank.) */
 int spgx_group_finalize(spgx_group *grp, int solverKind);
 
 /* Domain decomposition for VBD: every rank creates the SAME global group (same vertices, same energies), then declares
@@ -224,8 +233,18 @@ int spgx_get_vertex_incidence(spgx_group *grp, int64_t *rowptr, int32_t *entries
 int spgx_get_stencil_colors(spgx_group *grp, int energyId, int32_t *colors /* nStencils */);
 
 /* ---- state --------------------------------------------------------------------------------- */
-/* particleGroups()[i].positions() / velocities(): device -> host (either pointer may be NULL) */
+/* particleGroups()[i].positions() / velocities(): device -> host (either pointer may be NULL).  Waits for the steps
+ * enqueued so far; a halo exchange of theirs that timed out is reported here (SPGX_ERR_COMM), as it is by
+ * spgx_ctx_sync and by the next step call, so that steps enqueued with sync = 0 cannot hand back stale halo data. */
 int spgx_download(spgx_group *grp, double *x, double *v);
+/* The same two transfers without blocking the host, for a frame loop whose I/O overlaps the solve (the reference's loop reads
+ * positions() every frame for display, apps/solverCompare.cpp:878, and writes state on user edits, :1388, :1410-1415): the
+ * upload's host-to-device copy runs on its own stream into a staging pair while earlier steps still run, and is scattered
+ * into place behind them; the download gathers behind the steps enqueued so far and copies out on a third stream while
+ * later steps run.  x / v must be page-locked and stay untouched until spgx_transfer_wait or spgx_ctx_sync returns. */
+int spgx_upload_async(spgx_group *grp, const double *x, const double *v);
+int spgx_download_async(spgx_group *grp, double *x, double *v);
+int spgx_transfer_wait(spgx_group *grp);
 /* host -> device (callers may overwrite positions / velocities between steps, solverCompare.cpp:1388) */
 int spgx_upload(spgx_group *grp, const double *x, const double *v);
 /* ParticleGroup::reset (particleGroup.cpp:97-103): x <- xInitial, v <- 0 */

@@ -63,6 +63,11 @@ SIGNATURES = {
     "spgx_group_get_halo_mode": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "spgx_group_kernel_info": (C.c_int, [C.c_void_p, _lp]),
     "spgx_host_register": (C.c_int, [C.c_void_p, C.c_uint64]),
+    "spgx_host_alloc": (C.c_int, [C.c_uint64, C.POINTER(C.c_void_p)]),
+    "spgx_host_free": (C.c_int, [C.c_void_p]),
+    "spgx_upload_async": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_download_async": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_transfer_wait": (C.c_int, [C.c_void_p]),
     "spgx_host_unregister": (C.c_int, [C.c_void_p]),
     "spgx_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
     "spgx_group_destroy": (None, [C.c_void_p]),
@@ -214,10 +219,17 @@ def xpbd_partition_plan(n_verts: int, stencil_sets, rank: int, nranks: int, owne
 
 
 def pinned_empty(shape, dtype=np.float64) -> np.ndarray:
-    """A page-locked numpy array (cudaHostRegister) for the end-to-end upload / download path."""
-    a = np.empty(shape, dtype=dtype)
-    check(lib.spgx_host_register(a.ctypes.data_as(C.c_void_p), a.nbytes))
-    return a
+    """A page-locked numpy array (spgx_host_alloc: cudaHostAlloc) for the end-to-end upload / download path.  The memory is
+    released when the array and every view of it are gone (registering numpy's own allocation instead would leave the
+    pages registered after numpy frees them, and a later allocation straddling them fails in cudaMemcpyAsync)."""
+    import weakref
+    dtype = np.dtype(dtype)
+    n = int(np.prod(shape))
+    ptr = C.c_void_p()
+    check(lib.spgx_host_alloc(max(n * dtype.itemsize, 1), C.byref(ptr)))
+    buf = (C.c_char * max(n * dtype.itemsize, 1)).from_address(ptr.value)
+    weakref.finalize(buf, lib.spgx_host_free, C.c_void_p(ptr.value))
+    return np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
 
 
 # ---- device objects ----------------------------------------------------------------------------------
@@ -393,6 +405,16 @@ class Group:
 
     def download_into(self, x, v=None):
         check(lib.spgx_download(self.handle, _d(x), _d(v)))
+
+    def upload_async(self, x=None, v=None):
+        """x, v: pinned_empty arrays, global-sized; returns at once (see include/spgx.h)"""
+        check(lib.spgx_upload_async(self.handle, None if x is None else _d(x), None if v is None else _d(v)))
+
+    def download_async(self, x=None, v=None):
+        check(lib.spgx_download_async(self.handle, None if x is None else _d(x), None if v is None else _d(v)))
+
+    def transfer_wait(self):
+        check(lib.spgx_transfer_wait(self.handle))
 
     def upload(self, x=None, v=None):
         x = None if x is None else _f64(x)

@@ -234,11 +234,51 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     }
     grp.d_sliceDesc.upload(desc, st);
     SPGX_CUDA(cudaStreamSynchronize(st));
+    grp.sliceDescHost = std::move(desc);
     grp.nSlices = static_cast<int>(nSlices);
     grp.maxNbr = maxNbr;
     grp.streamBytes = bytes;
     for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
     return true;
+}
+
+// spgx_energy_update_record on an energy whose incidences live in streams: the colour pass never reads d_records for it,
+// it reads the canonical per-incidence records baked into the streams at finalize (buildStreams).  Re-canonicalise the S
+// incidences of the edited stencil and overwrite them in place.  Where an incidence sits: its owner's slot fixes the
+// warp-slice and the column; its rank among the owner's incidences of the same stream type (ascending flat index, the
+// order buildStreams walked) fixes the step and the lane group.  The rank is recounted from the stencil list (a linear
+// scan: record edits are rare, a table would cost 8 bytes per incidence at every finalize).
+static void patchStreamRecords(spgx_group &grp, const EnergyState &e, int stencil)
+{
+    const int G = grp.vbdLanes, VW = 32 / G;
+    cudaStream_t st = grp.ctx->stream;
+    const int32_t *ids = e.stencils.data() + static_cast<size_t>(stencil) * e.S;
+    const double *rec = e.records.data() + static_cast<size_t>(stencil) * e.NP;
+    for (int local = 0; local < e.S; ++local) {
+        const int type = streamTypeOf(e.kind, local);
+        if (type < 0) continue;
+        const int v = ids[local];
+        const int slot = grp.vert2slot[v];
+        if (slot < 0 || slot >= grp.nOwned) continue;  // a halo copy: its owner patches it
+        const int64_t flat = static_cast<int64_t>(stencil) * e.S + local;
+        uint32_t j = 0;  // incidences of v in this energy, of the same stream type, before this one
+        for (int64_t q = 0; q < flat; ++q)
+            if (e.stencils[static_cast<size_t>(q)] == v && streamTypeOf(e.kind, static_cast<int>(q % e.S)) == type) ++j;
+        int colour = 0;
+        while (grp.colorOffsets[colour + 1] <= slot) ++colour;
+        const int inColour = slot - static_cast<int>(grp.colorOffsets[colour]);
+        const size_t slice = static_cast<size_t>(grp.sliceBase[colour]) + inColour / VW;
+        const uint32_t t = grp.sliceDescHost[slice * kSliceDescWords + 2 + type] + j / G;
+        const int lane = static_cast<int>(j % G) * VW + inColour % VW;
+        int32_t nbr[3];
+        double q[16];
+        makeStreamRecord(e.kind, ids, rec, local, nbr, q);
+        const int NQ = streamNQ(type);
+        double *dst = grp.streams[type].d_params.ptr + static_cast<size_t>(t) * NQ * 32 + lane;
+        // q[k] goes to params[t][k][lane]: NQ doubles, 32 doubles apart
+        SPGX_CUDA(cudaMemcpy2DAsync(dst, 32 * sizeof(double), q, sizeof(double), sizeof(double), NQ, cudaMemcpyHostToDevice, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+    }
 }
 }  // namespace spgx
 
@@ -494,13 +534,22 @@ void spgx_ctx_destroy(spgx_ctx *ctx)
 {
     if (!ctx) return;
     commDestroy(ctx);
+    if (ctx->h2dStream) cudaStreamDestroy(ctx->h2dStream);
+    if (ctx->d2hStream) cudaStreamDestroy(ctx->d2hStream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
 
 int spgx_ctx_sync(spgx_ctx *ctx)
 {
-    return guarded([&] { SPGX_CUDA(cudaStreamSynchronize(ctx->stream)); });
+    return guarded([&] {
+        if (!ctx) throw StateError("null context");
+        SPGX_CUDA(cudaSetDevice(ctx->device));
+        SPGX_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ctx->h2dStream) SPGX_CUDA(cudaStreamSynchronize(ctx->h2dStream));
+        if (ctx->d2hStream) SPGX_CUDA(cudaStreamSynchronize(ctx->d2hStream));
+        for (spgx_group *g : ctx->groups) throwIfHaloTimedOut(g);
+    });
 }
 
 int spgx_host_register(void *ptr, uint64_t bytes)
@@ -510,6 +559,20 @@ int spgx_host_register(void *ptr, uint64_t bytes)
 int spgx_host_unregister(void *ptr)
 {
     return guarded([&] { SPGX_CUDA(cudaHostUnregister(ptr)); });
+}
+int spgx_host_alloc(uint64_t bytes, void **ptr)
+{
+    return guarded([&] {
+        if (!ptr) throw StateError("null argument");
+        *ptr = nullptr;
+        if (bytes) SPGX_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocPortable));
+    });
+}
+int spgx_host_free(void *ptr)
+{
+    return guarded([&] {
+        if (ptr) SPGX_CUDA(cudaFreeHost(ptr));
+    });
 }
 
 int spgx_group_create(spgx_ctx *ctx, int nVerts, const double *x, const double *x0, const double *mass,
@@ -526,6 +589,7 @@ int spgx_group_create(spgx_ctx *ctx, int nVerts, const double *x, const double *
         g->vPending.assign(3 * static_cast<size_t>(nVerts), 0.0);
         g->x0.assign(x0, x0 + 3 * static_cast<size_t>(nVerts));
         g->mass.assign(mass, mass + nVerts);
+        ctx->groups.push_back(g);
         *out = g;
     });
 }
@@ -534,6 +598,8 @@ void spgx_group_destroy(spgx_group *grp)
 {
     if (!grp) return;
     cudaSetDevice(grp->ctx->device);
+    auto &gs = grp->ctx->groups;
+    gs.erase(std::remove(gs.begin(), gs.end(), grp), gs.end());
     delete grp;
 }
 
@@ -601,6 +667,7 @@ int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int of
                                           count * sizeof(double), cudaMemcpyHostToDevice, grp->ctx->stream));
                 SPGX_CUDA(cudaStreamSynchronize(grp->ctx->stream));
             }
+            if (e.streamed) patchStreamRecords(*grp, e, stencil);
         }
     });
 }
@@ -613,12 +680,22 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         SPGX_CUDA(cudaSetDevice(grp->ctx->device));
         cudaStream_t st = grp->ctx->stream;
         const int V = grp->nVerts;
-        // preserve current state across a re-finalize
+        // preserve current state across a re-finalize: every slot the OLD layout holds, owned and halo (a partitioned rank's
+        // spgx_download returns owned entries only; its halo copies would restart from the initial state and the first
+        // colour passes of the next step would read them before the owners' pushes arrive)
         std::vector<double> xh, vh;
-        if (grp->finalized || grp->d_x.ptr) {
-            xh = grp->xInitial;  // a partitioned rank only gets its owned entries back
+        if ((grp->finalized || grp->d_x.ptr) && grp->d_x.ptr && grp->d_v.ptr) {
+            xh = grp->xInitial;
             vh.assign(3 * static_cast<size_t>(V), 0.0);
-            if (spgx_download(grp, xh.data(), vh.data()) != SPGX_OK) throw CudaError(spgx_last_error());
+            const size_t nOld = grp->d_x.count / 3;
+            std::vector<double> xs(3 * nOld), vs(3 * nOld);
+            SPGX_CUDA(cudaMemcpyAsync(xs.data(), grp->d_x.ptr, xs.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+            SPGX_CUDA(cudaMemcpyAsync(vs.data(), grp->d_v.ptr, vs.size() * sizeof(double), cudaMemcpyDeviceToHost, st));
+            SPGX_CUDA(cudaStreamSynchronize(st));
+            for (size_t s = 0; s < nOld && s < grp->slot2vert.size(); ++s) {
+                const size_t o = 3 * static_cast<size_t>(grp->slot2vert[s]);
+                for (int c = 0; c < 3; ++c) xh[o + c] = xs[3 * s + c], vh[o + c] = vs[3 * s + c];
+            }
         } else {
             xh = grp->xPending;
             vh = grp->vPending;

@@ -163,6 +163,7 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
     if (nsub < 1 || iters < 0 || nFrames < 0) throw std::runtime_error("invalid step parameters");
     SPGX_CUDA(cudaSetDevice(grp->ctx->device));
     cudaStream_t st = grp->ctx->stream;
+    throwIfHaloTimedOut(grp);  // of an earlier step enqueued with sync = 0
     spgx_group::GraphKey key;
     key.solver = solver;
     key.nsub = nsub;
@@ -225,11 +226,7 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
     grp->timings.kernel_launches = grp->launchCounter;
     if (sync) {
         SPGX_CUDA(cudaStreamSynchronize(st));
-        if (grp->p2p.hostError && *grp->p2p.hostError) {
-            *grp->p2p.hostError = 0;
-            throw CommError("halo exchange: a neighbouring rank did not raise its event counter within the timeout "
-                            "(SPGX_HALO_TIMEOUT_S): ranks out of step, or a rank died");
-        }
+        throwIfHaloTimedOut(grp);
         float ms = 0;
         SPGX_CUDA(cudaEventElapsedTime(&ms, grp->evStart, grp->evStop));
         grp->timings.total_ms = ms;
@@ -294,6 +291,7 @@ int spgx_download(spgx_group *grp, double *x, double *v)
             }
             SPGX_CUDA(cudaStreamSynchronize(st));
         }
+        throwIfHaloTimedOut(grp);  // steps enqueued with sync = 0 have completed by now: stale halo data must not pass silently
     });
 }
 
@@ -440,6 +438,107 @@ int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C,
         SPGX_CUDA(cudaGetLastError());
         std::copy(out, out + e.NC, C);
         std::copy(out + 4, out + 4 + 3 * e.S * e.NC, grad);
+    });
+}
+
+}  // extern "C"
+
+namespace
+{
+void ensureXfer(spgx_group *grp)
+{
+    spgx_ctx *ctx = grp->ctx;
+    if (!ctx->h2dStream) SPGX_CUDA(cudaStreamCreateWithFlags(&ctx->h2dStream, cudaStreamNonBlocking));
+    if (!ctx->d2hStream) SPGX_CUDA(cudaStreamCreateWithFlags(&ctx->d2hStream, cudaStreamNonBlocking));
+    auto &x = grp->xfer;
+    const size_t n3 = 3 * static_cast<size_t>(grp->nVerts);
+    if (x.d_inX.count != n3) {
+        x.d_inX.alloc(n3), x.d_inV.alloc(n3), x.d_outX.alloc(n3), x.d_outV.alloc(n3);
+        x.inUsed = x.outUsed = false;
+    }
+    for (cudaEvent_t *e : {&x.uploaded, &x.inFree, &x.outReady, &x.downloaded})
+        if (!*e) SPGX_CUDA(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+}
+}  // namespace
+
+extern "C" {
+
+// Asynchronous forms of spgx_upload / spgx_download for a frame loop whose host I/O should not serialise with the solve:
+//   H2D runs on its own stream into a staging pair (vertex order) while earlier steps still run; the scatter into slot
+//   order is enqueued on the compute stream behind them.  The download gathers into a second staging pair on the compute
+//   stream (behind the steps enqueued so far) and copies out on a third stream while later steps run.
+// Host buffers must be page-locked (spgx_host_alloc / spgx_host_register) and stay untouched until spgx_ctx_sync (or
+// spgx_transfer_wait) returns.
+int spgx_upload_async(spgx_group *grp, const double *x, const double *v)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        ensureXfer(grp);
+        auto &xf = grp->xfer;
+        cudaStream_t st = grp->ctx->stream, cs = grp->ctx->h2dStream;
+        const bool identity = grp->solverKind != SPGX_VBD;
+        const size_t lo = identity ? 0 : 3 * static_cast<size_t>(grp->localLo);
+        const size_t cnt = identity ? 3 * static_cast<size_t>(grp->nVerts) : 3 * static_cast<size_t>(grp->localHi - grp->localLo);
+        if (xf.inUsed) SPGX_CUDA(cudaStreamWaitEvent(cs, xf.inFree, 0));  // the previous scatter has read the staging pair
+        if (x && cnt) SPGX_CUDA(cudaMemcpyAsync(xf.d_inX.ptr + lo, x + lo, cnt * sizeof(double), cudaMemcpyHostToDevice, cs));
+        if (v && cnt) SPGX_CUDA(cudaMemcpyAsync(xf.d_inV.ptr + lo, v + lo, cnt * sizeof(double), cudaMemcpyHostToDevice, cs));
+        SPGX_CUDA(cudaEventRecord(xf.uploaded, cs));
+        SPGX_CUDA(cudaStreamWaitEvent(st, xf.uploaded, 0));
+        for (int k = 0; k < 2; ++k) {
+            const double *src = k == 0 ? (x ? xf.d_inX.ptr : nullptr) : (v ? xf.d_inV.ptr : nullptr);
+            double *dst = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
+            if (!src) continue;
+            if (identity)
+                SPGX_CUDA(cudaMemcpyAsync(dst, src, cnt * sizeof(double), cudaMemcpyDeviceToDevice, st));
+            else
+                launchPermute3(src, dst, grp->d_slot2vert.ptr, grp->nLocal, /*gather=*/true, st);
+        }
+        SPGX_CUDA(cudaEventRecord(xf.inFree, st));
+        xf.inUsed = true;
+    });
+}
+
+int spgx_download_async(spgx_group *grp, double *x, double *v)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized) throw StateError("group is not finalized");
+        if (!grp->ownedContiguous) throw StateError("asynchronous download needs a contiguous owned index range");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        ensureXfer(grp);
+        auto &xf = grp->xfer;
+        cudaStream_t st = grp->ctx->stream, cs = grp->ctx->d2hStream;
+        const bool identity = grp->solverKind != SPGX_VBD;
+        const size_t lo = identity ? 0 : 3 * static_cast<size_t>(grp->ownedLo);
+        const size_t cnt = identity ? 3 * static_cast<size_t>(grp->nVerts) : 3 * static_cast<size_t>(grp->ownedHi - grp->ownedLo);
+        if (xf.outUsed) SPGX_CUDA(cudaStreamWaitEvent(st, xf.downloaded, 0));  // the previous copy-out has left the staging pair
+        for (int k = 0; k < 2; ++k) {
+            double *dst = k == 0 ? (x ? xf.d_outX.ptr : nullptr) : (v ? xf.d_outV.ptr : nullptr);
+            const double *src = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
+            if (!dst) continue;
+            if (identity)
+                SPGX_CUDA(cudaMemcpyAsync(dst, src, cnt * sizeof(double), cudaMemcpyDeviceToDevice, st));
+            else
+                launchPermute3(src, dst, grp->d_slot2vert.ptr, grp->nOwned, /*gather=*/false, st);
+        }
+        SPGX_CUDA(cudaEventRecord(xf.outReady, st));
+        SPGX_CUDA(cudaStreamWaitEvent(cs, xf.outReady, 0));
+        if (x && cnt) SPGX_CUDA(cudaMemcpyAsync(x + lo, xf.d_outX.ptr + lo, cnt * sizeof(double), cudaMemcpyDeviceToHost, cs));
+        if (v && cnt) SPGX_CUDA(cudaMemcpyAsync(v + lo, xf.d_outV.ptr + lo, cnt * sizeof(double), cudaMemcpyDeviceToHost, cs));
+        SPGX_CUDA(cudaEventRecord(xf.downloaded, cs));
+        xf.outUsed = true;
+    });
+}
+
+// block until the asynchronous transfers enqueued so far have completed (the host buffers are the caller's again)
+int spgx_transfer_wait(spgx_group *grp)
+{
+    return guarded([&] {
+        if (!grp) throw StateError("null group");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        if (grp->ctx->h2dStream) SPGX_CUDA(cudaStreamSynchronize(grp->ctx->h2dStream));
+        if (grp->ctx->d2hStream) SPGX_CUDA(cudaStreamSynchronize(grp->ctx->d2hStream));
+        throwIfHaloTimedOut(grp);
     });
 }
 

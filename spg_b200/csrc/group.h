@@ -104,9 +104,11 @@ struct DevBuf {
 struct spgx_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t h2dStream = nullptr, d2hStream = nullptr;  // spgx_upload_async / spgx_download_async (created on first use)
     cudaDeviceProp prop{};
     void *comm = nullptr;  // ncclComm_t (comm.cu)
     int rank = 0, nRanks = 1;
+    std::vector<spgx_group *> groups;  // live groups of this context (spgx_ctx_sync reports their halo-exchange timeouts)
 };
 
 namespace spgx
@@ -196,6 +198,7 @@ struct spgx_group {
     };
     std::vector<StreamState> streams;  // indexed by stream type when non-empty
     spgx::DevBuf<uint32_t> d_sliceDesc, d_nbrIds;
+    std::vector<uint32_t> sliceDescHost;  // host copy of d_sliceDesc (spgx_energy_update_record patches stream records in place)
     int maxNbr = 0, nSlices = 0, vbdLookahead = 512, vbdPdl = 1, vbdCarveout = -1;
     unsigned streamMask = 0;
     double streamBytes = 0;  // bytes of stream + neighbour tables one full sweep reads (reported)
@@ -235,6 +238,13 @@ struct spgx_group {
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
     spgx::DevBuf<int32_t> d_slot2vert;
     spgx::DevBuf<double> d_eval;
+    // asynchronous state transfer (api_step.cu): staging in vertex order, one pair per direction, so that the upload of the
+    // next frame's inputs and the download of the previous frame's result overlap the step that is running
+    struct AsyncXfer {
+        spgx::DevBuf<double> d_inX, d_inV, d_outX, d_outV;
+        cudaEvent_t uploaded = nullptr, inFree = nullptr, outReady = nullptr, downloaded = nullptr;
+        bool inUsed = false, outUsed = false;
+    } xfer;
 
     // CUDA graph of one step() (keyed by the step parameters)
     bool graphMode = true;
@@ -276,12 +286,23 @@ struct spgx_group {
         if (newton.hostScalar) cudaFreeHost(newton.hostScalar);
         for (auto e : newton.ev)
             if (e) cudaEventDestroy(e);
+        for (auto e : {xfer.uploaded, xfer.inFree, xfer.outReady, xfer.downloaded})
+            if (e) cudaEventDestroy(e);
         spgx::p2pRelease(this);
     }
 };
 
 namespace spgx
 {
+// a wait of the peer-memory halo exchange ran into its timeout (halo.cuh): report it once, as SPGX_ERR_COMM
+inline void throwIfHaloTimedOut(spgx_group *grp)
+{
+    if (grp && grp->p2p.hostError && *grp->p2p.hostError) {
+        *grp->p2p.hostError = 0;
+        throw CommError("halo exchange: a neighbouring rank did not raise its event counter within the timeout "
+                        "(SPGX_HALO_TIMEOUT_S): ranks out of step, or a rank died");
+    }
+}
 int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
 // api_newton.cu: incidence tables, sparse pattern and work buffers of a group finalized with SPGX_NEWTON
 void newtonBuild(spgx_group *grp, cudaStream_t st);
