@@ -18,7 +18,25 @@ def main():
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
-    sc = {"cloth": lambda: S.cloth(37, 21), "beam": lambda: S.tet_beam(13, 4, 3, S.K_TET_SNH)}[scene_name]()
+    sc = {"cloth": lambda: S.cloth(37, 21), "beam": lambda: S.tet_beam(13, 4, 3, S.K_TET_SNH),
+          "cloth_edit": lambda: S.cloth(37, 21)}[scene_name]()
+
+    def run(g, reconnect=None, partitioned=False):
+        """the stepping sequence under test; "cloth_edit": a live edit in the middle (the picking anchor of
+        apps/solverCompare.cpp:717-726 on a vertex next to a strip boundary, then re-finalize: positions AND velocities of
+        owned and halo vertices must survive it -- ADVICE round 1)"""
+        g.vbd_step(0.01, 2, 5, frames=3)
+        if scene_name == "cloth_edit":
+            picked = 21 * (37 // world) + 3   # first row of rank 1's strip
+            anchor = np.concatenate([sc.x[picked] + np.array([0.0, 0.05, 0.0]), [1e4]])
+            g.add_energy(S.K_ANCHOR, np.array([[picked]], np.int32), anchor[None, :])
+            if partitioned:
+                g.disconnect_peers(dist)   # collective: nobody re-allocates an array a neighbour still maps
+            g.finalize(api.SPGX_VBD)
+            if reconnect:
+                reconnect()
+            g.vbd_step(0.01, 2, 5, frames=2)
+
     ctx = api.Context(lr)
     uid = torch.zeros(128, dtype=torch.uint8, device="cuda")
     if rank == 0:
@@ -35,7 +53,7 @@ def main():
             if mode == "p2p":
                 assert g.connect_peers(dist) == api.SPGX_HALO_P2P
             g.set_graph_mode(graph)
-            g.vbd_step(0.01, 2, 5, frames=3)
+            run(g, (lambda: g.connect_peers(dist)) if mode == "p2p" else None, partitioned=True)
             x = np.full((sc.n_vertices, 3), np.nan)
             v = np.full((sc.n_vertices, 3), np.nan)
             g.download_into(x, v)
@@ -53,7 +71,7 @@ def main():
     if rank == 0:
         g1 = api.Group.from_scene(ctx, sc)
         g1.finalize(api.SPGX_VBD)
-        g1.vbd_step(0.01, 2, 5, frames=3)
+        run(g1)
         x1, v1 = g1.download()
         np.savez(out, x1=x1, v1=v1, **{f"x_{m}_{int(gr)}": r[0] for (m, gr), r in results.items()},
                  **{f"v_{m}_{int(gr)}": r[1] for (m, gr), r in results.items()})

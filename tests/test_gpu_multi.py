@@ -17,7 +17,7 @@ def _ngpus():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("scene", ["cloth", "beam"])
+@pytest.mark.parametrize("scene", ["cloth", "beam", "cloth_edit"])
 def test_k_gpu_equals_one_gpu(tmp_path, scene):
     n = _ngpus()
     if n < 2:
