@@ -362,7 +362,8 @@ class Group:
         o = np.zeros(8, dtype=np.int64)
         check(lib.spgx_group_kernel_info(self.handle, o.ctypes.data_as(_lp)))
         return {"streamed": bool(o[0]), "lanes": int(o[1]), "slices": int(o[2]), "max_neighbours": int(o[3]),
-                "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5])}
+                "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5]), "uniform_slices": int(o[6]),
+                "variant": int(o[7]), "xpbd_cluster": False}
 
     def streamed(self) -> bool:
         return self.kernel_info()["streamed"]

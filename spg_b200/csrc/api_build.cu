@@ -127,7 +127,8 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         nbrRowptr[s + 1] = static_cast<uint32_t>(nbrList.size());
     }
     maxNbr = std::max(maxNbr, 1);
-    if (static_cast<size_t>(maxNbr) * 3 * VW * 8 * 4 > 200 * 1024) return false;  // 4 warps per block (vbd_stream.cuh)
+    // shared memory of a 4-warp block (vbd_stream.cuh: tile rows + the pair path's record ring, sized for the widest record)
+    if ((static_cast<size_t>(maxNbr + 3) * 3 * VW * 8 + 2 * (128 + 12 * 256)) * 4 > 200 * 1024) return false;
     for (auto &h : hs)
         if (h.energy >= 0) h.rowptr[NO] = static_cast<uint32_t>(h.idx.size());
 
@@ -158,6 +159,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
                          [](const spgx_group::PushEntry &a, const spgx_group::PushEntry &b) { return a.slot < b.slot; });
     }
     size_t pushCursor = 0, pushBefore = 0;
+    int64_t nUniform = 0;
     const size_t nSlices = sliceSlot.size();
     std::vector<uint32_t> desc((nSlices + 1) * kSliceDescWords, 0u);
     double bytes = 4.0 * desc.size();
@@ -167,6 +169,17 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
             desc[sl * kSliceDescWords + 0] = static_cast<uint32_t>(sliceSlot[sl]);
             desc[sl * kSliceDescWords + 1] = row;
             uint32_t rows = 0, csr = 0, readsHalo = 0;
+            // uniform: a full slice whose vertices all have the same number of incidences in every stream, a multiple
+            // of 2 G -- every lane then has a record in every step and the steps pair up (the pair path of the kernel)
+            uint32_t uniform = (sliceEnd[sl] - sliceSlot[sl] == VW) ? 1u : 0u;
+            for (auto &h : hs) {
+                if (h.energy < 0 || !uniform) continue;
+                const uint32_t c0 = h.rowptr[sliceSlot[sl] + 1] - h.rowptr[sliceSlot[sl]];
+                if (c0 % (2u * G) != 0u) uniform = 0;
+                for (int s = sliceSlot[sl]; s < sliceEnd[sl] && uniform; ++s)
+                    if (h.rowptr[s + 1] - h.rowptr[s] != c0) uniform = 0;
+            }
+            nUniform += uniform;
             for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
                 rows = std::max(rows, nbrRowptr[s + 1] - nbrRowptr[s]);
                 csr |= hasCsr[s];
@@ -175,15 +188,15 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
             }
             // boundary vertices of the slice: one push entry per (vertex, neighbouring rank that holds it as halo)
             while (pushCursor < pushAll.size() && pushAll[pushCursor].slot < sliceEnd[sl]) ++pushCursor;
-            if (pushCursor >= (1u << 30)) throw std::runtime_error("too many boundary vertices for the slice descriptor");
+            if (pushCursor >= (1u << 29)) throw std::runtime_error("too many boundary vertices for the slice descriptor");
             if (pushCursor > pushBefore) pushWarps[sliceColour[sl]]++;
-            desc[sl * kSliceDescWords + 7] = csr | (readsHalo << 1) | (static_cast<uint32_t>(pushBefore) << 2);
+            desc[sl * kSliceDescWords + 7] = csr | (readsHalo << 1) | (uniform << 2) | (static_cast<uint32_t>(pushBefore) << 3);
             pushBefore = pushCursor;
             row += rows;
         }
         desc[nSlices * kSliceDescWords + 0] = static_cast<uint32_t>(NO);
         desc[nSlices * kSliceDescWords + 1] = row;
-        desc[nSlices * kSliceDescWords + 7] = static_cast<uint32_t>(pushBefore) << 2;
+        desc[nSlices * kSliceDescWords + 7] = static_cast<uint32_t>(pushBefore) << 3;
         grp.p2p.pushLocal = pushAll;
         grp.p2p.pushWarps = pushWarps;
         std::vector<uint32_t> ids(static_cast<size_t>(row) * VW, 0u);
@@ -236,6 +249,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     SPGX_CUDA(cudaStreamSynchronize(st));
     grp.sliceDescHost = std::move(desc);
     grp.nSlices = static_cast<int>(nSlices);
+    grp.nUniformSlices = nUniform;
     grp.maxNbr = maxNbr;
     grp.streamBytes = bytes;
     for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
@@ -464,7 +478,7 @@ int spgx_group_kernel_info(spgx_group *grp, int64_t *out8)
     return guarded([&] {
         if (!grp || !grp->finalized || !out8) throw StateError("group is not finalized");
         out8[0] = grp->streamMask != 0, out8[1] = grp->vbdLanes, out8[2] = grp->nSlices, out8[3] = grp->maxNbr;
-        out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = 0, out8[7] = 0;
+        out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = grp->nUniformSlices, out8[7] = grp->vbdOcc;
     });
 }
 
@@ -747,7 +761,12 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 const int l = atoi(env);
                 if (l == 1 || l == 2 || l == 4) grp->vbdLanes = l;
             }
+            // kernel variant (vbd_stream.cuh launchStreamG): resident blocks per SM + 10 x "records through the shared-memory ring"
             grp->vbdOcc = 4;
+            if (const char *env = getenv("SPGX_VBD_VARIANT")) {
+                const int o = atoi(env);
+                if (o == 4 || o == 14 || o == 15 || o == 16) grp->vbdOcc = o;
+            }
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
                 const int64_t n = grp->colorOffsets[c + 1] - grp->colorOffsets[c];
@@ -808,6 +827,15 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (const char *env = getenv("SPGX_VBD_PDL")) grp->vbdPdl = atoi(env) != 0;
             grp->vbdCarveout = -1;
             if (const char *env = getenv("SPGX_VBD_CARVEOUT")) grp->vbdCarveout = std::min(100, std::max(-1, atoi(env)));
+            {
+                // L2 set-aside for the persisting window over the positions (api_step.cu): SPGX_VBD_L2PERSIST_MB, 0 = off
+                int mb = 32;  // measured on config 3: 16 / 32 / 48 / 64 / 96 MB -> 2.756 / 2.709 / 2.711 / 2.728 / 2.736 ms (off: 2.798)
+                if (const char *env = getenv("SPGX_VBD_L2PERSIST_MB")) mb = std::max(0, atoi(env));
+                size_t want = static_cast<size_t>(mb) << 20;
+                want = std::min(want, static_cast<size_t>(grp->ctx->prop.persistingL2CacheMaxSize));
+                if (want) SPGX_CUDA(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want));
+                grp->vbdL2Persist = static_cast<int64_t>(want);
+            }
             {
                 unsigned smask = 0, kmask = 0;
                 for (auto &e : grp->energies) {
@@ -906,10 +934,14 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         // state: local vertices (owned + halo) on the device; the staging buffer spans the global index range
         const int nLocalAll = grp->nLocal;
         const size_t n3 = 3 * static_cast<size_t>(nLocalAll);
-        grp->d_x.alloc(n3);
+        // [x | xInertial | mass] contiguous (x first: its address is what the peer-memory exchange exports)
+        grp->d_x.release(), grp->d_xInertial.release(), grp->d_mass.release();
+        grp->d_stateArena.alloc(2 * n3 + static_cast<size_t>(nLocalAll) + 2);
+        grp->d_x.view(grp->d_stateArena.ptr, n3);
+        grp->d_xInertial.view(grp->d_stateArena.ptr + n3, n3);
+        grp->d_mass.view(grp->d_stateArena.ptr + 2 * n3, static_cast<size_t>(nLocalAll));
         grp->d_v.alloc(n3);
         grp->d_xOld.alloc(n3);
-        grp->d_xInertial.alloc(n3);
         grp->d_stage.alloc(3 * static_cast<size_t>(V));
         grp->d_g.alloc(3);
         grp->d_eval.alloc(64);

@@ -52,9 +52,10 @@ SPGX_HD void addSymOuter2u(Sym3 &H, const V3d &u, const V3d &v)
     H.xx += 2.0 * (u.x * v.x);
     H.yy += 2.0 * (u.y * v.y);
     H.zz += 2.0 * (u.z * v.z);
-    H.xy += u.x * v.y + u.y * v.x;
-    H.xz += u.x * v.z + u.z * v.x;
-    H.yz += u.y * v.z + u.z * v.y;
+    // two fused multiply-adds straight into the accumulator (a product, an FMA and an add otherwise)
+    H.xy = ::fma(u.x, v.y, ::fma(u.y, v.x, H.xy));
+    H.xz = ::fma(u.x, v.z, ::fma(u.z, v.x, H.xz));
+    H.yz = ::fma(u.y, v.z, ::fma(u.z, v.y, H.yz));
 }
 // accumulate scale * u u^T into H
 SPGX_HD void addOuter(Sym3 &H, const V3d &u, double scale)

@@ -60,13 +60,15 @@ template <class T>
 struct DevBuf {
     T *ptr = nullptr;
     size_t count = 0;
+    bool owned = true;  // false: a view into another allocation (see view())
     DevBuf() = default;
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
-    DevBuf(DevBuf &&o) noexcept : ptr(o.ptr), count(o.count)
+    DevBuf(DevBuf &&o) noexcept : ptr(o.ptr), count(o.count), owned(o.owned)
     {
         o.ptr = nullptr;
         o.count = 0;
+        o.owned = true;
     }
     DevBuf &operator=(DevBuf &&o) noexcept
     {
@@ -74,17 +76,28 @@ struct DevBuf {
             release();
             ptr = o.ptr;
             count = o.count;
+            owned = o.owned;
             o.ptr = nullptr;
             o.count = 0;
+            o.owned = true;
         }
         return *this;
     }
     ~DevBuf() { release(); }
     void release()
     {
-        if (ptr) cudaFree(ptr);
+        if (ptr && owned) cudaFree(ptr);
         ptr = nullptr;
         count = 0;
+        owned = true;
+    }
+    // n elements of someone else's allocation starting at p (not freed here)
+    void view(T *p, size_t n)
+    {
+        release();
+        ptr = p;
+        count = n;
+        owned = false;
     }
     void alloc(size_t n)
     {
@@ -95,7 +108,7 @@ struct DevBuf {
     }
     void upload(const std::vector<T> &h, cudaStream_t s)
     {
-        alloc(h.size());
+        if (!(ptr && !owned && count == h.size())) alloc(h.size());  // a view of the right size is written in place
         if (!h.empty()) SPGX_CUDA(cudaMemcpyAsync(ptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, s));
     }
 };
@@ -199,7 +212,9 @@ struct spgx_group {
     std::vector<StreamState> streams;  // indexed by stream type when non-empty
     spgx::DevBuf<uint32_t> d_sliceDesc, d_nbrIds;
     std::vector<uint32_t> sliceDescHost;  // host copy of d_sliceDesc (spgx_energy_update_record patches stream records in place)
+    int64_t nUniformSlices = 0;  // slices that qualify for the pair path of the streaming kernel
     int maxNbr = 0, nSlices = 0, vbdLookahead = 512, vbdPdl = 1, vbdCarveout = -1;
+    int64_t vbdL2Persist = 0;  // bytes of L2 set aside for the persisting window over the positions (0: off)
     unsigned streamMask = 0;
     double streamBytes = 0;  // bytes of stream + neighbour tables one full sweep reads (reported)
     std::vector<int32_t> sliceBase;     // per colour: index of its first warp-slice (32 / vbdLanes vertices each)
@@ -235,6 +250,9 @@ struct spgx_group {
     spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
     int xpbdFused = 0;  // 0: one launch per pass, 1: cooperative kernel + cooperative-groups sync, 2: + hand-rolled barrier
     spgx::DevBuf<unsigned> d_xpbdBarrier;
+    // positions, inertial positions and masses of a VBD group are views into ONE allocation, so that a single L2
+    // access-policy window covers everything the colour pass reads per vertex besides the incidence streams
+    spgx::DevBuf<double> d_stateArena;
     spgx::DevBuf<double> d_x, d_v, d_xOld, d_xInertial, d_mass, d_invMass, d_stage, d_g;
     spgx::DevBuf<int32_t> d_slot2vert;
     spgx::DevBuf<double> d_eval;

@@ -61,7 +61,8 @@ struct VbdArgs {
     // per warp-slice descriptor, kSliceDescWords uint32 each, nSlices + 1 entries (the last one closes the ranges):
     //   [0] first slot, [1] first row of the unique-neighbour table, [2 + t] first step of stream type t,
     //   [7] bit 0: some vertex of the slice has incidences on the CSR path; bit 1: the slice reads halo slots;
-    //       bits 2..31: number of push entries (VbdHaloDev::push) of all earlier slices
+    //       bit 2: uniform slice (full, every vertex the same number of incidences per stream, a multiple of 2 G);
+    //       bits 3..31: number of push entries (VbdHaloDev::push) of all earlier slices
     const uint32_t *sliceDesc;
     const uint32_t *nbrIds;  // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
     int maxNbr;              // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
@@ -69,6 +70,8 @@ struct VbdArgs {
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
     int pdl;                 // 1: launch colour passes with programmatic stream serialization
     int carveout;            // preferred shared-memory carveout of the streaming kernel in percent (-1: maximum shared)
+    size_t l2PersistBytes;   // > 0: the position array is given a persisting L2 access-policy window of this many bytes
+    float l2HitRatio;        // fraction of the window that may persist (set-aside / window when the array is larger)
     VbdHaloDev halo;
 };
 

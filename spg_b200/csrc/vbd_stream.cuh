@@ -26,6 +26,11 @@ __device__ __forceinline__ void cpAsync8(double *smemDst, const double *gmemSrc)
     const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smemDst));
     asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(s), "l"(gmemSrc));
 }
+__device__ __forceinline__ void cpAsync4(uint32_t *smemDst, const uint32_t *gmemSrc)
+{
+    const unsigned s = static_cast<unsigned>(__cvta_generic_to_shared(smemDst));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(s), "l"(gmemSrc));
+}
 __device__ __forceinline__ void cpAsyncCommit()
 {
     asm volatile("cp.async.commit_group;");
@@ -33,6 +38,11 @@ __device__ __forceinline__ void cpAsyncCommit()
 __device__ __forceinline__ void cpAsyncWaitAll()
 {
     asm volatile("cp.async.wait_all;" ::: "memory");
+}
+// every group but the newest one has landed
+__device__ __forceinline__ void cpAsyncWaitAllButOne()
+{
+    asm volatile("cp.async.wait_group 1;" ::: "memory");
 }
 
 // generic CSR path: lanes of the vertex stride over its (stencil, local) entries of one energy
@@ -348,14 +358,96 @@ __device__ __forceinline__ void prefetchStreamIfPresent(const VbdArgs &a, const 
 
 constexpr int kStreamBlockThreads = 128;
 
+// ---- ring path: the record of the next step staged in shared memory ----
+// One step of the ring: the 32 index words, then NQmax rows of 32 doubles ([field][lane], as in global memory).
+template <unsigned SMASK>
+constexpr int ringStepBytes()
+{
+    return 128 + maxStreamNQ(SMASK) * 256;
+}
+// bytes of shared memory one warp owns: the neighbour tile (maxNbr rows + own position + inertial position + mass row) and,
+// with RING, two ring steps
+template <unsigned SMASK, int G, bool RING>
+__host__ __device__ inline size_t streamWarpSmemBytes(int maxNbr)
+{
+    constexpr int VW = 32 / G;
+    return static_cast<size_t>(maxNbr + 3) * 3 * VW * sizeof(double) + (RING ? 2 * ringStepBytes<SMASK>() : 0);
+}
+
+template <unsigned SMASK, int VW>
+struct RingOps {
+    // lane copies ITS OWN fields of step t of stream ST into ring step `stage`: nothing another lane wrote is ever read, so
+    // cp.async.wait_group alone orders the copies against the reads (no barrier, no __syncwarp); no register is held while
+    // the record is in flight, and none of its fields lives longer than the instruction that consumes it
+    template <int ST>
+    __device__ static __forceinline__ void issueStep(const VbdStreamDev &sd, uint32_t t, char *stage, int lane)
+    {
+        using SK = Stream<ST>;
+        cpAsync4(reinterpret_cast<uint32_t *>(stage) + lane, sd.idx + static_cast<size_t>(t) * 32 + lane);
+        const double *qp = sd.params + static_cast<size_t>(t) * (SK::NQ * 32) + lane;
+        double *dst = reinterpret_cast<double *>(stage + 128) + lane;
+#pragma unroll
+        for (int k = 0; k < SK::NQ; ++k) cpAsync8(dst + k * 32, qp + k * 32);
+    }
+    template <int ST>
+    __device__ static __forceinline__ void issueFrom(const VbdArgs &a, const StreamPipe<SMASK, VW> &pipe, uint32_t s, char *stage, int lane)
+    {
+        if constexpr (ST < kNumStreamTypes) {
+            if constexpr ((SMASK >> ST) & 1u) {
+                if (s < pipe.cum[ST]) {
+                    issueStep<ST>(a.s[ST], pipe.base[ST] + s, stage, lane);
+                    return;
+                }
+            }
+            issueFrom<ST + 1>(a, pipe, s, stage, lane);
+        }
+    }
+    template <int ST>
+    __device__ static __forceinline__ void evalStep(const char *stage, const double *P, const double *Pown, V3d &g, Sym3 &H, int lane)
+    {
+        using SK = Stream<ST>;
+        const uint32_t idx = reinterpret_cast<const uint32_t *>(stage)[lane];
+        if (idx == 0xFFFFFFFFu) return;
+        const double *qs = reinterpret_cast<const double *>(stage + 128) + lane;
+        double q[SK::NQ];
+        V3d xn[SK::NI];
+#pragma unroll
+        for (int k = 0; k < SK::NQ; ++k) q[k] = qs[k * 32];
+#pragma unroll
+        for (int k = 0; k < SK::NI; ++k) {
+            const double *p = P + ((idx >> (8 * k)) & 0xFFu) * (3 * VW);
+            xn[k] = V3d(p[0], p[VW], p[2 * VW]);
+        }
+        const V3d xo(Pown[0], Pown[VW], Pown[2 * VW]);  // re-read per step: six registers fewer across the loop
+        SK::eval(xo, xn, q, g, H);
+    }
+    template <int ST>
+    __device__ static __forceinline__ void evalFrom(const StreamPipe<SMASK, VW> &pipe, uint32_t s, const char *stage, const double *P,
+                                                    const double *Pown, V3d &g, Sym3 &H, int lane)
+    {
+        if constexpr (ST < kNumStreamTypes) {
+            if constexpr ((SMASK >> ST) & 1u) {
+                if (s < pipe.cum[ST]) {
+                    evalStep<ST>(stage, P, Pown, g, H, lane);
+                    return;
+                }
+            }
+            evalFrom<ST + 1>(pipe, s, stage, P, Pown, g, H, lane);
+        }
+    }
+};
+
 // The body of the colour pass; BT = threads per block.  Warps never synchronise with each other (each has its own tile),
 // so the block size only sets the granularity of the occupancy / register trade-off (registers are bounded by OCC resident
 // blocks of BT threads).
-template <unsigned SMASK, unsigned KMASK, int G, int BT>
+// RING: the record of the next step is prefetched into a two-step shared-memory ring with cp.async (no registers held, no
+// scoreboard wait) instead of the two-buffer register pipeline: ~30 registers fewer, which is what a fifth / sixth resident
+// block per SM needs.
+template <unsigned SMASK, unsigned KMASK, int G, int BT, bool RING>
 __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
-    extern __shared__ double tile[];
+    extern __shared__ __align__(128) char smemRaw[];
     const int warpInBlock = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
     const int warp = blockIdx.x * (BT / 32) + warpInBlock;
@@ -363,9 +455,13 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     if (warp >= nSlicesOfColour) return;  // whole warp past the colour
     const int v = lane % VW, sub = lane / VW;
     const int slice = sliceBase + warp;
-    // per warp: maxNbr neighbour rows + one row for the vertices' own positions
-    double *P = tile + static_cast<size_t>(warpInBlock) * ((a.maxNbr + 1) * 3 * VW) + v;
+    // per warp: [ring (RING) | maxNbr neighbour rows | own positions | inertial positions | masses]
+    char *warpSmem = smemRaw + static_cast<size_t>(warpInBlock) * streamWarpSmemBytes<SMASK, G, RING>(a.maxNbr);
+    char *ring = warpSmem;
+    double *P = reinterpret_cast<double *>(warpSmem + (RING ? 2 * ringStepBytes<SMASK>() : 0)) + v;
     double *Pown = P + a.maxNbr * (3 * VW);
+    double *Pin = Pown + 3 * VW;
+    double *Pmass = Pin + 3 * VW;
 
     SliceDesc d, n;
     d.load(a.sliceDesc, slice);
@@ -373,13 +469,25 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     const int slot = static_cast<int>(d.lo.x) + v;
     const bool valid = slot < end;
 
-    // 1. everything that does not depend on the previous colour pass: the first incidence record, the ids of the
-    // unique neighbours, and the streams of the slice `lookahead` slices further on (wrapping into the next colour /
-    // the next sweep) pulled from HBM into L2 with TMA bulk prefetches
+    // 1. everything that does not depend on the previous colour pass: the first incidence record(s), the ids of the
+    // unique neighbours, the vertex's mass and inertial position, and the streams of the slice `lookahead` slices further
+    // on (wrapping into the next colour / the next sweep) pulled from HBM into L2 with TMA bulk prefetches
     const StreamPipe<SMASK, VW> pipe(d, n);
     StreamRec<SMASK> r0, r1;
     r0.idx = r1.idx = 0xFFFFFFFFu;
-    if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
+    if (valid && sub == 0) {
+        const double *src = a.xInertial + 3 * static_cast<size_t>(slot);
+        cpAsync8(Pin, src);
+        cpAsync8(Pin + VW, src + 1);
+        cpAsync8(Pin + 2 * VW, src + 2);
+        cpAsync8(Pmass, a.mass + slot);
+    }
+    if constexpr (RING) {
+        if (pipe.total > 0) RingOps<SMASK, VW>::template issueFrom<0>(a, pipe, 0, ring, lane);
+    } else {
+        if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
+    }
+    cpAsyncCommit();
     constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
     const uint32_t nb = d.lo.y, ne = n.lo.y;
     uint32_t nid[PRE];
@@ -388,20 +496,19 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         const uint32_t k = nb + sub + j * G;
         nid[j] = k < ne ? __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v) : 0u;
     }
-    if (valid) {
-        prefetchLineL2(a.xInertial + 3 * static_cast<size_t>(slot));
-        prefetchLineL2(a.mass + slot);
-    }
-    if (a.lookahead > 0) {
+    if (a.lookahead > 0 && warpInBlock == 0) {
+        // ONE lane per block pulls the ranges of the block's BT / 32 consecutive slices, `lookahead` slices further on
+        // (issued by every warp this cost 171 issue slots per warp-slice, 9 % of the colour pass: ncu source page)
         int la = slice + a.lookahead;
         if (la >= a.nSlices) la -= a.nSlices;
+        const int lb = min(la + BT / 32, a.nSlices);
         if (lane == 0) {
             int la2 = la + a.lookahead;
             if (la2 >= a.nSlices) la2 -= a.nSlices;
             prefetchLineL2(a.sliceDesc + static_cast<size_t>(la2) * kSliceDescWords);
             SliceDesc pd, pn;
             pd.load(a.sliceDesc, la);
-            pn.load(a.sliceDesc, la + 1);
+            pn.load(a.sliceDesc, lb);
             bulkPrefetchL2(a.nbrIds + static_cast<size_t>(pd.lo.y) * VW, (pn.lo.y - pd.lo.y) * (VW * 4u));
             prefetchStreamIfPresent<SMASK, ST_BEND_EDGE>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_BEND_OPP>(a, pd, pn);
@@ -446,7 +553,8 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         cpAsync8(dst + 2 * VW, src + 2);
     }
     // the vertex's own position rides in the same asynchronous batch (a plain load here gets scheduled BEHIND the wait
-    // for the gather and costs a second, fully exposed L2 round trip: profiles/r1f_*)
+    // for the gather and costs a second, fully exposed L2 round trip: profiles/r1f_*); so do its mass and inertial
+    // position (first group above), which the epilogue used to fetch with exposed loads after the incidence loop
     if (valid && sub == 0) {
         const double *src = a.x + 3 * static_cast<size_t>(slot);
         cpAsync8(Pown, src);
@@ -454,56 +562,80 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         cpAsync8(Pown + 2 * VW, src + 2);
     }
     cpAsyncCommit();
-    cpAsyncWaitAll();
-    if constexpr (G > 1) __syncwarp();
-    V3d xo(0.0, 0.0, 0.0);
-    if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
-
-    // 3. incidence streams.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
-    // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
-    // current one has arrived (orderAfter) and right BEFORE it is evaluated, which puts one whole evaluation
-    // between every request and its wait.
     V3d f(0.0, 0.0, 0.0);
     Sym3 H{0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    for (uint32_t s = 0; s < pipe.total; s += 2) {
-        // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
-        int l = orderAfter(lane, r0.idx);
-        if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
-        pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
-        if (s + 1 >= pipe.total) break;
-        l = orderAfter(lane, r1.idx);
-        if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
-        pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
+    V3d xo(0.0, 0.0, 0.0);
+    if constexpr (RING) {
+        // 3a. ring path.  Groups in flight: [own data + step 0] [gather]; every iteration commits exactly one more group
+        // (step s + 1, possibly empty) and waits for all but that one.
+        for (uint32_t s = 0; s < pipe.total; ++s) {
+            char *cur = ring + (s & 1u) * ringStepBytes<SMASK>();
+            char *nxt = ring + ((s + 1u) & 1u) * ringStepBytes<SMASK>();
+            if (s + 1 < pipe.total) RingOps<SMASK, VW>::template issueFrom<0>(a, pipe, s + 1, nxt, lane);
+            cpAsyncCommit();
+            cpAsyncWaitAllButOne();
+            if constexpr (G > 1) {
+                if (s == 0) __syncwarp();  // the tile rows were written by the other lanes of the vertex
+            }
+            RingOps<SMASK, VW>::template evalFrom<0>(pipe, s, cur, P, Pown, f, H, lane);
+        }
+        cpAsyncWaitAll();
+        if constexpr (G > 1) __syncwarp();
+        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
+    } else {
+        cpAsyncWaitAll();
+        if constexpr (G > 1) __syncwarp();
+        if (valid) xo = V3d(Pown[0], Pown[VW], Pown[2 * VW]);
+        // 3b. register pipeline.  All record loads share one scoreboard barrier (ptxas), so a wait for the current record
+        // also waits for whatever record load was issued last: the next record is therefore requested right AFTER the
+        // current one has arrived (orderAfter) and right BEFORE it is evaluated, which puts one whole evaluation
+        // between every request and its wait.
+        for (uint32_t s = 0; s < pipe.total; s += 2) {
+            // (the tile pointer is routed through orderAfter too, so that the wait dominates the evaluation on every path)
+            int l = orderAfter(lane, r0.idx);
+            if (s + 1 < pipe.total) pipe.template loadFrom<0>(a, r1, s + 1, l);
+            pipe.template evalFrom<0>(r0, s, P + (l - lane), xo, f, H);
+            if (s + 1 >= pipe.total) break;
+            l = orderAfter(lane, r1.idx);
+            if (s + 2 < pipe.total) pipe.template loadFrom<0>(a, r0, s + 2, l);
+            pipe.template evalFrom<0>(r1, s + 1, P + (l - lane), xo, f, H);
+        }
     }
     // 4. energies without a stream (rare: the descriptor says whether the slice has any such incidence)
     if ((d.hi.w & 1u) && valid) accumulateCsrEnergies<KMASK>(a, slot, sub, G, f, H);
     // 5. reduce, solve, write
-    const V3d xn = reduceSolveWrite<G>(a, slot, valid, sub, xo, f, H, invdtSquared);
+    double mass = 0.0;
+    V3d xi(0.0, 0.0, 0.0);
+    if (valid && sub == 0) {
+        mass = Pmass[0];
+        xi = V3d(Pin[0], Pin[VW], Pin[2 * VW]);
+    }
+    const V3d xn = reduceSolveWriteWith<G>(a, slot, valid, sub, xo, f, H, invdtSquared, mass, xi);
     // 6. multi-GPU: boundary vertices of the slice go to the neighbours' halo slots over NVLink
     if (a.halo.nPeers) {
-        const uint32_t pb = d.hi.w >> 2, pe = n.hi.w >> 2;
+        const uint32_t pb = d.hi.w >> 3, pe = n.hi.w >> 3;
         if (pe > pb) haloPushSlice(a.halo, d.lo.x, pb, pe, lane, xn);
     }
 }
 
-template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, int BT = kStreamBlockThreads>
 __global__ void __launch_bounds__(BT, OCC)
     vbdStreamKernel(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
-    vbdStreamBody<SMASK, KMASK, G, BT>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
+    vbdStreamBody<SMASK, KMASK, G, BT, RING>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
 }
-template <unsigned SMASK, unsigned KMASK, int G, int OCC, int BT = kStreamBlockThreads>
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, int BT = kStreamBlockThreads>
 void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
 {
     constexpr int VW = 32 / G;
     const int n = end - begin;
     if (n <= 0) return;
     const int warps = (n + VW - 1) / VW;
-    if ((args.maxNbr + 1) * 3 * VW * 8 * (kStreamBlockThreads / 32) > 227 * 1024) return;  // rejected at finalize
     constexpr int warpsPerBlock = BT / 32;
     const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
-    const size_t smem = static_cast<size_t>(warpsPerBlock) * (args.maxNbr + 1) * 3 * VW * sizeof(double);
-    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC, BT>;
+    const size_t smem = static_cast<size_t>(warpsPerBlock) * streamWarpSmemBytes<SMASK, G, RING>(args.maxNbr);
+    if (smem > 227 * 1024) return;  // rejected at finalize (buildStreams)
+    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC, RING, BT>;
     static size_t configured = 0;  // per instantiation
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -520,23 +652,44 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     cfg.blockDim = dim3(BT);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cudaLaunchAttribute attr[2];
+    int na = 0;
+    if (args.pdl) {
+        attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[na].val.programmaticStreamSerializationAllowed = 1;
+        ++na;
+    }
+    if (args.l2PersistBytes) {
+        // the positions every gather reads stay in the L2 set-aside; the incidence streams (read once per sweep, 0.65 GB
+        // against 126 MB of L2) pass through as streaming and stop evicting them
+        attr[na].id = cudaLaunchAttributeAccessPolicyWindow;
+        attr[na].val.accessPolicyWindow.base_ptr = args.x;
+        attr[na].val.accessPolicyWindow.num_bytes = args.l2PersistBytes;
+        attr[na].val.accessPolicyWindow.hitRatio = args.l2HitRatio;
+        attr[na].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        attr[na].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        ++na;
+    }
     cfg.attrs = attr;
-    cfg.numAttrs = args.pdl ? 1 : 0;
+    cfg.numAttrs = na;
     cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
 }
 
+// variant = occ + 10 * ring: resident 128-thread blocks per SM (4: <= 128 registers, 5: <= 102, 6: <= 85) and whether the
+// records go through the shared-memory ring instead of the register pipeline.  Measured and rejected: 3 blocks; register
+// caps on the register pipeline, persistent warps, prefetch.global.L1 (round 1, profiles/r1f_*); two steps evaluated
+// together from a four-step ring on uniform slices (round 2, profiles/r2d_sweep.txt: ptxas keeps the two evaluations
+// sequential, the ring costs L1: 3.35 vs 2.89 ms per frame).
 template <unsigned SMASK, unsigned KMASK, int G>
-void launchStreamG(const VbdArgs &args, int occ, int begin, int end, int sliceBase, double invdtSquared,
+void launchStreamG(const VbdArgs &args, int variant, int begin, int end, int sliceBase, double invdtSquared,
                    cudaStream_t stream)
 {
-    // one occupancy point is compiled: 4 resident blocks of 128 threads (<= 128 registers).  Measured and rejected in
-    // round 1 (profiles/r1f_regcap_sweep_config3.txt, r1f_knob_sweep_config3.txt): 3 / 5 blocks, register caps at
-    // 120 / 112 / 104, persistent warps, prefetch.global.L1 of the record two steps ahead.
-    (void)occ;
-    launchStreamGO<SMASK, KMASK, G, 4>(args, begin, end, sliceBase, invdtSquared, stream);
+    switch (variant) {
+    case 14: launchStreamGO<SMASK, KMASK, G, 4, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    case 15: launchStreamGO<SMASK, KMASK, G, 5, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    case 16: launchStreamGO<SMASK, KMASK, G, 6, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    default: launchStreamGO<SMASK, KMASK, G, 4, false>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    }
 }
 
 template <unsigned SMASK, unsigned KMASK>

@@ -184,15 +184,16 @@ def test_xpbd_lambda_iterations_equal_reference_at_one(ctx):
 def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     """The streaming kernel (owner-centric incidence streams, every lanes-per-vertex variant) against the
     generic CSR kernel and the oracle on the same scene: all within the 1e-9 gate of each other."""
-    sc = {"cloth": lambda: S.cloth(23, 17), "snh": lambda: S.tet_beam(9, 4, 3, S.K_TET_SNH),
+    sc = {"cloth": lambda: S.cloth(14, 260), "snh": lambda: S.tet_beam(9, 4, 3, S.K_TET_SNH),
           "tstvk": lambda: S.tet_beam(7, 3, 4, S.K_TET_STVK)}[scene]()
     og = oracle_api.OracleGroup(oracle, sc)
     osol = oracle_api.OracleSolver(og, 0, 0.01, 2, 6)
     osol.step(1)
     xr, vr = osol.state()
     results = {}
-    for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [(f"g{l}", {"SPGX_VBD_LANES": str(l)}) for l in (1, 2, 4)]:
-        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES"):
+    for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [(f"g{l}v{var}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_VARIANT": str(var)})
+                                                           for l in (1, 2, 4) for var in (4, 14, 15, 16)]:
+        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_VARIANT"):
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -200,10 +201,14 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
         g.finalize(api.SPGX_VBD)
         g.vbd_step(0.01, 2, 6)
         results[name] = g.download()
+        assert g.kernel_info()["variant"] == int(name.split("v")[1]) if name != "csr" else True
         g.close()
     for name, (x, v) in results.items():
         assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8, name
         assert _rel(x, results["csr"][0]) <= 1e-11, name
+    for l in (1, 2, 4):   # the ring path evaluates the same records in the same order; the occupancy point changes nothing
+        for var in (14, 15, 16):
+            assert np.array_equal(results[f"g{l}v{var}"][0], results[f"g{l}v4"][0]), (l, var)
 
 
 def test_static_load_vbd_and_xpbd_refusal(ctx, oracle):

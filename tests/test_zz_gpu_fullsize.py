@@ -23,7 +23,7 @@ from spg_b200 import api, scenes as S  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 N = 1024
-KNOBS = ("SPGX_NO_STREAMS", "SPGX_VBD_LANES")
+KNOBS = ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_VARIANT")
 
 
 @pytest.fixture(scope="module")
