@@ -25,28 +25,6 @@ static void checkKind(int kind)
     if (kind < 0 || kind >= K_COUNT) throw std::runtime_error("unknown energy kind");
 }
 
-// bytes of the element record the gather model charges per incidence (SURVEY.md 8d / DESIGN.md)
-static double modelRecordBytes(int kind)
-{
-    switch (kind) {
-    case K_SPRING:
-    case K_SPRING_CONTINUUM: return 24;
-    case K_DISCRETE_BENDING: return 32;
-    case K_QUADRATIC_BENDING: return 56;
-    case K_MEMBRANE_STVK:
-    case K_MEMBRANE_CHOI:
-    case K_MEMBRANE_BW: return 68;
-    case K_TET_STVK:
-    case K_TET_SNH: return 112;
-    case K_ANCHOR:
-    case K_STATIC_LOAD: return 36;
-    case K_BENDING_BW: return 32;
-    case K_SPRING_SQUARED_CONTINUUM: return 24;
-    case K_TET_SSNH: return 112;
-    default: return 0;
-    }
-}
-
 // Streaming layout of the VBD colour pass (kernels.h, streams.cuh).  For every vertex (in slot order): the list of its
 // unique neighbours over all streamed incidences (first-seen order), and per stream type the canonical incidence
 // records referencing that list by 8-bit index.  Both are packed as sliced ELL over warp-slices of VW = 32 / G
@@ -686,6 +664,97 @@ int spgx_energy_update_record(spgx_group *grp, int energyId, int stencil, int of
     });
 }
 
+}  // extern "C"
+
+namespace
+{
+// Domain-decomposed XPBD (xpbd_partition.h; reference: the single-process pass loop of xpbd.cpp:82-103): global stencil
+// colours (bit-exact), the stencils this rank holds in (colour, id) order, local slots [owned ascending | halo ascending],
+// and per (energy, colour) pass the owned slots to send to / the halo slots to receive from every neighbour.
+void finalizeXpbdPartitioned(spgx_group *grp, const std::vector<FlatStencilsView> &sets, cudaStream_t st)
+{
+    const int V = grp->nVerts;
+    const size_t nE = grp->energies.size();
+    std::vector<const int32_t *> colorPtrs;
+    std::vector<int32_t> nColors;
+    for (size_t ei = 0; ei < nE; ++ei) {
+        auto &e = grp->energies[ei];
+        e.stencilColors = colorStencils(sets[ei]);  // xpbd.cpp:133-160, global: identical on every rank
+        int nc = 0;
+        for (int32_t c : e.stencilColors) nc = std::max(nc, c + 1);
+        colorPtrs.push_back(e.stencilColors.data());
+        nColors.push_back(nc);
+    }
+    const XpbdPlan plan = buildXpbdPlan(V, sets, colorPtrs, nColors, grp->owner.data(), grp->rank, grp->nRanks);
+    if (static_cast<int>(plan.peers.size()) > kMaxPeers) throw std::runtime_error("partitioned XPBD: too many neighbouring ranks");
+    grp->nOwned = plan.nOwned;
+    grp->nLocal = plan.nOwned + static_cast<int>(plan.halo.size());
+    grp->slot2vert.clear();
+    grp->vert2slot.assign(static_cast<size_t>(V), -1);
+    for (int v = 0; v < V; ++v)
+        if (grp->owner[v] == grp->rank) {
+            grp->vert2slot[v] = static_cast<int32_t>(grp->slot2vert.size());
+            grp->slot2vert.push_back(v);
+        }
+    for (int32_t v : plan.halo) {
+        grp->vert2slot[v] = static_cast<int32_t>(grp->slot2vert.size());
+        grp->slot2vert.push_back(v);
+    }
+    grp->peers.assign(plan.peers.begin(), plan.peers.end());
+    grp->vertexColors.clear();
+    grp->colorOffsets.clear();
+    grp->sendOffsets.clear(), grp->recvSlot.clear(), grp->recvCount.clear();
+    auto &xh = grp->xh;
+    xh = spgx_group::XpbdHaloState{};
+    xh.nPasses = plan.nPasses;
+    xh.halo = plan.halo;
+    xh.sendOffsets = plan.sendOffsets;
+    xh.recvOffsets = plan.recvOffsets;
+    xh.sendVerts = plan.sendVerts;
+    for (int32_t v : plan.sendVerts) xh.sendSlots.push_back(grp->vert2slot[v]);
+    for (int32_t v : plan.recvVerts) xh.recvSlots.push_back(grp->vert2slot[v]);
+    grp->p2p.sendSlots = xh.sendSlots;
+    grp->d_sendSlots.upload(xh.sendSlots, st);
+    grp->d_sendBuf.alloc(3 * xh.sendSlots.size());
+    xh.d_recvSlots.upload(xh.recvSlots, st);
+    xh.d_recvBuf.alloc(3 * xh.recvSlots.size());
+    grp->haloBytesPerSweep = static_cast<int64_t>(24 * xh.sendSlots.size());
+    int passBase = 0;
+    for (size_t ei = 0; ei < nE; ++ei) {
+        auto &e = grp->energies[ei];
+        const int nc = nColors[ei];
+        e.colorOffsets.assign(static_cast<size_t>(nc) + 1, 0);
+        e.order.clear();
+        for (int c = 0; c < nc; ++c) {
+            const int64_t a = plan.heldOffsets[passBase + c], b = plan.heldOffsets[passBase + c + 1];
+            e.order.insert(e.order.end(), plan.held.begin() + a, plan.held.begin() + b);
+            e.colorOffsets[c + 1] = static_cast<int64_t>(e.order.size());
+        }
+        passBase += nc;
+        const size_t nHeld = e.order.size();
+        e.positionOf.assign(static_cast<size_t>(e.n), -1);
+        std::vector<int32_t> st2(nHeld * e.S);
+        std::vector<double> rec2(nHeld * e.NP);
+        for (size_t pos = 0; pos < nHeld; ++pos) {
+            const int i = e.order[pos];
+            e.positionOf[i] = static_cast<int32_t>(pos);
+            for (int l = 0; l < e.S; ++l) st2[pos * e.S + l] = grp->vert2slot[e.stencils[static_cast<size_t>(i) * e.S + l]];
+            std::copy(e.records.begin() + static_cast<size_t>(i) * e.NP, e.records.begin() + static_cast<size_t>(i + 1) * e.NP,
+                      rec2.begin() + pos * e.NP);
+        }
+        e.d_stencils.upload(st2, st);
+        e.d_records.upload(rec2, st);
+        e.d_lambda.alloc(nHeld * e.NC);
+        e.d_rowptr.release();
+        e.d_entries.release();
+        e.streamed = false;
+        SPGX_CUDA(cudaStreamSynchronize(st));
+    }
+}
+}  // namespace
+
+extern "C" {
+
 int spgx_group_finalize(spgx_group *grp, int solverKind)
 {
     return guarded([&] {
@@ -715,6 +784,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             vh = grp->vPending;
         }
         grp->solverKind = solverKind;
+        grp->identityOrder = false;
         if (grp->graphExec) {
             cudaGraphExecDestroy(grp->graphExec);
             grp->graphExec = nullptr;
@@ -867,8 +937,13 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 std::sort(nbr.begin(), nbr.end());
                 grp->uniqueNeighbourSum += static_cast<double>(std::unique(nbr.begin(), nbr.end()) - nbr.begin());
             }
+        } else if (grp->partitioned && solverKind == SPGX_XPBD) {
+            finalizeXpbdPartitioned(grp, sets, st);
         } else {
-            if (grp->partitioned) throw std::runtime_error("domain decomposition is implemented for the VBD solver only");
+            if (grp->partitioned)
+                throw std::runtime_error("domain decomposition is implemented for the VBD and the (parallel Gauss-Seidel) XPBD solver only");
+            grp->identityOrder = true;
+            grp->xh = spgx_group::XpbdHaloState{};
             {
                 CgState *pinned = grp->newton.hostState;
                 double *pinnedScalar = grp->newton.hostScalar;
@@ -1050,7 +1125,8 @@ int spgx_model_bytes(spgx_group *grp, double *bytesPerIteration, double *bytesLo
             }
         } else {
             gather = 6.0 * 24.0 * V;
-            for (const auto &e : grp->energies) gather += static_cast<double>(e.n) * (modelRecordBytes(e.kind) + e.S * 56.0);
+            for (const auto &e : grp->energies)  // a partitioned rank projects the stencils it holds
+                gather += static_cast<double>(grp->partitioned ? static_cast<int64_t>(e.order.size()) : e.n) * (modelRecordBytes(e.kind) + e.S * 56.0);
             lower = gather;
         }
         if (bytesPerIteration) *bytesPerIteration = gather;

@@ -128,7 +128,14 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const bool useLambda = iters > 1;
     // graph mode: the whole frame is one cooperative launch with grid barriers between the passes; plain-launch mode
     // keeps one kernel per pass (and the per-phase events)
-    if (!serial && !timePhases && grp->graphMode && grp->xpbdFused && grp->d_xpbdPasses.count > 0) {
+    // domain-decomposed group (xpbd_partition.h): one one-way exchange per (energy, colour) pass -- peer-memory stores +
+    // event counters (the pass kernel waits for the neighbours' previous event, a push kernel stores what the pass moved and
+    // raises this one), or pack + ncclSend / ncclRecv + unpack
+    const bool p2p = grp->partitioned && grp->p2p.mode == SPGX_HALO_P2P && grp->p2p.connected;
+    const bool viaNccl = grp->partitioned && !p2p && !grp->peers.empty();
+    VbdHaloDev halo = p2p ? grp->p2p.dev : VbdHaloDev{};
+    const bool signalling = p2p && halo.nPeers > 0;
+    if (!serial && !timePhases && grp->graphMode && grp->xpbdFused && grp->d_xpbdPasses.count > 0 && !grp->partitioned) {
         XpbdFusedArgs fa{};
         fa.x = grp->d_x.ptr, fa.v = grp->d_v.ptr, fa.xOld = grp->d_xOld.ptr, fa.invMass = grp->d_invMass.ptr;
         fa.n3 = 3LL * grp->nLocal;
@@ -147,21 +154,45 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
         launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nLocal, dt, grp->graphKey.g, st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
+        if (signalling) {
+            // event 0: this rank's halo copies have been predicted; neighbours may store into them from now on
+            launchHaloSignal(halo, 0, st);
+            grp->launchCounter++;
+        }
         if (useLambda)
             for (auto &en : grp->energies)
                 if (en.d_lambda.ptr) SPGX_CUDA(cudaMemsetAsync(en.d_lambda.ptr, 0, en.d_lambda.count * sizeof(double), st));
-        for (int it = 0; it < iters; ++it)
+        int event = 0;
+        for (int it = 0; it < iters; ++it) {
+            int pass = 0;  // energy-major, colour-minor over the GLOBAL colours (xpbd_partition.h)
             for (auto &en : grp->energies) {
                 const int nColors = static_cast<int>(en.colorOffsets.size()) - 1;
-                for (int c = 0; c < nColors; ++c) {
+                for (int c = 0; c < nColors; ++c, ++pass) {
                     const int b = static_cast<int>(en.colorOffsets[c]), e = static_cast<int>(en.colorOffsets[c + 1]);
+                    ++event;
+                    halo.event = event;
                     if (e > b) {
                         launchXpbdPass(en.kind, grp->d_x.ptr, grp->d_invMass.ptr, en.d_stencils.ptr, en.d_records.ptr,
-                                       useLambda ? en.d_lambda.ptr : nullptr, b, e, dt, serial, st);
+                                       useLambda ? en.d_lambda.ptr : nullptr, b, e, dt, serial, st, signalling ? &halo : nullptr);
                         grp->launchCounter++;
+                    }
+                    if (signalling) {
+                        // what the pass moved goes to the neighbours that cannot compute it; the event is owed even when
+                        // this rank held no stencil of the pass
+                        launchXpbdHaloPush(halo, grp->d_x.ptr, static_cast<int>(grp->xh.pushOffsets[pass]),
+                                           static_cast<int>(grp->xh.pushOffsets[pass + 1]), event, st);
+                        grp->launchCounter++;
+                    } else if (viaNccl) {
+                        grp->launchCounter += enqueueXpbdHaloExchange(grp, pass, st);
                     }
                 }
             }
+        }
+        if (signalling) {
+            // the neighbours' stores of the last pass must have landed before the halo copies are finalized
+            launchHaloWaitAdvance(halo, event, grp->p2p.d_sync.ptr + kMaxPeers, st);
+            grp->launchCounter++;
+        }
         if (timePhases) grp->markPhase(st);
         launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
         grp->launchCounter++;
@@ -200,8 +231,12 @@ void runStep(spgx_group *grp, int solver, double dt, int nsub, int iters, const 
     if (grp->partitioned && !grp->commWarm && !(grp->p2p.mode == SPGX_HALO_P2P && grp->p2p.connected)) {
         // NCCL sets up its peer connections on first use (allocations, not capturable): exchange every colour once,
         // eagerly.  Halo copies already equal their owners' values, so this changes nothing.
-        const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
-        for (int c = 0; c < nColors; ++c) enqueueHaloExchange(grp, c, st);
+        if (solver == SPGX_VBD) {
+            const int nColors = static_cast<int>(grp->colorOffsets.size()) - 1;
+            for (int c = 0; c < nColors; ++c) enqueueHaloExchange(grp, c, st);
+        } else {
+            for (int pass = 0; pass < grp->xh.nPasses; ++pass) enqueueXpbdHaloExchange(grp, pass, st);
+        }
         SPGX_CUDA(cudaStreamSynchronize(st));
         grp->commWarm = true;
     }
@@ -276,7 +311,7 @@ int spgx_download(spgx_group *grp, double *x, double *v)
         }
         SPGX_CUDA(cudaSetDevice(grp->ctx->device));
         cudaStream_t st = grp->ctx->stream;
-        const bool identity = grp->solverKind != SPGX_VBD;
+        const bool identity = grp->identityOrder;
         for (int k = 0; k < 2; ++k) {
             double *dst = k == 0 ? x : v;
             const double *src = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
@@ -318,7 +353,7 @@ int spgx_upload(spgx_group *grp, const double *x, const double *v)
         }
         SPGX_CUDA(cudaSetDevice(grp->ctx->device));
         cudaStream_t st = grp->ctx->stream;
-        const bool identity = grp->solverKind != SPGX_VBD;
+        const bool identity = grp->identityOrder;
         for (int k = 0; k < 2; ++k) {
             const double *src = k == 0 ? x : v;
             double *dst = k == 0 ? grp->d_x.ptr : grp->d_v.ptr;
@@ -488,7 +523,7 @@ int spgx_upload_async(spgx_group *grp, const double *x, const double *v)
         ensureXfer(grp);
         auto &xf = grp->xfer;
         cudaStream_t st = grp->ctx->stream, cs = grp->ctx->h2dStream;
-        const bool identity = grp->solverKind != SPGX_VBD;
+        const bool identity = grp->identityOrder;
         const size_t lo = identity ? 0 : 3 * static_cast<size_t>(grp->localLo);
         const size_t cnt = identity ? 3 * static_cast<size_t>(grp->nVerts) : 3 * static_cast<size_t>(grp->localHi - grp->localLo);
         if (xf.inUsed) SPGX_CUDA(cudaStreamWaitEvent(cs, xf.inFree, 0));  // the previous scatter has read the staging pair
@@ -519,7 +554,7 @@ int spgx_download_async(spgx_group *grp, double *x, double *v)
         ensureXfer(grp);
         auto &xf = grp->xfer;
         cudaStream_t st = grp->ctx->stream, cs = grp->ctx->d2hStream;
-        const bool identity = grp->solverKind != SPGX_VBD;
+        const bool identity = grp->identityOrder;
         const size_t lo = identity ? 0 : 3 * static_cast<size_t>(grp->ownedLo);
         const size_t cnt = identity ? 3 * static_cast<size_t>(grp->nVerts) : 3 * static_cast<size_t>(grp->ownedHi - grp->ownedLo);
         if (xf.outUsed) SPGX_CUDA(cudaStreamWaitEvent(st, xf.downloaded, 0));  // the previous copy-out has left the staging pair

@@ -14,24 +14,17 @@
 
 namespace spgx
 {
+// generated from the registry (kinds.def): one enumerator per line of it, K_COUNT = the number of lines
 enum Kind : int {
-    K_SPRING = 0,
-    K_SPRING_CONTINUUM = 1,
-    K_DISCRETE_BENDING = 2,
-    K_QUADRATIC_BENDING = 3,
-    K_MEMBRANE_STVK = 4,
-    K_MEMBRANE_CHOI = 5,
-    K_MEMBRANE_BW = 6,
-    K_TET_STVK = 7,
-    K_TET_SNH = 8,
-    K_ANCHOR = 9,
-    // the remaining particle energies (generic dual-number path in both solvers)
-    K_BENDING_BW = 10,
-    K_SPRING_SQUARED_CONTINUUM = 11,
-    K_TET_SSNH = 12,
-    K_STATIC_LOAD = 13,
-    K_COUNT = 14
+#define SPGX_KIND(NAME, ID, BYTES) NAME = ID,
+#include "kinds.def"
+#undef SPGX_KIND
+    K_COUNT = 0
+#define SPGX_KIND(NAME, ID, BYTES) +1
+#include "kinds.def"
+#undef SPGX_KIND
 };
+static_assert(K_COUNT <= 32, "kind masks are 32-bit");
 
 template <int KIND>
 struct EnergyKind;
@@ -521,18 +514,58 @@ struct HasHandDerived<EK, decltype(void(EK::kHandDerived))> {
     static constexpr bool value = EK::kHandDerived;
 };
 
+}  // namespace spgx
+// kinds defined outside the library sources (tests/native/extra_kind.cuh shows the recipe; INTEGRATION.md "Adding an energy kind")
+#ifdef SPGX_EXTRA_KINDS_IMPL
+#include SPGX_EXTRA_KINDS_IMPL
+#endif
+namespace spgx
+{
+// per-kind sizes, generated from the registry and the EnergyKind<> traits (-1: unknown kind)
 SPGX_HD int kindStencilSize(int kind)
 {
     switch (kind) {
-    case K_SPRING:
-    case K_SPRING_CONTINUUM:
-    case K_SPRING_SQUARED_CONTINUUM: return 2;
-    case K_MEMBRANE_STVK:
-    case K_MEMBRANE_CHOI:
-    case K_MEMBRANE_BW: return 3;
-    case K_ANCHOR:
-    case K_STATIC_LOAD: return 1;
-    default: return 4;
+#define SPGX_KIND(NAME, ID, BYTES) case NAME: return EnergyKind<NAME>::S;
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return -1;
+    }
+}
+SPGX_HD int kindNumParams(int kind)
+{
+    switch (kind) {
+#define SPGX_KIND(NAME, ID, BYTES) case NAME: return EnergyKind<NAME>::NP;
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return -1;
+    }
+}
+SPGX_HD int kindNumModelParams(int kind)
+{
+    switch (kind) {
+#define SPGX_KIND(NAME, ID, BYTES) case NAME: return EnergyKind<NAME>::NMODEL;
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return -1;
+    }
+}
+SPGX_HD int kindNumConstraints(int kind)
+{
+    switch (kind) {
+#define SPGX_KIND(NAME, ID, BYTES) case NAME: return EnergyKind<NAME>::NC;
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return -1;
+    }
+}
+// bytes of the element record the gather model charges per incidence (SURVEY.md 8d / DESIGN.md)
+inline double modelRecordBytes(int kind)
+{
+    switch (kind) {
+#define SPGX_KIND(NAME, ID, BYTES) case NAME: return BYTES;
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return 0;
     }
 }
 }  // namespace spgx

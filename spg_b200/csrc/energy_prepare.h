@@ -105,6 +105,36 @@ inline double cotTheta(const H3 &a, const H3 &b)
 }
 }  // namespace prep
 
+// EnergyKind<K>::prepare(st, model, x0, p), when the specialisation has one
+template <class EK, class = void>
+struct HasPrepare {
+    static constexpr bool value = false;
+};
+template <class EK>
+struct HasPrepare<EK, decltype(void(&EK::prepare))> {
+    static constexpr bool value = true;
+};
+template <int KIND>
+inline bool prepareKindByTrait(const int *st, const double *model, const double *x0, double *p)
+{
+    if constexpr (HasPrepare<EnergyKind<KIND>>::value) {
+        EnergyKind<KIND>::prepare(st, model, x0, p);
+        return true;
+    } else {
+        return false;
+    }
+}
+inline bool prepareByTrait(int kind, const int *st, const double *model, const double *x0, double *p)
+{
+    switch (kind) {
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME: return prepareKindByTrait<NAME>(st, model, x0, p);
+#include "kinds.def"
+#undef SPGX_KIND
+    default: return false;
+    }
+}
+
 // model -> record for stencil `st` (vertex ids) with rest positions x0 (3 doubles per vertex)
 inline void prepareStencil(int kind, const int *st, const double *model, const double *x0, double *p)
 {
@@ -265,23 +295,10 @@ inline void prepareStencil(int kind, const int *st, const double *model, const d
         p[4] = 1.0 / model[3];
         break;
     }
-    default: throw std::runtime_error("unknown energy kind");
+    default:
+        // a kind that brings its own prepare() (registered through SPGX_EXTRA_KINDS_DEF / _IMPL)
+        if (!prepareByTrait(kind, st, model, x0, p)) throw std::runtime_error("unknown energy kind");
     }
 }
 
-inline int kindNumParams(int kind)
-{
-    static const int np[K_COUNT] = {3, 3, 3, 6, 10, 12, 10, 13, 14, 5, 3, 3, 13, 5};
-    return (kind >= 0 && kind < K_COUNT) ? np[kind] : -1;
-}
-inline int kindNumModelParams(int kind)
-{
-    static const int nm[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4};
-    return (kind >= 0 && kind < K_COUNT) ? nm[kind] : -1;
-}
-inline int kindNumConstraints(int kind)
-{
-    static const int nc[K_COUNT] = {1, 1, 1, 3, 3, 4, 3, 2, 2, 1, 1, 1, 2, 1};
-    return (kind >= 0 && kind < K_COUNT) ? nc[kind] : -1;
-}
 }  // namespace spgx

@@ -197,6 +197,21 @@ struct spgx_group {
         std::vector<void *> mapped;         // cudaIpcOpenMemHandle results to close
         spgx::VbdHaloDev dev{};
     } p2p;
+    // domain-decomposed XPBD (xpbd_partition.h): one exchange per (energy, colour) pass.  Pass ids are energy-major,
+    // colour-minor over ALL global colours of every energy (a pass this rank holds no stencil of still owes its event).
+    struct XpbdHaloState {
+        int nPasses = 0;
+        std::vector<int32_t> halo;          // global ids of the halo vertices, ascending (slot nOwned + i)
+        std::vector<int64_t> sendOffsets;   // nPasses * nPeers + 1, (pass, peer)-major, into sendSlots
+        std::vector<int32_t> sendSlots;     // owned local slots
+        std::vector<int32_t> sendVerts;     // the same entries as global vertex ids (resolved against the peers' halo lists)
+        std::vector<int64_t> recvOffsets;   // same shape, into recvSlots
+        std::vector<int32_t> recvSlots;     // halo local slots, in the sender's order
+        std::vector<int64_t> pushOffsets;   // nPasses + 1 into d_push (peer-memory exchange)
+        spgx::DevBuf<int32_t> d_recvSlots;
+        spgx::DevBuf<double> d_recvBuf;
+    } xh;
+    bool identityOrder = true;  // device slot == vertex id (every solver but VBD and partitioned XPBD)
     // vertex colouring / ordering (VBD); identity ordering for XPBD
     std::vector<int32_t> vertexColors;
     std::vector<int32_t> slot2vert, vert2slot;
@@ -322,6 +337,7 @@ inline void throwIfHaloTimedOut(spgx_group *grp)
     }
 }
 int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
+int enqueueXpbdHaloExchange(spgx_group *grp, int pass, cudaStream_t st);  // comm.cu
 // api_newton.cu: incidence tables, sparse pattern and work buffers of a group finalized with SPGX_NEWTON
 void newtonBuild(spgx_group *grp, cudaStream_t st);
 // peer-memory exchange (comm.cu)

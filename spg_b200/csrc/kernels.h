@@ -92,13 +92,18 @@ void launchFinalize(const double *x, const double *xOld, double *v, int nVerts, 
 // peer-memory halo exchange outside the colour passes (comm.cu): raise event `event` / wait for it and advance the epoch
 void launchHaloSignal(const VbdHaloDev &h, int event, cudaStream_t stream);
 void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, cudaStream_t stream);
+// XPBD: store entries [begin, end) of h.push into the neighbours' halo slots, then raise event `event` (one block that only
+// raises it when the range is empty)
+void launchXpbdHaloPush(const VbdHaloDev &h, const double *x, int begin, int end, int event, cudaStream_t stream);
 // dst[perm[i]] = src[i] (scatter) or dst[i] = src[perm[i]] (gather) over 3-vectors
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream);
 
 // energy.h:117-153 (springEnergy.cpp:48-68 for K_SPRING) for stencils [begin, end) of one colour.
 // lambda == nullptr: reference small-steps form; otherwise NC doubles per stencil are accumulated.
+// halo (may be null): a partitioned group under the peer-memory exchange; every block waits for the neighbours' event
+// halo->event - 1 before it reads positions.
 void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *stencils, const double *records,
-                    double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream);
+                    double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo = nullptr);
 
 // One (energy, colour) projection pass of a substep, as the fused XPBD kernel walks them (xpbd.cu)
 struct XpbdPassDev {

@@ -62,21 +62,6 @@ __device__ __forceinline__ void forceKind(const NewtonEnergyDev &en, const doubl
     }
 }
 
-#define SPGX_FOR_EACH_KIND(X)                                                                                          \
-    X(K_SPRING)                                                                                                        \
-    X(K_SPRING_CONTINUUM)                                                                                              \
-    X(K_DISCRETE_BENDING)                                                                                              \
-    X(K_QUADRATIC_BENDING)                                                                                             \
-    X(K_MEMBRANE_STVK)                                                                                                 \
-    X(K_MEMBRANE_CHOI)                                                                                                 \
-    X(K_MEMBRANE_BW)                                                                                                   \
-    X(K_TET_STVK)                                                                                                      \
-    X(K_TET_SNH)                                                                                                       \
-    X(K_ANCHOR)                                                                                                        \
-    X(K_BENDING_BW)                                                                                                    \
-    X(K_SPRING_SQUARED_CONTINUUM)                                                                                      \
-    X(K_TET_SSNH)                                                                                                      \
-    X(K_STATIC_LOAD)
 
 constexpr int kForceLanes = 4;  // lanes per vertex
 
@@ -95,10 +80,10 @@ __global__ void __launch_bounds__(128) systemForceKernel(const NewtonArgs a, dou
         for (int e = 0; e < a.nEnergies; ++e) {
             const NewtonEnergyDev &en = a.e[e];
             switch (en.kind) {
-#define X(KIND)                                                                                                        \
-    case KIND: forceKind<KIND>(en, a.x, v, sub, G, g); break;
-                SPGX_FOR_EACH_KIND(X)
-#undef X
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME: forceKind<NAME>(en, a.x, v, sub, G, g); break;
+#include "kinds.def"
+#undef SPGX_KIND
             default: break;
             }
         }
@@ -799,10 +784,10 @@ void launchElementHessians(const NewtonArgs &a, cudaStream_t stream)
 {
     for (int e = 0; e < a.nEnergies; ++e) {
         switch (a.e[e].kind) {
-#define X(KIND)                                                                                                        \
-    case KIND: launchElementHessianKind<KIND>(a.e[e], a.x, stream); break;
-            SPGX_FOR_EACH_KIND(X)
-#undef X
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME: launchElementHessianKind<NAME>(a.e[e], a.x, stream); break;
+#include "kinds.def"
+#undef SPGX_KIND
         default: break;
         }
     }

@@ -151,20 +151,10 @@ __global__ void evalVertexKernel(int kind, const double *x, const int32_t *ids, 
                                  double *out12, int fast)
 {
     switch (kind) {
-    case K_SPRING: evalOne<K_SPRING>(x, ids, rec, local, out12, fast); break;
-    case K_SPRING_CONTINUUM: evalOne<K_SPRING_CONTINUUM>(x, ids, rec, local, out12, fast); break;
-    case K_DISCRETE_BENDING: evalOne<K_DISCRETE_BENDING>(x, ids, rec, local, out12, fast); break;
-    case K_QUADRATIC_BENDING: evalOne<K_QUADRATIC_BENDING>(x, ids, rec, local, out12, fast); break;
-    case K_MEMBRANE_STVK: evalOne<K_MEMBRANE_STVK>(x, ids, rec, local, out12, fast); break;
-    case K_MEMBRANE_CHOI: evalOne<K_MEMBRANE_CHOI>(x, ids, rec, local, out12, fast); break;
-    case K_MEMBRANE_BW: evalOne<K_MEMBRANE_BW>(x, ids, rec, local, out12, fast); break;
-    case K_TET_STVK: evalOne<K_TET_STVK>(x, ids, rec, local, out12, fast); break;
-    case K_TET_SNH: evalOne<K_TET_SNH>(x, ids, rec, local, out12, fast); break;
-    case K_ANCHOR: evalOne<K_ANCHOR>(x, ids, rec, local, out12, fast); break;
-    case K_BENDING_BW: evalOne<K_BENDING_BW>(x, ids, rec, local, out12, fast); break;
-    case K_SPRING_SQUARED_CONTINUUM: evalOne<K_SPRING_SQUARED_CONTINUUM>(x, ids, rec, local, out12, fast); break;
-    case K_TET_SSNH: evalOne<K_TET_SSNH>(x, ids, rec, local, out12, fast); break;
-    case K_STATIC_LOAD: evalOne<K_STATIC_LOAD>(x, ids, rec, local, out12, fast); break;
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME: evalOne<NAME>(x, ids, rec, local, out12, fast); break;
+#include "kinds.def"
+#undef SPGX_KIND
     default: break;
     }
 }

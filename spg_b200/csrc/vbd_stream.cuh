@@ -104,20 +104,9 @@ __device__ __forceinline__ void accumulateCsrEnergies(const VbdArgs &a, int slot
     for (int e = 0; e < a.nEnergies; ++e) {
         const VbdEnergyDev &en = a.e[e];
         if (en.streamed) continue;
-        accumulateKindIfPresent<KMASK, K_SPRING>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_SPRING_CONTINUUM>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_DISCRETE_BENDING>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_QUADRATIC_BENDING>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_MEMBRANE_STVK>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_MEMBRANE_CHOI>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_MEMBRANE_BW>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_TET_STVK>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_TET_SNH>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_ANCHOR>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_BENDING_BW>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_SPRING_SQUARED_CONTINUUM>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_TET_SSNH>(en, a.x, slot, sub, G, g, H);
-        accumulateKindIfPresent<KMASK, K_STATIC_LOAD>(en, a.x, slot, sub, G, g, H);
+#define SPGX_KIND(NAME, ID, BYTES) accumulateKindIfPresent<KMASK, NAME>(en, a.x, slot, sub, G, g, H);
+#include "kinds.def"
+#undef SPGX_KIND
     }
 }
 

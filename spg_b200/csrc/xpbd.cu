@@ -13,6 +13,7 @@
 #include <cstdlib>
 
 #include "energies.cuh"
+#include "halo.cuh"
 #include "kernels.h"
 
 namespace spgx
@@ -125,11 +126,19 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
     }
 }
 
+// h.nPeers > 0: a rank of a partitioned group under the peer-memory exchange (halo.cuh, xpbd_partition.h): the neighbours'
+// pushes of the previous pass must have landed before any position is read.  One thread per block waits on the local flag
+// array (acquire), the block barrier orders the other threads' loads behind it.  (One kernel for both cases, so that a
+// partitioned run executes the very same instruction stream per stencil as a single-domain one.)
 template <int KIND>
 __global__ void __launch_bounds__(128) xpbdPassKernel(double *x, const double *invMass, const int32_t *stencils,
                                                       const double *records, double *lambda, int begin, int end,
-                                                      double dt)
+                                                      double dt, const VbdHaloDev h)
 {
+    if (h.nPeers > 0) {
+        if (threadIdx.x == 0) haloWaitAll(h, haloEpochBase(h) + static_cast<uint32_t>(h.event));
+        __syncthreads();
+    }
     const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (i < end) projectStencil<KIND>(x, invMass, stencils, records, lambda, i, dt);
 }
@@ -222,19 +231,12 @@ __global__ void __launch_bounds__(kFusedThreads) xpbdFusedKernel(const XpbdFused
             for (int q = 0; q < a.nPasses; ++q) {
                 const XpbdPassDev p = a.passes[q];
                 switch (p.kind) {
-                case K_SPRING: fusedPass<K_SPRING>(a, p, tid, nthreads); break;
-                case K_SPRING_CONTINUUM: fusedPass<K_SPRING_CONTINUUM>(a, p, tid, nthreads); break;
-                case K_DISCRETE_BENDING: fusedPass<K_DISCRETE_BENDING>(a, p, tid, nthreads); break;
-                case K_QUADRATIC_BENDING: fusedPass<K_QUADRATIC_BENDING>(a, p, tid, nthreads); break;
-                case K_MEMBRANE_STVK: fusedPass<K_MEMBRANE_STVK>(a, p, tid, nthreads); break;
-                case K_MEMBRANE_CHOI: fusedPass<K_MEMBRANE_CHOI>(a, p, tid, nthreads); break;
-                case K_MEMBRANE_BW: fusedPass<K_MEMBRANE_BW>(a, p, tid, nthreads); break;
-                case K_TET_STVK: fusedPass<K_TET_STVK>(a, p, tid, nthreads); break;
-                case K_TET_SNH: fusedPass<K_TET_SNH>(a, p, tid, nthreads); break;
-                case K_ANCHOR: fusedPass<K_ANCHOR>(a, p, tid, nthreads); break;
-                case K_BENDING_BW: fusedPass<K_BENDING_BW>(a, p, tid, nthreads); break;
-                case K_SPRING_SQUARED_CONTINUUM: fusedPass<K_SPRING_SQUARED_CONTINUUM>(a, p, tid, nthreads); break;
-                case K_TET_SSNH: fusedPass<K_TET_SSNH>(a, p, tid, nthreads); break;
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME:                                                                                                         \
+        fusedPass<NAME>(a, p, tid, nthreads);                                     \
+        break;
+#include "kinds.def"
+#undef SPGX_KIND
                 default: break;
                 }
                 grid.sync();  // stencils of the next colour / energy read what this one wrote
@@ -247,17 +249,18 @@ __global__ void __launch_bounds__(kFusedThreads) xpbdFusedKernel(const XpbdFused
 
 template <int KIND>
 void launchKind(double *x, const double *invMass, const int32_t *stencils, const double *records, double *lambda,
-                int begin, int end, double dt, bool serial, cudaStream_t stream)
+                int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo)
 {
     const int n = end - begin;
     if (n <= 0) return;
+    const VbdHaloDev h = (halo && halo->nPeers > 0) ? *halo : VbdHaloDev{};
     if (serial) {
         xpbdSerialKernel<KIND><<<1, 1, 0, stream>>>(x, invMass, stencils, records, lambda, begin, end, dt);
     } else {
         const int threads = 128;
         // opt-in: in a replayed CUDA graph the kernel boundary is already ~1 us; measured 1.82 vs 1.76 ms per frame at config 2
         static const bool pdl = getenv("SPGX_XPBD_PDL") && atoi(getenv("SPGX_XPBD_PDL")) != 0;
-        if (pdl) {
+        if (pdl && h.nPeers == 0) {
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3((n + threads - 1) / threads);
             cfg.blockDim = dim3(threads);
@@ -270,7 +273,7 @@ void launchKind(double *x, const double *invMass, const int32_t *stencils, const
             cudaLaunchKernelEx(&cfg, xpbdPassKernelPdl<KIND>, x, invMass, stencils, records, lambda, begin, end, dt);
         } else {
             xpbdPassKernel<KIND><<<(n + threads - 1) / threads, threads, 0, stream>>>(x, invMass, stencils, records, lambda,
-                                                                                     begin, end, dt);
+                                                                                     begin, end, dt, h);
         }
     }
 }
@@ -298,55 +301,28 @@ __global__ void evalConstraintsKernel(int kind, const double *x, const int32_t *
                                       double *outGrad)
 {
     switch (kind) {
-    case K_SPRING: evalConstraintsOne<K_SPRING>(x, ids, rec, outC, outGrad); break;
-    case K_SPRING_CONTINUUM: evalConstraintsOne<K_SPRING_CONTINUUM>(x, ids, rec, outC, outGrad); break;
-    case K_DISCRETE_BENDING: evalConstraintsOne<K_DISCRETE_BENDING>(x, ids, rec, outC, outGrad); break;
-    case K_QUADRATIC_BENDING: evalConstraintsOne<K_QUADRATIC_BENDING>(x, ids, rec, outC, outGrad); break;
-    case K_MEMBRANE_STVK: evalConstraintsOne<K_MEMBRANE_STVK>(x, ids, rec, outC, outGrad); break;
-    case K_MEMBRANE_CHOI: evalConstraintsOne<K_MEMBRANE_CHOI>(x, ids, rec, outC, outGrad); break;
-    case K_MEMBRANE_BW: evalConstraintsOne<K_MEMBRANE_BW>(x, ids, rec, outC, outGrad); break;
-    case K_TET_STVK: evalConstraintsOne<K_TET_STVK>(x, ids, rec, outC, outGrad); break;
-    case K_TET_SNH: evalConstraintsOne<K_TET_SNH>(x, ids, rec, outC, outGrad); break;
-    case K_ANCHOR: evalConstraintsOne<K_ANCHOR>(x, ids, rec, outC, outGrad); break;
-    case K_BENDING_BW: evalConstraintsOne<K_BENDING_BW>(x, ids, rec, outC, outGrad); break;
-    case K_SPRING_SQUARED_CONTINUUM: evalConstraintsOne<K_SPRING_SQUARED_CONTINUUM>(x, ids, rec, outC, outGrad); break;
-    case K_TET_SSNH: evalConstraintsOne<K_TET_SSNH>(x, ids, rec, outC, outGrad); break;
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME:                                                                                                         \
+        evalConstraintsOne<NAME>(x, ids, rec, outC, outGrad);                     \
+        break;
+#include "kinds.def"
+#undef SPGX_KIND
     default: break;
     }
 }
 }  // namespace
 
 void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *stencils, const double *records,
-                    double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream)
+                    double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo)
 {
     switch (kind) {
-    case K_SPRING: launchKind<K_SPRING>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
-    case K_SPRING_CONTINUUM:
-        launchKind<K_SPRING_CONTINUUM>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
+        // (a static load has no constraint form: its body is a stub and spgx_xpbd_step refuses it, staticLoadEnergy.cpp:8-13)
+#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
+    case NAME:                                                                                                         \
+        launchKind<NAME>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream, halo); \
         break;
-    case K_DISCRETE_BENDING:
-        launchKind<K_DISCRETE_BENDING>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_QUADRATIC_BENDING:
-        launchKind<K_QUADRATIC_BENDING>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_MEMBRANE_STVK:
-        launchKind<K_MEMBRANE_STVK>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_MEMBRANE_CHOI:
-        launchKind<K_MEMBRANE_CHOI>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_MEMBRANE_BW:
-        launchKind<K_MEMBRANE_BW>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_TET_STVK: launchKind<K_TET_STVK>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
-    case K_TET_SNH: launchKind<K_TET_SNH>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
-    case K_ANCHOR: launchKind<K_ANCHOR>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
-    case K_BENDING_BW: launchKind<K_BENDING_BW>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
-    case K_SPRING_SQUARED_CONTINUUM:
-        launchKind<K_SPRING_SQUARED_CONTINUUM>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream);
-        break;
-    case K_TET_SSNH: launchKind<K_TET_SSNH>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream); break;
+#include "kinds.def"
+#undef SPGX_KIND
     default: break;
     }
 }

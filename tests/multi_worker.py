@@ -19,12 +19,22 @@ def main():
     torch.cuda.set_device(lr)
     dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
     sc = {"cloth": lambda: S.cloth(37, 21), "beam": lambda: S.tet_beam(13, 4, 3, S.K_TET_SNH),
-          "cloth_edit": lambda: S.cloth(37, 21)}[scene_name]()
+          "cloth_edit": lambda: S.cloth(37, 21),
+          # domain-decomposed XPBD (SURVEY 8e "XPBD"): the config-2 scene (springs + quadratic bending + anchors) and a beam
+          "xpbd_cloth": lambda: S.cloth(37, 21, S.K_SPRING, S.K_QUADRATIC_BENDING),
+          "xpbd_cloth_lambda": lambda: S.cloth(29, 17, S.K_MEMBRANE_STVK, S.K_DISCRETE_BENDING),
+          "xpbd_beam": lambda: S.tet_beam(13, 4, 3, S.K_TET_SNH)}[scene_name]()
+    xpbd = scene_name.startswith("xpbd")
+    solver_kind = api.SPGX_XPBD if xpbd else api.SPGX_VBD
 
     def run(g, reconnect=None, partitioned=False):
         """the stepping sequence under test; "cloth_edit": a live edit in the middle (the picking anchor of
         apps/solverCompare.cpp:717-726 on a vertex next to a strip boundary, then re-finalize: positions AND velocities of
         owned and halo vertices must survive it -- ADVICE round 1)"""
+        if xpbd:
+            # reference semantics (20 substeps x 1 pass) and, for one scene, 3 iterations with lambda kept on the device
+            g.xpbd_step(0.01, 20, 3 if scene_name == "xpbd_cloth_lambda" else 1, frames=2)
+            return
         g.vbd_step(0.01, 2, 5, frames=3)
         if scene_name == "cloth_edit":
             picked = 21 * (37 // world) + 3   # first row of rank 1's strip
@@ -48,7 +58,7 @@ def main():
         for graph in (True, False):
             g = api.Group.from_scene(ctx, sc)
             g.set_partition(rank, world)
-            g.finalize(api.SPGX_VBD)
+            g.finalize(solver_kind)
             assert g.halo_mode() == api.SPGX_HALO_NCCL
             if mode == "p2p":
                 assert g.connect_peers(dist) == api.SPGX_HALO_P2P
@@ -70,7 +80,7 @@ def main():
             g.close()
     if rank == 0:
         g1 = api.Group.from_scene(ctx, sc)
-        g1.finalize(api.SPGX_VBD)
+        g1.finalize(solver_kind)
         run(g1)
         x1, v1 = g1.download()
         np.savez(out, x1=x1, v1=v1, **{f"x_{m}_{int(gr)}": r[0] for (m, gr), r in results.items()},

@@ -1,4 +1,5 @@
-"""Multi-GPU identity gate: the domain-decomposed VBD sweep with per-colour
+"""Multi-GPU identity gate: the domain-decomposed XPBD pass loop (one exchange per
+(energy, colour) pass, xpbd_partition.h) and the domain-decomposed VBD sweep with per-colour
 halo exchange (NCCL point-to-point, and the fused peer-memory exchange) on k GPUs reproduces the single-GPU result bit for bit (every vertex update is a deterministic
 function of its stencil neighbours and the per-vertex accumulation order is kept).  Needs >= 2 GPUs; skipped otherwise."""
 import subprocess
@@ -17,7 +18,7 @@ def _ngpus():
     return torch.cuda.device_count()
 
 
-@pytest.mark.parametrize("scene", ["cloth", "beam", "cloth_edit"])
+@pytest.mark.parametrize("scene", ["cloth", "beam", "cloth_edit", "xpbd_cloth", "xpbd_cloth_lambda", "xpbd_beam"])
 def test_k_gpu_equals_one_gpu(tmp_path, scene):
     n = _ngpus()
     if n < 2:

@@ -63,7 +63,10 @@ def test_oracle_steps_match_golden(oracle, name):
     sol.step(frames)
     x, v = sol.state()
     if kind != MI.SYMPLECTIC:
-        assert np.array_equal(sol.cg_iterations(), G[f"step_{name}_cg"])
+        # the compiled reference reproduces its own counts; the independent restatement (different summation order in the
+        # products) may cross the |r| <= 1e-5 |b| threshold one iteration earlier or later
+        slack = 0 if oracle.kind == "reference" else 1
+        assert np.abs(sol.cg_iterations() - G[f"step_{name}_cg"]).max() <= slack
     # symplectic Euler at 200-400 substeps accumulates its omp-atomic summation order: 1e-9 still holds
     assert _rel(x, G[f"step_{name}_x"]) <= RTOL and _rel(v, G[f"step_{name}_v"]) <= 1e-8
 
