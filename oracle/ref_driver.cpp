@@ -80,6 +80,14 @@ const int kStencilSize[K_COUNT] = {2, 2, 4, 4, 3, 3, 3, 4, 4, 1, 4, 2, 4, 1};
 const int kNumModelParams[K_COUNT] = {2, 2, 2, 2, 2, 3, 3, 2, 2, 4, 2, 2, 2, 4};
 
 thread_local std::string g_error;
+}  // namespace
+// a test may bring an energy of its own, written against the reference's authoring base class (tests/native/extra_energy_ref.h,
+// Makefile target ref_extra): it supplies makeExtraEnergy / extraKindStencilSize / extraKindNumModelParams
+#ifdef SPG_EXTRA_ENERGY_IMPL
+#include SPG_EXTRA_ENERGY_IMPL
+#endif
+namespace
+{
 
 struct RefGroup {
     spg::ParticleGroup pg;
@@ -281,6 +289,9 @@ std::shared_ptr<spg::ParticleGroup::EnergyT> makeEnergy(int kind, int n, const i
         return e;
     }
     default:
+#ifdef SPG_EXTRA_ENERGY_IMPL
+        if (auto e = makeExtraEnergy(kind, n, st, p)) return e;
+#endif
         throw std::runtime_error("unknown energy kind");
     }
 }
@@ -309,11 +320,17 @@ void ref_omp_set_threads(int n)
 
 int ref_kind_stencil_size(int kind)
 {
+#ifdef SPG_EXTRA_ENERGY_IMPL
+    if (kind >= K_COUNT) return extraKindStencilSize(kind);
+#endif
     return (kind >= 0 && kind < K_COUNT) ? kStencilSize[kind] : -1;
 }
 
 int ref_kind_num_model_params(int kind)
 {
+#ifdef SPG_EXTRA_ENERGY_IMPL
+    if (kind >= K_COUNT) return extraKindNumModelParams(kind);
+#endif
     return (kind >= 0 && kind < K_COUNT) ? kNumModelParams[kind] : -1;
 }
 
@@ -473,6 +490,9 @@ int ref_constraints_and_gradient(void *h, int e, int stencil, double *C, double 
                   tryConstraints<SpringSquaredContinuumEnergy>(en, g->pg, stencil, C, grad) ||
                   tryConstraints<StableSquaredNeoHookeanEnergy>(en, g->pg, stencil, C, grad) ||
                   tryConstraints<StaticLoadEnergy>(en, g->pg, stencil, C, grad);
+#ifdef SPG_EXTRA_ENERGY_IMPL
+        ok = ok || tryConstraints<SPG_EXTRA_ENERGY_TYPE>(en, g->pg, stencil, C, grad);
+#endif
         if (!ok) throw std::runtime_error("unsupported energy type");
     });
 }
@@ -518,6 +538,9 @@ int ref_effective_stiffness(void *h, int e, int stencil, double *K, double *A)
                   tryStiffness<SpringAnchorEnergy>(en, stencil, K, A) || tryStiffness<BaraffWitkinBendingEnergy>(en, stencil, K, A) ||
                   tryStiffness<SpringSquaredContinuumEnergy>(en, stencil, K, A) ||
                   tryStiffness<StableSquaredNeoHookeanEnergy>(en, stencil, K, A) || tryStiffness<StaticLoadEnergy>(en, stencil, K, A);
+#ifdef SPG_EXTRA_ENERGY_IMPL
+        ok = ok || tryStiffness<SPG_EXTRA_ENERGY_TYPE>(en, stencil, K, A);
+#endif
         if (!ok) throw std::runtime_error("unsupported energy type");
     });
 }

@@ -14,7 +14,10 @@ import numpy as np
 
 from . import scenes as _scenes
 
-_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libspgx.so"
+import os
+
+# SPGX_LIB: another build of the same sources (tests/test_extra_kind.py loads the one with an extra energy kind registered)
+_LIB_PATH = Path(os.environ.get("SPGX_LIB") or Path(__file__).resolve().parent / "lib" / "libspgx.so")
 if not _LIB_PATH.exists():
     raise ImportError(f"{_LIB_PATH} is missing: build it with `python -m spg_b200.build` "
                       "(__graft_entry__.build()). There is no CPU fallback.")
@@ -281,7 +284,7 @@ class Group:
     def add_energy(self, kind: int, stencils, params) -> int:
         s, p = _i32(stencils), _f64(params)
         eid = C.c_int(-1)
-        n = s.size // _scenes.STENCIL_SIZE[kind]
+        n = s.size // lib.spgx_kind_stencil_size(kind)
         check(lib.spgx_group_add_energy(self.handle, kind, n, _i(s), _d(p), C.byref(eid)))
         self.kinds.append(kind)
         self.n_stencils.append(n)
@@ -472,7 +475,7 @@ class Group:
         return rowptr, cols, vals
 
     def element_hessian(self, eid: int, stencil: int) -> np.ndarray:
-        k = 3 * _scenes.STENCIL_SIZE[self.kinds[eid]]
+        k = 3 * lib.spgx_kind_stencil_size(self.kinds[eid])
         h = np.empty((k, k))
         check(lib.spgx_element_hessian(self.handle, eid, stencil, _d(h)))
         return h
@@ -498,7 +501,7 @@ class Group:
     def eval_constraints(self, eid: int, stencil: int):
         kind = self.kinds[eid]
         nc = lib.spgx_kind_num_constraints(kind)
-        k = 3 * _scenes.STENCIL_SIZE[kind]
+        k = 3 * lib.spgx_kind_stencil_size(kind)
         c = np.empty(nc)
         g = np.empty((k, nc))
         check(lib.spgx_eval_constraints(self.handle, eid, stencil, _d(c), _d(g)))

@@ -47,12 +47,26 @@ def _stale(target: Path, deps: list[Path]) -> bool:
     return any(d.exists() and d.stat().st_mtime > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> Path:
-    """Compile every .cu for sm_100a and link spg_b200/lib/libspgx.so."""
+EXTRA_DIR = ROOT / "tests" / "native"
+LIB_EXTRA = LIBDIR / "libspgx_extra.so"
+
+
+def build_library(force: bool = False, verbose: bool = False, extra_kind: bool = False) -> Path:
+    """Compile every .cu for sm_100a and link spg_b200/lib/libspgx.so.
+
+    extra_kind: the same sources with the throw-away 15th energy kind of tests/native/extra_kind.{def,cuh} registered
+    (-DSPGX_EXTRA_KINDS_DEF / -DSPGX_EXTRA_KINDS_IMPL) -> spg_b200/lib/libspgx_extra.so, loaded only by tests/test_extra_kind.py:
+    the proof that an energy plugs in without touching the library sources."""
     nvcc = _nvcc()
     LIBDIR.mkdir(parents=True, exist_ok=True)
+    OBJDIR = ROOT / "build" / ("obj_extra" if extra_kind else "obj")
+    LIB = LIB_EXTRA if extra_kind else globals()["LIB"]
+    NVCC_FLAGS = list(globals()["NVCC_FLAGS"])
     OBJDIR.mkdir(parents=True, exist_ok=True)
     hdrs = [CSRC / h for h in HEADERS] + [ROOT / "include" / "spgx.h", Path(__file__)]
+    if extra_kind:
+        NVCC_FLAGS += [f'-DSPGX_EXTRA_KINDS_DEF="{EXTRA_DIR / "extra_kind.def"}"', f'-DSPGX_EXTRA_KINDS_IMPL="{EXTRA_DIR / "extra_kind.cuh"}"']
+        hdrs += [EXTRA_DIR / "extra_kind.def", EXTRA_DIR / "extra_kind.cuh"]
     # a host compiler whose OpenMP / libstdc++ pieces are complete (see oracle/Makefile)
     ccbin = ["-ccbin", "/usr/bin/g++"] if Path("/usr/bin/g++").exists() else []
 
@@ -84,7 +98,7 @@ def build_oracle(verbose: bool = False) -> dict:
     odir = ROOT / "oracle"
     targets = ["port"] if (odir / "spg_port.cpp").exists() else []
     if Path("/root/reference/spg/source").exists():
-        targets.append("ref")
+        targets += ["ref", "ref_extra"]
     for t in targets:
         res = subprocess.run(["make", "-C", str(odir), "-j8", t], capture_output=True, text=True)
         out[t] = res.returncode == 0
@@ -98,5 +112,7 @@ def build_oracle(verbose: bool = False) -> dict:
 if __name__ == "__main__":
     force = "--force" in sys.argv
     print(build_library(force=force, verbose="-v" in sys.argv))
+    if "--extra" in sys.argv:
+        print(build_library(force=force, verbose="-v" in sys.argv, extra_kind=True))
     if "--oracle" in sys.argv:
         print(build_oracle(verbose=True))

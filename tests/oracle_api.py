@@ -9,13 +9,15 @@ bench.py's cpu_baseline / --impl reference legs may import this module.
 """
 from __future__ import annotations
 
+import os
 import ctypes as C
 from pathlib import Path
 
 import numpy as np
 
 ROOT = Path(__file__).resolve().parent.parent
-REF_LIB = ROOT / "oracle" / "_ref" / "libspgref.so"
+# SPGX_ORACLE_REF_LIB: the reference + a test's own energy (oracle/Makefile target ref_extra, tests/test_extra_kind.py)
+REF_LIB = Path(os.environ.get("SPGX_ORACLE_REF_LIB") or ROOT / "oracle" / "_ref" / "libspgref.so")
 PORT_LIB = ROOT / "oracle" / "libspgport.so"
 
 _dp = C.POINTER(C.c_double)
