@@ -302,6 +302,11 @@ int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, i
 /* constraintsAndGradient: C (nC) and gradient (3S x nC row-major) on the current device positions */
 int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C, double *grad);
 
+/* Debug aid (what Verbosity::Debug of the facade runs after every step; the reference has no counterpart, SURVEY.md
+ * section 5): counts the non-finite components of the positions and velocities this rank owns, on the device.
+ * out3 = [non-finite position components, non-finite velocity components, first offending vertex id or -1]. */
+int spgx_check_finite(spgx_group *grp, int64_t *out3);
+
 /* ---- algorithmic byte model ---------------------------------- */
 /* bytes one VBD iteration (all colours) / one XPBD substep must move under the gather model */
 int spgx_model_bytes(spgx_group *grp, double *bytesPerIteration, double *bytesLowerBound);

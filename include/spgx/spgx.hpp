@@ -338,6 +338,15 @@ protected:
                 }
             check(stepGroup(s.handle, g));
             s.deviceDirty = true;
+            if (m_verbosity == Verbosity::Debug) {
+                // a device-side NaN / Inf scan of the state after every step (the reference's Debug level prints; a GPU path
+                // that goes non-finite would otherwise only show up at the next positions() read)
+                int64_t bad[3] = {0, 0, -1};
+                check(spgx_check_finite(s.handle, bad));
+                if (bad[0] || bad[1])
+                    throw std::runtime_error("non-finite state after step(): " + std::to_string(bad[0]) + " position and " +
+                                             std::to_string(bad[1]) + " velocity components, first at vertex " + std::to_string(bad[2]));
+            }
         }
         m_precomputationUpdateRequired = false;
         m_time += m_dtStep;

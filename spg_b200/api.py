@@ -94,6 +94,7 @@ SIGNATURES = {
     "spgx_eval_vertex_force_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]),
     "spgx_eval_constraints": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
     "spgx_model_bytes": (C.c_int, [C.c_void_p, _dp, _dp]),
+    "spgx_check_finite": (C.c_int, [C.c_void_p, _lp]),
     "spgx_implicit_step": (C.c_int, [C.c_void_p, C.c_int, C.c_double, C.c_int, _dp, C.c_double, C.c_int, C.c_int, C.c_int]),
     "spgx_symplectic_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, _dp, C.c_int, C.c_int]),
     "spgx_last_cg_iterations": (C.c_int, [C.c_void_p, _ip, C.c_int, C.POINTER(C.c_int)]),
@@ -506,6 +507,12 @@ class Group:
         g = np.empty((k, nc))
         check(lib.spgx_eval_constraints(self.handle, eid, stencil, _d(c), _d(g)))
         return c, g
+
+    def check_finite(self):
+        """(non-finite position components, non-finite velocity components, first offending vertex or -1), counted on the device"""
+        o = np.zeros(3, np.int64)
+        check(lib.spgx_check_finite(self.handle, o.ctypes.data_as(_lp)))
+        return int(o[0]), int(o[1]), int(o[2])
 
     def model_bytes(self):
         a, b = C.c_double(0), C.c_double(0)

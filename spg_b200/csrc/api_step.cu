@@ -427,6 +427,27 @@ int spgx_xpbd_step(spgx_group *grp, double dt, int nsubsteps, int iterations, co
     });
 }
 
+int spgx_check_finite(spgx_group *grp, int64_t *out3)
+{
+    return guarded([&] {
+        if (!grp || !grp->finalized || !out3) throw StateError("group is not finalized");
+        SPGX_CUDA(cudaSetDevice(grp->ctx->device));
+        cudaStream_t st = grp->ctx->stream;
+        DevBuf<unsigned long long> d;
+        d.alloc(3);
+        const unsigned long long init[3] = {0ull, 0ull, ~0ull};
+        SPGX_CUDA(cudaMemcpyAsync(d.ptr, init, sizeof(init), cudaMemcpyHostToDevice, st));
+        launchCheckFinite(grp->d_x.ptr, grp->d_v.ptr, grp->nOwned, d.ptr, st);
+        unsigned long long h[3];
+        SPGX_CUDA(cudaMemcpyAsync(h, d.ptr, sizeof(h), cudaMemcpyDeviceToHost, st));
+        SPGX_CUDA(cudaStreamSynchronize(st));
+        SPGX_CUDA(cudaGetLastError());
+        out3[0] = static_cast<int64_t>(h[0]);
+        out3[1] = static_cast<int64_t>(h[1]);
+        out3[2] = h[2] == ~0ull ? -1 : static_cast<int64_t>(grp->slot2vert[static_cast<size_t>(h[2] - 1)]);
+    });
+}
+
 int spgx_last_timings(spgx_group *grp, spgx_timings *out)
 {
     return guarded([&] {

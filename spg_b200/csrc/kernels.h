@@ -95,6 +95,9 @@ void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, 
 // XPBD: store entries [begin, end) of h.push into the neighbours' halo slots, then raise event `event` (one block that only
 // raises it when the range is empty)
 void launchXpbdHaloPush(const VbdHaloDev &h, const double *x, int begin, int end, int event, cudaStream_t stream);
+// non-finite components of x / v over the first nVerts slots: out3 = [count x, count v, smallest bad slot + 1]; the caller
+// initialises out3 to {0, 0, ~0}
+void launchCheckFinite(const double *x, const double *v, int nVerts, unsigned long long *out3, cudaStream_t stream);
 // dst[perm[i]] = src[i] (scatter) or dst[i] = src[perm[i]] (gather) over 3-vectors
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream);
 

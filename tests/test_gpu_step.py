@@ -252,3 +252,19 @@ def test_xpbd_fused_frame_equals_per_pass_launches(ctx, iters, monkeypatch):
     for name in ("passes_graph", "passes_plain", "fused_barrier"):
         assert np.array_equal(results["fused"][0], results[name][0]), name
         assert np.array_equal(results["fused"][1], results[name][1]), name
+
+
+@pytest.mark.parametrize("solver", [api.SPGX_VBD, api.SPGX_XPBD])
+def test_debug_scan_finds_non_finite_state(ctx, solver):
+    """spgx_check_finite (what Verbosity::Debug of the facade runs after every step): clean after a step, and a NaN planted
+    in one vertex is found, counted and located in the caller's vertex numbering (VBD keeps its state in colour order)"""
+    sc = S.cloth(12, 9) if solver == api.SPGX_VBD else S.cloth(12, 9, S.K_SPRING, S.K_QUADRATIC_BENDING)
+    g = api.Group.from_scene(ctx, sc)
+    g.finalize(solver)
+    (g.vbd_step if solver == api.SPGX_VBD else g.xpbd_step)(0.01, 2, 3)
+    assert g.check_finite() == (0, 0, -1)
+    x, v = g.download()
+    x[41, 1] = np.nan
+    v[77] = np.inf
+    g.upload(x, v)
+    assert g.check_finite() == (1, 3, 41)
