@@ -177,12 +177,16 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         desc[nSlices * kSliceDescWords + 7] = static_cast<uint32_t>(pushBefore) << 3;
         grp.p2p.pushLocal = pushAll;
         grp.p2p.pushWarps = pushWarps;
-        std::vector<uint32_t> ids(static_cast<size_t>(row) * VW, 0u);
-        for (size_t sl = 0; sl < nSlices; ++sl)
+        // packed: slice sl starts at its cumulative row; fixed stride (vbdNbrFixed): at row sl * maxNbr, so that the kernel can
+        // request the ids before the descriptor has arrived (unused rows hold slot 0, a harmless gather target)
+        const bool fixed = grp.vbdNbrFixed != 0;
+        std::vector<uint32_t> ids((fixed ? nSlices * static_cast<size_t>(maxNbr) : static_cast<size_t>(row)) * VW, 0u);
+        for (size_t sl = 0; sl < nSlices; ++sl) {
+            const size_t row0 = fixed ? sl * static_cast<size_t>(maxNbr) : static_cast<size_t>(desc[sl * kSliceDescWords + 1]);
             for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s)
                 for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
-                    ids[(static_cast<size_t>(desc[sl * kSliceDescWords + 1]) + (k - nbrRowptr[s])) * VW + (s - sliceSlot[sl])] =
-                        nbrList[k];
+                    ids[(row0 + (k - nbrRowptr[s])) * VW + (s - sliceSlot[sl])] = nbrList[k];
+        }
         grp.d_nbrIds.upload(ids, st);
         bytes += 4.0 * ids.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
@@ -829,14 +833,16 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             }
             if (const char *env = getenv("SPGX_VBD_LANES")) {
                 const int l = atoi(env);
-                if (l == 1 || l == 2 || l == 4) grp->vbdLanes = l;
+                if (l == 2 || l == 4) grp->vbdLanes = l;
             }
             // kernel variant (vbd_stream.cuh launchStreamG): resident blocks per SM + 10 x "records through the shared-memory ring"
             grp->vbdOcc = 4;
             if (const char *env = getenv("SPGX_VBD_VARIANT")) {
                 const int o = atoi(env);
-                if (o == 4 || o == 14 || o == 15 || o == 16) grp->vbdOcc = o;
+                if (o == 4 || o == 15) grp->vbdOcc = o;
             }
+            grp->vbdNbrFixed = 1;
+            if (const char *env = getenv("SPGX_VBD_NBRFIXED")) grp->vbdNbrFixed = atoi(env) != 0;
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
                 const int64_t n = grp->colorOffsets[c + 1] - grp->colorOffsets[c];

@@ -53,6 +53,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
     args.sliceDesc = grp->d_sliceDesc.ptr;
     args.nbrIds = grp->d_nbrIds.ptr;
     args.maxNbr = grp->maxNbr;
+    args.nbrFixed = grp->vbdNbrFixed;
     args.nSlices = grp->nSlices;
     args.lookahead = std::min(grp->vbdLookahead, std::max(grp->nSlices - 1, 0));
     args.pdl = grp->vbdPdl;
@@ -83,7 +84,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
         launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->d_xInertial.ptr, grp->nLocal, dt, grp->graphKey.g,
                       st);
         grp->launchCounter++;
-        if (signalling) {
+        if (signalling && !(args.halo.debug & 8)) {
             // event 0: this rank's halo copies have been predicted; neighbours may store into them from now on
             launchHaloSignal(args.halo, 0, st);
             grp->launchCounter++;
@@ -106,7 +107,7 @@ void enqueueVbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaSt
                 // every rank takes part in the exchange of colour c, whether or not it owns vertices of that colour
                 if (viaNccl) grp->launchCounter += enqueueHaloExchange(grp, c, st);
             }
-        if (signalling) {
+        if (signalling && !(args.halo.debug & 8)) {
             // the neighbours' stores of the last pass must have landed before the halo copies are finalized; the epoch
             // advances by the events of this substep
             launchHaloWaitAdvance(args.halo, event, grp->p2p.d_sync.ptr + kMaxPeers, st);
@@ -437,14 +438,14 @@ int spgx_check_finite(spgx_group *grp, int64_t *out3)
         d.alloc(3);
         const unsigned long long init[3] = {0ull, 0ull, ~0ull};
         SPGX_CUDA(cudaMemcpyAsync(d.ptr, init, sizeof(init), cudaMemcpyHostToDevice, st));
-        launchCheckFinite(grp->d_x.ptr, grp->d_v.ptr, grp->nOwned, d.ptr, st);
+        launchCheckFinite(grp->d_x.ptr, grp->d_v.ptr, grp->d_slot2vert.ptr, grp->nOwned, d.ptr, st);
         unsigned long long h[3];
         SPGX_CUDA(cudaMemcpyAsync(h, d.ptr, sizeof(h), cudaMemcpyDeviceToHost, st));
         SPGX_CUDA(cudaStreamSynchronize(st));
         SPGX_CUDA(cudaGetLastError());
         out3[0] = static_cast<int64_t>(h[0]);
         out3[1] = static_cast<int64_t>(h[1]);
-        out3[2] = h[2] == ~0ull ? -1 : static_cast<int64_t>(grp->slot2vert[static_cast<size_t>(h[2] - 1)]);
+        out3[2] = h[2] == ~0ull ? -1 : static_cast<int64_t>(h[2] - 1);
     });
 }
 

@@ -425,6 +425,7 @@ void p2pConnect(spgx_group *grp, int nBlobs, const void *const *blobs, const int
     double timeoutS = 10.0;
     if (const char *env = getenv("SPGX_HALO_TIMEOUT_S")) timeoutS = std::max(0.001, atof(env));
     dev.timeoutNs = static_cast<unsigned long long>(timeoutS * 1e9);
+    dev.debug = getenv("SPGX_DEBUG_HALO") ? atoi(getenv("SPGX_DEBUG_HALO")) : 0;
     p.dev = dev;
     p.connected = true;
     p.mode = SPGX_HALO_P2P;

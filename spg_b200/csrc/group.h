@@ -218,6 +218,7 @@ struct spgx_group {
     std::vector<int64_t> colorOffsets;
     int vbdLanes = 4;                   // threads per vertex in the VBD colour pass
     int vbdOcc = 4;                     // resident-blocks-per-SM hint of the streaming kernel
+    int vbdNbrFixed = 1;                // neighbour table at a fixed stride per slice (kernels.h: VbdArgs::nbrFixed)
     // streaming layout (kernels.h): unique-neighbour tables + one stream per (energy, stream type)
     struct StreamState {
         int type = 0;

@@ -47,6 +47,9 @@ struct VbdHaloDev {
     const uint32_t *epochBase;
     uint32_t *error;                 // set to 1 when a wait ran into the timeout
     unsigned long long timeoutNs;
+    int debug;                       // timing experiments only (SPGX_DEBUG_HALO, results are wrong): bit 0 skip the waits,
+                                     // bit 1 skip the system fences of the pushing warps, bit 2 skip the remote stores, bit 3 skip the
+                                     // signal / wait-advance kernels around the sweeps, bit 4 skip the push code of boundary slices
 };
 
 struct VbdArgs {
@@ -66,6 +69,7 @@ struct VbdArgs {
     const uint32_t *sliceDesc;
     const uint32_t *nbrIds;  // [row][VW] slot ids; row k of a slice = k-th unique neighbour of each of its vertices
     int maxNbr;              // largest unique-neighbour count of any vertex (sizes the shared-memory tile)
+    int nbrFixed;            // 1: nbrIds has a fixed stride of maxNbr rows per slice (rows past a slice's count hold slot 0)
     int nSlices;             // all colours
     int lookahead;           // slices ahead whose streams are pulled into L2 (0: off)
     int pdl;                 // 1: launch colour passes with programmatic stream serialization
@@ -95,9 +99,10 @@ void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, 
 // XPBD: store entries [begin, end) of h.push into the neighbours' halo slots, then raise event `event` (one block that only
 // raises it when the range is empty)
 void launchXpbdHaloPush(const VbdHaloDev &h, const double *x, int begin, int end, int event, cudaStream_t stream);
-// non-finite components of x / v over the first nVerts slots: out3 = [count x, count v, smallest bad slot + 1]; the caller
-// initialises out3 to {0, 0, ~0}
-void launchCheckFinite(const double *x, const double *v, int nVerts, unsigned long long *out3, cudaStream_t stream);
+// non-finite components of x / v over the first nVerts slots: out3 = [count x, count v, smallest offending vertex id + 1];
+// the caller initialises out3 to {0, 0, ~0}
+void launchCheckFinite(const double *x, const double *v, const int32_t *slot2vert, int nVerts, unsigned long long *out3,
+                       cudaStream_t stream);
 // dst[perm[i]] = src[i] (scatter) or dst[i] = src[perm[i]] (gather) over 3-vectors
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream);
 

@@ -45,25 +45,26 @@ __global__ void permute3Kernel(const double *__restrict__ src, double *__restric
     dst[b + 2] = src[a + 2];
 }
 // Verbosity::Debug check: counts the non-finite components of x and v over the first n slots and keeps the smallest
-// offending slot.  out: [count in x, count in v, first slot + 1 (0: none)]
-__global__ void checkFiniteKernel(const double *__restrict__ x, const double *__restrict__ v, long long n3,
-                                  unsigned long long *__restrict__ out)
+// offending vertex id (the caller's numbering).  out: [count in x, count in v, vertex + 1]
+__global__ void checkFiniteKernel(const double *__restrict__ x, const double *__restrict__ v, const int32_t *__restrict__ slot2vert,
+                                  long long n3, unsigned long long *__restrict__ out)
 {
     const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i >= n3) return;
     const bool bx = !isfinite(x[i]), bv = !isfinite(v[i]);
     if (bx) atomicAdd(out, 1ull);
     if (bv) atomicAdd(out + 1, 1ull);
-    if (bx || bv) atomicMin(out + 2, static_cast<unsigned long long>(i / 3) + 1ull);
+    if (bx || bv) atomicMin(out + 2, static_cast<unsigned long long>(slot2vert[i / 3]) + 1ull);
 }
 }  // namespace
 
-void launchCheckFinite(const double *x, const double *v, int nVerts, unsigned long long *out3, cudaStream_t stream)
+void launchCheckFinite(const double *x, const double *v, const int32_t *slot2vert, int nVerts, unsigned long long *out3,
+                       cudaStream_t stream)
 {
     const long long n3 = 3LL * nVerts;
     if (n3 == 0) return;
     const int threads = 256;
-    checkFiniteKernel<<<static_cast<unsigned>((n3 + threads - 1) / threads), threads, 0, stream>>>(x, v, n3, out3);
+    checkFiniteKernel<<<static_cast<unsigned>((n3 + threads - 1) / threads), threads, 0, stream>>>(x, v, slot2vert, n3, out3);
 }
 
 void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nVerts, double dt, const double *g3,

@@ -180,14 +180,14 @@ __device__ __forceinline__ void haloPushSlice(const VbdHaloDev &h, uint32_t firs
         const double px = __shfl_sync(0xffffffffu, xn.x, src);
         const double py = __shfl_sync(0xffffffffu, xn.y, src);
         const double pz = __shfl_sync(0xffffffffu, xn.z, src);
-        if (has) {
+        if (has && !(h.debug & 4)) {
             double *dst = h.peerX[e.y >> 28] + 3 * static_cast<size_t>(e.y & 0x0FFFFFFFu);
             dst[0] = px;
             dst[1] = py;
             dst[2] = pz;
         }
     }
-    __threadfence_system();
+    if (!(h.debug & 2)) __threadfence_system();
     __syncwarp();
     if (lane == 0) {
         const uint32_t done = atomicAdd(h.pushDone, 1u) + 1u;
@@ -432,7 +432,11 @@ struct RingOps {
 // RING: the record of the next step is prefetched into a two-step shared-memory ring with cp.async (no registers held, no
 // scoreboard wait) instead of the two-buffer register pipeline: ~30 registers fewer, which is what a fifth / sixth resident
 // block per SM needs.
-template <unsigned SMASK, unsigned KMASK, int G, int BT, bool RING>
+// NBRFIXED: the unique-neighbour table has a fixed stride of maxNbr rows per slice (padded with slot 0), so its address
+// follows from the slice number alone and the ids are requested TOGETHER with the descriptor instead of after it: one L2
+// round trip less in the serial prologue descriptor -> neighbour ids -> gather (profiles/r2j_vbd_stream_stalls.txt: that
+// chain is most of the 28 % long-scoreboard share).
+template <unsigned SMASK, unsigned KMASK, int G, int BT, bool RING, bool NBRFIXED>
 __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
     constexpr int VW = 32 / G;  // vertices per warp
@@ -452,6 +456,15 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     double *Pin = Pown + 3 * VW;
     double *Pmass = Pin + 3 * VW;
 
+    constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
+    uint32_t nid[PRE];
+    if constexpr (NBRFIXED) {
+#pragma unroll
+        for (int j = 0; j < PRE; ++j) {
+            const int k = sub + j * G;  // rows past the slice's own count hold slot 0
+            nid[j] = k < a.maxNbr ? __ldg(a.nbrIds + (static_cast<size_t>(slice) * a.maxNbr + k) * VW + v) : 0u;
+        }
+    }
     SliceDesc d, n;
     d.load(a.sliceDesc, slice);
     n.load(a.sliceDesc, slice + 1);
@@ -477,13 +490,15 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
         if (pipe.total > 0) pipe.template loadFrom<0>(a, r0, 0, lane);
     }
     cpAsyncCommit();
-    constexpr int PRE = G == 1 ? 12 : (G == 2 ? 8 : 4);  // neighbour ids per lane fetched ahead of the dependency wait
-    const uint32_t nb = d.lo.y, ne = n.lo.y;
-    uint32_t nid[PRE];
+    // rows [nb, ne) of the neighbour table are the slice's (descriptor word 1 counts rows cumulatively in both layouts)
+    const uint32_t nb = NBRFIXED ? static_cast<uint32_t>(slice) * static_cast<uint32_t>(a.maxNbr) : d.lo.y;
+    const uint32_t ne = nb + (n.lo.y - d.lo.y);
+    if constexpr (!NBRFIXED) {
 #pragma unroll
-    for (int j = 0; j < PRE; ++j) {
-        const uint32_t k = nb + sub + j * G;
-        nid[j] = k < ne ? __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v) : 0u;
+        for (int j = 0; j < PRE; ++j) {
+            const uint32_t k = nb + sub + j * G;
+            nid[j] = k < ne ? __ldg(a.nbrIds + static_cast<size_t>(k) * VW + v) : 0u;
+        }
     }
     if (a.lookahead > 0 && warpInBlock == 0) {
         // ONE lane per block pulls the ranges of the block's BT / 32 consecutive slices, `lookahead` slices further on
@@ -498,12 +513,25 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
             SliceDesc pd, pn;
             pd.load(a.sliceDesc, la);
             pn.load(a.sliceDesc, lb);
-            bulkPrefetchL2(a.nbrIds + static_cast<size_t>(pd.lo.y) * VW, (pn.lo.y - pd.lo.y) * (VW * 4u));
+            if constexpr (NBRFIXED)
+                bulkPrefetchL2(a.nbrIds + static_cast<size_t>(la) * a.maxNbr * VW, static_cast<uint32_t>(lb - la) * a.maxNbr * (VW * 4u));
+            else
+                bulkPrefetchL2(a.nbrIds + static_cast<size_t>(pd.lo.y) * VW, (pn.lo.y - pd.lo.y) * (VW * 4u));
             prefetchStreamIfPresent<SMASK, ST_BEND_EDGE>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_BEND_OPP>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_MEMBRANE_STVK>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_TET_SNH>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_TET_STVK>(a, pd, pn);
+        }
+    }
+    if (a.halo.nPeers && lane == 0) {
+        // multi-GPU: the slice's push entries are read at the very end of the warp's life (haloPushSlice): have them in L2 by
+        // then (profiles/r2m_halo_overhead_breakdown_2gpu.txt: the bookkeeping of the boundary slices, not the fences or the
+        // remote stores, is the larger half of what the exchange costs)
+        const uint32_t pb = d.hi.w >> 3, pe = n.hi.w >> 3;
+        if (pe > pb) {
+            prefetchLineL2(a.halo.push + pb);
+            prefetchLineL2(a.halo.push + pe - 1);
         }
     }
     // 2. positions: wait for the previous colour pass (programmatic dependent launch: this grid may have started
@@ -518,7 +546,7 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
             haloRaise(a.halo, haloEpochBase(a.halo) + static_cast<uint32_t>(a.halo.event) + 1u);
         }
         if (d.hi.w & 2u) {
-            if (lane == 0) haloWaitAll(a.halo, haloEpochBase(a.halo) + static_cast<uint32_t>(a.halo.event));
+            if (lane == 0 && !(a.halo.debug & 1)) haloWaitAll(a.halo, haloEpochBase(a.halo) + static_cast<uint32_t>(a.halo.event));
             __syncwarp();
         }
     }
@@ -603,17 +631,17 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
     // 6. multi-GPU: boundary vertices of the slice go to the neighbours' halo slots over NVLink
     if (a.halo.nPeers) {
         const uint32_t pb = d.hi.w >> 3, pe = n.hi.w >> 3;
-        if (pe > pb) haloPushSlice(a.halo, d.lo.x, pb, pe, lane, xn);
+        if (pe > pb && !(a.halo.debug & 16)) haloPushSlice(a.halo, d.lo.x, pb, pe, lane, xn);
     }
 }
 
-template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, int BT = kStreamBlockThreads>
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, bool NBRFIXED, int BT = kStreamBlockThreads>
 __global__ void __launch_bounds__(BT, OCC)
     vbdStreamKernel(const __grid_constant__ VbdArgs a, int end, int sliceBase, int nSlicesOfColour, double invdtSquared)
 {
-    vbdStreamBody<SMASK, KMASK, G, BT, RING>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
+    vbdStreamBody<SMASK, KMASK, G, BT, RING, NBRFIXED>(a, end, sliceBase, nSlicesOfColour, invdtSquared);
 }
-template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, int BT = kStreamBlockThreads>
+template <unsigned SMASK, unsigned KMASK, int G, int OCC, bool RING, bool NBRFIXED, int BT = kStreamBlockThreads>
 void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, double invdtSquared, cudaStream_t stream)
 {
     constexpr int VW = 32 / G;
@@ -624,7 +652,7 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     const int blocks = (warps + warpsPerBlock - 1) / warpsPerBlock;
     const size_t smem = static_cast<size_t>(warpsPerBlock) * streamWarpSmemBytes<SMASK, G, RING>(args.maxNbr);
     if (smem > 227 * 1024) return;  // rejected at finalize (buildStreams)
-    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC, RING, BT>;
+    auto kernel = vbdStreamKernel<SMASK, KMASK, G, OCC, RING, NBRFIXED, BT>;
     static size_t configured = 0;  // per instantiation
     if (smem > configured) {
         cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
@@ -664,20 +692,25 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
     cudaLaunchKernelEx(&cfg, kernel, args, end, sliceBase, warps, invdtSquared);
 }
 
-// variant = occ + 10 * ring: resident 128-thread blocks per SM (4: <= 128 registers, 5: <= 102, 6: <= 85) and whether the
-// records go through the shared-memory ring instead of the register pipeline.  Measured and rejected: 3 blocks; register
-// caps on the register pipeline, persistent warps, prefetch.global.L1 (round 1, profiles/r1f_*); two steps evaluated
-// together from a four-step ring on uniform slices (round 2, profiles/r2d_sweep.txt: ptxas keeps the two evaluations
-// sequential, the ring costs L1: 3.35 vs 2.89 ms per frame).
+// variant = occ + 10 * ring: resident 128-thread blocks per SM and whether the records go through the shared-memory ring
+// instead of the register pipeline: 4 (register pipeline, <= 128 registers) and 15 (ring, 5 blocks, <= 102 registers) are
+// compiled.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
+// (profiles/r2d ... r2i_sweep.txt); 3 blocks, register caps on the register pipeline, persistent warps, prefetch.global.L1
+// (round 1, profiles/r1f_*); two steps evaluated together from a four-step ring (ptxas keeps the two evaluations sequential).
 template <unsigned SMASK, unsigned KMASK, int G>
 void launchStreamG(const VbdArgs &args, int variant, int begin, int end, int sliceBase, double invdtSquared,
                    cudaStream_t stream)
 {
-    switch (variant) {
-    case 14: launchStreamGO<SMASK, KMASK, G, 4, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    case 15: launchStreamGO<SMASK, KMASK, G, 5, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    case 16: launchStreamGO<SMASK, KMASK, G, 6, true>(args, begin, end, sliceBase, invdtSquared, stream); break;
-    default: launchStreamGO<SMASK, KMASK, G, 4, false>(args, begin, end, sliceBase, invdtSquared, stream); break;
+    if (args.nbrFixed) {
+        if (variant == 15)
+            launchStreamGO<SMASK, KMASK, G, 5, true, true>(args, begin, end, sliceBase, invdtSquared, stream);
+        else
+            launchStreamGO<SMASK, KMASK, G, 4, false, true>(args, begin, end, sliceBase, invdtSquared, stream);
+    } else {
+        if (variant == 15)
+            launchStreamGO<SMASK, KMASK, G, 5, true, false>(args, begin, end, sliceBase, invdtSquared, stream);
+        else
+            launchStreamGO<SMASK, KMASK, G, 4, false, false>(args, begin, end, sliceBase, invdtSquared, stream);
     }
 }
 
@@ -685,11 +718,10 @@ template <unsigned SMASK, unsigned KMASK>
 void launchStream(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
                   cudaStream_t stream)
 {
-    switch (lanes) {
-    case 1: launchStreamG<SMASK, KMASK, 1>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
-    case 4: launchStreamG<SMASK, KMASK, 4>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
-    default: launchStreamG<SMASK, KMASK, 2>(args, occ, begin, end, sliceBase, invdtSquared, stream); break;
-    }
+    if (lanes == 4)
+        launchStreamG<SMASK, KMASK, 4>(args, occ, begin, end, sliceBase, invdtSquared, stream);
+    else
+        launchStreamG<SMASK, KMASK, 2>(args, occ, begin, end, sliceBase, invdtSquared, stream);
 }
 
 constexpr unsigned sbit(int k)

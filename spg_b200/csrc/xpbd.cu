@@ -20,21 +20,82 @@ namespace spgx
 {
 namespace
 {
+// the generic block projection (energy.h:117-153): C and dC/dx with first-order duals over the 3S stencil DOFs
+template <int KIND>
+__device__ __forceinline__ void projectGeneric(double *__restrict__ x, const int *id, const double *w, const V3d *px, const double *p,
+                                               double *__restrict__ lambda, int i, double dt2)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int S = EK::S, NC = EK::NC, K = 3 * S;
+    using D1 = Dual<K, false>;
+    V3<D1> xs[S];
+#pragma unroll
+    for (int s = 0; s < S; ++s)
+        xs[s] = V3<D1>(D1(px[s].x, 3 * s), D1(px[s].y, 3 * s + 1), D1(px[s].z, 3 * s + 2));
+    D1 C[NC];
+    EK::constraints(xs, p, C);
+    double A[NC][NC];
+    double rhs[NC];
+#pragma unroll
+    for (int a = 0; a < NC; ++a) {
+#pragma unroll
+        for (int b = a; b < NC; ++b) {
+            double acc = 0.0;
+#pragma unroll
+            for (int k = 0; k < K; ++k) acc += C[a].g[k] * (w[k / 3] * C[b].g[k]);
+            acc += EK::alpha(p, a, b) / dt2;
+            if (a == b) acc += 1e-10;
+            A[a][b] = acc;
+            A[b][a] = acc;
+        }
+        rhs[a] = -C[a].v;
+    }
+    if (lambda) {
+#pragma unroll
+        for (int a = 0; a < NC; ++a)
+#pragma unroll
+            for (int b = 0; b < NC; ++b) rhs[a] -= (EK::alpha(p, a, b) / dt2) * lambda[static_cast<size_t>(i) * NC + b];
+    }
+    solveSmall<NC>(A, rhs);  // rhs <- dlambda
+    if (lambda) {
+#pragma unroll
+        for (int a = 0; a < NC; ++a) lambda[static_cast<size_t>(i) * NC + a] += rhs[a];
+    }
+#pragma unroll
+    for (int s = 0; s < S; ++s) {
+        double d[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            double acc = 0.0;
+#pragma unroll
+            for (int a = 0; a < NC; ++a) acc += (w[s] * C[a].g[3 * s + c]) * rhs[a];
+            d[c] = acc;
+        }
+        const size_t o = 3 * static_cast<size_t>(id[s]);
+        x[o] = px[s].x + d[0];
+        x[o + 1] = px[s].y + d[1];
+        x[o + 2] = px[s].z + d[2];
+    }
+}
+
 // PDL: the caller was launched with programmatic stream serialization; the stencil's vertex ids and inverse masses (never
 // written by a pass) are fetched before griddepcontrol.wait, i.e. while the previous pass may still be draining
 template <int KIND, bool PDL = false>
 __device__ __forceinline__ void projectStencil(double *__restrict__ x, const double *__restrict__ invMass,
                                                const int32_t *__restrict__ stencils, const double *__restrict__ records,
-                                               double *__restrict__ lambda, int i, double dt)
+                                               double *__restrict__ lambda, int i, double dt, bool handProject = true)
 {
     using EK = EnergyKind<KIND>;
-    constexpr int S = EK::S, NC = EK::NC, K = 3 * S;
-    using D1 = Dual<K, false>;
+    constexpr int S = EK::S, NC = EK::NC;
     const int32_t *ids = stencils + static_cast<size_t>(i) * S;
-    const double *p = records + static_cast<size_t>(i) * EK::NP;
     int id[S];
     double w[S];
     V3d px[S];
+    // everything a pass never writes -- vertex ids, inverse masses, the stencil's record -- is requested up front (under PDL:
+    // before the dependency wait, i.e. while the previous pass may still be draining)
+    double p[EK::NP];
+#pragma unroll
+    for (int k = 0; k < EK::NP; ++k) p[k] = __ldg(records + static_cast<size_t>(i) * EK::NP + k);
 #pragma unroll
     for (int s = 0; s < S; ++s) {
         id[s] = __ldg(ids + s);
@@ -74,86 +135,50 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
         x[o1 + 1] = px[1].y - w[1] * (n.y * scale);
         x[o1 + 2] = px[1].z - w[1] * (n.z * scale);
         return;
+    } else if constexpr (HasHandProject<EK>::value) {
+        if (handProject) {
+            EK::project(px, w, p, dt2, lambda ? lambda + static_cast<size_t>(i) * NC : nullptr);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+                const size_t o = 3 * static_cast<size_t>(id[s]);
+                x[o] = px[s].x;
+                x[o + 1] = px[s].y;
+                x[o + 2] = px[s].z;
+            }
+            return;
+        }
+        projectGeneric<KIND>(x, id, w, px, p, lambda, i, dt2);
     } else {
-        V3<D1> xs[S];
-#pragma unroll
-        for (int s = 0; s < S; ++s)
-            xs[s] = V3<D1>(D1(px[s].x, 3 * s), D1(px[s].y, 3 * s + 1), D1(px[s].z, 3 * s + 2));
-        D1 C[NC];
-        EK::constraints(xs, p, C);
-        double A[NC][NC];
-        double rhs[NC];
-#pragma unroll
-        for (int a = 0; a < NC; ++a) {
-#pragma unroll
-            for (int b = a; b < NC; ++b) {
-                double acc = 0.0;
-#pragma unroll
-                for (int k = 0; k < K; ++k) acc += C[a].g[k] * (w[k / 3] * C[b].g[k]);
-                acc += EK::alpha(p, a, b) / dt2;
-                if (a == b) acc += 1e-10;
-                A[a][b] = acc;
-                A[b][a] = acc;
-            }
-            rhs[a] = -C[a].v;
-        }
-        if (lambda) {
-#pragma unroll
-            for (int a = 0; a < NC; ++a)
-#pragma unroll
-                for (int b = 0; b < NC; ++b) rhs[a] -= (EK::alpha(p, a, b) / dt2) * lambda[static_cast<size_t>(i) * NC + b];
-        }
-        solveSmall<NC>(A, rhs);  // rhs <- dlambda
-        if (lambda) {
-#pragma unroll
-            for (int a = 0; a < NC; ++a) lambda[static_cast<size_t>(i) * NC + a] += rhs[a];
-        }
-#pragma unroll
-        for (int s = 0; s < S; ++s) {
-            double d[3];
-#pragma unroll
-            for (int c = 0; c < 3; ++c) {
-                double acc = 0.0;
-#pragma unroll
-                for (int a = 0; a < NC; ++a) acc += (w[s] * C[a].g[3 * s + c]) * rhs[a];
-                d[c] = acc;
-            }
-            const size_t o = 3 * static_cast<size_t>(id[s]);
-            x[o] = px[s].x + d[0];
-            x[o + 1] = px[s].y + d[1];
-            x[o + 2] = px[s].z + d[2];
-        }
+        projectGeneric<KIND>(x, id, w, px, p, lambda, i, dt2);
     }
 }
 
-// h.nPeers > 0: a rank of a partitioned group under the peer-memory exchange (halo.cuh, xpbd_partition.h): the neighbours'
-// pushes of the previous pass must have landed before any position is read.  One thread per block waits on the local flag
-// array (acquire), the block barrier orders the other threads' loads behind it.  (One kernel for both cases, so that a
-// partitioned run executes the very same instruction stream per stencil as a single-domain one.)
 template <int KIND>
 __global__ void __launch_bounds__(128) xpbdPassKernel(double *x, const double *invMass, const int32_t *stencils,
                                                       const double *records, double *lambda, int begin, int end,
-                                                      double dt, const VbdHaloDev h)
+                                                      double dt, bool handProject, const VbdHaloDev h)
 {
     if (h.nPeers > 0) {
         if (threadIdx.x == 0) haloWaitAll(h, haloEpochBase(h) + static_cast<uint32_t>(h.event));
         __syncthreads();
     }
     const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < end) projectStencil<KIND>(x, invMass, stencils, records, lambda, i, dt);
+    if (i < end) projectStencil<KIND>(x, invMass, stencils, records, lambda, i, dt, handProject);
 }
 // the same pass under programmatic dependent launch: the next pass may become resident and run its prologue while this
 // one drains (config 2 is 540 passes of 10-30 k stencils per frame: the kernel boundary is most of a pass)
 template <int KIND>
 __global__ void __launch_bounds__(128) xpbdPassKernelPdl(double *x, const double *invMass, const int32_t *stencils,
                                                          const double *records, double *lambda, int begin, int end,
-                                                         double dt)
+                                                         double dt, bool handProject)
 {
     asm volatile("griddepcontrol.launch_dependents;");
     const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < end) projectStencil<KIND, true>(x, invMass, stencils, records, lambda, i, dt);
+    if (i < end) projectStencil<KIND, true>(x, invMass, stencils, records, lambda, i, dt, handProject);
     // threads past the end leave without waiting: the grid as a whole still completes only after its waiting threads
 }
+
+__global__ void xpbdEmptyKernel(double *) {}
 
 // serial Gauss-Seidel path (xpbd.cpp:96-102): one thread walks the stencils in index order
 template <int KIND>
@@ -254,12 +279,24 @@ void launchKind(double *x, const double *invMass, const int32_t *stencils, const
     const int n = end - begin;
     if (n <= 0) return;
     const VbdHaloDev h = (halo && halo->nPeers > 0) ? *halo : VbdHaloDev{};
+    // SPGX_XPBD_HAND=0: kinds with a hand-derived projection (EnergyKind<>::project) take the generic dual-number path instead
+    static const bool hand = !(getenv("SPGX_XPBD_HAND") && atoi(getenv("SPGX_XPBD_HAND")) == 0);
     if (serial) {
         xpbdSerialKernel<KIND><<<1, 1, 0, stream>>>(x, invMass, stencils, records, lambda, begin, end, dt);
     } else {
-        const int threads = 128;
-        // opt-in: in a replayed CUDA graph the kernel boundary is already ~1 us; measured 1.82 vs 1.76 ms per frame at config 2
-        static const bool pdl = getenv("SPGX_XPBD_PDL") && atoi(getenv("SPGX_XPBD_PDL")) != 0;
+        // measurement knobs: SPGX_XPBD_THREADS (block size, <= 128), SPGX_XPBD_DEBUG_EMPTY=1 (same grids, empty kernels: the
+        // launch floor of the pass sequence; results are wrong)
+        // one warp per block: a pass of 10-30 k stencils is one partial wave either way, and 4 x as many blocks spread it over
+        // every SM (config 2: 1.59 / 1.52 / 1.45 ms per frame at 128 / 64 / 32 threads, profiles/r2m_xpbd_sweep_config2.txt)
+        static const int threads = getenv("SPGX_XPBD_THREADS") ? std::min(128, std::max(32, atoi(getenv("SPGX_XPBD_THREADS")))) : 32;
+        static const bool empty = getenv("SPGX_XPBD_DEBUG_EMPTY") && atoi(getenv("SPGX_XPBD_DEBUG_EMPTY")) != 0;
+        if (empty) {
+            xpbdEmptyKernel<<<(n + threads - 1) / threads, threads, 0, stream>>>(x);
+            return;
+        }
+        // programmatic dependent launch: the next pass is resident and has its ids, inverse masses and record in registers
+        // when this one completes (config 2: 1.45 -> 1.41 ms per frame at 32 threads; SPGX_XPBD_PDL=0 turns it off)
+        static const bool pdl = !(getenv("SPGX_XPBD_PDL") && atoi(getenv("SPGX_XPBD_PDL")) == 0);
         if (pdl && h.nPeers == 0) {
             cudaLaunchConfig_t cfg{};
             cfg.gridDim = dim3((n + threads - 1) / threads);
@@ -270,10 +307,10 @@ void launchKind(double *x, const double *invMass, const int32_t *stencils, const
             attr[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
             cfg.numAttrs = 1;
-            cudaLaunchKernelEx(&cfg, xpbdPassKernelPdl<KIND>, x, invMass, stencils, records, lambda, begin, end, dt);
+            cudaLaunchKernelEx(&cfg, xpbdPassKernelPdl<KIND>, x, invMass, stencils, records, lambda, begin, end, dt, hand);
         } else {
             xpbdPassKernel<KIND><<<(n + threads - 1) / threads, threads, 0, stream>>>(x, invMass, stencils, records, lambda,
-                                                                                     begin, end, dt, h);
+                                                                                     begin, end, dt, hand, h);
         }
     }
 }
