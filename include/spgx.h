@@ -302,6 +302,49 @@ int spgx_eval_vertex_force_hessian(spgx_group *grp, int energyId, int stencil, i
 /* constraintsAndGradient: C (nC) and gradient (3S x nC row-major) on the current device positions */
 int spgx_eval_constraints(spgx_group *grp, int energyId, int stencil, double *C, double *grad);
 
+/* ---- rigid bodies ----------------------------------------------------------------------
+ * Replaces RigidBodyGroup (spg/include/spg/sim/simObject/rigidBodyGroup.h:14-111, spg/source/sim/simObject/rigidBodyGroup.cpp)
+ * under VBD::step and XPBD::step (the RigidBodyGroup branches of vbd.cpp:63-72, :104-147 and xpbd.cpp:60-70, projectPosition
+ * with the 6 x 6 inverse-mass block, energy.h:117-153).  A body has 6 DOFs: centre of mass and an orientation kept as a
+ * rotation matrix that is composed incrementally (rigidBodyGroup.cpp:64-78), with the axis-angle vector theta re-derived from
+ * it.  Energy kinds and their addStencil parameters (modelParams, per stencil):
+ *   SPGX_RB_SPRING                 rigidBodySpringEnergy.cpp:36             {local0.xyz, local1.xyz, restLength, stiffness}
+ *   SPGX_RB_SPRING_SQUARED         rigidBodySpringSquaredEnergy.cpp:35      {local0.xyz, local1.xyz, restLength, stiffness}
+ *   SPGX_RB_SPRING_ANCHOR          rigidBodySpringAnchorEnergy.cpp:68       {local.xyz, anchor.xyz, stiffness}
+ *   SPGX_RB_ORIENTATION_ALIGNMENT  rigidBodyOrientationAlignmentEnergy.cpp:30 {stiffness}
+ */
+typedef struct spgx_rb_group spgx_rb_group;
+enum spgx_rb_kind { SPGX_RB_SPRING = 0, SPGX_RB_SPRING_SQUARED = 1, SPGX_RB_SPRING_ANCHOR = 2, SPGX_RB_ORIENTATION_ALIGNMENT = 3 };
+int spgx_rb_kind_stencil_size(int kind);
+int spgx_rb_kind_num_model_params(int kind);
+/* RigidBodyGroup::addBody for nBodies bodies (rigidBodyGroup.cpp:138-160): x, theta 3 doubles per body (theta: axis * angle),
+ * localInertia 9 doubles per body (row-major, body frame). Velocities start at zero. */
+int spgx_rb_group_create(spgx_ctx *ctx, int nBodies, const double *x, const double *theta, const double *mass,
+                         const double *localInertia, spgx_rb_group **out);
+void spgx_rb_group_destroy(spgx_rb_group *grp);
+/* RigidBodyGroup::addEnergy / removeEnergy (rigidBodyGroup.cpp:162-178); same validation messages as the energies' addStencil */
+int spgx_rb_group_add_energy(spgx_rb_group *grp, int kind, int nStencils, const int32_t *stencils, const double *modelParams,
+                             int *energyId);
+int spgx_rb_group_remove_energy(spgx_rb_group *grp, int energyId);
+/* RBSpringAnchorEnergy::updateAnchor (rigidBodySpringAnchorEnergy.h:17) */
+int spgx_rb_energy_update_anchor(spgx_rb_group *grp, int energyId, int stencil, const double *anchor3);
+/* colouring over bodies (SPGX_VBD, vbd.cpp:203-268) or over stencils per energy (SPGX_XPBD, xpbd.cpp:133-160;
+ * SPGX_XPBD_SERIAL: index order), upload. May be called again after add / remove: the state is kept. */
+int spgx_rb_group_finalize(spgx_rb_group *grp, int solverKind);
+/* nFrames x step() of the solver the group was finalized for; iterations: VBD sweeps per substep (XPBD: passes per substep,
+ * the reference runs 1). gravity: 3 doubles or NULL for (0, -9.8, 0). Blocking. */
+int spgx_rb_step(spgx_rb_group *grp, double dt, int nsubsteps, int iterations, const double *gravity, int nFrames);
+/* any pointer may be NULL. rotation: 9 doubles per body, row-major */
+int spgx_rb_download(spgx_rb_group *grp, double *x, double *theta, double *v, double *omega, double *rotation);
+/* setPositions / setVelocities (rigidBodyGroup.cpp:43-63): rotation matrices and inertias are rebuilt from theta */
+int spgx_rb_upload(spgx_rb_group *grp, const double *x, const double *theta, const double *v, const double *omega);
+int spgx_rb_reset(spgx_rb_group *grp);
+int spgx_rb_get_body_colors(spgx_rb_group *grp, int32_t *colors);
+int spgx_rb_get_stencil_colors(spgx_rb_group *grp, int energyId, int32_t *colors);
+/* per-element parity hooks: constraintsAndGradient (C: 1, grad: 6 S) and accumulateVertexForce / Hessian (6, 6 x 6) */
+int spgx_rb_eval_constraint(spgx_rb_group *grp, int energyId, int stencil, double *C, double *grad);
+int spgx_rb_eval_vertex(spgx_rb_group *grp, int energyId, int stencil, int local, double *force6, double *hess36);
+
 /* Debug aid (what Verbosity::Debug of the facade runs after every step; the reference has no counterpart, SURVEY.md
  * section 5): counts the non-finite components of the positions and velocities this rank owns, on the device.
  * out3 = [non-finite position components, non-finite velocity components, first offending vertex id or -1]. */

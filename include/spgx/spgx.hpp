@@ -208,6 +208,150 @@ inline void Energy::preparePrecomputations(const ParticleGroup &obj) const
                               reinterpret_cast<const Real *>(obj.positions0().data()), records.data()));
 }
 
+// ---- rigid bodies (rigidBodyGroup.h:14-111 and the four energies of spg/include/spg/sim/energy/rigidBody*.h) --------------
+using Matrix3 = std::array<Real, 9>;  // row-major 3 x 3
+
+class RigidBodyEnergy  // Energy<RigidBodyGroup>: host-side stencil + model-parameter lists
+{
+public:
+    virtual ~RigidBodyEnergy() = default;
+    int kind() const { return m_kind; }
+    int nStencils() const { return static_cast<int>(m_params.size()) / spgx_rb_kind_num_model_params(m_kind); }
+    int stencilSize() const { return spgx_rb_kind_stencil_size(m_kind); }
+    const std::vector<int> &flatStencils() const { return m_stencils; }
+    const std::vector<Real> &modelParams() const { return m_params; }
+    const std::string &name() const { return m_name; }
+    unsigned long long revision() const { return m_revision; }
+
+protected:
+    RigidBodyEnergy(int kind, const char *name) : m_kind(kind), m_name(name) {}
+    template <size_t S>
+    void push(const std::array<int, S> &stencil, std::initializer_list<Real> params)
+    {
+        m_stencils.insert(m_stencils.end(), stencil.begin(), stencil.end());
+        m_params.insert(m_params.end(), params.begin(), params.end());
+        ++m_revision;
+    }
+    int m_kind;
+    std::string m_name;
+    std::vector<int> m_stencils;
+    std::vector<Real> m_params;
+    unsigned long long m_revision{0};
+};
+
+class RBSpringEnergy : public RigidBodyEnergy  // rigidBodySpringEnergy.h:8-22
+{
+public:
+    static constexpr int s_stencilSize = 2;
+    RBSpringEnergy() : RigidBodyEnergy(SPGX_RB_SPRING, "RBSpringEnergy") {}
+    void addStencil(std::array<int, 2> stencil, const std::array<Vector3, 2> &localRigidBodyPoints, Real restLength, Real stiffness)
+    {
+        const auto &a = localRigidBodyPoints[0], &b = localRigidBodyPoints[1];
+        push<2>(stencil, {a.x, a.y, a.z, b.x, b.y, b.z, restLength, stiffness});
+    }
+};
+class RBSpringSquaredEnergy : public RigidBodyEnergy  // rigidBodySpringSquaredEnergy.h
+{
+public:
+    static constexpr int s_stencilSize = 2;
+    RBSpringSquaredEnergy() : RigidBodyEnergy(SPGX_RB_SPRING_SQUARED, "RBSpringSquaredEnergy") {}
+    void addStencil(std::array<int, 2> stencil, const std::array<Vector3, 2> &localRigidBodyPoints, Real restLength, Real stiffness)
+    {
+        const auto &a = localRigidBodyPoints[0], &b = localRigidBodyPoints[1];
+        push<2>(stencil, {a.x, a.y, a.z, b.x, b.y, b.z, restLength, stiffness});
+    }
+};
+class RBSpringAnchorEnergy : public RigidBodyEnergy  // rigidBodySpringAnchorEnergy.h:8-30
+{
+public:
+    static constexpr int s_stencilSize = 1;
+    RBSpringAnchorEnergy() : RigidBodyEnergy(SPGX_RB_SPRING_ANCHOR, "RBSpringAnchorEnergy") {}
+    void addStencil(std::array<int, 1> stencil, const Vector3 &localRigidBodyPoint, const Vector3 &anchor, Real stiffness)
+    {
+        push<1>(stencil, {localRigidBodyPoint.x, localRigidBodyPoint.y, localRigidBodyPoint.z, anchor.x, anchor.y, anchor.z, stiffness});
+    }
+    void updateAnchor(int i, const Vector3 &anchor)  // picked up by every solver holding this energy at its next step()
+    {
+        m_params[7 * i + 3] = anchor.x, m_params[7 * i + 4] = anchor.y, m_params[7 * i + 5] = anchor.z;
+        ++m_anchorRevision;
+    }
+    Vector3 anchor(int i) const { return {m_params[7 * i + 3], m_params[7 * i + 4], m_params[7 * i + 5]}; }
+    unsigned long long anchorRevision() const { return m_anchorRevision; }
+
+protected:
+    unsigned long long m_anchorRevision{0};
+};
+class RBOrientationAlignmentEnergy : public RigidBodyEnergy  // rigidBodyOrientationAlignmentEnergy.h
+{
+public:
+    static constexpr int s_stencilSize = 2;
+    RBOrientationAlignmentEnergy() : RigidBodyEnergy(SPGX_RB_ORIENTATION_ALIGNMENT, "RBOrientationAlignmentEnergy") {}
+    void addStencil(std::array<int, 2> stencil, Real stiffness) { push<2>(stencil, {stiffness}); }
+};
+
+class RigidBodyGroup  // rigidBodyGroup.h:14-111 (host mirror; the solver owns the device copy)
+{
+public:
+    static constexpr int s_nDOFs = 6;
+    using EnergyT = RigidBodyEnergy;
+    const std::vector<Vector3> &positions() const { return m_x; }
+    std::vector<Vector3> &positions() { return m_x; }
+    const std::vector<Vector3> &positions0() const { return m_x0; }
+    const std::vector<Vector3> &thetas() const { return m_theta; }
+    std::vector<Vector3> &thetas() { return m_theta; }
+    const std::vector<Vector3> &thetas0() const { return m_theta0; }
+    std::vector<Vector3> &velocities() { return m_v; }
+    const std::vector<Vector3> &velocities() const { return m_v; }
+    std::vector<Vector3> &omegas() { return m_omega; }
+    const std::vector<Vector3> &omegas() const { return m_omega; }
+    const std::vector<Real> &masses() const { return m_m; }
+    const std::vector<Real> &invMasses() const { return m_w; }
+    const std::vector<Matrix3> &localInertias() const { return m_localInertia; }
+    // refreshed from the device together with the positions (the reference keeps them in step on the host)
+    const std::vector<Matrix3> &rotationMatrices() const { return m_rotationMatrix; }
+    std::vector<Matrix3> &rotationMatrices() { return m_rotationMatrix; }
+    const std::vector<Vector3> &initialPositions() const { return m_xInitial; }
+    const std::vector<Vector3> &initialThetas() const { return m_thetaInitial; }
+    std::vector<std::shared_ptr<EnergyT>> &energies() { return m_energies; }
+    const std::vector<std::shared_ptr<EnergyT>> &energies() const { return m_energies; }
+    int nDOF() const { return static_cast<int>(m_x.size()) * 6; }
+    int size() const { return static_cast<int>(m_x.size()); }
+    // addBody (rigidBodyGroup.cpp:138-160); the visual mesh of the reference's signature is a rendering concern and not kept
+    void addBody(const Vector3 &p, const Vector3 &p0, Real mass, const Vector3 &theta, const Vector3 &theta0, const Matrix3 &localInertia)
+    {
+        m_x.push_back(p), m_xInitial.push_back(p), m_x0.push_back(p0);
+        m_v.emplace_back(0, 0, 0), m_omega.emplace_back(0, 0, 0);
+        m_m.push_back(mass), m_w.push_back(mass == 0 ? 0 : 1 / mass);
+        m_theta.push_back(theta), m_thetaInitial.push_back(theta), m_theta0.push_back(theta0);
+        m_localInertia.push_back(localInertia);
+        m_rotationMatrix.push_back(Matrix3{1, 0, 0, 0, 1, 0, 0, 0, 1});  // replaced by the solver's matrices at the first sync
+    }
+    void addEnergy(std::shared_ptr<EnergyT> energy) { m_energies.push_back(std::move(energy)); }
+    void removeEnergy(const std::shared_ptr<EnergyT> &energy)  // rigidBodyGroup.cpp:167-178
+    {
+        for (auto it = m_energies.begin(); it != m_energies.end(); ++it)
+            if (*it == energy) {
+                m_energies.erase(it);
+                return;
+            }
+    }
+    void setName(std::string name) { m_name = std::move(name); }
+    void reset()  // rigidBodyGroup.cpp:180-192
+    {
+        m_x = m_xInitial;
+        m_theta = m_thetaInitial;
+        for (auto &v : m_v) v = Vector3(0, 0, 0);
+        for (auto &w : m_omega) w = Vector3(0, 0, 0);
+    }
+
+protected:
+    std::string m_name;
+    std::vector<Vector3> m_x, m_xInitial, m_x0, m_v, m_theta, m_thetaInitial, m_theta0, m_omega;
+    std::vector<Matrix3> m_rotationMatrix, m_localInertia;
+    std::vector<Real> m_m, m_w;
+    std::vector<std::shared_ptr<EnergyT>> m_energies;
+};
+
 namespace solver
 {
 // BaseSolver (baseSolver.h:14-41) over device-resident copies of the particle groups
@@ -218,6 +362,7 @@ public:
     virtual ~BaseSolver()
     {
         for (auto &s : m_slots) spgx_group_destroy(s.handle);
+        for (auto &s : m_rbSlots) spgx_rb_group_destroy(s.handle);
         spgx_ctx_destroy(m_ctx);
     }
     BaseSolver(const BaseSolver &) = delete;
@@ -229,6 +374,22 @@ public:
         m_groups.push_back(object);
         m_slots.emplace_back();
         m_slots.back().hostDirty = false;
+    }
+    void addObject(const RigidBodyGroup &object)  // baseSolver.cpp:35
+    {
+        m_rbGroups.push_back(object);
+        m_rbSlots.emplace_back();
+    }
+    std::vector<RigidBodyGroup> &rbGroups()  // baseSolver.h:23
+    {
+        syncToHost();
+        for (auto &s : m_rbSlots) s.hostDirty = true;
+        return m_rbGroups;
+    }
+    const std::vector<RigidBodyGroup> &rbGroups() const
+    {
+        const_cast<BaseSolver *>(this)->syncToHost();
+        return m_rbGroups;
     }
     // host mirrors; the non-const accessor marks them for upload before the next step
     std::vector<ParticleGroup> &particleGroups()
@@ -242,7 +403,7 @@ public:
         const_cast<BaseSolver *>(this)->syncToHost();
         return m_groups;
     }
-    int numSimObjects() { return static_cast<int>(m_groups.size()); }
+    int numSimObjects() { return static_cast<int>(m_groups.size() + m_rbGroups.size()); }
     void setDt(Real dt) { m_dtStep = dt; }
     Real dt() { return m_dtStep; }
     void setNumSubsteps(int n) { m_nsubsteps = n; }
@@ -253,6 +414,10 @@ public:
         for (size_t i = 0; i < m_groups.size(); ++i) {
             m_groups[i].reset();
             m_slots[i].hostDirty = true;
+        }
+        for (size_t i = 0; i < m_rbGroups.size(); ++i) {
+            m_rbGroups[i].reset();
+            m_rbSlots[i].hostDirty = true;
         }
         m_time = 0;
     }
@@ -277,6 +442,69 @@ protected:
     };
     virtual int solverKind() const = 0;
     virtual int stepGroup(spgx_group *g, const Real *gravity) = 0;
+    // rigid bodies run under VBD and XPBD (the implicit-Euler family's rigid-body branches are not built)
+    virtual int rbIterations() const { return 1; }
+    struct RbSlot {
+        spgx_rb_group *handle{nullptr};
+        bool built{false}, hostDirty{false}, deviceDirty{false};
+        std::vector<unsigned long long> revisions, anchorRevisions;
+        std::vector<const RigidBodyEnergy *> identities;
+    };
+    void buildRb(size_t i)
+    {
+        RigidBodyGroup &g = m_rbGroups[i];
+        RbSlot &s = m_rbSlots[i];
+        if (s.handle) {
+            syncToHost();
+            spgx_rb_group_destroy(s.handle);
+            s.handle = nullptr;
+        }
+        check(spgx_rb_group_create(m_ctx, g.size(), reinterpret_cast<const Real *>(g.initialPositions().data()),
+                                   reinterpret_cast<const Real *>(g.initialThetas().data()), g.masses().data(),
+                                   reinterpret_cast<const Real *>(g.localInertias().data()), &s.handle));
+        s.identities.clear(), s.revisions.clear(), s.anchorRevisions.clear();
+        for (auto &e : g.energies()) {
+            check(spgx_rb_group_add_energy(s.handle, e->kind(), e->nStencils(), e->flatStencils().data(), e->modelParams().data(), nullptr));
+            s.identities.push_back(e.get());
+            s.revisions.push_back(e->revision());
+            auto *a = dynamic_cast<RBSpringAnchorEnergy *>(e.get());
+            s.anchorRevisions.push_back(a ? a->anchorRevision() : 0);
+        }
+        check(spgx_rb_group_finalize(s.handle, solverKind()));
+        check(spgx_rb_upload(s.handle, reinterpret_cast<const Real *>(g.positions().data()), reinterpret_cast<const Real *>(g.thetas().data()),
+                             reinterpret_cast<const Real *>(g.velocities().data()), reinterpret_cast<const Real *>(g.omegas().data())));
+        s.built = true;
+        s.hostDirty = s.deviceDirty = false;
+    }
+    void stepRbGroups(const Real *gravity)
+    {
+        for (size_t i = 0; i < m_rbGroups.size(); ++i) {
+            RigidBodyGroup &g = m_rbGroups[i];
+            RbSlot &s = m_rbSlots[i];
+            bool changed = g.energies().size() != s.identities.size();
+            for (size_t e = 0; e < g.energies().size() && !changed; ++e)
+                changed = g.energies()[e].get() != s.identities[e] || g.energies()[e]->revision() != s.revisions[e];
+            if (!s.built || m_precomputationUpdateRequired || changed) buildRb(i);
+            if (s.hostDirty) {
+                check(spgx_rb_upload(s.handle, reinterpret_cast<const Real *>(g.positions().data()),
+                                     reinterpret_cast<const Real *>(g.thetas().data()), reinterpret_cast<const Real *>(g.velocities().data()),
+                                     reinterpret_cast<const Real *>(g.omegas().data())));
+                s.hostDirty = false;
+            }
+            for (size_t e = 0; e < g.energies().size(); ++e)
+                if (auto *a = dynamic_cast<RBSpringAnchorEnergy *>(g.energies()[e].get())) {
+                    if (a->anchorRevision() == s.anchorRevisions[e]) continue;
+                    for (int st = 0; st < a->nStencils(); ++st) {
+                        const Vector3 p = a->anchor(st);
+                        const Real v[3] = {p.x, p.y, p.z};
+                        check(spgx_rb_energy_update_anchor(s.handle, static_cast<int>(e), st, v));
+                    }
+                    s.anchorRevisions[e] = a->anchorRevision();
+                }
+            check(spgx_rb_step(s.handle, m_dtStep, m_nsubsteps, rbIterations(), gravity, 1));
+            s.deviceDirty = true;
+        }
+    }
 
     bool topologyChanged(const ParticleGroup &g, const Slot &s) const
     {
@@ -348,11 +576,22 @@ protected:
                                              std::to_string(bad[1]) + " velocity components, first at vertex " + std::to_string(bad[2]));
             }
         }
+        stepRbGroups(g);
         m_precomputationUpdateRequired = false;
         m_time += m_dtStep;
     }
     void syncToHost()
     {
+        for (size_t i = 0; i < m_rbGroups.size(); ++i) {
+            RbSlot &s = m_rbSlots[i];
+            if (s.handle && s.deviceDirty) {
+                RigidBodyGroup &g = m_rbGroups[i];
+                check(spgx_rb_download(s.handle, reinterpret_cast<Real *>(g.positions().data()), reinterpret_cast<Real *>(g.thetas().data()),
+                                       reinterpret_cast<Real *>(g.velocities().data()), reinterpret_cast<Real *>(g.omegas().data()),
+                                       reinterpret_cast<Real *>(g.rotationMatrices().data())));
+                s.deviceDirty = false;
+            }
+        }
         for (size_t i = 0; i < m_groups.size(); ++i) {
             Slot &s = m_slots[i];
             if (s.handle && s.deviceDirty) {
@@ -366,6 +605,8 @@ protected:
     spgx_ctx *m_ctx{nullptr};
     std::vector<ParticleGroup> m_groups;
     std::vector<Slot> m_slots;
+    std::vector<RigidBodyGroup> m_rbGroups;
+    std::vector<RbSlot> m_rbSlots;
     Vector3 m_gravity{0, -9.8, 0};
     Real m_time{0};
     Real m_dtStep{0.01};
@@ -387,6 +628,7 @@ public:
 
 protected:
     int solverKind() const override { return SPGX_VBD; }
+    int rbIterations() const override { return m_iterations; }
     int stepGroup(spgx_group *g, const Real *gravity) override
     {
         return spgx_vbd_step(g, m_dtStep, m_nsubsteps, m_iterations, gravity, 1, 1);

@@ -31,6 +31,10 @@
 #include <spg/sim/energy/springSquaredContinuumEnergy.h>
 #include <spg/sim/energy/stableSquaredNeoHookeanEnergy.h>
 #include <spg/sim/energy/staticLoadEnergy.h>
+#include <spg/sim/energy/rigidBodySpringEnergy.h>
+#include <spg/sim/energy/rigidBodySpringSquaredEnergy.h>
+#include <spg/sim/energy/rigidBodySpringAnchorEnergy.h>
+#include <spg/sim/energy/rigidBodyOrientationAlignmentEnergy.h>
 #include <spg/sim/solver/vbd.h>
 #include <spg/sim/solver/xpbd.h>
 #include <spg/sim/solver/implicitEulerBaraffWitkin.h>
@@ -1145,4 +1149,200 @@ void *ref_scene_beam(int nX, int nY, int nZ, int tetKind)
     return s;
 }
 
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------
+// Rigid bodies: the reference's RigidBodyGroup and its four energies under the reference's own
+// VBD / XPBD.  Kind numbering = enum spgx_rb_kind of include/spgx.h.
+// ---------------------------------------------------------------------------------------------
+namespace
+{
+struct RefRbGroup {
+    spg::RigidBodyGroup rb;
+    std::vector<std::shared_ptr<spg::RigidBodyGroup::EnergyT>> energies;
+};
+struct RefRbSolver {
+    std::unique_ptr<OracleVBD> vbd;
+    std::unique_ptr<OracleXPBD> xpbd;
+    spg::solver::BaseSolver *base() { return vbd ? static_cast<spg::solver::BaseSolver *>(vbd.get()) : xpbd.get(); }
+};
+spg::Vector3 v3(const double *p) { return spg::Vector3(p[0], p[1], p[2]); }
+}  // namespace
+
+extern "C" {
+void *ref_rb_group_create(int n, const double *x, const double *theta, const double *mass, const double *localInertia)
+{
+    auto *g = new RefRbGroup;
+    // a visual mesh is carried per body (rigidBodyGroup.h:99) and never read by the solvers: one triangle
+    const std::vector<spg::Vector3> verts{{0, 0, 0}, {1, 0, 0}, {0, 1, 0}};
+    const spg::TriangleMesh mesh(verts, verts, {spg::Int3{0, 1, 2}});
+    for (int i = 0; i < n; ++i) {
+        spg::Matrix3 I;
+        for (int r = 0; r < 3; ++r)
+            for (int c = 0; c < 3; ++c) I(r, c) = localInertia[9 * i + 3 * r + c];
+        g->rb.addBody(v3(x + 3 * i), v3(x + 3 * i), mass[i], v3(theta + 3 * i), v3(theta + 3 * i), I, mesh);
+    }
+    return g;
+}
+void ref_rb_group_destroy(void *h) { delete static_cast<RefRbGroup *>(h); }
+
+int ref_rb_group_add_energy(void *h, int kind, int n, const int32_t *st, const double *p)
+{
+    return guarded([&] {
+        auto *g = static_cast<RefRbGroup *>(h);
+        std::shared_ptr<spg::RigidBodyGroup::EnergyT> out;
+        if (kind == 0) {
+            auto e = std::make_shared<spg::RBSpringEnergy>();
+            for (int i = 0; i < n; ++i)
+                e->addStencil({st[2 * i], st[2 * i + 1]}, {v3(p + 8 * i), v3(p + 8 * i + 3)}, p[8 * i + 6], p[8 * i + 7]);
+            out = e;
+        } else if (kind == 1) {
+            auto e = std::make_shared<spg::RBSpringSquaredEnergy>();
+            for (int i = 0; i < n; ++i)
+                e->addStencil({st[2 * i], st[2 * i + 1]}, {v3(p + 8 * i), v3(p + 8 * i + 3)}, p[8 * i + 6], p[8 * i + 7]);
+            out = e;
+        } else if (kind == 2) {
+            auto e = std::make_shared<spg::RBSpringAnchorEnergy>();
+            for (int i = 0; i < n; ++i) e->addStencil({st[i]}, v3(p + 7 * i), v3(p + 7 * i + 3), p[7 * i + 6]);
+            out = e;
+        } else if (kind == 3) {
+            auto e = std::make_shared<spg::RBOrientationAlignmentEnergy>();
+            for (int i = 0; i < n; ++i) e->addStencil({st[2 * i], st[2 * i + 1]}, p[i]);
+            out = e;
+        } else {
+            throw std::runtime_error("unknown rigid-body energy kind");
+        }
+        g->rb.addEnergy(out);
+        g->energies.push_back(out);
+    });
+}
+
+// state of a group (before it is handed to a solver) or of the solver's own copy
+static void rbGetState(const spg::RigidBodyGroup &rb, double *x, double *theta, double *v, double *omega, double *R)
+{
+    for (int i = 0; i < rb.size(); ++i)
+        for (int c = 0; c < 3; ++c) {
+            if (x) x[3 * i + c] = rb.positions()[i][c];
+            if (theta) theta[3 * i + c] = rb.thetas()[i][c];
+            if (v) v[3 * i + c] = rb.velocities()[i][c];
+            if (omega) omega[3 * i + c] = rb.omegas()[i][c];
+            if (R)
+                for (int d = 0; d < 3; ++d) R[9 * i + 3 * c + d] = rb.rotationMatrices()[i](c, d);
+        }
+}
+static void rbSetState(spg::RigidBodyGroup &rb, const double *x, const double *theta, const double *v, const double *omega)
+{
+    const int n = rb.size();
+    spg::VectorX pos(6 * n), vel(6 * n);
+    rb.getPositions(pos, 0);
+    rb.getVelocities(vel, 0);
+    for (int i = 0; i < n; ++i)
+        for (int c = 0; c < 3; ++c) {
+            if (x) pos[6 * i + c] = x[3 * i + c];
+            if (theta) pos[6 * i + 3 + c] = theta[3 * i + c];
+            if (v) vel[6 * i + c] = v[3 * i + c];
+            if (omega) vel[6 * i + 3 + c] = omega[3 * i + c];
+        }
+    rb.setPositions(pos, 0);  // rebuilds rotation matrices and inertias (rigidBodyGroup.cpp:43-53)
+    rb.setVelocities(vel, 0);
+}
+void ref_rb_group_get_state(void *h, double *x, double *theta, double *v, double *omega, double *R)
+{
+    rbGetState(static_cast<RefRbGroup *>(h)->rb, x, theta, v, omega, R);
+}
+void ref_rb_group_set_state(void *h, const double *x, const double *theta, const double *v, const double *omega)
+{
+    rbSetState(static_cast<RefRbGroup *>(h)->rb, x, theta, v, omega);
+}
+
+// constraintsAndGradient (C: 1, grad: 6 S) through the public virtual
+extern "C++" template <class E>
+bool tryRbConstraints(spg::RigidBodyGroup::EnergyT *en, spg::RigidBodyGroup &rb, int stencil, double *C, double *grad)
+{
+    auto *p = dynamic_cast<E *>(en);
+    if (!p) return false;
+    auto [c, gr] = p->constraintsAndGradient(stencil, rb);
+    C[0] = c[0];
+    for (int i = 0; i < gr.rows(); ++i) grad[i] = gr(i, 0);
+    return true;
+}
+int ref_rb_constraint(void *h, int e, int stencil, double *C, double *grad)
+{
+    return guarded([&] {
+        auto *g = static_cast<RefRbGroup *>(h);
+        auto *en = g->energies.at(e).get();
+        const bool ok = tryRbConstraints<spg::RBSpringEnergy>(en, g->rb, stencil, C, grad) ||
+                        tryRbConstraints<spg::RBSpringSquaredEnergy>(en, g->rb, stencil, C, grad) ||
+                        tryRbConstraints<spg::RBSpringAnchorEnergy>(en, g->rb, stencil, C, grad) ||
+                        tryRbConstraints<spg::RBOrientationAlignmentEnergy>(en, g->rb, stencil, C, grad);
+        if (!ok) throw std::runtime_error("unsupported energy type");
+    });
+}
+// what VBD accumulates per incidence (vbd.cpp:135-136): force (6) and the 6 x 6 diagonal block, row-major
+int ref_rb_vertex_force_hessian(void *h, int e, int stencil, int local, double *force6, double *hess36)
+{
+    return guarded([&] {
+        auto *g = static_cast<RefRbGroup *>(h);
+        auto &en = g->energies.at(e);
+        spg::Vector<6> f = spg::Vector<6>::Zero();
+        spg::Matrix<6, 6> H = spg::Matrix<6, 6>::Zero();
+        en->accumulateVertexForce(stencil, local, g->rb, f);
+        en->accumulateVertexHessian(stencil, local, g->rb, H);
+        for (int i = 0; i < 6; ++i) {
+            force6[i] = f[i];
+            for (int j = 0; j < 6; ++j) hess36[6 * i + j] = H(i, j);
+        }
+    });
+}
+
+// kind: 0 VBD, 1 XPBD (parallel Gauss-Seidel), 2 XPBD (serial)
+void *ref_rb_solver_create(int kind, void *group, double dt, int substeps, int iterations, const double *gravity)
+{
+    auto *s = new RefRbSolver;
+    auto *g = static_cast<RefRbGroup *>(group);
+    if (kind == 0) {
+        s->vbd = std::make_unique<OracleVBD>();
+        s->vbd->setIterations(iterations);
+    } else {
+        s->xpbd = std::make_unique<OracleXPBD>(kind == 1);
+    }
+    s->base()->addObject(g->rb);
+    s->base()->setDt(dt);
+    s->base()->setNumSubsteps(substeps);
+    if (gravity) s->base()->setGravity(spg::Vector3(gravity[0], gravity[1], gravity[2]));
+    return s;
+}
+void ref_rb_solver_destroy(void *h) { delete static_cast<RefRbSolver *>(h); }
+int ref_rb_solver_step(void *h, int nFrames)
+{
+    return guarded([&] {
+        auto *s = static_cast<RefRbSolver *>(h);
+        std::ostringstream sink;  // VBD::computeParallelVertexGroups prints unconditionally (vbd.cpp:228)
+        auto *old = std::cout.rdbuf(sink.rdbuf());
+        try {
+            for (int f = 0; f < nFrames; ++f) s->base()->step();
+        } catch (...) {
+            std::cout.rdbuf(old);
+            throw;
+        }
+        std::cout.rdbuf(old);
+    });
+}
+void ref_rb_solver_get_state(void *h, double *x, double *theta, double *v, double *omega, double *R)
+{
+    rbGetState(static_cast<RefRbSolver *>(h)->base()->rbGroups()[0], x, theta, v, omega, R);
+}
+void ref_rb_solver_set_state(void *h, const double *x, const double *theta, const double *v, const double *omega)
+{
+    rbSetState(static_cast<RefRbSolver *>(h)->base()->rbGroups()[0], x, theta, v, omega);
+}
+int ref_rb_solver_update_anchor(void *h, void *group, int e, int stencil, const double *anchor3)
+{
+    return guarded([&] {
+        (void)h;  // energies are shared between the group and the solver's copy (rigidBodyGroup.h: shared_ptr)
+        auto *a = dynamic_cast<spg::RBSpringAnchorEnergy *>(static_cast<RefRbGroup *>(group)->energies.at(e).get());
+        if (!a) throw std::runtime_error("not an anchor energy");
+        a->updateAnchor(stencil, v3(anchor3));
+    });
+}
 }  // extern "C"

@@ -102,6 +102,23 @@ SIGNATURES = {
     "spgx_system_stiffness": (C.c_int, [C.c_void_p, _lp, _ip, _ip, _dp]),
     "spgx_element_hessian": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp]),
     "spgx_linear_solve": (C.c_int, [C.c_void_p, C.c_double, C.c_double, _dp, _dp, C.c_double, C.c_int, C.POINTER(C.c_int)]),
+    # rigid bodies
+    "spgx_rb_kind_stencil_size": (C.c_int, [C.c_int]),
+    "spgx_rb_kind_num_model_params": (C.c_int, [C.c_int]),
+    "spgx_rb_group_create": (C.c_int, [C.c_void_p, C.c_int, _dp, _dp, _dp, _dp, C.POINTER(C.c_void_p)]),
+    "spgx_rb_group_destroy": (None, [C.c_void_p]),
+    "spgx_rb_group_add_energy": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _ip, _dp, C.POINTER(C.c_int)]),
+    "spgx_rb_group_remove_energy": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_rb_energy_update_anchor": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp]),
+    "spgx_rb_group_finalize": (C.c_int, [C.c_void_p, C.c_int]),
+    "spgx_rb_step": (C.c_int, [C.c_void_p, C.c_double, C.c_int, C.c_int, _dp, C.c_int]),
+    "spgx_rb_download": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp, _dp]),
+    "spgx_rb_upload": (C.c_int, [C.c_void_p, _dp, _dp, _dp, _dp]),
+    "spgx_rb_reset": (C.c_int, [C.c_void_p]),
+    "spgx_rb_get_body_colors": (C.c_int, [C.c_void_p, _ip]),
+    "spgx_rb_get_stencil_colors": (C.c_int, [C.c_void_p, C.c_int, _ip]),
+    "spgx_rb_eval_constraint": (C.c_int, [C.c_void_p, C.c_int, C.c_int, _dp, _dp]),
+    "spgx_rb_eval_vertex": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]),
 }
 for _name, (_res, _args) in SIGNATURES.items():
     _fn = getattr(lib, _name)
@@ -522,6 +539,97 @@ class Group:
     def close(self):
         if self.handle:
             lib.spgx_group_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+SPGX_RB_SPRING, SPGX_RB_SPRING_SQUARED, SPGX_RB_SPRING_ANCHOR, SPGX_RB_ORIENTATION_ALIGNMENT = 0, 1, 2, 3
+
+
+class RbGroup:
+    """A solver's device-resident copy of one RigidBodyGroup (rigidBodyGroup.h:14-111) under VBD or XPBD."""
+
+    def __init__(self, ctx: Context, x, theta, mass, local_inertia):
+        self.ctx = ctx
+        x, theta, mass, inertia = _f64(x), _f64(theta), _f64(mass), _f64(local_inertia)
+        self.n = int(mass.shape[0])
+        self.handle = C.c_void_p()
+        self.kinds = []
+        check(lib.spgx_rb_group_create(ctx.handle, self.n, _d(x), _d(theta), _d(mass), _d(inertia), C.byref(self.handle)))
+
+    @classmethod
+    def from_scene(cls, ctx: Context, scene: "_scenes.RbScene") -> "RbGroup":
+        g = cls(ctx, scene.x, scene.theta, scene.mass, scene.local_inertia)
+        for e in scene.energies:
+            g.add_energy(e.kind, e.stencils, e.params)
+        return g
+
+    def add_energy(self, kind: int, stencils, params) -> int:
+        s, p = _i32(stencils), _f64(params)
+        eid = C.c_int(-1)
+        n = s.size // max(lib.spgx_rb_kind_stencil_size(kind), 1)
+        check(lib.spgx_rb_group_add_energy(self.handle, kind, n, _i(s), _d(p), C.byref(eid)))
+        self.kinds.append(kind)
+        return eid.value
+
+    def remove_energy(self, eid: int):
+        check(lib.spgx_rb_group_remove_energy(self.handle, eid))
+        del self.kinds[eid]
+
+    def update_anchor(self, eid: int, stencil: int, anchor):
+        a = _f64(anchor)
+        check(lib.spgx_rb_energy_update_anchor(self.handle, eid, stencil, _d(a)))
+
+    def finalize(self, solver_kind: int):
+        check(lib.spgx_rb_group_finalize(self.handle, solver_kind))
+
+    def step(self, dt, substeps, iterations=1, gravity=(0.0, -9.8, 0.0), frames=1):
+        g = _f64(gravity)
+        check(lib.spgx_rb_step(self.handle, dt, substeps, iterations, _d(g), frames))
+
+    def download(self):
+        """x, theta, v, omega [n, 3] and the rotation matrices [n, 3, 3]"""
+        x, th, v, om = (np.empty((self.n, 3)) for _ in range(4))
+        R = np.empty((self.n, 3, 3))
+        check(lib.spgx_rb_download(self.handle, _d(x), _d(th), _d(v), _d(om), _d(R)))
+        return x, th, v, om, R
+
+    def upload(self, x=None, theta=None, v=None, omega=None):
+        a = [None if t is None else _f64(t) for t in (x, theta, v, omega)]
+        check(lib.spgx_rb_upload(self.handle, *[None if t is None else _d(t) for t in a]))
+
+    def reset(self):
+        check(lib.spgx_rb_reset(self.handle))
+
+    def body_colors(self) -> np.ndarray:
+        c = np.empty(self.n, np.int32)
+        check(lib.spgx_rb_get_body_colors(self.handle, _i(c)))
+        return c
+
+    def stencil_colors(self, eid: int, n: int) -> np.ndarray:
+        c = np.empty(n, np.int32)
+        check(lib.spgx_rb_get_stencil_colors(self.handle, eid, _i(c)))
+        return c
+
+    def eval_constraint(self, eid: int, stencil: int):
+        k = 6 * lib.spgx_rb_kind_stencil_size(self.kinds[eid])
+        c, g = C.c_double(0), np.empty(k)
+        check(lib.spgx_rb_eval_constraint(self.handle, eid, stencil, C.byref(c), _d(g)))
+        return c.value, g
+
+    def eval_vertex(self, eid: int, stencil: int, local: int):
+        f, h = np.empty(6), np.empty((6, 6))
+        check(lib.spgx_rb_eval_vertex(self.handle, eid, stencil, local, _d(f), _d(h)))
+        return f, h
+
+    def close(self):
+        if self.handle:
+            lib.spgx_rb_group_destroy(self.handle)
             self.handle = C.c_void_p()
 
     def __del__(self):

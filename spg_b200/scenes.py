@@ -213,3 +213,80 @@ def tet_beam(nx: int, ny: int, nz: int, kind: int = K_TET_SNH) -> Scene:
     young, poisson = float(np.float32(1e3)), float(np.float32(0.2))
     scene.energies.append(SceneEnergy(kind, tets, np.tile(np.array([young, poisson]), (tets.shape[0], 1))))
     return scene
+
+
+# ---- rigid-body scenes (apps/solverCompare.cpp:524-660): width = height = depth = mass = 1 (floats, :699) -------------------
+RB_SPRING, RB_SPRING_SQUARED, RB_SPRING_ANCHOR, RB_ORIENTATION_ALIGNMENT = 0, 1, 2, 3
+
+
+@dataclass
+class RbScene:
+    x: np.ndarray              # [n, 3] centres of mass
+    theta: np.ndarray          # [n, 3] axis * angle
+    mass: np.ndarray           # [n]
+    local_inertia: np.ndarray  # [n, 3, 3] body frame
+    energies: list = field(default_factory=list)
+    name: str = ""
+
+    @property
+    def n_bodies(self) -> int:
+        return int(self.mass.shape[0])
+
+
+def _box_inertia(mass, width, height, depth):
+    f32 = np.float32
+    w, h, d = f32(width), f32(height), f32(depth)
+    # 1.0 / 12.0 * mass * (height * height + depth * depth): the sums of squares are float arithmetic (solverCompare.cpp:541-543)
+    I = np.zeros((3, 3))
+    I[0, 0] = 1.0 / 12.0 * mass * float(h * h + d * d)
+    I[1, 1] = 1.0 / 12.0 * mass * float(w * w + d * d)
+    I[2, 2] = 1.0 / 12.0 * mass * float(w * w + h * h)
+    return I
+
+
+def rb_anchored(mass=1.0, width=1.0, height=1.0, depth=1.0) -> RbScene:
+    """createAnchoredRigidBody (solverCompare.cpp:524-555): one box held by three anchor springs"""
+    w, h = float(np.float32(width)), float(np.float32(height))
+    sc = RbScene(np.zeros((1, 3)), np.zeros((1, 3)), np.array([mass]), _box_inertia(mass, width, height, depth)[None], name="anchored rigid body")
+    params = np.array([[0, h * 0.5, 0, 0, h * 0.5, -1, 100], [w * 0.5, -h * 0.5, 0, w, -h * 0.5, 1, 100],
+                       [-w * 0.5, -h * 0.5, 0, -w, -h * 0.5, 1, 100]], dtype=np.float64)
+    sc.energies.append(SceneEnergy(RB_SPRING_ANCHOR, np.zeros((3, 1), np.int32), params))
+    return sc
+
+
+def rb_articulated(n_bodies: int, mass=1.0, width=1.0, height=1.0, depth=1.0) -> RbScene:
+    """createArticulatedRigidBody (solverCompare.cpp:557-603): a row of boxes joined by squared springs of rest length 0
+    and orientation alignment, the first one pinned by three stiff anchors"""
+    w, h = float(np.float32(width)), float(np.float32(height))
+    x = np.zeros((n_bodies, 3))
+    x[:, 0] = w * np.arange(n_bodies)
+    I = np.repeat(_box_inertia(mass, width, height, depth)[None], n_bodies, 0)
+    sc = RbScene(x, np.zeros((n_bodies, 3)), np.full(n_bodies, mass), I, name="articulated rigid body")
+    anchors = np.array([[0, h * 0.5, 0, 0, h * 0.5, 0, 1e10], [0, -h * 0.5, 0, 0, -h * 0.5, 0, 1e10],
+                        [-w * 0.5, 0, 0, -w * 0.5, 0, 0, 1e10]], dtype=np.float64)
+    sc.energies.append(SceneEnergy(RB_SPRING_ANCHOR, np.zeros((3, 1), np.int32), anchors))
+    if n_bodies > 1:
+        st = np.stack([np.arange(n_bodies - 1), np.arange(1, n_bodies)], 1).astype(np.int32)
+        sp = np.tile(np.array([w * 0.5, 0, 0, -w * 0.5, 0, 0, 0, 1e10]), (n_bodies - 1, 1))
+        sc.energies.append(SceneEnergy(RB_SPRING_SQUARED, st, sp))
+        sc.energies.append(SceneEnergy(RB_ORIENTATION_ALIGNMENT, st.copy(), np.full((n_bodies - 1, 1), 1e5)))
+    return sc
+
+
+def rb_chain(n_bodies: int, mass=1.0, width=1.0, height=1.0, depth=1.0) -> RbScene:
+    """createRigidBodyChain (solverCompare.cpp:605-660): boxes along a diagonal joined corner to corner by springs of rest
+    length sqrt(2 width) (a FLOAT square root, :654), the first one hung from an anchor"""
+    w, h = float(np.float32(width)), float(np.float32(height))
+    x = np.zeros((n_bodies, 3))
+    step = float(np.float32(height) + np.float32(1))  # -(height + 1) * i: float arithmetic
+    x[:, 0] = -step * np.arange(n_bodies)
+    x[:, 2] = -step * np.arange(n_bodies)
+    I = np.repeat(_box_inertia(mass, width, height, depth)[None], n_bodies, 0)
+    sc = RbScene(x, np.zeros((n_bodies, 3)), np.full(n_bodies, mass), I, name="rigid body chain")
+    sc.energies.append(SceneEnergy(RB_SPRING_ANCHOR, np.zeros((1, 1), np.int32), np.array([[w * 0.5, h * 0.5, 0, w * 0.5, h * 0.5, 0, 100.0]])))
+    if n_bodies > 1:
+        st = np.stack([np.arange(n_bodies - 1), np.arange(1, n_bodies)], 1).astype(np.int32)
+        rest = float(np.sqrt(np.float32(width) * np.float32(2)))
+        sp = np.tile(np.array([-w * 0.5, -h * 0.5, 0, w * 0.5, h * 0.5, 0, rest, 100.0]), (n_bodies - 1, 1))
+        sc.energies.append(SceneEnergy(RB_SPRING, st, sp))
+    return sc

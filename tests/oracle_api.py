@@ -86,6 +86,22 @@ class Oracle:
         L.ref_vbd_inject_colors.argtypes = [C.c_void_p, _ip, C.c_int]
         L.ref_xpbd_stencil_colors.argtypes = [C.c_void_p, C.c_int, _ip, C.POINTER(C.c_int)]
         L.ref_xpbd_inject_colors.argtypes = [C.c_void_p, C.c_int, _ip, C.c_int]
+        if hasattr(L, "ref_rb_group_create"):  # the compiled reference only: rigid bodies
+            L.ref_rb_group_create.restype = C.c_void_p
+            L.ref_rb_group_create.argtypes = [C.c_int, _dp, _dp, _dp, _dp]
+            L.ref_rb_group_destroy.argtypes = [C.c_void_p]
+            L.ref_rb_group_add_energy.argtypes = [C.c_void_p, C.c_int, C.c_int, _ip, _dp]
+            L.ref_rb_group_get_state.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp]
+            L.ref_rb_group_set_state.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp]
+            L.ref_rb_constraint.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp]
+            L.ref_rb_vertex_force_hessian.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]
+            L.ref_rb_solver_create.restype = C.c_void_p
+            L.ref_rb_solver_create.argtypes = [C.c_int, C.c_void_p, C.c_double, C.c_int, C.c_int, _dp]
+            L.ref_rb_solver_destroy.argtypes = [C.c_void_p]
+            L.ref_rb_solver_step.argtypes = [C.c_void_p, C.c_int]
+            L.ref_rb_solver_get_state.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, _dp]
+            L.ref_rb_solver_set_state.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp]
+            L.ref_rb_solver_update_anchor.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, _dp]
         L.ref_omp_max_threads.restype = C.c_int
         # implicit-Euler family probes (both oracles export them)
         L.ref_solver_cg_iterations.argtypes = [C.c_void_p, _ip, C.c_int, C.POINTER(C.c_int)]
@@ -359,6 +375,92 @@ class OracleSolver:
 
 
 _cache: dict = {}
+
+
+class OracleRbGroup:
+    """the reference's RigidBodyGroup with its energies (compiled reference only)"""
+    STENCIL = [2, 2, 1, 2]
+
+    def __init__(self, oracle: Oracle, scene):
+        if not hasattr(oracle.lib, "ref_rb_group_create"):
+            raise OracleError("this oracle has no rigid bodies (the CPU restatement covers particle groups only)")
+        self.o = oracle
+        self.n = scene.n_bodies
+        x, th, m, I = _f64(scene.x), _f64(scene.theta), _f64(scene.mass), _f64(scene.local_inertia)
+        self.h = C.c_void_p(oracle.lib.ref_rb_group_create(self.n, _d(x), _d(th), _d(m), _d(I)))
+        self.kinds = []
+        for e in scene.energies:
+            st, p = _i32(e.stencils), _f64(e.params)
+            oracle.check(oracle.lib.ref_rb_group_add_energy(self.h, e.kind, st.shape[0], _i(st), _d(p)))
+            self.kinds.append(e.kind)
+
+    def state(self):
+        x, th, v, om = (np.empty((self.n, 3)) for _ in range(4))
+        R = np.empty((self.n, 3, 3))
+        self.o.lib.ref_rb_group_get_state(self.h, _d(x), _d(th), _d(v), _d(om), _d(R))
+        return x, th, v, om, R
+
+    def set_state(self, x=None, theta=None, v=None, omega=None):
+        a = [None if t is None else _f64(t) for t in (x, theta, v, omega)]
+        self.o.lib.ref_rb_group_set_state(self.h, *[None if t is None else _d(t) for t in a])
+
+    def constraint(self, e, stencil):
+        c, g = np.empty(1), np.empty(6 * self.STENCIL[self.kinds[e]])
+        self.o.check(self.o.lib.ref_rb_constraint(self.h, e, stencil, _d(c), _d(g)))
+        return float(c[0]), g
+
+    def vertex_force_hessian(self, e, stencil, local):
+        f, h = np.empty(6), np.empty((6, 6))
+        self.o.check(self.o.lib.ref_rb_vertex_force_hessian(self.h, e, stencil, local, _d(f), _d(h)))
+        return f, h
+
+    def close(self):
+        if self.h:
+            self.o.lib.ref_rb_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class OracleRbSolver:
+    """kind: 0 = VBD, 1 = XPBD parallel Gauss-Seidel, 2 = XPBD serial, on a copy of the rigid-body group"""
+
+    def __init__(self, group: OracleRbGroup, kind: int, dt=0.01, substeps=1, iterations=1, gravity=(0.0, -9.8, 0.0)):
+        self.g, self.o = group, group.o
+        grav = _f64(gravity)
+        self.h = C.c_void_p(self.o.lib.ref_rb_solver_create(kind, group.h, dt, substeps, iterations, _d(grav)))
+
+    def step(self, frames=1):
+        self.o.check(self.o.lib.ref_rb_solver_step(self.h, frames))
+
+    def state(self):
+        x, th, v, om = (np.empty((self.g.n, 3)) for _ in range(4))
+        R = np.empty((self.g.n, 3, 3))
+        self.o.lib.ref_rb_solver_get_state(self.h, _d(x), _d(th), _d(v), _d(om), _d(R))
+        return x, th, v, om, R
+
+    def set_state(self, x=None, theta=None, v=None, omega=None):
+        a = [None if t is None else _f64(t) for t in (x, theta, v, omega)]
+        self.o.lib.ref_rb_solver_set_state(self.h, *[None if t is None else _d(t) for t in a])
+
+    def update_anchor(self, e, stencil, anchor):
+        a = _f64(anchor)
+        self.o.check(self.o.lib.ref_rb_solver_update_anchor(self.h, self.g.h, e, stencil, _d(a)))
+
+    def close(self):
+        if self.h:
+            self.o.lib.ref_rb_solver_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def load(prefer: str = "reference") -> Oracle:

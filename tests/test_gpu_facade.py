@@ -74,3 +74,27 @@ def test_rope_facade_picking_matches_oracle(tmp_path, oracle, solver, substeps, 
         osol.step(1)
     xr, _ = osol.state()
     assert np.abs(x - xr).max() <= 1e-8 * np.abs(xr).max()
+
+
+@pytest.mark.parametrize("solver,substeps,iters", [("vbd", 2, 6), ("xpbd", 10, 1)])
+def test_rigid_body_chain_facade_matches_reference(tmp_path, ref_oracle, solver, substeps, iters):
+    """RigidBodyGroup + RBSpringEnergy + RBSpringAnchorEnergy through the facade (examples/rb_chain_facade.cpp builds the
+    reference application's chain scene, apps/solverCompare.cpp:605-660, and drags the anchor half way) against the compiled
+    reference on the same scene and the same edit"""
+    exe = tmp_path / "rb_chain_facade"
+    subprocess.run(["g++", "-std=c++17", "-O1", "-I", str(ROOT / "include"), str(ROOT / "examples" / "rb_chain_facade.cpp"),
+                    "-L", str(ROOT / "spg_b200" / "lib"), "-lspgx", f"-Wl,-rpath,{ROOT / 'spg_b200' / 'lib'}", "-o", str(exe)],
+                   check=True)
+    n, frames = 6, 6
+    res = subprocess.run([str(exe), solver, str(n), str(frames), str(substeps), str(iters)], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    out = np.array([[float(a) for a in l.split()] for l in res.stdout.strip().splitlines()])
+    sc = S.rb_chain(n)
+    og = oracle_api.OracleRbGroup(ref_oracle, sc)
+    osol = oracle_api.OracleRbSolver(og, 0 if solver == "vbd" else 1, 0.01, substeps, iters)
+    osol.step(frames // 2)
+    osol.update_anchor(0, 0, [0.7, 0.6, 0.1])
+    osol.step(frames - frames // 2)
+    xr, thr = osol.state()[:2]
+    assert np.abs(out[:, :3] - xr).max() <= 1e-8 * np.abs(xr).max()
+    assert np.abs(out[:, 3:] - thr).max() <= 1e-7 * max(np.abs(thr).max(), 1e-30)
