@@ -115,6 +115,12 @@ int spgx_color_vertices(int nVerts, int nSets, const int32_t *const *entries, co
                         const int32_t *stencilSizes, int32_t *colors);
 /* coloring::colorStencils, graphColoring.cpp:51-70. colors: nEntries / stencilSize ints out. */
 int spgx_color_stencils(const int32_t *entries, int64_t nEntries, int stencilSize, int32_t *colors);
+/* spgx_color_vertices built on the device of `ctx`: the greedy colouring evaluated level by
+ * level over its dependency DAG -- a node's colour depends only on its lower-indexed neighbours' -- hence the same colours
+ * bit for bit (spg_b200/csrc/colour.cu). *rounds (may be NULL): the number of levels. spgx_group_finalize(SPGX_VBD) uses it
+ * for groups of 500 k vertices and more (SPGX_DEVICE_COLOURING=0 / 1 overrides). */
+int spgx_color_vertices_device(spgx_ctx *ctx, int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
+                               const int32_t *stencilSizes, int32_t *colors, int *rounds);
 /* addStencil + preparePrecomputations of one energy kind on rest positions x0: writes
  * nStencils * spgx_kind_num_record_params(kind) doubles. Same validation as the reference. */
 int spgx_prepare_energy(int kind, int nStencils, const int32_t *stencils, const double *modelParams,
@@ -221,7 +227,7 @@ enum spgx_halo_mode { SPGX_HALO_NONE = 0, SPGX_HALO_NCCL = 1, SPGX_HALO_P2P = 2 
 int spgx_group_set_halo_mode(spgx_group *grp, int mode);
 int spgx_group_get_halo_mode(spgx_group *grp, int *mode);
 /* out8 = [streaming kernel in use, lanes per vertex, warp-slices, largest unique-neighbour count, halo mode,
- * boundary stores per sweep, 0, 0] */
+ * boundary stores per sweep, dependency levels of the device-built colouring (0: host colouring), kernel variant] */
 int spgx_group_kernel_info(spgx_group *grp, int64_t *out8);
 
 /* structure queries for the bit-exactness gates */

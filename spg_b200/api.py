@@ -47,6 +47,7 @@ SIGNATURES = {
     "spgx_kind_num_record_params": (C.c_int, [C.c_int]),
     "spgx_color_vertices": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip]),
     "spgx_color_stencils": (C.c_int, [_ip, C.c_int64, C.c_int, _ip]),
+    "spgx_color_vertices_device": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.POINTER(C.c_int)]),
     "spgx_prepare_energy": (C.c_int, [C.c_int, C.c_int, _ip, _dp, C.c_int, _dp, _dp]),
     "spgx_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "spgx_ctx_destroy": (None, [C.c_void_p]),
@@ -165,6 +166,19 @@ def color_vertices(n_verts: int, stencil_sets) -> np.ndarray:
     colors = np.empty(n_verts, dtype=np.int32)
     check(lib.spgx_color_vertices(n_verts, len(sets), ptrs, n_entries.ctypes.data_as(_lp), _i(sizes), _i(colors)))
     return colors
+
+
+def color_vertices_device(ctx, n_verts: int, stencil_sets):
+    """color_vertices built on the device (spg_b200/csrc/colour.cu): (colours, dependency levels)"""
+    sets = [_i32(s) for s in stencil_sets]
+    ptrs = (_ip * len(sets))(*[_i(s) for s in sets])
+    n_entries = np.array([s.size for s in sets], dtype=np.int64)
+    sizes = np.array([s.shape[1] for s in sets], dtype=np.int32)
+    colors = np.empty(n_verts, dtype=np.int32)
+    rounds = C.c_int(0)
+    check(lib.spgx_color_vertices_device(ctx.handle, n_verts, len(sets), ptrs, n_entries.ctypes.data_as(_lp), _i(sizes), _i(colors),
+                                         C.byref(rounds)))
+    return colors, rounds.value
 
 
 def color_stencils(stencils) -> np.ndarray:
@@ -383,7 +397,7 @@ class Group:
         o = np.zeros(8, dtype=np.int64)
         check(lib.spgx_group_kernel_info(self.handle, o.ctypes.data_as(_lp)))
         return {"streamed": bool(o[0]), "lanes": int(o[1]), "slices": int(o[2]), "max_neighbours": int(o[3]),
-                "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5]), "uniform_slices": int(o[6]),
+                "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5]), "colouring_rounds": int(o[6]),
                 "variant": int(o[7]), "xpbd_cluster": False}
 
     def streamed(self) -> bool:

@@ -231,7 +231,6 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     SPGX_CUDA(cudaStreamSynchronize(st));
     grp.sliceDescHost = std::move(desc);
     grp.nSlices = static_cast<int>(nSlices);
-    grp.nUniformSlices = nUniform;
     grp.maxNbr = maxNbr;
     grp.streamBytes = bytes;
     for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
@@ -460,7 +459,7 @@ int spgx_group_kernel_info(spgx_group *grp, int64_t *out8)
     return guarded([&] {
         if (!grp || !grp->finalized || !out8) throw StateError("group is not finalized");
         out8[0] = grp->streamMask != 0, out8[1] = grp->vbdLanes, out8[2] = grp->nSlices, out8[3] = grp->maxNbr;
-        out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = grp->nUniformSlices, out8[7] = grp->vbdOcc;
+        out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = grp->colouringRounds, out8[7] = grp->vbdOcc;
     });
 }
 
@@ -802,10 +801,21 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         grp->uniqueNeighbourSum = 0;
         if (solverKind == SPGX_VBD) {
             std::vector<Incidence> inc;
-            for (auto &fs : sets) inc.push_back(buildIncidence(V, fs));
-            grp->vertexColors = colorVertices(V, sets, &inc);  // vbd.cpp:203-229 (global: identical on every rank)
+            // vbd.cpp:203-229 (global: identical on every rank).  Large groups are coloured on the device (colour.cu: the same
+            // colours bit for bit, tests/test_gpu_colouring.py); SPGX_DEVICE_COLOURING=0 / 1 forces the host / device form
+            bool onDevice = V >= 500000;  // 3 x faster than the host pass at 1 M vertices, 6 x at 16 M (profiles/r2o_device_colouring.txt)
+            if (const char *env = getenv("SPGX_DEVICE_COLOURING")) onDevice = atoi(env) != 0;
+            grp->colouringRounds = 0;
+            if (!onDevice)
+                for (auto &fs : sets) inc.push_back(buildIncidence(V, fs));
+            grp->vertexColors = onDevice ? colorVerticesDevice(grp->ctx, V, sets, &grp->colouringRounds) : colorVertices(V, sets, &inc);
             LocalView lv = buildLocalView(V, grp->vertexColors, sets, grp->partitioned ? grp->owner.data() : nullptr,
                                           grp->rank, grp->nRanks);
+            // vertex -> (stencil, local) incidence (vbd.cpp:231-268): the host colouring needed the global table; otherwise only
+            // the rows of owned vertices are read below, and those are complete over the stencils this rank keeps
+            if (onDevice)
+                for (size_t ei = 0; ei < nE; ++ei)
+                    inc.push_back(grp->partitioned ? buildIncidenceOf(V, sets[ei], lv.localStencils[ei]) : buildIncidence(V, sets[ei]));
             grp->nOwned = lv.nOwned;
             grp->nLocal = lv.nLocal;
             grp->slot2vert = lv.slot2vert;

@@ -214,6 +214,7 @@ struct spgx_group {
     bool identityOrder = true;  // device slot == vertex id (every solver but VBD and partitioned XPBD)
     // vertex colouring / ordering (VBD); identity ordering for XPBD
     std::vector<int32_t> vertexColors;
+    int colouringRounds = 0;  // > 0: the colouring was built on the device in that many dependency levels (colour.cu)
     std::vector<int32_t> slot2vert, vert2slot;
     std::vector<int64_t> colorOffsets;
     int vbdLanes = 4;                   // threads per vertex in the VBD colour pass
@@ -228,7 +229,6 @@ struct spgx_group {
     std::vector<StreamState> streams;  // indexed by stream type when non-empty
     spgx::DevBuf<uint32_t> d_sliceDesc, d_nbrIds;
     std::vector<uint32_t> sliceDescHost;  // host copy of d_sliceDesc (spgx_energy_update_record patches stream records in place)
-    int64_t nUniformSlices = 0;  // slices that qualify for the pair path of the streaming kernel
     int maxNbr = 0, nSlices = 0, vbdLookahead = 512, vbdPdl = 1, vbdCarveout = -1;
     int64_t vbdL2Persist = 0;  // bytes of L2 set aside for the persisting window over the positions (0: off)
     unsigned streamMask = 0;
@@ -338,6 +338,12 @@ inline void throwIfHaloTimedOut(spgx_group *grp)
     }
 }
 int enqueueHaloExchange(spgx_group *grp, int colour, cudaStream_t st);  // comm.cu
+}  // namespace spgx
+#include "host_build.h"
+namespace spgx
+{
+// colour.cu: colorVertices (graphColoring.cpp:72-84) as a level-by-level evaluation of its dependency DAG on the device
+std::vector<int32_t> colorVerticesDevice(spgx_ctx *ctx, int nVerts, const std::vector<FlatStencilsView> &sets, int *rounds);
 int enqueueXpbdHaloExchange(spgx_group *grp, int pass, cudaStream_t st);  // comm.cu
 // api_newton.cu: incidence tables, sparse pattern and work buffers of a group finalized with SPGX_NEWTON
 void newtonBuild(spgx_group *grp, cudaStream_t st);

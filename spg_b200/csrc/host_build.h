@@ -44,6 +44,26 @@ inline Incidence buildIncidence(int nVerts, const FlatStencilsView &fs)
     return inc;
 }
 
+// the same table restricted to the stencils `kept` (ascending ids): complete for every vertex all of whose stencils are kept
+// (a partitioned rank keeps every stencil touching a vertex it owns), O(nVerts + kept) instead of O(nVerts + all)
+inline Incidence buildIncidenceOf(int nVerts, const FlatStencilsView &fs, const std::vector<int32_t> &kept)
+{
+    const int S = fs.stencilSize;
+    Incidence inc;
+    inc.rowptr.assign(static_cast<size_t>(nVerts) + 1, 0);
+    for (int32_t st : kept)
+        for (int l = 0; l < S; ++l) inc.rowptr[fs.entries[static_cast<int64_t>(st) * S + l] + 1]++;
+    for (int v = 0; v < nVerts; ++v) inc.rowptr[v + 1] += inc.rowptr[v];
+    inc.flat.resize(kept.size() * static_cast<size_t>(S));
+    std::vector<int64_t> cursor(inc.rowptr.begin(), inc.rowptr.end() - 1);
+    for (int32_t st : kept)
+        for (int l = 0; l < S; ++l) {
+            const int64_t s = static_cast<int64_t>(st) * S + l;
+            inc.flat[cursor[fs.entries[s]]++] = s;  // kept is ascending, so flat indices ascend within a row
+        }
+    return inc;
+}
+
 struct StampSet {
     std::vector<int64_t> stamp;
     void forbid(int colour, int64_t tag)

@@ -282,3 +282,36 @@ def test_gpu_robust_newton_iterations_vs_oracle(ctx, oracle, scene, kind):
     assert _rel(x, xr) <= 1e-6 and _rel(v, vr) <= 1e-4, (_rel(x, xr), _rel(v, vr))
     g.close()
 
+
+
+@pytest.mark.gpu
+def test_gpu_hand_derived_membrane_hessian_equals_the_generic_one(ctx, oracle, monkeypatch):
+    """membraneStvkHessianKernel (SPGX_MEMBRANE_HAND=1: the 9 x 9 StVK membrane Hessian derived by hand, staged stores)
+    against the generic mixed-dual path and the oracle: element Hessians of a deformed cloth, the assembled matrix, one
+    Newton dx step with the same CG iteration count"""
+    from spg_b200 import api
+    sc = S.cloth(13, 9)
+    rng = np.random.default_rng(4)
+    x = sc.x + 2e-2 * rng.standard_normal(sc.x.shape)
+    out = {}
+    for hand in ("0", "1"):
+        monkeypatch.setenv("SPGX_MEMBRANE_HAND", hand)
+        g = api.Group.from_scene(ctx, sc)
+        g.finalize(api.SPGX_NEWTON)
+        g.upload(x, np.zeros_like(x))
+        eid = [i for i, e in enumerate(sc.energies) if e.kind == S.K_MEMBRANE_STVK][0]
+        hs = np.stack([g.element_hessian(eid, st) for st in range(0, sc.energies[eid].stencils.shape[0], 7)])
+        _, _, blocks = g.system_stiffness()
+        g.implicit_step(api.SPGX_IE_NEWTON_DX, 0.01, 1)
+        out[hand] = (hs, blocks, g.download()[0], g.cg_iterations())
+        g.close()
+    og = oracle_api.OracleGroup(oracle, sc)
+    og.set_state(x, np.zeros_like(x))
+    for k, st in enumerate(range(0, sc.energies[eid].stencils.shape[0], 7)):
+        _, href = og.grad_hess(eid, st)
+        assert _rel(out["1"][0][k], href) <= 1e-11
+    assert _rel(out["1"][0], out["0"][0]) <= 1e-12 and _rel(out["1"][1], out["0"][1]) <= 1e-12
+    # the two matrices differ in the last bits, and on a noisy state the CG (stopped at |r| <= 1e-5 |b|) may cross its threshold
+    # an iteration or two apart (observed 123 vs 121): this is why the hand-derived kernel stays opt-in -- the golden step cases
+    # hold the DEFAULT path to the reference's exact iteration counts
+    assert np.abs(out["1"][3] - out["0"][3]).max() <= 3 and _rel(out["1"][2], out["0"][2]) <= 1e-6
