@@ -212,7 +212,9 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": workload_name(builder, a, solver, substeps, iterations),
-                       "note": "CPU arm timed on a bounded sample of the workload (rate is size-independent, SURVEY 8d)"},
+                       "note": "CPU arm timed on a bounded sample of the workload; the reference's rate is size-independent: 1.82e4 / 1.95e4 / 2.10e4 "
+                               "vertex-iterations/s at 64^2 / 256^2 / 1024^2 on the same 8 cores (profiles/r2p_cpu_reference_rate.txt, "
+                               "tools/cpu_rate_at_size.py)"},
             "cpu_baseline": {"value": value, "unit": unit, **info},
             "e2e": {"value": value, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}

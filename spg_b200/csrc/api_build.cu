@@ -2,6 +2,11 @@
 // finalize (colouring + incidence + upload).  See include/spgx.h for the reference interface each
 // entry point replaces.
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <exception>
+#include <thread>
+#include <sched.h>
 #include <cstdlib>
 #include <cstring>
 
@@ -20,6 +25,56 @@ void setLastError(const std::string &msg)
     g_lastError = msg;
 }
 
+// SPGX_FINALIZE_TIMING=1: where spgx_group_finalize spends its host time, one line per phase on stderr
+struct PhaseTimer {
+    bool on = getenv("SPGX_FINALIZE_TIMING") && atoi(getenv("SPGX_FINALIZE_TIMING")) != 0;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void lap(const char *what)
+    {
+        if (!on) return;
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[spgx finalize] %-28s %8.3f s\n", what, std::chrono::duration<double>(now - t).count());
+        t = now;
+    }
+};
+
+// fn(begin, end, chunk) over [0, n) in contiguous chunks on host threads (SPGX_HOST_THREADS, default: the cores this process
+// may use, at most 32).  Chunk boundaries are a function of n and the thread count only.
+template <class F>
+static void parallelChunks(int64_t n, int nChunks, F &&fn)
+{
+    nChunks = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(nChunks, n)));
+    std::vector<std::thread> pool;
+    std::vector<std::exception_ptr> err(static_cast<size_t>(nChunks));
+    for (int c = 0; c < nChunks; ++c) {
+        const int64_t b = n * c / nChunks, e = n * (c + 1) / nChunks;
+        auto body = [&fn, &err, b, e, c] {
+            try {
+                fn(b, e, c);
+            } catch (...) {
+                err[static_cast<size_t>(c)] = std::current_exception();
+            }
+        };
+        if (c + 1 < nChunks)
+            pool.emplace_back(body);
+        else
+            body();
+    }
+    for (auto &t : pool) t.join();
+    for (auto &e : err)
+        if (e) std::rethrow_exception(e);
+}
+static int hostThreads()
+{
+    if (const char *env = getenv("SPGX_HOST_THREADS")) return std::max(1, atoi(env));
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int n = 0;
+    if (sched_getaffinity(0, sizeof(set), &set) == 0) n = CPU_COUNT(&set);
+    if (n <= 0) n = static_cast<int>(std::thread::hardware_concurrency());
+    return std::max(1, std::min(n, 32));
+}
+
 static void checkKind(int kind)
 {
     if (kind < 0 || kind >= K_COUNT) throw std::runtime_error("unknown energy kind");
@@ -35,6 +90,7 @@ static void checkKind(int kind)
 // energies map to the same stream type, or the neighbour tile would not fit in shared memory.
 static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cudaStream_t st)
 {
+    PhaseTimer pt;
     const int V = grp.nVerts, NO = grp.nOwned, G = grp.vbdLanes, VW = 32 / G;  // V: global vertices, NO: owned slots
     const int nColors = static_cast<int>(grp.colorOffsets.size()) - 1;
     struct HostStream {
@@ -61,49 +117,94 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     }
     if (!any) return false;
 
+    // per slot: unique neighbours (first-seen order) and the canonical records of its incidences -- slots are independent, so
+    // contiguous chunks of slots are built on host threads into chunk-local arrays and concatenated in slot order
     std::vector<uint32_t> nbrRowptr(static_cast<size_t>(NO) + 1, 0);
     std::vector<uint32_t> nbrList;
-    std::vector<int32_t> mark(static_cast<size_t>(V), -1), localIdx(static_cast<size_t>(V), 0);
     std::vector<uint8_t> hasCsr(static_cast<size_t>(NO), 0);
     int maxNbr = 0;
-    for (int s = 0; s < NO; ++s) {
-        const int v = grp.slot2vert[s];
-        const uint32_t nb0 = static_cast<uint32_t>(nbrList.size());
-        for (auto &h : hs)
-            if (h.energy >= 0) h.rowptr[s] = static_cast<uint32_t>(h.idx.size());
-        for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
-            const auto &e = grp.energies[ei];
-            if (streamTypeOf(e.kind, 0) < 0) {
-                if (inc[ei].rowptr[v + 1] > inc[ei].rowptr[v]) hasCsr[s] = 1;
-                continue;
-            }
-            for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
-                const int64_t stencil = inc[ei].flat[q] / e.S;
-                const int local = static_cast<int>(inc[ei].flat[q] % e.S);
-                const int type = streamTypeOf(e.kind, local);
-                HostStream &h = hs[type];
-                int32_t nbr[3];
-                double rq[16];
-                makeStreamRecord(e.kind, e.stencils.data() + stencil * e.S, e.records.data() + stencil * e.NP, local, nbr, rq);
-                uint32_t word = 0;
-                for (int k = 0; k < streamNI(type); ++k) {
-                    const int u = nbr[k];
-                    if (mark[u] != s) {
-                        mark[u] = s;
-                        localIdx[u] = static_cast<int32_t>(nbrList.size() - nb0);
-                        nbrList.push_back(static_cast<uint32_t>(grp.vert2slot[u]));
+    (void)V;
+    {
+        const int nChunks = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(hostThreads(), NO / 4096 + 1)));
+        struct Chunk {
+            std::vector<uint32_t> nbr;
+            std::vector<uint32_t> idx[ST_COUNT];
+            std::vector<double> q[ST_COUNT];
+            int maxNbr = 0;
+            bool tooMany = false;
+        };
+        std::vector<Chunk> chunks(static_cast<size_t>(nChunks));
+        parallelChunks(NO, nChunks, [&](int64_t s0, int64_t s1, int c) {
+            Chunk &ck = chunks[static_cast<size_t>(c)];
+            std::vector<int32_t> seen;  // neighbour vertex ids of the current slot (a handful: a linear scan beats a V-sized mark array)
+            for (int64_t s = s0; s < s1; ++s) {
+                const int v = grp.slot2vert[static_cast<size_t>(s)];
+                seen.clear();
+                const size_t nb0 = ck.nbr.size();
+                for (int t = 0; t < ST_COUNT; ++t)
+                    if (hs[t].energy >= 0) hs[t].rowptr[static_cast<size_t>(s)] = static_cast<uint32_t>(ck.idx[t].size());  // chunk-local for now
+                for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+                    const auto &e = grp.energies[ei];
+                    if (streamTypeOf(e.kind, 0) < 0) {
+                        if (inc[ei].rowptr[v + 1] > inc[ei].rowptr[v]) hasCsr[static_cast<size_t>(s)] = 1;
+                        continue;
                     }
-                    word |= static_cast<uint32_t>(localIdx[u]) << (8 * k);
+                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                        const int64_t stencil = inc[ei].flat[q] / e.S;
+                        const int local = static_cast<int>(inc[ei].flat[q] % e.S);
+                        const int type = streamTypeOf(e.kind, local);
+                        int32_t nbr[3];
+                        double rq[16];
+                        makeStreamRecord(e.kind, e.stencils.data() + stencil * e.S, e.records.data() + stencil * e.NP, local, nbr, rq);
+                        uint32_t word = 0;
+                        for (int k = 0; k < streamNI(type); ++k) {
+                            const int u = nbr[k];
+                            size_t li = 0;
+                            while (li < seen.size() && seen[li] != u) ++li;
+                            if (li == seen.size()) {
+                                seen.push_back(u);
+                                ck.nbr.push_back(static_cast<uint32_t>(grp.vert2slot[u]));
+                            }
+                            word |= static_cast<uint32_t>(li & 0xFFu) << (8 * k);
+                        }
+                        ck.idx[type].push_back(word);
+                        ck.q[type].insert(ck.q[type].end(), rq, rq + hs[type].NQ);
+                    }
                 }
-                h.idx.push_back(word);
-                h.q.insert(h.q.end(), rq, rq + h.NQ);
+                const int cnt = static_cast<int>(ck.nbr.size() - nb0);
+                if (cnt > 254) ck.tooMany = true;
+                ck.maxNbr = std::max(ck.maxNbr, cnt);
+                nbrRowptr[static_cast<size_t>(s) + 1] = static_cast<uint32_t>(cnt);  // a count for now
             }
+        });
+        for (const auto &ck : chunks) {
+            if (ck.tooMany) return false;
+            maxNbr = std::max(maxNbr, ck.maxNbr);
         }
-        const int cnt = static_cast<int>(nbrList.size() - nb0);
-        if (cnt > 254) return false;
-        maxNbr = std::max(maxNbr, cnt);
-        nbrRowptr[s + 1] = static_cast<uint32_t>(nbrList.size());
+        // chunk-local offsets -> global ones, then the chunks' arrays side by side
+        for (int s = 0; s < NO; ++s) nbrRowptr[static_cast<size_t>(s) + 1] += nbrRowptr[static_cast<size_t>(s)];
+        nbrList.resize(nbrRowptr[static_cast<size_t>(NO)]);
+        std::vector<size_t> idxBase[ST_COUNT];
+        for (int t = 0; t < ST_COUNT; ++t) {
+            if (hs[t].energy < 0) continue;
+            idxBase[t].assign(static_cast<size_t>(nChunks) + 1, 0);
+            for (int c = 0; c < nChunks; ++c) idxBase[t][static_cast<size_t>(c) + 1] = idxBase[t][static_cast<size_t>(c)] + chunks[static_cast<size_t>(c)].idx[t].size();
+            hs[t].idx.resize(idxBase[t][static_cast<size_t>(nChunks)]);
+            hs[t].q.resize(idxBase[t][static_cast<size_t>(nChunks)] * static_cast<size_t>(hs[t].NQ));
+        }
+        parallelChunks(NO, nChunks, [&](int64_t s0, int64_t s1, int c) {
+            const Chunk &ck = chunks[static_cast<size_t>(c)];
+            std::copy(ck.nbr.begin(), ck.nbr.end(), nbrList.begin() + nbrRowptr[static_cast<size_t>(s0)]);
+            for (int t = 0; t < ST_COUNT; ++t) {
+                if (hs[t].energy < 0) continue;
+                const size_t base = idxBase[t][static_cast<size_t>(c)];
+                std::copy(ck.idx[t].begin(), ck.idx[t].end(), hs[t].idx.begin() + base);
+                std::copy(ck.q[t].begin(), ck.q[t].end(), hs[t].q.begin() + base * static_cast<size_t>(hs[t].NQ));
+                for (int64_t s = s0; s < s1; ++s) hs[t].rowptr[static_cast<size_t>(s)] += static_cast<uint32_t>(base);
+            }
+        });
     }
+    pt.lap("  streams: records per slot");
     maxNbr = std::max(maxNbr, 1);
     // shared memory of a 4-warp block (vbd_stream.cuh: tile rows + the pair path's record ring, sized for the widest record)
     if ((static_cast<size_t>(maxNbr + 3) * 3 * VW * 8 + 2 * (128 + 12 * 256)) * 4 > 200 * 1024) return false;
@@ -181,16 +282,19 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         // request the ids before the descriptor has arrived (unused rows hold slot 0, a harmless gather target)
         const bool fixed = grp.vbdNbrFixed != 0;
         std::vector<uint32_t> ids((fixed ? nSlices * static_cast<size_t>(maxNbr) : static_cast<size_t>(row)) * VW, 0u);
-        for (size_t sl = 0; sl < nSlices; ++sl) {
-            const size_t row0 = fixed ? sl * static_cast<size_t>(maxNbr) : static_cast<size_t>(desc[sl * kSliceDescWords + 1]);
-            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s)
-                for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
-                    ids[(row0 + (k - nbrRowptr[s])) * VW + (s - sliceSlot[sl])] = nbrList[k];
-        }
+        parallelChunks(static_cast<int64_t>(nSlices), hostThreads(), [&](int64_t a, int64_t b, int) {
+            for (size_t sl = static_cast<size_t>(a); sl < static_cast<size_t>(b); ++sl) {
+                const size_t row0 = fixed ? sl * static_cast<size_t>(maxNbr) : static_cast<size_t>(desc[sl * kSliceDescWords + 1]);
+                for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s)
+                    for (uint32_t k = nbrRowptr[s]; k < nbrRowptr[s + 1]; ++k)
+                        ids[(row0 + (k - nbrRowptr[s])) * VW + (s - sliceSlot[sl])] = nbrList[k];
+            }
+        });
         grp.d_nbrIds.upload(ids, st);
         bytes += 4.0 * ids.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
+    pt.lap("  streams: descriptors + ids");
     grp.streams.clear();
     grp.streams.resize(ST_COUNT);
     grp.streamMask = 0;
@@ -209,16 +313,18 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         const size_t T = step;
         std::vector<uint32_t> idx(T * 32, 0xFFFFFFFFu);
         std::vector<double> params(T * NQ * 32, 0.0);
-        for (size_t sl = 0; sl < nSlices; ++sl)
-            for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
-                uint32_t j = 0;
-                for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
-                    const size_t t = desc[sl * kSliceDescWords + 2 + type] + j / G;
-                    const int lane = static_cast<int>(j % G) * VW + (s - sliceSlot[sl]);
-                    idx[t * 32 + lane] = h.idx[r];
-                    for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
+        parallelChunks(static_cast<int64_t>(nSlices), hostThreads(), [&](int64_t a, int64_t b, int) {
+            for (size_t sl = static_cast<size_t>(a); sl < static_cast<size_t>(b); ++sl)
+                for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
+                    uint32_t j = 0;
+                    for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
+                        const size_t t = desc[sl * kSliceDescWords + 2 + type] + j / G;
+                        const int lane = static_cast<int>(j % G) * VW + (s - sliceSlot[sl]);
+                        idx[t * 32 + lane] = h.idx[r];
+                        for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
+                    }
                 }
-            }
+        });
         auto &out = grp.streams[type];
         out.type = type;
         out.d_idx.upload(idx, st);
@@ -227,6 +333,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         bytes += 4.0 * idx.size() + 8.0 * params.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
+    pt.lap("  streams: SoA fill + uploads");
     grp.d_sliceDesc.upload(desc, st);
     SPGX_CUDA(cudaStreamSynchronize(st));
     grp.sliceDescHost = std::move(desc);
@@ -800,6 +907,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         grp->vert2slot.assign(V, 0);
         grp->uniqueNeighbourSum = 0;
         if (solverKind == SPGX_VBD) {
+            PhaseTimer pt;
             std::vector<Incidence> inc;
             // vbd.cpp:203-229 (global: identical on every rank).  Large groups are coloured on the device (colour.cu: the same
             // colours bit for bit, tests/test_gpu_colouring.py); SPGX_DEVICE_COLOURING=0 / 1 forces the host / device form
@@ -809,13 +917,19 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             if (!onDevice)
                 for (auto &fs : sets) inc.push_back(buildIncidence(V, fs));
             grp->vertexColors = onDevice ? colorVerticesDevice(grp->ctx, V, sets, &grp->colouringRounds) : colorVertices(V, sets, &inc);
+            pt.lap("colouring (+ host incidence)");
             LocalView lv = buildLocalView(V, grp->vertexColors, sets, grp->partitioned ? grp->owner.data() : nullptr,
                                           grp->rank, grp->nRanks);
+            pt.lap("local view");
             // vertex -> (stencil, local) incidence (vbd.cpp:231-268): the host colouring needed the global table; otherwise only
             // the rows of owned vertices are read below, and those are complete over the stencils this rank keeps
-            if (onDevice)
-                for (size_t ei = 0; ei < nE; ++ei)
-                    inc.push_back(grp->partitioned ? buildIncidenceOf(V, sets[ei], lv.localStencils[ei]) : buildIncidence(V, sets[ei]));
+            if (onDevice) {
+                inc.resize(nE);  // one host thread per energy
+                parallelChunks(static_cast<int64_t>(nE), static_cast<int>(nE), [&](int64_t a, int64_t b, int) {
+                    for (int64_t ei = a; ei < b; ++ei)
+                        inc[ei] = grp->partitioned ? buildIncidenceOf(V, sets[ei], lv.localStencils[ei]) : buildIncidence(V, sets[ei]);
+                });
+            }
             grp->nOwned = lv.nOwned;
             grp->nLocal = lv.nLocal;
             grp->slot2vert = lv.slot2vert;
@@ -859,46 +973,60 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 const int VW = 32 / grp->vbdLanes;
                 grp->sliceBase[c + 1] = grp->sliceBase[c] + static_cast<int32_t>((n + VW - 1) / VW);
             }
-            // incidence in slot order (vbd.cpp:231-268 keeps ascending flat index per vertex and energy)
-            std::vector<int32_t> nbr;
-            for (size_t ei = 0; ei < nE; ++ei) {
-                auto &e = grp->energies[ei];
-                if (static_cast<uint64_t>(e.n) >= (1ull << 30)) throw std::runtime_error("too many stencils in one energy");
-                // global stencil id -> position among the stencils this rank keeps (-1: not kept)
-                const auto &kept = lv.localStencils[ei];
-                e.positionOf.assign(static_cast<size_t>(e.n), -1);
-                for (size_t k = 0; k < kept.size(); ++k) e.positionOf[kept[k]] = static_cast<int32_t>(k);
-                std::vector<uint32_t> rowptr(static_cast<size_t>(nLocal) + 1, 0), entries;
-                uint32_t cursor = 0;
-                e.ownedIncidences = 0;
-                for (int s = 0; s < nLocal; ++s) {
-                    const int v = grp->slot2vert[s];
-                    rowptr[s] = cursor;
-                    if (s >= nOwned) continue;  // halo vertices are never updated here
-                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
-                        const int64_t flat = inc[ei].flat[q];
-                        entries.push_back((static_cast<uint32_t>(e.positionOf[flat / e.S]) << 2) | static_cast<uint32_t>(flat % e.S));
-                        ++cursor;
+            // incidence in slot order (vbd.cpp:231-268 keeps ascending flat index per vertex and energy): the host tables of the
+            // energies are built on one thread each, then uploaded
+            struct EnergyTables {
+                std::vector<uint32_t> rowptr, entries;
+                std::vector<int32_t> slotStencils;
+                std::vector<double> keptRecords;
+            };
+            std::vector<EnergyTables> tables(nE);
+            parallelChunks(static_cast<int64_t>(nE), static_cast<int>(nE), [&](int64_t ea, int64_t eb, int) {
+                for (int64_t ei = ea; ei < eb; ++ei) {
+                    auto &e = grp->energies[ei];
+                    auto &tb = tables[ei];
+                    if (static_cast<uint64_t>(e.n) >= (1ull << 30)) throw std::runtime_error("too many stencils in one energy");
+                    // global stencil id -> position among the stencils this rank keeps (-1: not kept)
+                    const auto &kept = lv.localStencils[ei];
+                    e.positionOf.assign(static_cast<size_t>(e.n), -1);
+                    for (size_t k = 0; k < kept.size(); ++k) e.positionOf[kept[k]] = static_cast<int32_t>(k);
+                    tb.rowptr.assign(static_cast<size_t>(nLocal) + 1, 0);
+                    uint32_t cursor = 0;
+                    for (int s = 0; s < nLocal; ++s) {
+                        const int v = grp->slot2vert[s];
+                        tb.rowptr[s] = cursor;
+                        if (s >= nOwned) continue;  // halo vertices are never updated here
+                        for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                            const int64_t flat = inc[ei].flat[q];
+                            tb.entries.push_back((static_cast<uint32_t>(e.positionOf[flat / e.S]) << 2) | static_cast<uint32_t>(flat % e.S));
+                            ++cursor;
+                        }
+                    }
+                    tb.rowptr[nLocal] = cursor;
+                    e.ownedIncidences = cursor;
+                    tb.slotStencils.resize(kept.size() * e.S);
+                    tb.keptRecords.resize(kept.size() * e.NP);
+                    for (size_t k = 0; k < kept.size(); ++k) {
+                        for (int l = 0; l < e.S; ++l)
+                            tb.slotStencils[k * e.S + l] = grp->vert2slot[e.stencils[static_cast<size_t>(kept[k]) * e.S + l]];
+                        std::copy(e.records.begin() + static_cast<size_t>(kept[k]) * e.NP,
+                                  e.records.begin() + static_cast<size_t>(kept[k] + 1) * e.NP, tb.keptRecords.begin() + k * e.NP);
                     }
                 }
-                rowptr[nLocal] = cursor;
-                e.ownedIncidences = cursor;
-                std::vector<int32_t> slotStencils(kept.size() * e.S);
-                std::vector<double> keptRecords(kept.size() * e.NP);
-                for (size_t k = 0; k < kept.size(); ++k) {
-                    for (int l = 0; l < e.S; ++l)
-                        slotStencils[k * e.S + l] = grp->vert2slot[e.stencils[static_cast<size_t>(kept[k]) * e.S + l]];
-                    std::copy(e.records.begin() + static_cast<size_t>(kept[k]) * e.NP,
-                              e.records.begin() + static_cast<size_t>(kept[k] + 1) * e.NP, keptRecords.begin() + k * e.NP);
-                }
-                e.d_stencils.upload(slotStencils, st);
-                e.d_records.upload(keptRecords, st);
-                e.d_rowptr.upload(rowptr, st);
-                e.d_entries.upload(entries, st);
+            });
+            for (size_t ei = 0; ei < nE; ++ei) {
+                auto &e = grp->energies[ei];
+                auto &tb = tables[ei];
+                e.d_stencils.upload(tb.slotStencils, st);
+                e.d_records.upload(tb.keptRecords, st);
+                e.d_rowptr.upload(tb.rowptr, st);
+                e.d_entries.upload(tb.entries, st);
                 e.streamed = false;
                 e.order.clear();
                 SPGX_CUDA(cudaStreamSynchronize(st));
             }
+            tables.clear();
+            pt.lap("incidence + CSR + uploads");
             // streaming layout, when the group's mix of energies has a compiled streaming kernel
             grp->streams.clear();
             grp->streamMask = 0;
@@ -938,21 +1066,33 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                     }
                 }
             }
+            pt.lap("stream layout (buildStreams)");
             // distinct stencil neighbours per vertex (for the byte model)
-            for (int v = 0; v < V; ++v) {
-                if (grp->vert2slot[v] < 0 || grp->vert2slot[v] >= nOwned) continue;
-                nbr.clear();
-                for (size_t ei = 0; ei < nE; ++ei) {
-                    const auto &e = grp->energies[ei];
-                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
-                        const int64_t base = (inc[ei].flat[q] / e.S) * e.S;
-                        for (int l = 0; l < e.S; ++l)
-                            if (e.stencils[base + l] != v) nbr.push_back(e.stencils[base + l]);
+            {
+                const int nChunks = hostThreads();
+                std::vector<double> partial(static_cast<size_t>(nChunks), 0.0);
+                parallelChunks(V, nChunks, [&](int64_t a, int64_t b, int c) {
+                    std::vector<int32_t> nb;
+                    double sum = 0;
+                    for (int64_t v = a; v < b; ++v) {
+                        if (grp->vert2slot[v] < 0 || grp->vert2slot[v] >= nOwned) continue;
+                        nb.clear();
+                        for (size_t ei = 0; ei < nE; ++ei) {
+                            const auto &e = grp->energies[ei];
+                            for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
+                                const int64_t base = (inc[ei].flat[q] / e.S) * e.S;
+                                for (int l = 0; l < e.S; ++l)
+                                    if (e.stencils[base + l] != v) nb.push_back(e.stencils[base + l]);
+                            }
+                        }
+                        std::sort(nb.begin(), nb.end());
+                        sum += static_cast<double>(std::unique(nb.begin(), nb.end()) - nb.begin());
                     }
-                }
-                std::sort(nbr.begin(), nbr.end());
-                grp->uniqueNeighbourSum += static_cast<double>(std::unique(nbr.begin(), nbr.end()) - nbr.begin());
+                    partial[static_cast<size_t>(c)] = sum;
+                });
+                for (double p : partial) grp->uniqueNeighbourSum += p;  // integer-valued: the order of the sum is immaterial
             }
+            pt.lap("unique-neighbour count");
         } else if (grp->partitioned && solverKind == SPGX_XPBD) {
             finalizeXpbdPartitioned(grp, sets, st);
         } else {

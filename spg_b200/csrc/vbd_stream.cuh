@@ -696,7 +696,8 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
 // instead of the register pipeline: 4 (register pipeline, <= 128 registers) and 15 (ring, 5 blocks, <= 102 registers) are
 // compiled.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
 // (profiles/r2d ... r2i_sweep.txt); 3 blocks, register caps on the register pipeline, persistent warps, prefetch.global.L1
-// (round 1, profiles/r1f_*); two steps evaluated together from a four-step ring (ptxas keeps the two evaluations sequential).
+// (round 1, profiles/r1f_*); two steps evaluated together from a four-step ring (ptxas keeps the two evaluations sequential);
+// the register pipeline in 2-warp blocks, 8 resident (2.748 vs 2.702 ms on config 3).
 template <unsigned SMASK, unsigned KMASK, int G>
 void launchStreamG(const VbdArgs &args, int variant, int begin, int end, int sliceBase, double invdtSquared,
                    cudaStream_t stream)
