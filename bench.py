@@ -491,6 +491,10 @@ def measure_single(ctx, cfg_id, steps, warmup, rows=0, e2e=True, cpu=True, clock
                 "algorithmic_bytes_per_unit": bytes_iter * sweeps / units_per_frame,
                 "lower_bound_frac": bytes_lower * sweeps / (solve_ms_per_frame * 1e-3) / 1e9 / peak,
                 "kernel_share_of_step": solve_ms_per_frame / (tp.total_ms / rf), "peak_source": peak_src}
+    # the same bytes over the whole step AS TIMED (graph replay, predict / finalize included): `frac` above is measured with
+    # per-phase events in plain-launch mode, where a launch-bound sequence (XPBD: 540 passes of a few microseconds) pays the
+    # full launch latency per pass that the replayed graph does not
+    roofline["frac_of_timed_step"] = bytes_iter * sweeps / (total_ms / steps * 1e-3) / 1e9 / peak
     if fp64 is not None:
         roofline["fp64_pipe_pct_ncu"] = fp64   # the FP64 pipe co-binds this kernel
     if traffic:

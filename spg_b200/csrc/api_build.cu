@@ -855,6 +855,7 @@ void finalizeXpbdPartitioned(spgx_group *grp, const std::vector<FlatStencilsView
         e.d_stencils.upload(st2, st);
         e.d_records.upload(rec2, st);
         e.d_lambda.alloc(nHeld * e.NC);
+        e.d_stencilW.alloc(st2.size());
         e.d_rowptr.release();
         e.d_entries.release();
         e.streamed = false;
@@ -1139,6 +1140,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 e.d_stencils.upload(st2, st);
                 e.d_records.upload(rec2, st);
                 e.d_lambda.alloc(solverKind == SPGX_NEWTON ? 0 : static_cast<size_t>(e.n) * e.NC);
+                e.d_stencilW.alloc(solverKind == SPGX_NEWTON ? 0 : st2.size());
                 e.d_rowptr.release();
                 e.d_entries.release();
                 SPGX_CUDA(cudaStreamSynchronize(st));
@@ -1153,7 +1155,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 for (size_t c = 0; c + 1 < e.colorOffsets.size(); ++c)
                     if (e.colorOffsets[c + 1] > e.colorOffsets[c])
                         passes.push_back({e.kind, static_cast<int>(e.colorOffsets[c]), static_cast<int>(e.colorOffsets[c + 1]), e.NC,
-                                          e.d_stencils.ptr, e.d_records.ptr, e.d_lambda.ptr});
+                                          e.d_stencils.ptr, e.d_records.ptr, e.d_lambda.ptr, e.d_stencilW.ptr});
             grp->d_xpbdPasses.upload(passes, st);
             SPGX_CUDA(cudaStreamSynchronize(st));
             // opt-in: measured on B200 at config 2 the grid barrier (~4 us with 148 co-resident blocks) costs more than
@@ -1184,6 +1186,9 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
         }
         grp->d_mass.upload(ms, st);
         grp->d_invMass.upload(ws, st);
+        if (solverKind == SPGX_XPBD || solverKind == SPGX_XPBD_SERIAL)
+            for (auto &e : grp->energies)  // inverse masses per stencil vertex: a pass requests them with the ids, not after them
+                launchGatherScalar(grp->d_invMass.ptr, e.d_stencils.ptr, static_cast<long long>(e.d_stencilW.count), e.d_stencilW.ptr, st);
         // global index range the local vertices span (upload / download move only that range)
         grp->localLo = V;
         grp->localHi = 0;

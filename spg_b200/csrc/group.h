@@ -151,6 +151,7 @@ struct EnergyState {
     std::vector<int32_t> positionOf;     // stencil id -> position
     std::vector<int64_t> colorOffsets;   // nColors + 1
     DevBuf<double> d_lambda;
+    DevBuf<double> d_stencilW;  // XPBD: inverse masses per stencil vertex, in the order of d_stencils
 };
 }  // namespace spgx
 

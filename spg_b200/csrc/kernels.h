@@ -103,14 +103,18 @@ void launchXpbdHaloPush(const VbdHaloDev &h, const double *x, int begin, int end
 // the caller initialises out3 to {0, 0, ~0}
 void launchCheckFinite(const double *x, const double *v, const int32_t *slot2vert, int nVerts, unsigned long long *out3,
                        cudaStream_t stream);
+// dst[i] = src[idx[i]]
+void launchGatherScalar(const double *src, const int32_t *idx, long long n, double *dst, cudaStream_t stream);
 // dst[perm[i]] = src[i] (scatter) or dst[i] = src[perm[i]] (gather) over 3-vectors
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream);
 
 // energy.h:117-153 (springEnergy.cpp:48-68 for K_SPRING) for stencils [begin, end) of one colour.
 // lambda == nullptr: reference small-steps form; otherwise NC doubles per stencil are accumulated.
+// stencilW: the inverse masses of every stencil's vertices, S per stencil in the order of `stencils` (gathered once at
+// finalize: a pass then requests ids, inverse masses and record TOGETHER instead of the masses after the ids).
 // halo (may be null): a partitioned group under the peer-memory exchange; every block waits for the neighbours' event
 // halo->event - 1 before it reads positions.
-void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *stencils, const double *records,
+void launchXpbdPass(int kind, double *x, const double *stencilW, const int32_t *stencils, const double *records,
                     double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo = nullptr);
 
 // One (energy, colour) projection pass of a substep, as the fused XPBD kernel walks them (xpbd.cu)
@@ -119,10 +123,10 @@ struct XpbdPassDev {
     const int32_t *stencils;
     const double *records;
     double *lambda;  // NC doubles per stencil of the energy (used when iterations > 1)
+    const double *stencilW;  // inverse masses per stencil vertex (launchXpbdPass)
 };
 struct XpbdFusedArgs {
     double *x, *v, *xOld;
-    const double *invMass;
     long long n3;               // 3 * vertices
     const XpbdPassDev *passes;  // device array, reference order: energies in insertion order, colours ascending
     int nPasses, nsub, iters, useLambda;

@@ -67,6 +67,20 @@ void launchCheckFinite(const double *x, const double *v, const int32_t *slot2ver
     checkFiniteKernel<<<static_cast<unsigned>((n3 + threads - 1) / threads), threads, 0, stream>>>(x, v, slot2vert, n3, out3);
 }
 
+namespace
+{
+__global__ void gatherScalarKernel(const double *__restrict__ src, const int32_t *__restrict__ idx, long long n, double *__restrict__ dst)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+}  // namespace
+void launchGatherScalar(const double *src, const int32_t *idx, long long n, double *dst, cudaStream_t stream)
+{
+    if (n == 0) return;
+    gatherScalarKernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(src, idx, n, dst);
+}
+
 void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nVerts, double dt, const double *g3,
                    cudaStream_t stream)
 {

@@ -81,7 +81,7 @@ __device__ __forceinline__ void projectGeneric(double *__restrict__ x, const int
 // PDL: the caller was launched with programmatic stream serialization; the stencil's vertex ids and inverse masses (never
 // written by a pass) are fetched before griddepcontrol.wait, i.e. while the previous pass may still be draining
 template <int KIND, bool PDL = false>
-__device__ __forceinline__ void projectStencil(double *__restrict__ x, const double *__restrict__ invMass,
+__device__ __forceinline__ void projectStencil(double *__restrict__ x, const double *__restrict__ stencilW,
                                                const int32_t *__restrict__ stencils, const double *__restrict__ records,
                                                double *__restrict__ lambda, int i, double dt, bool handProject = true)
 {
@@ -99,7 +99,7 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
 #pragma unroll
     for (int s = 0; s < S; ++s) {
         id[s] = __ldg(ids + s);
-        w[s] = __ldg(invMass + id[s]);
+        w[s] = __ldg(stencilW + static_cast<size_t>(i) * S + s);
     }
     if constexpr (PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
 #pragma unroll
@@ -154,7 +154,7 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
 }
 
 template <int KIND>
-__global__ void __launch_bounds__(128) xpbdPassKernel(double *x, const double *invMass, const int32_t *stencils,
+__global__ void __launch_bounds__(128) xpbdPassKernel(double *x, const double *stencilW, const int32_t *stencils,
                                                       const double *records, double *lambda, int begin, int end,
                                                       double dt, bool handProject, const VbdHaloDev h)
 {
@@ -163,18 +163,18 @@ __global__ void __launch_bounds__(128) xpbdPassKernel(double *x, const double *i
         __syncthreads();
     }
     const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < end) projectStencil<KIND>(x, invMass, stencils, records, lambda, i, dt, handProject);
+    if (i < end) projectStencil<KIND>(x, stencilW, stencils, records, lambda, i, dt, handProject);
 }
 // the same pass under programmatic dependent launch: the next pass may become resident and run its prologue while this
 // one drains (config 2 is 540 passes of 10-30 k stencils per frame: the kernel boundary is most of a pass)
 template <int KIND>
-__global__ void __launch_bounds__(128) xpbdPassKernelPdl(double *x, const double *invMass, const int32_t *stencils,
+__global__ void __launch_bounds__(128) xpbdPassKernelPdl(double *x, const double *stencilW, const int32_t *stencils,
                                                          const double *records, double *lambda, int begin, int end,
                                                          double dt, bool handProject)
 {
     asm volatile("griddepcontrol.launch_dependents;");
     const int i = begin + blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < end) projectStencil<KIND, true>(x, invMass, stencils, records, lambda, i, dt, handProject);
+    if (i < end) projectStencil<KIND, true>(x, stencilW, stencils, records, lambda, i, dt, handProject);
     // threads past the end leave without waiting: the grid as a whole still completes only after its waiting threads
 }
 
@@ -182,11 +182,11 @@ __global__ void xpbdEmptyKernel(double *) {}
 
 // serial Gauss-Seidel path (xpbd.cpp:96-102): one thread walks the stencils in index order
 template <int KIND>
-__global__ void xpbdSerialKernel(double *x, const double *invMass, const int32_t *stencils, const double *records,
+__global__ void xpbdSerialKernel(double *x, const double *stencilW, const int32_t *stencils, const double *records,
                                  double *lambda, int begin, int end, double dt)
 {
     for (int i = begin; i < end; ++i) {
-        projectStencil<KIND>(x, invMass, stencils, records, lambda, i, dt);
+        projectStencil<KIND>(x, stencilW, stencils, records, lambda, i, dt);
         __threadfence();
     }
 }
@@ -196,7 +196,7 @@ template <int KIND>
 __device__ __forceinline__ void fusedPass(const XpbdFusedArgs &a, const XpbdPassDev &p, long long tid, long long nthreads)
 {
     for (long long i = p.begin + tid; i < p.end; i += nthreads)
-        projectStencil<KIND>(a.x, a.invMass, p.stencils, p.records, a.useLambda ? p.lambda : nullptr, static_cast<int>(i), a.dt);
+        projectStencil<KIND>(a.x, p.stencilW, p.stencils, p.records, a.useLambda ? p.lambda : nullptr, static_cast<int>(i), a.dt);
 }
 
 constexpr int kFusedThreads = 256;
@@ -273,7 +273,7 @@ __global__ void __launch_bounds__(kFusedThreads) xpbdFusedKernel(const XpbdFused
 }
 
 template <int KIND>
-void launchKind(double *x, const double *invMass, const int32_t *stencils, const double *records, double *lambda,
+void launchKind(double *x, const double *stencilW, const int32_t *stencils, const double *records, double *lambda,
                 int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo)
 {
     const int n = end - begin;
@@ -282,7 +282,7 @@ void launchKind(double *x, const double *invMass, const int32_t *stencils, const
     // SPGX_XPBD_HAND=0: kinds with a hand-derived projection (EnergyKind<>::project) take the generic dual-number path instead
     static const bool hand = !(getenv("SPGX_XPBD_HAND") && atoi(getenv("SPGX_XPBD_HAND")) == 0);
     if (serial) {
-        xpbdSerialKernel<KIND><<<1, 1, 0, stream>>>(x, invMass, stencils, records, lambda, begin, end, dt);
+        xpbdSerialKernel<KIND><<<1, 1, 0, stream>>>(x, stencilW, stencils, records, lambda, begin, end, dt);
     } else {
         // measurement knobs: SPGX_XPBD_THREADS (block size, <= 128), SPGX_XPBD_DEBUG_EMPTY=1 (same grids, empty kernels: the
         // launch floor of the pass sequence; results are wrong)
@@ -307,9 +307,9 @@ void launchKind(double *x, const double *invMass, const int32_t *stencils, const
             attr[0].val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = attr;
             cfg.numAttrs = 1;
-            cudaLaunchKernelEx(&cfg, xpbdPassKernelPdl<KIND>, x, invMass, stencils, records, lambda, begin, end, dt, hand);
+            cudaLaunchKernelEx(&cfg, xpbdPassKernelPdl<KIND>, x, stencilW, stencils, records, lambda, begin, end, dt, hand);
         } else {
-            xpbdPassKernel<KIND><<<(n + threads - 1) / threads, threads, 0, stream>>>(x, invMass, stencils, records, lambda,
+            xpbdPassKernel<KIND><<<(n + threads - 1) / threads, threads, 0, stream>>>(x, stencilW, stencils, records, lambda,
                                                                                      begin, end, dt, hand, h);
         }
     }
@@ -349,14 +349,14 @@ __global__ void evalConstraintsKernel(int kind, const double *x, const int32_t *
 }
 }  // namespace
 
-void launchXpbdPass(int kind, double *x, const double *invMass, const int32_t *stencils, const double *records,
+void launchXpbdPass(int kind, double *x, const double *stencilW, const int32_t *stencils, const double *records,
                     double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo)
 {
     switch (kind) {
         // (a static load has no constraint form: its body is a stub and spgx_xpbd_step refuses it, staticLoadEnergy.cpp:8-13)
 #define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
     case NAME:                                                                                                         \
-        launchKind<NAME>(x, invMass, stencils, records, lambda, begin, end, dt, serial, stream, halo); \
+        launchKind<NAME>(x, stencilW, stencils, records, lambda, begin, end, dt, serial, stream, halo); \
         break;
 #include "kinds.def"
 #undef SPGX_KIND
