@@ -121,6 +121,19 @@ int spgx_color_stencils(const int32_t *entries, int64_t nEntries, int stencilSiz
  * for groups of 500 k vertices and more (SPGX_DEVICE_COLOURING=0 / 1 overrides). */
 int spgx_color_vertices_device(spgx_ctx *ctx, int nVerts, int nSets, const int32_t *const *entries, const int64_t *nEntries,
                                const int32_t *stencilSizes, int32_t *colors, int *rounds);
+/* spgx_color_vertices_device for callers that may not allocate. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid
+ * it). It calls no cudaMalloc / cudaFree / allocating routine: its scratch is one static device array inside the library
+ * (about 13 MiB on every GPU that loads it, until exit), which limits it to SPGX_NOALLOC_MAX_VERTS vertices and
+ * SPGX_NOALLOC_MAX_ENTRIES stencil entries over all sets; larger inputs fail with a message naming the limit.
+ * d_entries: nSets DEVICE arrays (the pointer array itself, nEntries and stencilSizes are host memory); d_colors: nVerts ints
+ * on the DEVICE; *rounds (host, may be NULL). Same colours as spgx_color_vertices / _device, bit for bit. Runs on the
+ * context's stream and returns after it completes. All calls on a device share the scratch: calls that overlap on the GPU
+ * (other threads or contexts) race. */
+#define SPGX_NOALLOC_MAX_VERTS 262144
+#define SPGX_NOALLOC_MAX_ENTRIES 2097152
+int spgx_color_vertices_noalloc(spgx_ctx *ctx, int nVerts, int nSets, const int32_t *const *d_entries, const int64_t *nEntries,
+                                const int32_t *stencilSizes, int32_t *d_colors, int *rounds);
 /* addStencil + preparePrecomputations of one energy kind on rest positions x0: writes
  * nStencils * spgx_kind_num_record_params(kind) doubles. Same validation as the reference. */
 int spgx_prepare_energy(int kind, int nStencils, const int32_t *stencils, const double *modelParams,

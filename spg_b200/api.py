@@ -48,6 +48,7 @@ SIGNATURES = {
     "spgx_color_vertices": (C.c_int, [C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip]),
     "spgx_color_stencils": (C.c_int, [_ip, C.c_int64, C.c_int, _ip]),
     "spgx_color_vertices_device": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(_ip), _lp, _ip, _ip, C.POINTER(C.c_int)]),
+    "spgx_color_vertices_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p), _lp, _ip, C.c_void_p, C.POINTER(C.c_int)]),
     "spgx_prepare_energy": (C.c_int, [C.c_int, C.c_int, _ip, _dp, C.c_int, _dp, _dp]),
     "spgx_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "spgx_ctx_destroy": (None, [C.c_void_p]),
@@ -179,6 +180,23 @@ def color_vertices_device(ctx, n_verts: int, stencil_sets):
     check(lib.spgx_color_vertices_device(ctx.handle, n_verts, len(sets), ptrs, n_entries.ctypes.data_as(_lp), _i(sizes), _i(colors),
                                          C.byref(rounds)))
     return colors, rounds.value
+
+
+NOALLOC_MAX_VERTS = 262144     # SPGX_NOALLOC_MAX_VERTS, include/spgx.h
+NOALLOC_MAX_ENTRIES = 2097152  # SPGX_NOALLOC_MAX_ENTRIES
+
+
+def color_vertices_noalloc(ctx, n_verts: int, d_entries, n_entries, stencil_sizes, d_colors: int) -> int:
+    """spgx_color_vertices_noalloc: the device colouring out of the library's static scratch (no cudaMalloc / cudaFree).
+    d_entries: DEVICE addresses (ints) of the flat int32 stencil arrays, n_entries / stencil_sizes: their lengths and
+    stencil sizes, d_colors: DEVICE address of n_verts int32. Returns the number of dependency levels."""
+    ptrs = (C.c_void_p * len(d_entries))(*[int(p) for p in d_entries])
+    n_entries = np.ascontiguousarray(n_entries, dtype=np.int64)
+    sizes = np.ascontiguousarray(stencil_sizes, dtype=np.int32)
+    rounds = C.c_int(0)
+    check(lib.spgx_color_vertices_noalloc(ctx.handle, n_verts, len(d_entries), ptrs, n_entries.ctypes.data_as(_lp), _i(sizes),
+                                          C.c_void_p(int(d_colors)), C.byref(rounds)))
+    return rounds.value
 
 
 def color_stencils(stencils) -> np.ndarray:

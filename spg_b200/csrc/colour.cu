@@ -18,6 +18,7 @@
 #include <cooperative_groups.h>
 
 #include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "group.h"
@@ -322,5 +323,202 @@ extern "C" int spgx_color_vertices_device(spgx_ctx *ctx, int nVerts, int nSets, 
         for (int s = 0; s < nSets; ++s) sets.push_back({entries[s], nEntries[s], stencilSizes[s]});
         const auto c = colorVerticesDevice(ctx, nVerts, sets, rounds);
         std::copy(c.begin(), c.end(), colors);
+    });
+}
+
+// ---- the same colouring for callers that may not allocate -------------------------------------------------------------------
+// spgx_color_vertices_noalloc: no counterpart in the reference; added for callers that
+// cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Everything
+// colorVerticesDevice allocates per call -- incidence counts, row pointers, incidence lists, readiness counters, the two
+// frontiers, the frontier sizes and the result state -- lives in ONE file-scope device array of a fixed, modest size
+// (kNoAllocMaxVerts vertices, kNoAllocMaxEntries stencil entries: about 13 MiB, held by every GPU that loads the library
+// until exit).  Inputs and the output are the caller's DEVICE buffers; the row-pointer scan runs on the device instead of the
+// host.  Every call shares the array and finds the previous call's contents in it: what has to start at zero is cleared at
+// the start of each call, and two calls that overlap on the GPU (two streams, two threads, two contexts on one device) race.
+namespace spgx
+{
+namespace
+{
+constexpr int kNoAllocMaxVerts = SPGX_NOALLOC_MAX_VERTS;            // include/spgx.h
+constexpr long long kNoAllocMaxEntries = SPGX_NOALLOC_MAX_ENTRIES;
+
+struct NoAllocScratch {
+    uint32_t sizes[4];   // three rotating frontier sizes (+ pad)
+    uint32_t state[4];   // levels, nodes coloured, out-of-range entries seen, pad
+    uint32_t pad[56];    // the arrays below start on a 256-byte boundary
+    uint32_t deg[kNoAllocMaxVerts];           // incidence counts, then the fill cursor
+    uint32_t nodePtr[kNoAllocMaxVerts + 64];  // nVerts + 1 used
+    uint32_t cnt[kNoAllocMaxVerts];
+    int32_t frontier[2][kNoAllocMaxVerts];
+    int32_t nodeEdges[kNoAllocMaxEntries];
+};
+}  // namespace
+}  // namespace spgx
+
+// In host code this name is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress (below).
+static __device__ __align__(256) unsigned char g_colourNoAllocScratch[sizeof(spgx::NoAllocScratch)];
+
+namespace spgx
+{
+namespace
+{
+// an entry outside [0, nVerts) is counted, not followed (the allocating entry point validates on the host instead)
+__global__ void rangeCheckKernel(const ColourSets cs, long long nEntries, int nVerts, uint32_t *bad)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= nEntries) return;
+    const int k = setOfEntry(cs, i);
+    const int v = cs.entries[k][i - cs.entryBase[k]];
+    if (v < 0 || v >= nVerts) atomicAdd(bad, 1u);
+}
+
+// nodePtr[0] = 0, nodePtr[v + 1] = deg[0] + ... + deg[v]: one block, a contiguous run of nodes per thread, the per-thread
+// totals scanned through shared memory (the allocating entry point scans on the host)
+constexpr int kScanThreads = 1024;
+__global__ void __launch_bounds__(kScanThreads) rowPointerKernel(const uint32_t *deg, uint32_t *nodePtr, int n)
+{
+    __shared__ uint32_t warpTotals[kScanThreads / 32];
+    const int per = (n + kScanThreads - 1) / kScanThreads;
+    const int begin = min(n, static_cast<int>(threadIdx.x) * per), end = min(n, begin + per);
+    uint32_t sum = 0;
+    for (int v = begin; v < end; ++v) sum += deg[v];
+    uint32_t incl = sum;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+    }
+    if (lane == 31) warpTotals[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = warpTotals[lane];
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t up = __shfl_up_sync(0xffffffffu, w, d);
+            if (lane >= d) w += up;
+        }
+        warpTotals[lane] = w;
+    }
+    __syncthreads();
+    uint32_t run = incl - sum + (warp ? warpTotals[warp - 1] : 0u);
+    if (threadIdx.x == 0) nodePtr[0] = 0u;
+    for (int v = begin; v < end; ++v) {
+        run += deg[v];
+        nodePtr[v + 1] = run;
+    }
+}
+
+// the device address of the scratch array, taken once per device with that device current
+NoAllocScratch *noAllocScratch(int device)
+{
+    constexpr int kMaxDevices = 64;
+    static std::mutex mutex;
+    static NoAllocScratch *address[kMaxDevices] = {};
+    if (device < 0 || device >= kMaxDevices) throw std::runtime_error("spgx_color_vertices_noalloc: device ordinal out of range");
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!address[device]) {
+        SPGX_CUDA(cudaSetDevice(device));
+        void *p = nullptr;
+        SPGX_CUDA(cudaGetSymbolAddress(&p, g_colourNoAllocScratch));
+        address[device] = static_cast<NoAllocScratch *>(p);
+    }
+    return address[device];
+}
+}  // namespace
+}  // namespace spgx
+
+// d_entries: nSets DEVICE arrays of vertex ids (the array of pointers itself is host memory); d_colors: nVerts ints on the
+// device; *rounds (host, may be NULL): levels of the dependency DAG.  Runs on the context's stream and returns after it.
+extern "C" int spgx_color_vertices_noalloc(spgx_ctx *ctx, int nVerts, int nSets, const int32_t *const *d_entries, const int64_t *nEntries,
+                                           const int32_t *stencilSizes, int32_t *d_colors, int *rounds)
+{
+    return guarded([&] {
+        if (!ctx) throw StateError("null context");
+        if (rounds) *rounds = 0;
+        if (nVerts < 0 || nSets < 0) throw std::runtime_error("spgx_color_vertices_noalloc: negative size");
+        if (nVerts > kNoAllocMaxVerts)
+            throw std::runtime_error("spgx_color_vertices_noalloc: " + std::to_string(nVerts) + " vertices exceed the static scratch (" +
+                                     std::to_string(kNoAllocMaxVerts) + "); use spgx_color_vertices_device");
+        if (nSets > kMaxSets) throw std::runtime_error("too many stencil sets for the device colouring");
+        ColourSets cs{};
+        cs.nSets = nSets;
+        long long total = 0, nEdges = 0;
+        for (int k = 0; k < nSets; ++k) {
+            if (nEntries[k] < 0 || stencilSizes[k] <= 0 || nEntries[k] % stencilSizes[k]) throw std::runtime_error("spgx_color_vertices_noalloc: bad stencil set");
+            cs.entries[k] = d_entries[k];
+            cs.S[k] = stencilSizes[k];
+            cs.entryBase[k] = total;
+            cs.edgeBase[k] = static_cast<int>(nEdges);
+            total += nEntries[k];
+            nEdges += nEntries[k] / stencilSizes[k];
+            if (total > kNoAllocMaxEntries)
+                throw std::runtime_error("spgx_color_vertices_noalloc: the stencil entries exceed the static scratch (" +
+                                         std::to_string(kNoAllocMaxEntries) + "); use spgx_color_vertices_device");
+        }
+        cs.entryBase[nSets] = total;
+        cs.edgeBase[nSets] = static_cast<int>(nEdges);
+        if (nVerts == 0) return;
+        if (!d_colors) throw std::runtime_error("spgx_color_vertices_noalloc: null output");
+        NoAllocScratch *sc = noAllocScratch(ctx->device);  // the device address, never the host-side name of the array
+        SPGX_CUDA(cudaSetDevice(ctx->device));
+        cudaStream_t st = ctx->stream;
+        const int threads = 256;
+        const auto blocks = [&](long long n) { return static_cast<unsigned>((n + threads - 1) / threads); };
+        const size_t vBytes = static_cast<size_t>(nVerts) * sizeof(uint32_t);
+
+        // the array keeps the previous call's contents: sizes, state and the incidence counts start at zero
+        SPGX_CUDA(cudaMemsetAsync(sc->sizes, 0, sizeof(sc->sizes) + sizeof(sc->state), st));
+        SPGX_CUDA(cudaMemsetAsync(sc->deg, 0, vBytes, st));
+        SPGX_CUDA(cudaMemsetAsync(d_colors, 0xFF, vBytes, st));
+        uint32_t host[4] = {0, 0, 0, 0};
+        if (total) {
+            rangeCheckKernel<<<blocks(total), threads, 0, st>>>(cs, total, nVerts, sc->state + 2);
+            SPGX_CUDA(cudaMemcpyAsync(host, sc->state, sizeof(host), cudaMemcpyDeviceToHost, st));
+            SPGX_CUDA(cudaStreamSynchronize(st));
+            if (host[2]) throw std::runtime_error("Trying to add edge to graph with invalid node indices");
+            degreeKernel<<<blocks(total), threads, 0, st>>>(cs, total, sc->deg);
+        }
+        rowPointerKernel<<<1, kScanThreads, 0, st>>>(sc->deg, sc->nodePtr, nVerts);
+        SPGX_CUDA(cudaMemsetAsync(sc->deg, 0, vBytes, st));  // reused as the fill cursor
+        if (total) fillKernel<<<blocks(total), threads, 0, st>>>(cs, total, sc->nodePtr, sc->deg, sc->nodeEdges);
+        dependencyKernel<<<blocks(nVerts), threads, 0, st>>>(cs, nVerts, sc->nodePtr, sc->nodeEdges, sc->cnt, sc->frontier[0], sc->sizes);
+
+        int coop = 0, perSm = 0;
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, ctx->device);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, colourAllLevelsKernel, kLevelThreads, 0);
+        bool doneOnDevice = false;
+        if (coop && perSm >= 1) {
+            const int gridBlocks = std::min(ctx->prop.multiProcessorCount, 96);
+            int32_t *fa = sc->frontier[0], *fb = sc->frontier[1], *colourPtr = d_colors;
+            uint32_t *sizesPtr = sc->sizes, *cntPtr = sc->cnt, *statePtr = sc->state;
+            const uint32_t *np = sc->nodePtr;
+            const int32_t *ne = sc->nodeEdges;
+            void *kargs[] = {&cs, &np, &ne, &fa, &fb, &sizesPtr, &colourPtr, &cntPtr, &statePtr};
+            if (cudaLaunchCooperativeKernel(reinterpret_cast<void *>(colourAllLevelsKernel), dim3(gridBlocks), dim3(kLevelThreads), kargs, 0, st) ==
+                cudaSuccess) {
+                SPGX_CUDA(cudaMemcpyAsync(host, sc->state, sizeof(host), cudaMemcpyDeviceToHost, st));
+                SPGX_CUDA(cudaStreamSynchronize(st));
+                doneOnDevice = true;
+            } else {
+                cudaGetLastError();
+            }
+        }
+        if (!doneOnDevice) {  // one launch per level, the frontier size read back in between
+            host[0] = host[1] = 0;
+            for (uint32_t level = 0;; ++level) {
+                uint32_t size = 0;
+                SPGX_CUDA(cudaMemcpyAsync(&size, sc->sizes + level % 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                SPGX_CUDA(cudaStreamSynchronize(st));
+                if (size == 0) break;
+                SPGX_CUDA(cudaMemsetAsync(sc->sizes + (level + 1) % 3, 0, sizeof(uint32_t), st));
+                colourLevelKernel<<<blocks(size), threads, 0, st>>>(cs, sc->nodePtr, sc->nodeEdges, sc->frontier[level & 1u], size, d_colors, sc->cnt,
+                                                                   sc->frontier[1 - (level & 1u)], sc->sizes + (level + 1) % 3);
+                host[0] = level + 1;
+                host[1] += size;
+            }
+            SPGX_CUDA(cudaStreamSynchronize(st));
+        }
+        SPGX_CUDA(cudaGetLastError());
+        if (static_cast<long long>(host[1]) != nVerts) throw std::runtime_error("device colouring: the dependency levels did not reach every vertex");
+        if (rounds) *rounds = static_cast<int>(host[0]);
     });
 }
