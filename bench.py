@@ -491,6 +491,10 @@ def measure_single(ctx, cfg_id, steps, warmup, rows=0, e2e=True, cpu=True, clock
                 "algorithmic_bytes_per_unit": bytes_iter * sweeps / units_per_frame,
                 "lower_bound_frac": bytes_lower * sweeps / (solve_ms_per_frame * 1e-3) / 1e9 / peak,
                 "kernel_share_of_step": solve_ms_per_frame / (tp.total_ms / rf), "peak_source": peak_src}
+    if solver == "vbd":
+        # variant: resident blocks + 10 x "records through the shared-memory ring"; wedge_records: fan triangles whose membrane and
+        # two hinges are ONE record of the colour pass (streams.cuh: ST_WEDGE)
+        roofline["kernel_variant"] = {"lanes": info["lanes"], "variant": info["variant"], "wedge_records": info["wedge_records"]}
     # the same bytes over the whole step AS TIMED (graph replay, predict / finalize included): `frac` above is measured with
     # per-phase events in plain-launch mode, where a launch-bound sequence (XPBD: 540 passes of a few microseconds) pays the
     # full launch latency per pass that the replayed graph does not

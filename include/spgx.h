@@ -239,7 +239,7 @@ enum spgx_halo_mode { SPGX_HALO_NONE = 0, SPGX_HALO_NCCL = 1, SPGX_HALO_P2P = 2 
 /* choose the exchange of the next step() (P2P needs a connected group); *mode out when not NULL */
 int spgx_group_set_halo_mode(spgx_group *grp, int mode);
 int spgx_group_get_halo_mode(spgx_group *grp, int *mode);
-/* out8 = [streaming kernel in use, lanes per vertex, warp-slices, largest unique-neighbour count, halo mode,
+/* out8 = [stream types in use (bit mask of the streaming kernel's record types, 0: generic path) | wedge records << 8, lanes per vertex, warp-slices, largest unique-neighbour count, halo mode,
  * boundary stores per sweep, dependency levels of the device-built colouring (0: host colouring), kernel variant] */
 int spgx_group_kernel_info(spgx_group *grp, int64_t *out8);
 

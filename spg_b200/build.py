@@ -20,8 +20,8 @@ LIBDIR = ROOT / "spg_b200" / "lib"
 OBJDIR = ROOT / "build" / "obj"
 LIB = LIBDIR / "libspgx.so"
 
-CU_SOURCES = ["api_build.cu", "api_step.cu", "vbd.cu", "vbd_stream_cloth.cu", "vbd_stream_tets.cu", "xpbd.cu", "state.cu", "comm.cu", "newton.cu", "api_newton.cu", "rigid.cu", "colour.cu"]
-HEADERS = ["dual.cuh", "halo.cuh", "linalg.cuh", "energies.cuh", "streams.cuh", "vbd_stream.cuh", "energy_prepare.h", "host_build.h", "partition.h",
+CU_SOURCES = ["api_build.cu", "api_step.cu", "vbd.cu", "vbd_stream_cloth.cu", "vbd_stream_cloth_wedge.cu", "vbd_stream_tets.cu", "xpbd.cu", "state.cu", "comm.cu", "newton.cu", "api_newton.cu", "rigid.cu", "colour.cu"]
+HEADERS = ["dual.cuh", "halo.cuh", "linalg.cuh", "energies.cuh", "streams.cuh", "stream_records.h", "vbd_stream.cuh", "energy_prepare.h", "host_build.h", "partition.h",
            "kernels.h", "group.h", "kinds.def", "xpbd_partition.h", "hinge_hessian.cuh", "membrane_hessian.cuh", "rigid.cuh"]
 
 NVCC_FLAGS = [

@@ -2,6 +2,7 @@
 // finalize (colouring + incidence + upload).  See include/spgx.h for the reference interface each
 // entry point replaces.
 #include <algorithm>
+#include <array>
 #include <chrono>
 #include <cstdio>
 #include <exception>
@@ -15,6 +16,7 @@
 #include "host_build.h"
 #include "partition.h"
 #include "xpbd_partition.h"
+#include "stream_records.h"
 #include "streams.cuh"
 
 namespace spgx
@@ -80,6 +82,32 @@ static void checkKind(int kind)
     if (kind < 0 || kind >= K_COUNT) throw std::runtime_error("unknown energy kind");
 }
 
+// the group's energies as stream_records.h sees them (vertex ids, reference order)
+static std::vector<StreamEnergyView> streamEnergyViews(const spgx_group &grp, const std::vector<Incidence> &inc)
+{
+    std::vector<StreamEnergyView> views(grp.energies.size());
+    for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+        const auto &e = grp.energies[ei];
+        views[ei] = {e.kind, e.S, e.NP, e.stencils.data(), e.records.data(), inc[ei].rowptr.data(), inc[ei].flat.data()};
+    }
+    return views;
+}
+// which energies form wedges (streams.cuh: Stream<ST_WEDGE>): exactly one discrete-bending and one StVK-membrane energy and no
+// tetrahedra (the wedge stream takes the descriptor word of ST_TET_STVK); -1, -1 otherwise or with SPGX_VBD_WEDGE=0
+static void streamWedgeEnergies(const spgx_group &grp, int &wedgeB, int &wedgeM)
+{
+    wedgeB = wedgeM = -1;
+    if (!grp.vbdWedge) return;
+    int nb = 0, nm = 0, nt = 0, b = -1, m = -1;
+    for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+        const int k = grp.energies[ei].kind;
+        if (k == K_DISCRETE_BENDING) ++nb, b = static_cast<int>(ei);
+        if (k == K_MEMBRANE_STVK) ++nm, m = static_cast<int>(ei);
+        if (k == K_TET_SNH || k == K_TET_STVK) ++nt;
+    }
+    if (nb == 1 && nm == 1 && nt == 0) wedgeB = b, wedgeM = m;
+}
+
 // Streaming layout of the VBD colour pass (kernels.h, streams.cuh).  For every vertex (in slot order): the list of its
 // unique neighbours over all streamed incidences (first-seen order), and per stream type the canonical incidence
 // records referencing that list by 8-bit index.  Both are packed as sliced ELL over warp-slices of VW = 32 / G
@@ -116,9 +144,19 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         }
     }
     if (!any) return false;
+    // wedges (streams.cuh: Stream<ST_WEDGE>): a cloth whose discrete bending and StVK membrane cover the same triangles
+    const std::vector<StreamEnergyView> views = streamEnergyViews(grp, inc);
+    int wedgeB = -1, wedgeM = -1;
+    streamWedgeEnergies(grp, wedgeB, wedgeM);
+    if (wedgeB >= 0) {
+        hs[ST_WEDGE].energy = wedgeM;
+        hs[ST_WEDGE].NQ = streamNQ(ST_WEDGE);
+        hs[ST_WEDGE].rowptr.assign(static_cast<size_t>(NO) + 1, 0);
+    }
 
-    // per slot: unique neighbours (first-seen order) and the canonical records of its incidences -- slots are independent, so
-    // contiguous chunks of slots are built on host threads into chunk-local arrays and concatenated in slot order
+    // per slot: unique neighbours (first-seen order) and the canonical records of its incidences (stream_records.h) -- slots
+    // are independent, so contiguous chunks of slots are built on host threads into chunk-local arrays and concatenated in
+    // slot order
     std::vector<uint32_t> nbrRowptr(static_cast<size_t>(NO) + 1, 0);
     std::vector<uint32_t> nbrList;
     std::vector<uint8_t> hasCsr(static_cast<size_t>(NO), 0);
@@ -136,42 +174,15 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         std::vector<Chunk> chunks(static_cast<size_t>(nChunks));
         parallelChunks(NO, nChunks, [&](int64_t s0, int64_t s1, int c) {
             Chunk &ck = chunks[static_cast<size_t>(c)];
-            std::vector<int32_t> seen;  // neighbour vertex ids of the current slot (a handful: a linear scan beats a V-sized mark array)
+            SlotScratch sc;
             for (int64_t s = s0; s < s1; ++s) {
                 const int v = grp.slot2vert[static_cast<size_t>(s)];
-                seen.clear();
-                const size_t nb0 = ck.nbr.size();
                 for (int t = 0; t < ST_COUNT; ++t)
                     if (hs[t].energy >= 0) hs[t].rowptr[static_cast<size_t>(s)] = static_cast<uint32_t>(ck.idx[t].size());  // chunk-local for now
-                for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
-                    const auto &e = grp.energies[ei];
-                    if (streamTypeOf(e.kind, 0) < 0) {
-                        if (inc[ei].rowptr[v + 1] > inc[ei].rowptr[v]) hasCsr[static_cast<size_t>(s)] = 1;
-                        continue;
-                    }
-                    for (int64_t q = inc[ei].rowptr[v]; q < inc[ei].rowptr[v + 1]; ++q) {
-                        const int64_t stencil = inc[ei].flat[q] / e.S;
-                        const int local = static_cast<int>(inc[ei].flat[q] % e.S);
-                        const int type = streamTypeOf(e.kind, local);
-                        int32_t nbr[3];
-                        double rq[16];
-                        makeStreamRecord(e.kind, e.stencils.data() + stencil * e.S, e.records.data() + stencil * e.NP, local, nbr, rq);
-                        uint32_t word = 0;
-                        for (int k = 0; k < streamNI(type); ++k) {
-                            const int u = nbr[k];
-                            size_t li = 0;
-                            while (li < seen.size() && seen[li] != u) ++li;
-                            if (li == seen.size()) {
-                                seen.push_back(u);
-                                ck.nbr.push_back(static_cast<uint32_t>(grp.vert2slot[u]));
-                            }
-                            word |= static_cast<uint32_t>(li & 0xFFu) << (8 * k);
-                        }
-                        ck.idx[type].push_back(word);
-                        ck.q[type].insert(ck.q[type].end(), rq, rq + hs[type].NQ);
-                    }
-                }
-                const int cnt = static_cast<int>(ck.nbr.size() - nb0);
+                if (appendSlotRecords(views.data(), static_cast<int>(views.size()), v, wedgeB, wedgeM, sc, ck.idx, ck.q))
+                    hasCsr[static_cast<size_t>(s)] = 1;
+                for (const int32_t u : sc.seen) ck.nbr.push_back(static_cast<uint32_t>(grp.vert2slot[u]));
+                const int cnt = static_cast<int>(sc.seen.size());
                 if (cnt > 254) ck.tooMany = true;
                 ck.maxNbr = std::max(ck.maxNbr, cnt);
                 nbrRowptr[static_cast<size_t>(s) + 1] = static_cast<uint32_t>(cnt);  // a count for now
@@ -304,12 +315,12 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         const int NQ = h.NQ;
         uint32_t step = 0;
         for (size_t sl = 0; sl < nSlices; ++sl) {
-            desc[sl * kSliceDescWords + 2 + type] = step;
+            desc[sl * kSliceDescWords + streamDescWord(type)] = step;
             uint32_t steps = 0;
             for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) steps = std::max(steps, (h.rowptr[s + 1] - h.rowptr[s] + G - 1) / G);
             step += steps;
         }
-        desc[nSlices * kSliceDescWords + 2 + type] = step;
+        desc[nSlices * kSliceDescWords + streamDescWord(type)] = step;
         const size_t T = step;
         std::vector<uint32_t> idx(T * 32, 0xFFFFFFFFu);
         std::vector<double> params(T * NQ * 32, 0.0);
@@ -318,7 +329,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
                 for (int s = sliceSlot[sl]; s < sliceEnd[sl]; ++s) {
                     uint32_t j = 0;
                     for (uint32_t r = h.rowptr[s]; r < h.rowptr[s + 1]; ++r, ++j) {
-                        const size_t t = desc[sl * kSliceDescWords + 2 + type] + j / G;
+                        const size_t t = desc[sl * kSliceDescWords + streamDescWord(type)] + j / G;
                         const int lane = static_cast<int>(j % G) * VW + (s - sliceSlot[sl]);
                         idx[t * 32 + lane] = h.idx[r];
                         for (int k = 0; k < NQ; ++k) params[(t * NQ + k) * 32 + lane] = h.q[static_cast<size_t>(r) * NQ + k];
@@ -329,7 +340,7 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
         out.type = type;
         out.d_idx.upload(idx, st);
         out.d_params.upload(params, st);
-        grp.streamMask |= 1u << type;
+        if (T > 0) grp.streamMask |= 1u << type;  // (a type without a single record -- e.g. every membrane incidence joined a wedge -- has no stream)
         bytes += 4.0 * idx.size() + 8.0 * params.size();
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
@@ -340,45 +351,62 @@ static bool buildStreams(spgx_group &grp, const std::vector<Incidence> &inc, cud
     grp.nSlices = static_cast<int>(nSlices);
     grp.maxNbr = maxNbr;
     grp.streamBytes = bytes;
+    grp.wedgeRecords = static_cast<int64_t>(hs[ST_WEDGE].idx.size());
     for (auto &e : grp.energies) e.streamed = streamTypeOf(e.kind, 0) >= 0;
     return true;
 }
 
 // spgx_energy_update_record on an energy whose incidences live in streams: the colour pass never reads d_records for it,
-// it reads the canonical per-incidence records baked into the streams at finalize (buildStreams).  Re-canonicalise the S
-// incidences of the edited stencil and overwrite them in place.  Where an incidence sits: its owner's slot fixes the
-// warp-slice and the column; its rank among the owner's incidences of the same stream type (ascending flat index, the
-// order buildStreams walked) fixes the step and the lane group.  The rank is recounted from the stencil list (a linear
-// scan: record edits are rare, a table would cost 8 bytes per incidence at every finalize).
-static void patchStreamRecords(spgx_group &grp, const EnergyState &e, int stencil)
+// it reads the canonical per-incidence records baked into the streams at finalize (buildStreams).  For every vertex of the
+// edited stencil that this rank owns, the vertex's records are built again (stream_records.h: the same function, so the same
+// assignment of incidences to stream types, wedges included, and the same order) and their constants overwritten in place.
+// Where record j of a type sits: the vertex's slot fixes the warp-slice and the column, j the step and the lane group.
+// The incidence lists come from a scan of the stencil arrays (record edits are rare; a table would cost 8 bytes per incidence
+// at every finalize).
+static void patchStreamRecords(spgx_group &grp, const EnergyState &edited, int stencil)
 {
     const int G = grp.vbdLanes, VW = 32 / G;
     cudaStream_t st = grp.ctx->stream;
-    const int32_t *ids = e.stencils.data() + static_cast<size_t>(stencil) * e.S;
-    const double *rec = e.records.data() + static_cast<size_t>(stencil) * e.NP;
-    for (int local = 0; local < e.S; ++local) {
-        const int type = streamTypeOf(e.kind, local);
-        if (type < 0) continue;
-        const int v = ids[local];
+    int wedgeB = -1, wedgeM = -1;
+    streamWedgeEnergies(grp, wedgeB, wedgeM);
+    for (int local = 0; local < edited.S; ++local) {
+        const int v = edited.stencils[static_cast<size_t>(stencil) * edited.S + local];
+        bool earlier = false;  // the same vertex twice in the stencil: patched once
+        for (int l = 0; l < local; ++l) earlier |= edited.stencils[static_cast<size_t>(stencil) * edited.S + l] == v;
         const int slot = grp.vert2slot[v];
-        if (slot < 0 || slot >= grp.nOwned) continue;  // a halo copy: its owner patches it
-        const int64_t flat = static_cast<int64_t>(stencil) * e.S + local;
-        uint32_t j = 0;  // incidences of v in this energy, of the same stream type, before this one
-        for (int64_t q = 0; q < flat; ++q)
-            if (e.stencils[static_cast<size_t>(q)] == v && streamTypeOf(e.kind, static_cast<int>(q % e.S)) == type) ++j;
+        if (earlier || slot < 0 || slot >= grp.nOwned) continue;  // a halo copy: its owner patches it
+        // incidence lists of v alone, addressed as "vertex 0" of a one-row CSR per energy
+        std::vector<std::vector<int64_t>> flat(grp.energies.size());
+        std::vector<std::array<int64_t, 2>> rowptr(grp.energies.size());
+        std::vector<StreamEnergyView> views(grp.energies.size());
+        for (size_t ei = 0; ei < grp.energies.size(); ++ei) {
+            const auto &e = grp.energies[ei];
+            if (streamTypeOf(e.kind, 0) >= 0)
+                for (size_t q = 0; q < e.stencils.size(); ++q)
+                    if (e.stencils[q] == v) flat[ei].push_back(static_cast<int64_t>(q));
+            rowptr[ei] = {0, static_cast<int64_t>(flat[ei].size())};
+            // (rows are looked up at index v: shift the base pointers so that row v is the one row there is)
+            views[ei] = {e.kind, e.S, e.NP, e.stencils.data(), e.records.data(), rowptr[ei].data() - v, flat[ei].data()};
+        }
+        SlotScratch sc;
+        std::vector<uint32_t> idx[ST_COUNT];
+        std::vector<double> q[ST_COUNT];
+        appendSlotRecords(views.data(), static_cast<int>(views.size()), v, wedgeB, wedgeM, sc, idx, q);
         int colour = 0;
         while (grp.colorOffsets[colour + 1] <= slot) ++colour;
         const int inColour = slot - static_cast<int>(grp.colorOffsets[colour]);
         const size_t slice = static_cast<size_t>(grp.sliceBase[colour]) + inColour / VW;
-        const uint32_t t = grp.sliceDescHost[slice * kSliceDescWords + 2 + type] + j / G;
-        const int lane = static_cast<int>(j % G) * VW + inColour % VW;
-        int32_t nbr[3];
-        double q[16];
-        makeStreamRecord(e.kind, ids, rec, local, nbr, q);
-        const int NQ = streamNQ(type);
-        double *dst = grp.streams[type].d_params.ptr + static_cast<size_t>(t) * NQ * 32 + lane;
-        // q[k] goes to params[t][k][lane]: NQ doubles, 32 doubles apart
-        SPGX_CUDA(cudaMemcpy2DAsync(dst, 32 * sizeof(double), q, sizeof(double), sizeof(double), NQ, cudaMemcpyHostToDevice, st));
+        for (int type = 0; type < ST_COUNT; ++type) {
+            const int NQ = streamNQ(type);
+            for (size_t j = 0; j < idx[type].size(); ++j) {
+                const uint32_t t = grp.sliceDescHost[slice * kSliceDescWords + streamDescWord(type)] + static_cast<uint32_t>(j) / G;
+                const int lane = static_cast<int>(j % G) * VW + inColour % VW;
+                double *dst = grp.streams[type].d_params.ptr + static_cast<size_t>(t) * NQ * 32 + lane;
+                // q[k] goes to params[t][k][lane]: NQ doubles, 32 doubles apart
+                SPGX_CUDA(cudaMemcpy2DAsync(dst, 32 * sizeof(double), q[type].data() + j * NQ, sizeof(double), sizeof(double), NQ,
+                                            cudaMemcpyHostToDevice, st));
+            }
+        }
         SPGX_CUDA(cudaStreamSynchronize(st));
     }
 }
@@ -565,7 +593,7 @@ int spgx_group_kernel_info(spgx_group *grp, int64_t *out8)
 {
     return guarded([&] {
         if (!grp || !grp->finalized || !out8) throw StateError("group is not finalized");
-        out8[0] = grp->streamMask != 0, out8[1] = grp->vbdLanes, out8[2] = grp->nSlices, out8[3] = grp->maxNbr;
+        out8[0] = static_cast<int64_t>(grp->streamMask) | (grp->wedgeRecords << 8), out8[1] = grp->vbdLanes, out8[2] = grp->nSlices, out8[3] = grp->maxNbr;
         out8[4] = grp->p2p.mode, out8[5] = static_cast<int64_t>(grp->p2p.sendSlots.size()), out8[6] = grp->colouringRounds, out8[7] = grp->vbdOcc;
     });
 }
@@ -961,13 +989,15 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                 if (l == 2 || l == 4) grp->vbdLanes = l;
             }
             // kernel variant (vbd_stream.cuh launchStreamG): resident blocks per SM + 10 x "records through the shared-memory ring"
-            grp->vbdOcc = 4;
+            grp->vbdOcc = 0;  // 0: chosen once the streams are built (4, or 14 for a group with wedge records)
             if (const char *env = getenv("SPGX_VBD_VARIANT")) {
                 const int o = atoi(env);
-                if (o == 4 || o == 15) grp->vbdOcc = o;
+                if (o == 4 || o == 14 || o == 15) grp->vbdOcc = o;
             }
             grp->vbdNbrFixed = 1;
             if (const char *env = getenv("SPGX_VBD_NBRFIXED")) grp->vbdNbrFixed = atoi(env) != 0;
+            grp->vbdWedge = 1;
+            if (const char *env = getenv("SPGX_VBD_WEDGE")) grp->vbdWedge = atoi(env) != 0;
             grp->sliceBase.assign(grp->colorOffsets.size(), 0);
             for (size_t c = 0; c + 1 < grp->colorOffsets.size(); ++c) {
                 const int64_t n = grp->colorOffsets[c + 1] - grp->colorOffsets[c];
@@ -1032,6 +1062,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             grp->streams.clear();
             grp->streamMask = 0;
             grp->maxNbr = 0;
+            grp->wedgeRecords = 0;
             grp->streamBytes = 0;
             grp->d_sliceDesc.release();
             grp->d_nbrIds.release();
@@ -1067,6 +1098,7 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
                     }
                 }
             }
+            if (grp->vbdOcc == 0) grp->vbdOcc = grp->wedgeRecords > 0 ? 14 : 4;  // vbd_stream.cuh: launchStreamG
             pt.lap("stream layout (buildStreams)");
             // distinct stencil neighbours per vertex (for the byte model)
             {

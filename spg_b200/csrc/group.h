@@ -221,6 +221,8 @@ struct spgx_group {
     int vbdLanes = 4;                   // threads per vertex in the VBD colour pass
     int vbdOcc = 4;                     // resident-blocks-per-SM hint of the streaming kernel
     int vbdNbrFixed = 1;                // neighbour table at a fixed stride per slice (kernels.h: VbdArgs::nbrFixed)
+    int vbdWedge = 1;                   // membrane + bending incidences of one fan triangle joined into one record (streams.cuh: ST_WEDGE)
+    int64_t wedgeRecords = 0;           // wedge records of the owned vertices (kernel_info)
     // streaming layout (kernels.h): unique-neighbour tables + one stream per (energy, stream type)
     struct StreamState {
         int type = 0;

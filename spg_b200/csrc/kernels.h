@@ -18,7 +18,7 @@ struct VbdEnergyDev {
     int streamed;              // 1: every incidence of this energy lives in a stream below (the CSR path skips it)
 };
 
-constexpr int kNumStreamTypes = 5;  // StreamType (streams.cuh)
+constexpr int kNumStreamTypes = 6;  // StreamType (streams.cuh)
 constexpr int kSliceDescWords = 8;
 // One owner-centric incidence stream (streams.cuh): a sliced ELL over warp-slices of VW = 32 / G consecutive slots of
 // one colour.  Step t of a slice holds one incidence per lane (lane = sub * VW + v carries incidence t * G + sub of the
@@ -62,7 +62,8 @@ struct VbdArgs {
     int nStreams;
     VbdStreamDev s[kNumStreamTypes];  // indexed by StreamType
     // per warp-slice descriptor, kSliceDescWords uint32 each, nSlices + 1 entries (the last one closes the ranges):
-    //   [0] first slot, [1] first row of the unique-neighbour table, [2 + t] first step of stream type t,
+    //   [0] first slot, [1] first row of the unique-neighbour table, [streamDescWord(t)] first step of stream type t (2 + t;
+    //       the wedge stream of a cloth takes the word of ST_TET_STVK),
     //   [7] bit 0: some vertex of the slice has incidences on the CSR path; bit 1: the slice reads halo slots;
     //       bit 2: uniform slice (full, every vertex the same number of incidences per stream, a multiple of 2 G);
     //       bits 3..31: number of push entries (VbdHaloDev::push) of all earlier slices

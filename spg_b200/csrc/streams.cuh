@@ -26,7 +26,8 @@ enum StreamType : int {
     ST_MEMBRANE_STVK = 2,  // StVK membrane triangle
     ST_TET_SNH = 3,        // stable Neo-Hookean tetrahedron
     ST_TET_STVK = 4,       // StVK tetrahedron
-    ST_COUNT = 5
+    ST_WEDGE = 5,          // one triangle of the owner's fan: its StVK membrane + the two discrete-bending hinges that share its normal
+    ST_COUNT = 6
 };
 
 // 1 / x and 1 / sqrt(x) to double precision from the hardware seed (MUFU.RCP64H / RSQ64H) and two Newton steps,
@@ -295,6 +296,100 @@ struct Stream<ST_TET_STVK> {
     }
 };
 
+// ---- wedge: one triangle of the owner's fan with the two hinges that share its normal --------------------------------
+// A cloth vertex o with n incident triangles has n membrane incidences, n hinges whose edge starts at o and n hinges whose
+// edge lies opposite to o: three incidences per triangle (o, A, B) of the fan --
+//   the StVK membrane of (o, A, B),
+//   the hinge on the edge o-A, canonical (x0, x1, x2, x3) = (o, A, B, C), C = the vertex beyond o-A,
+//   the hinge on the edge A-B seen from o, canonical (x0, x1, x2, x3) = (A, B, o, R), R = the vertex beyond A-B
+// -- and as separate incidences each of them fetches o's neighbours, forms the edge vectors and the triangle normal
+// N = (A - o) x (B - o) and inverts |N|^2 for itself.  As ONE record (neighbours {A, B, C, R}, 4 x 8 bits;
+// q = {g_A(2), g_B(2), K00, K01, K22 | theta0, K of o-A | theta0, K of A-B}) the edge vectors, N, 1 / |N|^2, a = B - A and
+// T = a x N are formed once (T is t1 of the first hinge AND e x N1 of the second), the two sym2(N, .) Hessian terms merge
+// into one, a third of the neighbour reads and two of three loop steps go away.  Same formulas as the three evaluators
+// above (ST_MEMBRANE_STVK, ST_BEND_EDGE, ST_BEND_OPP), to which incidences that do not complete a wedge (mesh boundary,
+// non-manifold input) still go; which incidence joins which wedge is decided on the host (api_build.cu: buildSlotRecords).
+template <>
+struct Stream<ST_WEDGE> {
+    static constexpr int NI = 4, NQ = 11;
+    SPGX_HD static void eval(const V3d &xo, const V3d *xn, const double *q, V3d &gAcc, Sym3 &HAcc)
+    {
+        const V3d eA = xn[0] - xo, eB = xn[1] - xo;
+        {  // membrane (membraneStvkEnergy.cpp:9-28), dp = eA, dq = eB
+            const V3d F0 = eA * q[0] + eB * q[2], F1 = eA * q[1] + eB * q[3];
+            const double K00 = q[4], K01 = q[5], K22 = q[6];
+            const double C0 = 0.5 * (dot(F0, F0) - 1.0), C1 = 0.5 * (dot(F1, F1) - 1.0), C2 = dot(F0, F1);
+            const double s0 = K00 * C0 + K01 * C1, s1 = K01 * C0 + K00 * C1, s2 = K22 * C2;
+            const double ga = -(q[0] + q[2]), gb = -(q[1] + q[3]);
+            const double al0 = s0 * ga + s2 * gb, al1 = s1 * gb + s2 * ga;
+            gAcc.x = ::fma(al0, F0.x, ::fma(al1, F1.x, gAcc.x));
+            gAcc.y = ::fma(al0, F0.y, ::fma(al1, F1.y, gAcc.y));
+            gAcc.z = ::fma(al0, F0.z, ::fma(al1, F1.z, gAcc.z));
+            const double gaa = ga * ga, gbb = gb * gb, gab = ga * gb;
+            const double geo = s0 * gaa + s1 * gbb + 2.0 * (s2 * gab);
+            const double A = K00 * gaa + K22 * gbb, B = K00 * gbb + K22 * gaa, C = (K01 + K22) * gab;
+            const V3d P0 = F0 * A + F1 * C, P1 = F1 * B + F0 * C;
+            HAcc.xx = ::fma(F0.x, P0.x, ::fma(F1.x, P1.x, HAcc.xx + geo));
+            HAcc.yy = ::fma(F0.y, P0.y, ::fma(F1.y, P1.y, HAcc.yy + geo));
+            HAcc.zz = ::fma(F0.z, P0.z, ::fma(F1.z, P1.z, HAcc.zz + geo));
+            HAcc.xy = ::fma(F0.x, P0.y, ::fma(F1.x, P1.y, HAcc.xy));
+            HAcc.xz = ::fma(F0.x, P0.z, ::fma(F1.x, P1.z, HAcc.xz));
+            HAcc.yz = ::fma(F0.y, P0.z, ::fma(F1.y, P1.z, HAcc.yz));
+        }
+        // shared by the two hinges
+        const V3d N = cross(eA, eB);
+        const double iN = fastRcp(dot(N, N));
+        const V3d a = eB - eA;  // B - A
+        const V3d T = cross(a, N);
+        V3d vN;        // the Hessian gets sym2(N, vN), the gradient cN * N
+        double cN;
+        {  // hinge on o-A, owner at the start of the edge (Stream<ST_BEND_EDGE> with e = eA, a, b = C - A, N1 = N, t1 = T)
+            const V3d b = xn[2] - xn[0];
+            const V3d N2 = cross(b, eA);
+            const double ee = dot(eA, eA);
+            const double ie = fastRsqrt(ee);
+            const double le = ee * ie;
+            const double d = fastAtan2(-le * dot(N, b), dot(N, N2)) - q[7];
+            const double K = q[8], Kd = K * d;
+            const double i2 = fastRcp(dot(N2, N2));
+            const double ae = dot(a, eA), be = dot(b, eA);
+            const double phia = ae * ie, phib = be * ie;
+            const double ie3 = ie * ie * ie;
+            const V3d ga = a * ie - eA * (ae * ie3), gb = b * ie - eA * (be * ie3);
+            const double w1 = phia * iN, w2 = phib * i2;
+            const V3d g = -(N * w1 + N2 * w2);
+            const V3d t2 = cross(b, N2);
+            const double hKd = 0.5 * Kd;
+            vN = ga * (hKd * iN) - T * (Kd * w1 * iN);
+            const V3d v2 = gb * (hKd * i2) + t2 * (Kd * w2 * i2);
+            addSymOuter2u(HAcc, N2, v2);
+            addOuter(HAcc, g, K);
+            // Kd g = -(Kd w1) N - (Kd w2) N2: the N part joins the second hinge's
+            cN = -(Kd * w1);
+            const double c2 = -(Kd * w2);
+            gAcc.x = ::fma(c2, N2.x, gAcc.x);
+            gAcc.y = ::fma(c2, N2.y, gAcc.y);
+            gAcc.z = ::fma(c2, N2.z, gAcc.z);
+        }
+        {  // hinge on A-B, owner opposite (Stream<ST_BEND_OPP> with e = a, b = R - B, N1 = N, e x N1 = T)
+            const V3d b = xn[3] - xn[1];
+            const V3d N2 = cross(b, a);
+            const double aa = dot(a, a);
+            const double la = aa * fastRsqrt(aa);
+            const double d = fastAtan2(-la * dot(N, b), dot(N, N2)) - q[9];
+            const double K = q[10], Kd = K * d;
+            const double c = -la * iN;  // grad(theta) = c N
+            const double Kc = K * c;
+            vN = vN + T * (Kd * c * iN) + N * (0.5 * Kc * c);
+            cN = ::fma(Kd, c, cN);
+        }
+        addSymOuter2u(HAcc, N, vN);
+        gAcc.x = ::fma(cN, N.x, gAcc.x);
+        gAcc.y = ::fma(cN, N.y, gAcc.y);
+        gAcc.z = ::fma(cN, N.z, gAcc.z);
+    }
+};
+
 // ---- host side: which stream an incidence of `kind` at stencil position `local` goes to, and its canonical record ----
 // returns -1 when the kind has no stream (it then runs through the generic CSR path of the kernel)
 SPGX_HD int streamTypeOf(int kind, int local)
@@ -309,7 +404,14 @@ SPGX_HD int streamTypeOf(int kind, int local)
 }
 SPGX_HD int streamNI(int st)
 {
-    return st == ST_MEMBRANE_STVK ? 2 : 3;
+    return st == ST_MEMBRANE_STVK ? 2 : (st == ST_WEDGE ? 4 : 3);
+}
+// word of the 8-word slice descriptor (kernels.h: VbdArgs::sliceDesc) that holds the first step of a stream type.  Words 2..6
+// are the five single-incidence types; a wedge stream only exists next to cloth streams and takes the word of ST_TET_STVK
+// (buildStreams forms no wedges in a group that also holds tetrahedra)
+SPGX_HD constexpr int streamDescWord(int st)
+{
+    return st == ST_WEDGE ? 2 + ST_TET_STVK : 2 + st;
 }
 SPGX_HD int streamNQ(int st)
 {
@@ -319,6 +421,7 @@ SPGX_HD int streamNQ(int st)
     case ST_MEMBRANE_STVK: return 7;
     case ST_TET_SNH: return 12;
     case ST_TET_STVK: return 11;
+    case ST_WEDGE: return 11;
     default: return 0;
     }
 }
@@ -365,6 +468,41 @@ SPGX_HD void makeStreamRecord(int kind, const int32_t *stencil, const double *p,
     }
 }
 
+// The wedge record of owner o = tri[localT] (streams.cuh: Stream<ST_WEDGE>).  tri / pm: a K_MEMBRANE_STVK stencil and its
+// record; he / ph: the K_DISCRETE_BENDING stencil whose hinge edge joins o (position localE < 2) to A, and its record; ho / po:
+// the one whose hinge edge is {A, B} with o opposite (position localO >= 2).  A is the triangle vertex after (aNext) or
+// before o in the stencil's cyclic order, B the other one.  The hinge angle changes sign when the edge is reversed or the
+// opposite vertices are swapped (discreteBendingEnergy.cpp:9-30), so bringing a stencil into the canonical order only
+// negates theta0.  nbr: {A, B, C, R} out; returns false when the three stencils do not form a wedge around o.
+SPGX_HD bool makeWedgeRecord(const int32_t *tri, const double *pm, int localT, bool aNext, const int32_t *he, const double *ph,
+                             int localE, const int32_t *ho, const double *po, int localO, int32_t *nbr, double *q)
+{
+    const int ia = aNext ? (localT + 1) % 3 : (localT + 2) % 3, ib = aNext ? (localT + 2) % 3 : (localT + 1) % 3;
+    const int32_t o = tri[localT], A = tri[ia], B = tri[ib];
+    if (localE > 1 || localO < 2 || he[localE] != o || he[1 - localE] != A || ho[localO] != o) return false;
+    double th0E = localE == 0 ? ph[0] : -ph[0];  // (o, A, he[2], he[3])
+    int32_t C;
+    if (he[2] == B)
+        C = he[3];
+    else if (he[3] == B)
+        C = he[2], th0E = -th0E;  // opposite vertices swapped
+    else
+        return false;
+    double th0O = localO == 2 ? po[0] : -po[0];  // (ho[0], ho[1], o, R)
+    const int32_t R = ho[localO == 2 ? 3 : 2];
+    if (ho[0] == A && ho[1] == B) {
+    } else if (ho[0] == B && ho[1] == A)
+        th0O = -th0O;  // edge reversed
+    else
+        return false;
+    nbr[0] = A, nbr[1] = B, nbr[2] = C, nbr[3] = R;
+    const double gs[3][2] = {{-(pm[0] + pm[2]), -(pm[1] + pm[3])}, {pm[0], pm[1]}, {pm[2], pm[3]}};
+    q[0] = gs[ia][0], q[1] = gs[ia][1], q[2] = gs[ib][0], q[3] = gs[ib][1];
+    q[4] = pm[4], q[5] = pm[5], q[6] = pm[6];
+    q[7] = th0E, q[8] = ph[1], q[9] = th0O, q[10] = po[1];
+    return true;
+}
+
 // run one canonical evaluator by runtime stream type (tests, host and device)
 SPGX_HD void evalStream(int st, const V3d &xo, const V3d *xn, const double *q, V3d &g, Sym3 &H)
 {
@@ -374,6 +512,7 @@ SPGX_HD void evalStream(int st, const V3d &xo, const V3d *xn, const double *q, V
     case ST_MEMBRANE_STVK: Stream<ST_MEMBRANE_STVK>::eval(xo, xn, q, g, H); break;
     case ST_TET_SNH: Stream<ST_TET_SNH>::eval(xo, xn, q, g, H); break;
     case ST_TET_STVK: Stream<ST_TET_STVK>::eval(xo, xn, q, g, H); break;
+    case ST_WEDGE: Stream<ST_WEDGE>::eval(xo, xn, q, g, H); break;
     default: break;
     }
 }

@@ -78,8 +78,10 @@ void launchVbdPass(const VbdArgs &args, unsigned kindMask, unsigned streamMask, 
                    int sliceBase, double invdtSquared, cudaStream_t stream)
 {
     if (args.nStreams > 0) {
-        if ((streamMask & ~kStreamsCloth) == 0)
+        if ((streamMask & ~kStreamsClothSingle) == 0)
             launchStreamCloth(args, lanes, occ, begin, end, sliceBase, invdtSquared, stream);
+        else if ((streamMask & ~kStreamsCloth) == 0)
+            launchStreamClothWedge(args, lanes, occ, begin, end, sliceBase, invdtSquared, stream);
         else
             launchStreamTets(args, lanes, occ, begin, end, sliceBase, invdtSquared, stream);
         return;

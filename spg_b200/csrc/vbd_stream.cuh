@@ -210,7 +210,8 @@ struct SliceDesc {
     template <int ST>
     __device__ __forceinline__ uint32_t stream() const
     {
-        return ST == 0 ? lo.z : ST == 1 ? lo.w : ST == 2 ? hi.x : ST == 3 ? hi.y : hi.z;
+        constexpr int w = streamDescWord(ST);
+        return w == 2 ? lo.z : w == 3 ? lo.w : w == 4 ? hi.x : w == 5 ? hi.y : hi.z;
     }
 };
 
@@ -222,6 +223,7 @@ constexpr int maxStreamNQ(unsigned smask)
     if ((smask >> ST_MEMBRANE_STVK) & 1u) m = Stream<ST_MEMBRANE_STVK>::NQ > m ? Stream<ST_MEMBRANE_STVK>::NQ : m;
     if ((smask >> ST_TET_SNH) & 1u) m = Stream<ST_TET_SNH>::NQ > m ? Stream<ST_TET_SNH>::NQ : m;
     if ((smask >> ST_TET_STVK) & 1u) m = Stream<ST_TET_STVK>::NQ > m ? Stream<ST_TET_STVK>::NQ : m;
+    if ((smask >> ST_WEDGE) & 1u) m = Stream<ST_WEDGE>::NQ > m ? Stream<ST_WEDGE>::NQ : m;
     return m;
 }
 
@@ -259,15 +261,23 @@ struct StreamRec {
 // cumulative count exceeds s (a warp-uniform branch).  Running the two-deep register prefetch over the concatenated
 // sequence keeps the record loads two steps ahead across stream boundaries as well, so only the first two loads of a
 // warp are exposed (and those overlap the neighbour gather).
+// position in the concatenated step sequence -> stream type: wedges first -- they carry nearly all of a cloth's steps, so the
+// warp-uniform search for a step's type ends at its first comparison
+constexpr int streamAt(int i)
+{
+    return i == 0 ? ST_WEDGE : i - 1;
+}
+
 template <unsigned SMASK, int VW>
 struct StreamPipe {
     uint32_t base[kNumStreamTypes];  // first step of the type minus the concatenated index where the type begins
     uint32_t cum[kNumStreamTypes];   // concatenated index one past the type's last step
     uint32_t total;
 
-    template <int ST>
+    template <int I>
     __device__ __forceinline__ void init(const SliceDesc &d, const SliceDesc &n, uint32_t &acc)
     {
+        constexpr int ST = streamAt(I);
         if constexpr ((SMASK >> ST) & 1u) {
             const uint32_t t0 = d.stream<ST>(), t1 = n.stream<ST>();
             base[ST] = t0 - acc;
@@ -283,33 +293,36 @@ struct StreamPipe {
         init<2>(d, n, acc);
         init<3>(d, n, acc);
         init<4>(d, n, acc);
+        init<5>(d, n, acc);
         total = acc;
     }
-    template <int ST>
+    template <int I>
     __device__ __forceinline__ void loadFrom(const VbdArgs &a, StreamRec<SMASK> &r, uint32_t s, int lane) const
     {
-        if constexpr (ST < kNumStreamTypes) {
+        if constexpr (I < kNumStreamTypes) {
+            constexpr int ST = streamAt(I);
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < cum[ST]) {
                     r.template load<ST>(a.s[ST], base[ST] + s, lane);
                     return;
                 }
             }
-            loadFrom<ST + 1>(a, r, s, lane);
+            loadFrom<I + 1>(a, r, s, lane);
         }
     }
-    template <int ST>
+    template <int I>
     __device__ __forceinline__ void evalFrom(const StreamRec<SMASK> &r, uint32_t s, const double *P, const V3d &xo, V3d &g,
                                              Sym3 &H) const
     {
-        if constexpr (ST < kNumStreamTypes) {
+        if constexpr (I < kNumStreamTypes) {
+            constexpr int ST = streamAt(I);
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < cum[ST]) {
                     r.template eval<ST, VW>(P, xo, g, H);
                     return;
                 }
             }
-            evalFrom<ST + 1>(r, s, P, xo, g, H);
+            evalFrom<I + 1>(r, s, P, xo, g, H);
         }
     }
 };
@@ -378,17 +391,18 @@ struct RingOps {
 #pragma unroll
         for (int k = 0; k < SK::NQ; ++k) cpAsync8(dst + k * 32, qp + k * 32);
     }
-    template <int ST>
+    template <int I>
     __device__ static __forceinline__ void issueFrom(const VbdArgs &a, const StreamPipe<SMASK, VW> &pipe, uint32_t s, char *stage, int lane)
     {
-        if constexpr (ST < kNumStreamTypes) {
+        if constexpr (I < kNumStreamTypes) {
+            constexpr int ST = streamAt(I);
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < pipe.cum[ST]) {
                     issueStep<ST>(a.s[ST], pipe.base[ST] + s, stage, lane);
                     return;
                 }
             }
-            issueFrom<ST + 1>(a, pipe, s, stage, lane);
+            issueFrom<I + 1>(a, pipe, s, stage, lane);
         }
     }
     template <int ST>
@@ -410,18 +424,19 @@ struct RingOps {
         const V3d xo(Pown[0], Pown[VW], Pown[2 * VW]);  // re-read per step: six registers fewer across the loop
         SK::eval(xo, xn, q, g, H);
     }
-    template <int ST>
+    template <int I>
     __device__ static __forceinline__ void evalFrom(const StreamPipe<SMASK, VW> &pipe, uint32_t s, const char *stage, const double *P,
                                                     const double *Pown, V3d &g, Sym3 &H, int lane)
     {
-        if constexpr (ST < kNumStreamTypes) {
+        if constexpr (I < kNumStreamTypes) {
+            constexpr int ST = streamAt(I);
             if constexpr ((SMASK >> ST) & 1u) {
                 if (s < pipe.cum[ST]) {
                     evalStep<ST>(stage, P, Pown, g, H, lane);
                     return;
                 }
             }
-            evalFrom<ST + 1>(pipe, s, stage, P, Pown, g, H, lane);
+            evalFrom<I + 1>(pipe, s, stage, P, Pown, g, H, lane);
         }
     }
 };
@@ -522,6 +537,7 @@ __device__ __forceinline__ void vbdStreamBody(const VbdArgs &a, int end, int sli
             prefetchStreamIfPresent<SMASK, ST_MEMBRANE_STVK>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_TET_SNH>(a, pd, pn);
             prefetchStreamIfPresent<SMASK, ST_TET_STVK>(a, pd, pn);
+            prefetchStreamIfPresent<SMASK, ST_WEDGE>(a, pd, pn);
         }
     }
     if (a.halo.nPeers && lane == 0) {
@@ -693,8 +709,10 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
 }
 
 // variant = occ + 10 * ring: resident 128-thread blocks per SM and whether the records go through the shared-memory ring
-// instead of the register pipeline: 4 (register pipeline, <= 128 registers) and 15 (ring, 5 blocks, <= 102 registers) are
-// compiled.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
+// instead of the register pipeline: 4 (register pipeline, <= 128 registers), 14 (ring, 4 blocks, <= 128 registers) and 15
+// (ring, 5 blocks, <= 102 registers) are compiled.  A cloth with wedge records (streams.cuh: ST_WEDGE, 11 constants a record)
+// runs 14: two such records in flight in registers spill (164 bytes), and so does the wedge evaluator under 102 registers;
+// config 3, profiles/r2s_sweep.txt: 14 2.40 ms per frame, 15 2.95, 4 3.37.  Everything else runs 4.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
 // (profiles/r2d ... r2i_sweep.txt); 3 blocks, register caps on the register pipeline, persistent warps, prefetch.global.L1
 // (round 1, profiles/r1f_*); two steps evaluated together from a four-step ring (ptxas keeps the two evaluations sequential);
 // the register pipeline in 2-warp blocks, 8 resident (2.748 vs 2.702 ms on config 3).
@@ -705,11 +723,15 @@ void launchStreamG(const VbdArgs &args, int variant, int begin, int end, int sli
     if (args.nbrFixed) {
         if (variant == 15)
             launchStreamGO<SMASK, KMASK, G, 5, true, true>(args, begin, end, sliceBase, invdtSquared, stream);
+        else if (variant == 14)
+            launchStreamGO<SMASK, KMASK, G, 4, true, true>(args, begin, end, sliceBase, invdtSquared, stream);
         else
             launchStreamGO<SMASK, KMASK, G, 4, false, true>(args, begin, end, sliceBase, invdtSquared, stream);
     } else {
         if (variant == 15)
             launchStreamGO<SMASK, KMASK, G, 5, true, false>(args, begin, end, sliceBase, invdtSquared, stream);
+        else if (variant == 14)
+            launchStreamGO<SMASK, KMASK, G, 4, true, false>(args, begin, end, sliceBase, invdtSquared, stream);
         else
             launchStreamGO<SMASK, KMASK, G, 4, false, false>(args, begin, end, sliceBase, invdtSquared, stream);
     }
@@ -729,13 +751,17 @@ constexpr unsigned sbit(int k)
 {
     return 1u << k;
 }
-constexpr unsigned kStreamsCloth = sbit(ST_BEND_EDGE) | sbit(ST_BEND_OPP) | sbit(ST_MEMBRANE_STVK);
+constexpr unsigned kStreamsClothSingle = sbit(ST_BEND_EDGE) | sbit(ST_BEND_OPP) | sbit(ST_MEMBRANE_STVK);
+constexpr unsigned kStreamsCloth = kStreamsClothSingle | sbit(ST_WEDGE);
 constexpr unsigned kStreamsTets = sbit(ST_TET_SNH) | sbit(ST_TET_STVK);
 constexpr unsigned kKindsAnchor = sbit(K_ANCHOR);
 
 // one translation unit per combination (compile time)
 void launchStreamCloth(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
                        cudaStream_t stream);
+// the same with the wedge evaluator compiled in (its registers would cost the single-incidence kernel its spill-free pipeline)
+void launchStreamClothWedge(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
+                            cudaStream_t stream);
 void launchStreamTets(const VbdArgs &args, int lanes, int occ, int begin, int end, int sliceBase, double invdtSquared,
                       cudaStream_t stream);
 }  // namespace spgx

@@ -191,10 +191,15 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     osol.step(1)
     xr, vr = osol.state()
     results = {}
-    for name, env in [("csr", {"SPGX_NO_STREAMS": "1"})] + [(f"g{l}v{var}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_VARIANT": str(var)})
-                                                           for l in (2, 4) for var in (4, 15)] + \
-            [("g2v4packed", {"SPGX_VBD_LANES": "2", "SPGX_VBD_VARIANT": "4", "SPGX_VBD_NBRFIXED": "0"})]:
-        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_VARIANT", "SPGX_VBD_NBRFIXED"):
+    cases = [("csr", {"SPGX_NO_STREAMS": "1"})]
+    cases += [(f"g{l}v{var}", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_VARIANT": str(var)}) for l in (2, 4) for var in (4, 14, 15)]
+    cases += [("g2v4packed", {"SPGX_VBD_LANES": "2", "SPGX_VBD_VARIANT": "4", "SPGX_VBD_NBRFIXED": "0"})]
+    # single-incidence records only (no wedges: streams.cuh ST_WEDGE), register pipeline and ring
+    cases += [(f"g{l}v{var}single", {"SPGX_VBD_LANES": str(l), "SPGX_VBD_VARIANT": str(var), "SPGX_VBD_WEDGE": "0"})
+              for l, var in ((2, 4), (4, 15))]
+    knobs = ("SPGX_NO_STREAMS", "SPGX_VBD_LANES", "SPGX_VBD_VARIANT", "SPGX_VBD_NBRFIXED", "SPGX_VBD_WEDGE")
+    for name, env in cases:
+        for k in knobs:
             monkeypatch.delenv(k, raising=False)
         for k, v in env.items():
             monkeypatch.setenv(k, v)
@@ -202,13 +207,25 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
         g.finalize(api.SPGX_VBD)
         g.vbd_step(0.01, 2, 6)
         results[name] = g.download()
-        assert g.kernel_info()["variant"] == int(name.split("v")[1].replace("packed", "")) if name != "csr" else True
+        info = g.kernel_info()
+        if name != "csr":
+            assert info["variant"] == int(name.split("v")[1].replace("packed", "").replace("single", ""))
+            # a cloth's membrane and bending incidences pair up into wedges (three incidences a record) unless switched off:
+            # every triangle corner whose two hinges exist, i.e. all but the corners next to the mesh boundary
+            if scene == "cloth" and "single" not in name:
+                n_corners = 3 * sc.energies[1].stencils.shape[0]
+                assert 0.8 * n_corners < info["wedge_records"] <= n_corners, info
+            else:
+                assert info["wedge_records"] == 0, info
         g.close()
+    for k in knobs:
+        monkeypatch.delenv(k, raising=False)
     for name, (x, v) in results.items():
         assert _rel(x, xr) <= RTOL and _rel(v, vr) <= 1e-8, name
         assert _rel(x, results["csr"][0]) <= 1e-11, name
     for l in (2, 4):   # the ring path evaluates the same records in the same order; the occupancy point changes nothing
         assert np.array_equal(results[f"g{l}v15"][0], results[f"g{l}v4"][0]), l
+        assert np.array_equal(results[f"g{l}v14"][0], results[f"g{l}v4"][0]), l
     assert np.array_equal(results["g2v4packed"][0], results["g2v4"][0])   # the layout of the neighbour table changes nothing
 
 
