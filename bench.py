@@ -477,11 +477,10 @@ def measure_single(ctx, cfg_id, steps, warmup, rows=0, e2e=True, cpu=True, clock
     passes_per_frame = substeps * iterations * (ncol if solver == "vbd" else sum(g.num_colors(e) for e in range(len(sc.energies))))
     solve_ms_per_frame = tp.solve_ms / rf
     sweeps = iterations * substeps if solver == "vbd" else substeps
+    info = g.kernel_info()
     achieved = bytes_iter * sweeps / (solve_ms_per_frame * 1e-3) / 1e9
     peak, peak_src = peaks()
-    info = g.kernel_info()
-    kernel = (("vbdStreamKernel" if g.streamed() else "vbdPassKernel") if solver == "vbd"
-              else ("xpbdClusterKernel" if info.get("xpbd_cluster") else "xpbdPassKernel"))
+    kernel = ("vbdStreamKernel" if g.streamed() else "vbdPassKernel") if solver == "vbd" else "xpbdPassKernel"
     traffic, fp64, tsrc = ncu_traffic(cfg_id)
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "traffic_source": tsrc, "kernel": kernel,

@@ -416,7 +416,7 @@ class Group:
         check(lib.spgx_group_kernel_info(self.handle, o.ctypes.data_as(_lp)))
         return {"streamed": bool(o[0] & 0xFF), "stream_mask": int(o[0] & 0xFF), "wedge_records": int(o[0] >> 8), "lanes": int(o[1]), "slices": int(o[2]), "max_neighbours": int(o[3]),
                 "halo_mode": int(o[4]), "boundary_stores_per_sweep": int(o[5]), "colouring_rounds": int(o[6]),
-                "variant": int(o[7]), "xpbd_cluster": False}
+                "variant": int(o[7])}
 
     def streamed(self) -> bool:
         return self.kernel_info()["streamed"]

@@ -1179,23 +1179,6 @@ int spgx_group_finalize(spgx_group *grp, int solverKind)
             }
             if (solverKind == SPGX_NEWTON) newtonBuild(grp, st);
         }
-        // pass table of the fused XPBD frame: energies in insertion order, colours ascending (xpbd.cpp:84-95)
-        grp->d_xpbdPasses.release();
-        if (solverKind == SPGX_XPBD) {
-            std::vector<XpbdPassDev> passes;
-            for (auto &e : grp->energies)
-                for (size_t c = 0; c + 1 < e.colorOffsets.size(); ++c)
-                    if (e.colorOffsets[c + 1] > e.colorOffsets[c])
-                        passes.push_back({e.kind, static_cast<int>(e.colorOffsets[c]), static_cast<int>(e.colorOffsets[c + 1]), e.NC,
-                                          e.d_stencils.ptr, e.d_records.ptr, e.d_lambda.ptr, e.d_stencilW.ptr});
-            grp->d_xpbdPasses.upload(passes, st);
-            SPGX_CUDA(cudaStreamSynchronize(st));
-            // opt-in: measured on B200 at config 2 the grid barrier (~4 us with 148 co-resident blocks) costs more than
-            // the kernel boundary it replaces (~3 us per pass in a replayed graph): 2.43 vs 1.75 ms per frame
-            grp->xpbdFused = 0;
-            if (const char *env = getenv("SPGX_XPBD_FUSED")) grp->xpbdFused = std::min(2, std::max(0, atoi(env)));
-            grp->d_xpbdBarrier.alloc(1);
-        }
         // state: local vertices (owned + halo) on the device; the staging buffer spans the global index range
         const int nLocalAll = grp->nLocal;
         const size_t n3 = 3 * static_cast<size_t>(nLocalAll);

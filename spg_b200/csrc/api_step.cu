@@ -127,8 +127,6 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const double invdt = 1 / dt;
     const bool serial = grp->solverKind == SPGX_XPBD_SERIAL;
     const bool useLambda = iters > 1;
-    // graph mode: the whole frame is one cooperative launch with grid barriers between the passes; plain-launch mode
-    // keeps one kernel per pass (and the per-phase events)
     // domain-decomposed group (xpbd_partition.h): one one-way exchange per (energy, colour) pass -- peer-memory stores +
     // event counters (the pass kernel waits for the neighbours' previous event, a push kernel stores what the pass moved and
     // raises this one), or pack + ncclSend / ncclRecv + unpack
@@ -136,21 +134,6 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const bool viaNccl = grp->partitioned && !p2p && !grp->peers.empty();
     VbdHaloDev halo = p2p ? grp->p2p.dev : VbdHaloDev{};
     const bool signalling = p2p && halo.nPeers > 0;
-    if (!serial && !timePhases && grp->graphMode && grp->xpbdFused && grp->d_xpbdPasses.count > 0 && !grp->partitioned) {
-        XpbdFusedArgs fa{};
-        fa.x = grp->d_x.ptr, fa.v = grp->d_v.ptr, fa.xOld = grp->d_xOld.ptr;
-        fa.n3 = 3LL * grp->nLocal;
-        fa.passes = grp->d_xpbdPasses.ptr;
-        fa.nPasses = static_cast<int>(grp->d_xpbdPasses.count);
-        fa.nsub = nsub, fa.iters = iters, fa.useLambda = useLambda ? 1 : 0;
-        fa.dt = dt, fa.invdt = invdt, fa.gx = grp->graphKey.g[0], fa.gy = grp->graphKey.g[1], fa.gz = grp->graphKey.g[2];
-        fa.barrier = grp->xpbdFused == 2 ? grp->d_xpbdBarrier.ptr : nullptr;
-        if (launchXpbdFused(fa, st)) {
-            grp->launchCounter++;
-            return;
-        }
-        cudaGetLastError();  // not co-schedulable here: fall through to one launch per pass
-    }
     // (measured and removed: the velocity update of a substep fused with the prediction of the next into one launch on the
     // programmatic-dependent-launch chain of the passes -- 1.63 vs 1.375 ms per frame at config 2)
     for (int s = 0; s < nsub; ++s) {

@@ -266,9 +266,6 @@ struct spgx_group {
         double elemHessianBytes = 0;
         cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};  // substep start, system assembled, linear system solved
     } newton;
-    spgx::DevBuf<spgx::XpbdPassDev> d_xpbdPasses;  // fused XPBD frame (xpbd.cu): every (energy, colour) pass of a substep
-    int xpbdFused = 0;  // 0: one launch per pass, 1: cooperative kernel + cooperative-groups sync, 2: + hand-rolled barrier
-    spgx::DevBuf<unsigned> d_xpbdBarrier;
     // positions, inertial positions and masses of a VBD group are views into ONE allocation, so that a single L2
     // access-policy window covers everything the colour pass reads per vertex besides the incidence streams
     spgx::DevBuf<double> d_stateArena;

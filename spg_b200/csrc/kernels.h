@@ -118,28 +118,6 @@ void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, 
 void launchXpbdPass(int kind, double *x, const double *stencilW, const int32_t *stencils, const double *records,
                     double *lambda, int begin, int end, double dt, bool serial, cudaStream_t stream, const VbdHaloDev *halo = nullptr);
 
-// One (energy, colour) projection pass of a substep, as the fused XPBD kernel walks them (xpbd.cu)
-struct XpbdPassDev {
-    int kind, begin, end, nc;
-    const int32_t *stencils;
-    const double *records;
-    double *lambda;  // NC doubles per stencil of the energy (used when iterations > 1)
-    const double *stencilW;  // inverse masses per stencil vertex (launchXpbdPass)
-};
-struct XpbdFusedArgs {
-    double *x, *v, *xOld;
-    long long n3;               // 3 * vertices
-    const XpbdPassDev *passes;  // device array, reference order: energies in insertion order, colours ascending
-    int nPasses, nsub, iters, useLambda;
-    double dt, invdt, gx, gy, gz;  // dt of one substep
-    unsigned *barrier;             // one zeroed device word: arrival counter of the hand-rolled grid barrier (null: cooperative-groups sync)
-};
-// XPBD::step (xpbd.cpp:44-123) as ONE cooperative launch: predict, every (energy, colour) pass and finalize of every
-// substep, separated by grid-wide barriers instead of kernel boundaries (config 2 is launch-latency-bound: 27 passes of
-// 10-30 k stencils per substep).  Same per-stencil arithmetic as launchXpbdPass.  Returns false when the device cannot
-// co-schedule the grid (the caller falls back to one launch per pass).
-bool launchXpbdFused(const XpbdFusedArgs &args, cudaStream_t stream);
-
 // ---- implicit-Euler family and symplectic Euler (newton.cu; reference: spg/source/sim/solver/implicitEulerBase.cpp) ----
 struct NewtonEnergyDev {
     int kind;

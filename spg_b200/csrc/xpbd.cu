@@ -7,8 +7,6 @@
 // in registers and scatters x_s += w_s gradC_s dlambda.  Stencils of one colour share no vertex, so the
 // scatter is race free.  With `lambda` the full XPBD right-hand side -C - alpha~ lambda is used and lambda is
 // accumulated on device; without it this is the reference's "small steps" form (dlambda = -A^-1 C).
-#include <cooperative_groups.h>
-
 #include <algorithm>
 #include <cstdlib>
 
@@ -22,8 +20,7 @@ namespace
 {
 // the generic block projection (energy.h:117-153): C and dC/dx with first-order duals over the 3S stencil DOFs
 template <int KIND>
-__device__ __forceinline__ void projectGeneric(double *__restrict__ x, const int *id, const double *w, const V3d *px, const double *p,
-                                               double *__restrict__ lambda, int i, double dt2)
+__device__ __forceinline__ void projectGeneric(const double *w, V3d *px, const double *p, double *__restrict__ lambda, int i, double dt2)
 {
     using EK = EnergyKind<KIND>;
     constexpr int S = EK::S, NC = EK::NC, K = 3 * S;
@@ -71,10 +68,50 @@ __device__ __forceinline__ void projectGeneric(double *__restrict__ x, const int
             for (int a = 0; a < NC; ++a) acc += (w[s] * C[a].g[3 * s + c]) * rhs[a];
             d[c] = acc;
         }
-        const size_t o = 3 * static_cast<size_t>(id[s]);
-        x[o] = px[s].x + d[0];
-        x[o + 1] = px[s].y + d[1];
-        x[o + 2] = px[s].z + d[2];
+        px[s] = V3d(px[s].x + d[0], px[s].y + d[1], px[s].z + d[2]);
+    }
+}
+
+// The projection of one stencil on operands that are already in registers: px <- the projected positions.  Returns false
+// when the stencil moves nothing (the spring's early-outs).  Shared by the per-pass kernels (positions in global memory) and
+// the single-thread serial path: same arithmetic.
+template <int KIND>
+__device__ __forceinline__ bool projectLoaded(V3d *px, const double *w, const double *p, double *__restrict__ lambda, int i, double dt,
+                                              bool handProject)
+{
+    using EK = EnergyKind<KIND>;
+    constexpr int NC = EK::NC;
+    const double dt2 = dt * dt;
+    if constexpr (KIND == K_SPRING) {
+        // springEnergy.cpp:48-68 (early-outs at 1e-6, no +1e-10 regularisation)
+        constexpr double eps = 1.0e-6;
+        const double wSum = w[0] + w[1];
+        if (wSum < eps) return false;
+        const double alphaTilde = p[2] / dt2;
+        V3d n = px[1] - px[0];
+        const double d = ::sqrt(dot(n, n));
+        if (d < eps) return false;
+        n = V3d(n.x / d, n.y / d, n.z / d);
+        double c = d - p[0];
+        if (lambda) {
+            const double lam = lambda[i];
+            const double dl = (-c - alphaTilde * lam) / (wSum + alphaTilde);
+            lambda[i] = lam + dl;
+            c = -dl * (wSum + alphaTilde);
+        }
+        const double scale = c / (wSum + alphaTilde);
+        px[0] = V3d(px[0].x + w[0] * (n.x * scale), px[0].y + w[0] * (n.y * scale), px[0].z + w[0] * (n.z * scale));
+        px[1] = V3d(px[1].x - w[1] * (n.x * scale), px[1].y - w[1] * (n.y * scale), px[1].z - w[1] * (n.z * scale));
+        return true;
+    } else if constexpr (HasHandProject<EK>::value) {
+        if (handProject)
+            EK::project(px, w, p, dt2, lambda ? lambda + static_cast<size_t>(i) * NC : nullptr);
+        else
+            projectGeneric<KIND>(w, px, p, lambda, i, dt2);
+        return true;
+    } else {
+        projectGeneric<KIND>(w, px, p, lambda, i, dt2);
+        return true;
     }
 }
 
@@ -86,7 +123,7 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
                                                double *__restrict__ lambda, int i, double dt, bool handProject = true)
 {
     using EK = EnergyKind<KIND>;
-    constexpr int S = EK::S, NC = EK::NC;
+    constexpr int S = EK::S;
     const int32_t *ids = stencils + static_cast<size_t>(i) * S;
     int id[S];
     double w[S];
@@ -107,49 +144,13 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
         const size_t o = 3 * static_cast<size_t>(id[s]);
         px[s] = V3d(x[o], x[o + 1], x[o + 2]);
     }
-    const double dt2 = dt * dt;
-
-    if constexpr (KIND == K_SPRING) {
-        // springEnergy.cpp:48-68 (early-outs at 1e-6, no +1e-10 regularisation)
-        constexpr double eps = 1.0e-6;
-        const double wSum = w[0] + w[1];
-        if (wSum < eps) return;
-        const double alphaTilde = p[2] / dt2;
-        V3d n = px[1] - px[0];
-        const double d = ::sqrt(dot(n, n));
-        if (d < eps) return;
-        n = V3d(n.x / d, n.y / d, n.z / d);
-        double c = d - p[0];
-        if (lambda) {
-            const double lam = lambda[i];
-            const double dl = (-c - alphaTilde * lam) / (wSum + alphaTilde);
-            lambda[i] = lam + dl;
-            c = -dl * (wSum + alphaTilde);
-        }
-        const double scale = c / (wSum + alphaTilde);
-        const size_t o0 = 3 * static_cast<size_t>(id[0]), o1 = 3 * static_cast<size_t>(id[1]);
-        x[o0] = px[0].x + w[0] * (n.x * scale);
-        x[o0 + 1] = px[0].y + w[0] * (n.y * scale);
-        x[o0 + 2] = px[0].z + w[0] * (n.z * scale);
-        x[o1] = px[1].x - w[1] * (n.x * scale);
-        x[o1 + 1] = px[1].y - w[1] * (n.y * scale);
-        x[o1 + 2] = px[1].z - w[1] * (n.z * scale);
-        return;
-    } else if constexpr (HasHandProject<EK>::value) {
-        if (handProject) {
-            EK::project(px, w, p, dt2, lambda ? lambda + static_cast<size_t>(i) * NC : nullptr);
+    if (!projectLoaded<KIND>(px, w, p, lambda, i, dt, handProject)) return;
 #pragma unroll
-            for (int s = 0; s < S; ++s) {
-                const size_t o = 3 * static_cast<size_t>(id[s]);
-                x[o] = px[s].x;
-                x[o + 1] = px[s].y;
-                x[o + 2] = px[s].z;
-            }
-            return;
-        }
-        projectGeneric<KIND>(x, id, w, px, p, lambda, i, dt2);
-    } else {
-        projectGeneric<KIND>(x, id, w, px, p, lambda, i, dt2);
+    for (int s = 0; s < S; ++s) {
+        const size_t o = 3 * static_cast<size_t>(id[s]);
+        x[o] = px[s].x;
+        x[o + 1] = px[s].y;
+        x[o + 2] = px[s].z;
     }
 }
 
@@ -188,87 +189,6 @@ __global__ void xpbdSerialKernel(double *x, const double *stencilW, const int32_
     for (int i = begin; i < end; ++i) {
         projectStencil<KIND>(x, stencilW, stencils, records, lambda, i, dt);
         __threadfence();
-    }
-}
-
-// ---- fused frame: one cooperative launch, grid barriers between passes --------------------------------------------
-template <int KIND>
-__device__ __forceinline__ void fusedPass(const XpbdFusedArgs &a, const XpbdPassDev &p, long long tid, long long nthreads)
-{
-    for (long long i = p.begin + tid; i < p.end; i += nthreads)
-        projectStencil<KIND>(a.x, p.stencilW, p.stencils, p.records, a.useLambda ? p.lambda : nullptr, static_cast<int>(i), a.dt);
-}
-
-constexpr int kFusedThreads = 256;
-
-// Grid barrier on one monotone arrival counter: barrier k is passed when the counter reaches k * gridDim.x.  One
-// red.release + one polling ld.acquire per block (the cooperative-groups barrier measured ~4 us per pass at 148 blocks).
-struct GridBarrier {
-    unsigned *counter;
-    unsigned target = 0;
-    cooperative_groups::grid_group grid;
-    __device__ explicit GridBarrier(unsigned *c) : counter(c), grid(cooperative_groups::this_grid()) {}
-    __device__ __forceinline__ void sync()
-    {
-        if (!counter) {
-            grid.sync();
-            return;
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            target += gridDim.x;
-            asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(counter), "r"(1u) : "memory");
-            unsigned v;
-            do {
-                asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
-            } while (v < target);
-            __threadfence();  // gpu-scope fence: drops this SM's L1 lines, the other threads of the block read x afresh
-        }
-        __syncthreads();
-    }
-};
-
-__global__ void __launch_bounds__(kFusedThreads) xpbdFusedKernel(const XpbdFusedArgs a)
-{
-    GridBarrier grid(a.barrier);
-    const long long tid = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
-    const long long nthreads = static_cast<long long>(gridDim.x) * blockDim.x;
-    for (int sub = 0; sub < a.nsub; ++sub) {
-        // predict (state.cu predictKernel, same arithmetic): xOld <- x; v += dt g; x += v dt
-        for (long long i = tid; i < a.n3; i += nthreads) {
-            const int c = static_cast<int>(i % 3);
-            const double dtg = a.dt * (c == 0 ? a.gx : (c == 1 ? a.gy : a.gz));
-            const double xo = a.x[i];
-            const double vn = a.v[i] + dtg;
-            const double xn = xo + vn * a.dt;
-            a.xOld[i] = xo;
-            a.v[i] = vn;
-            a.x[i] = xn;
-        }
-        if (a.useLambda)
-            for (int q = 0; q < a.nPasses; ++q) {
-                const XpbdPassDev p = a.passes[q];
-                for (long long i = static_cast<long long>(p.begin) * p.nc + tid; i < static_cast<long long>(p.end) * p.nc; i += nthreads)
-                    p.lambda[i] = 0.0;
-            }
-        grid.sync();
-        for (int it = 0; it < a.iters; ++it)
-            for (int q = 0; q < a.nPasses; ++q) {
-                const XpbdPassDev p = a.passes[q];
-                switch (p.kind) {
-#define SPGX_KIND(NAME, ID, BYTES)                                                                                     \
-    case NAME:                                                                                                         \
-        fusedPass<NAME>(a, p, tid, nthreads);                                     \
-        break;
-#include "kinds.def"
-#undef SPGX_KIND
-                default: break;
-                }
-                grid.sync();  // stencils of the next colour / energy read what this one wrote
-            }
-        // finalize (state.cu finalizeKernel): v <- (x - xOld) * invdt
-        for (long long i = tid; i < a.n3; i += nthreads) a.v[i] = (a.x[i] - a.xOld[i]) * a.invdt;
-        if (sub + 1 < a.nsub) grid.sync();
     }
 }
 
@@ -362,33 +282,6 @@ void launchXpbdPass(int kind, double *x, const double *stencilW, const int32_t *
 #undef SPGX_KIND
     default: break;
     }
-}
-
-bool launchXpbdFused(const XpbdFusedArgs &args, cudaStream_t stream)
-{
-    static int blocks = -1;  // co-resident capacity, one block per SM at most (the barrier cost grows with the grid)
-    if (blocks < 0) {
-        int dev = 0, sms = 0, perSm = 0, coop = 0;
-        cudaGetDevice(&dev);
-        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, xpbdFusedKernel, kFusedThreads, 0);
-        blocks = (coop && perSm >= 1) ? sms : 0;
-        if (const char *env = getenv("SPGX_XPBD_FUSED_BLOCKS")) blocks = std::min(blocks, std::max(1, atoi(env)));
-    }
-    if (blocks <= 0) return false;
-    if (args.barrier && cudaMemsetAsync(args.barrier, 0, sizeof(unsigned), stream) != cudaSuccess) return false;
-    cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(blocks);
-    cfg.blockDim = dim3(kFusedThreads);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
-    attr[0].id = cudaLaunchAttributeCooperative;
-    attr[0].val.cooperative = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    return cudaLaunchKernelEx(&cfg, xpbdFusedKernel, args) == cudaSuccess;
 }
 
 void launchEvalConstraints(int kind, const double *x, const int32_t *stencil, const double *record, double *outC,

@@ -251,27 +251,6 @@ def test_static_load_vbd_and_xpbd_refusal(ctx, oracle):
     g2.close()
 
 
-@pytest.mark.parametrize("iters", [1, 3])
-def test_xpbd_fused_frame_equals_per_pass_launches(ctx, iters, monkeypatch):
-    """The cooperative one-launch-per-frame XPBD kernel (grid barriers between passes) against one kernel per
-    (energy, colour) pass, CUDA-graph replay and plain launches: the same per-stencil arithmetic, bit-identical."""
-    sc = S.cloth(24, 19, S.K_SPRING, S.K_QUADRATIC_BENDING)
-    results = {}
-    for name, fused, graph in (("fused", "1", True), ("fused_barrier", "2", True), ("passes_graph", "0", True),
-                               ("passes_plain", "0", False)):
-        monkeypatch.setenv("SPGX_XPBD_FUSED", fused)
-        g = api.Group.from_scene(ctx, sc)
-        g.finalize(api.SPGX_XPBD)
-        g.set_graph_mode(graph)
-        g.xpbd_step(0.01, 5, iters, frames=3)
-        results[name] = g.download()
-        assert g.timings().kernel_launches == (3 if name.startswith("fused") else g.timings().kernel_launches)
-        g.close()
-    for name in ("passes_graph", "passes_plain", "fused_barrier"):
-        assert np.array_equal(results["fused"][0], results[name][0]), name
-        assert np.array_equal(results["fused"][1], results[name][1]), name
-
-
 @pytest.mark.parametrize("solver", [api.SPGX_VBD, api.SPGX_XPBD])
 def test_debug_scan_finds_non_finite_state(ctx, solver):
     """spgx_check_finite (what Verbosity::Debug of the facade runs after every step): clean after a step, and a NaN planted

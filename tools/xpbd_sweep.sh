@@ -17,5 +17,3 @@ run SPGX_XPBD_HAND=1 SPGX_XPBD_THREADS=32
 run SPGX_XPBD_HAND=1 SPGX_XPBD_THREADS=64 SPGX_XPBD_PDL=1
 run SPGX_XPBD_DEBUG_EMPTY=1
 run SPGX_XPBD_DEBUG_EMPTY=1 SPGX_XPBD_THREADS=32
-run SPGX_XPBD_HAND=1 SPGX_XPBD_FUSED=1
-run SPGX_XPBD_HAND=1 SPGX_XPBD_FUSED=2
