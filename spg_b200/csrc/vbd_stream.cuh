@@ -712,7 +712,8 @@ void launchStreamGO(const VbdArgs &args, int begin, int end, int sliceBase, doub
 // instead of the register pipeline: 4 (register pipeline, <= 128 registers), 14 (ring, 4 blocks, <= 128 registers) and 15
 // (ring, 5 blocks, <= 102 registers) are compiled.  A cloth with wedge records (streams.cuh: ST_WEDGE, 11 constants a record)
 // runs 14: two such records in flight in registers spill (164 bytes), and so does the wedge evaluator under 102 registers;
-// config 3, profiles/r2s_sweep.txt: 14 2.40 ms per frame, 15 2.95, 4 3.37.  Everything else runs 4.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
+// config 3, profiles/r2s_sweep.txt: 14 2.32 ms per frame, 15 2.95, 4 3.37; the ring with 3 / 2 resident blocks (158 / 167
+// registers, what ptxas takes without a cap) 2.44 / 3.03 ms: measured, not compiled.  Everything else runs 4.  Measured and rejected, no longer compiled: one lane per vertex, ring with 4 or 6 blocks
 // (profiles/r2d ... r2i_sweep.txt); 3 blocks, register caps on the register pipeline, persistent warps, prefetch.global.L1
 // (round 1, profiles/r1f_*); two steps evaluated together from a four-step ring (ptxas keeps the two evaluations sequential);
 // the register pipeline in 2-warp blocks, 8 resident (2.748 vs 2.702 ms on config 3).

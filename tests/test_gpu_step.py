@@ -229,6 +229,56 @@ def test_vbd_streaming_kernel_variants_agree(ctx, oracle, scene, monkeypatch):
     assert np.array_equal(results["g2v4packed"][0], results["g2v4"][0])   # the layout of the neighbour table changes nothing
 
 
+@pytest.mark.parametrize("case", ["shuffled", "holes", "strip"])
+def test_vbd_wedge_records_on_irregular_input(ctx, oracle, case, monkeypatch):
+    """Wedge records (streams.cuh: ST_WEDGE -- a fan triangle's membrane and its two hinges as one record of the colour pass) on
+    input that does not pair up cleanly: triangle stencils rotated and hinge stencils reordered at random (the canonicalisation
+    moves the order into the sign of the rest angle), a third of the hinges and a tenth of the triangles missing (what completes
+    no wedge stays a single-incidence record), a two-row strip (every vertex on the boundary).  Against the generic CSR kernel
+    (1e-11) and the reference (1e-9) after one frame."""
+    rng = np.random.default_rng(7)
+    sc = S.cloth(2, 40) if case == "strip" else S.cloth(18, 23)
+    bend, mem = sc.energies[0], sc.energies[1]
+    if case in ("shuffled", "holes"):
+        rot = rng.integers(0, 3, size=mem.stencils.shape[0])
+        mem.stencils = np.stack([np.roll(t, -r) for t, r in zip(mem.stencils, rot)]).astype(np.int32)
+        flip = rng.random(bend.stencils.shape[0]) < 0.5
+        swap = rng.random(bend.stencils.shape[0]) < 0.5
+        st = bend.stencils.copy()
+        st[flip, 0], st[flip, 1] = bend.stencils[flip, 1], bend.stencils[flip, 0]
+        a, b = st[swap, 2].copy(), st[swap, 3].copy()
+        st[swap, 2], st[swap, 3] = b, a
+        bend.stencils = st
+    if case == "holes":
+        keep = rng.random(bend.stencils.shape[0]) > 0.33
+        bend.stencils, bend.params = bend.stencils[keep], bend.params[keep]
+        keep = rng.random(mem.stencils.shape[0]) > 0.1
+        mem.stencils, mem.params = mem.stencils[keep], mem.params[keep]
+    og = oracle_api.OracleGroup(oracle, sc)
+    osol = oracle_api.OracleSolver(og, 0, 0.01, 2, 6)
+    osol.step(1)
+    xr, vr = osol.state()
+    out = {}
+    for name, env in (("csr", {"SPGX_NO_STREAMS": "1"}), ("wedge", {}), ("single", {"SPGX_VBD_WEDGE": "0"})):
+        for k in ("SPGX_NO_STREAMS", "SPGX_VBD_WEDGE"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = api.Group.from_scene(ctx, sc)
+        g.finalize(api.SPGX_VBD)
+        info = g.kernel_info()
+        if name == "wedge":
+            n_corners = 3 * mem.stencils.shape[0]
+            assert 0 < info["wedge_records"] < n_corners if case != "strip" else info["wedge_records"] >= 0, info
+        g.vbd_step(0.01, 2, 6)
+        out[name] = g.download()
+        g.close()
+    monkeypatch.delenv("SPGX_VBD_WEDGE", raising=False)
+    for name in ("wedge", "single"):
+        assert _rel(out[name][0], out["csr"][0]) <= 1e-11, name
+        assert _rel(out[name][0], xr) <= RTOL and _rel(out[name][1], vr) <= 1e-8, name
+
+
 def test_static_load_vbd_and_xpbd_refusal(ctx, oracle):
     """StaticLoadEnergy is energy-only: VBD matches the reference, XPBD throws the reference's message
     (staticLoadEnergy.cpp:8-13) through the C ABI."""
