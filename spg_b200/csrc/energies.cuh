@@ -208,22 +208,31 @@ struct EnergyKind<K_QUADRATIC_BENDING> {
     // 1e-10) I -- the off-diagonal sums are sums of exact zeros -- and dlambda = -C / that scalar: ~40 flops instead of a
     // 12-wide dual pass and a 3 x 3 solve (the survey's "AD on a linear map").  lambda: 3 doubles or null.
     static constexpr bool kHandProject = true;
-    SPGX_HD static void project(V3d *x, const double *w, const double *p, double dt2, double *lambda)
+    // The half of the projection that does not read a position -- alpha~ and 1 / (sum_s w_s c_s^2 + alpha~ + 1e-10): the XPBD
+    // pass computes it AHEAD of its wait for the previous pass (xpbd.cu), so that the dependent chain behind the position
+    // gather is C, one multiplication and the update instead of C, the sum and three divisions.
+    SPGX_HD static void projectPrepare(const double *w, const double *p, double dt2, double *pre)
     {
-        const V3d C = x[0] * p[0] + x[1] * p[1] + x[2] * p[2] + x[3] * p[3];
         const double alphaTilde = p[5] / dt2;
         double a = 0.0;
 #pragma unroll
         for (int s = 0; s < 4; ++s) a += p[s] * (w[s] * p[s]);
         a += alphaTilde;
         a += 1e-10;
+        pre[0] = alphaTilde;
+        pre[1] = 1.0 / a;
+    }
+    SPGX_HD static void projectPrepared(V3d *x, const double *w, const double *p, const double *pre, double *lambda)
+    {
+        const V3d C = x[0] * p[0] + x[1] * p[1] + x[2] * p[2] + x[3] * p[3];
+        const double alphaTilde = pre[0], inva = pre[1];
         V3d rhs(-C.x, -C.y, -C.z);
         if (lambda) {
             rhs.x -= alphaTilde * lambda[0];
             rhs.y -= alphaTilde * lambda[1];
             rhs.z -= alphaTilde * lambda[2];
         }
-        const V3d dl(rhs.x / a, rhs.y / a, rhs.z / a);
+        const V3d dl(rhs.x * inva, rhs.y * inva, rhs.z * inva);
         if (lambda) {
             lambda[0] += dl.x;
             lambda[1] += dl.y;
@@ -234,6 +243,12 @@ struct EnergyKind<K_QUADRATIC_BENDING> {
             const double ws = w[s] * p[s];
             x[s] = V3d(x[s].x + ws * dl.x, x[s].y + ws * dl.y, x[s].z + ws * dl.z);
         }
+    }
+    SPGX_HD static void project(V3d *x, const double *w, const double *p, double dt2, double *lambda)
+    {
+        double pre[2];
+        projectPrepare(w, p, dt2, pre);
+        projectPrepared(x, w, p, pre, lambda);
     }
 };
 

@@ -13,6 +13,7 @@
 #include "energies.cuh"
 #include "halo.cuh"
 #include "kernels.h"
+#include "streams.cuh"
 
 namespace spgx
 {
@@ -72,40 +73,66 @@ __device__ __forceinline__ void projectGeneric(const double *w, V3d *px, const d
     }
 }
 
-// The projection of one stencil on operands that are already in registers: px <- the projected positions.  Returns false
-// when the stencil moves nothing (the spring's early-outs).  Shared by the per-pass kernels (positions in global memory) and
-// the single-thread serial path: same arithmetic.
+// What a projection computes from the inverse masses and the record alone (no position): requested ahead of the pass's wait
+// for the previous pass, so that the divisions are off the dependent chain gather -> projection -> store that bounds a pass
+// (config 2: 540 passes a frame, each one that chain).
+struct ProjectPre {
+    double v[2];
+};
 template <int KIND>
-__device__ __forceinline__ bool projectLoaded(V3d *px, const double *w, const double *p, double *__restrict__ lambda, int i, double dt,
-                                              bool handProject)
+__device__ __forceinline__ ProjectPre projectPrepare(const double *w, const double *p, double dt, bool handProject)
+{
+    using EK = EnergyKind<KIND>;
+    ProjectPre pre{{0.0, 0.0}};
+    const double dt2 = dt * dt;
+    if constexpr (KIND == K_SPRING) {
+        const double alphaTilde = p[2] / dt2;
+        pre.v[0] = alphaTilde;
+        pre.v[1] = 1.0 / (w[0] + w[1] + alphaTilde);
+    } else if constexpr (HasHandProject<EK>::value) {
+        if (handProject) EK::projectPrepare(w, p, dt2, pre.v);
+    }
+    return pre;
+}
+
+// The projection of one stencil on operands that are already in registers: px <- the projected positions.  Returns false
+// when the stencil moves nothing (the spring's early-outs).  Shared by the per-pass kernels and the single-thread serial path.
+template <int KIND>
+__device__ __forceinline__ bool projectLoaded(V3d *px, const double *w, const double *p, const ProjectPre &pre, double *__restrict__ lambda,
+                                              int i, double dt, bool handProject)
 {
     using EK = EnergyKind<KIND>;
     constexpr int NC = EK::NC;
     const double dt2 = dt * dt;
     if constexpr (KIND == K_SPRING) {
-        // springEnergy.cpp:48-68 (early-outs at 1e-6, no +1e-10 regularisation)
+        // springEnergy.cpp:48-68 (early-outs at 1e-6, no +1e-10 regularisation).  The reference divides by the length and by
+        // w0 + w1 + alpha~; here the length comes from one reciprocal square root (d = |n|^2 / sqrt(|n|^2), n / d = n rsqrt) and the
+        // second denominator's reciprocal from projectPrepare: the same values to a unit in the last place, a dependent chain
+        // of ~15 instead of ~60 FP64 instructions behind the gather
         constexpr double eps = 1.0e-6;
         const double wSum = w[0] + w[1];
         if (wSum < eps) return false;
-        const double alphaTilde = p[2] / dt2;
+        const double alphaTilde = pre.v[0], invDen = pre.v[1];
         V3d n = px[1] - px[0];
-        const double d = ::sqrt(dot(n, n));
-        if (d < eps) return false;
-        n = V3d(n.x / d, n.y / d, n.z / d);
+        const double dd = dot(n, n);
+        if (dd < eps * eps) return false;  // d < eps
+        const double invd = fastRsqrt(dd);
+        const double d = dd * invd;
+        n = V3d(n.x * invd, n.y * invd, n.z * invd);
         double c = d - p[0];
         if (lambda) {
             const double lam = lambda[i];
-            const double dl = (-c - alphaTilde * lam) / (wSum + alphaTilde);
+            const double dl = (-c - alphaTilde * lam) * invDen;
             lambda[i] = lam + dl;
             c = -dl * (wSum + alphaTilde);
         }
-        const double scale = c / (wSum + alphaTilde);
+        const double scale = c * invDen;
         px[0] = V3d(px[0].x + w[0] * (n.x * scale), px[0].y + w[0] * (n.y * scale), px[0].z + w[0] * (n.z * scale));
         px[1] = V3d(px[1].x - w[1] * (n.x * scale), px[1].y - w[1] * (n.y * scale), px[1].z - w[1] * (n.z * scale));
         return true;
     } else if constexpr (HasHandProject<EK>::value) {
         if (handProject)
-            EK::project(px, w, p, dt2, lambda ? lambda + static_cast<size_t>(i) * NC : nullptr);
+            EK::projectPrepared(px, w, p, pre.v, lambda ? lambda + static_cast<size_t>(i) * NC : nullptr);
         else
             projectGeneric<KIND>(w, px, p, lambda, i, dt2);
         return true;
@@ -138,13 +165,14 @@ __device__ __forceinline__ void projectStencil(double *__restrict__ x, const dou
         id[s] = __ldg(ids + s);
         w[s] = __ldg(stencilW + static_cast<size_t>(i) * S + s);
     }
+    const ProjectPre pre = projectPrepare<KIND>(w, p, dt, handProject);
     if constexpr (PDL) asm volatile("griddepcontrol.wait;" ::: "memory");
 #pragma unroll
     for (int s = 0; s < S; ++s) {
         const size_t o = 3 * static_cast<size_t>(id[s]);
         px[s] = V3d(x[o], x[o + 1], x[o + 2]);
     }
-    if (!projectLoaded<KIND>(px, w, p, lambda, i, dt, handProject)) return;
+    if (!projectLoaded<KIND>(px, w, p, pre, lambda, i, dt, handProject)) return;
 #pragma unroll
     for (int s = 0; s < S; ++s) {
         const size_t o = 3 * static_cast<size_t>(id[s]);
