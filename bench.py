@@ -337,12 +337,24 @@ def run_implicit(args):
     return 0
 
 
-def kernel_source_hash():
-    """sha256 over the CUDA sources the library is built from: ties an ncu capture (profiles/traffic.json) to a build"""
+# the sources a config's dominant kernel is compiled from (spg_b200/csrc): an ncu capture of that kernel stays valid while
+# THESE are unchanged; None = every source of the library
+KERNEL_SOURCES = {
+    3: ["vbd_stream.cuh", "vbd_stream_cloth_wedge.cu", "vbd_stream_cloth.cu", "streams.cuh", "energies.cuh", "dual.cuh", "linalg.cuh",
+        "halo.cuh", "kernels.h", "kinds.def"],
+    6: ["newton.cu", "hinge_hessian.cuh", "membrane_hessian.cuh", "energies.cuh", "dual.cuh", "linalg.cuh", "kernels.h", "kinds.def"],
+}
+
+
+def kernel_source_hash(cfg_id=None):
+    """sha256 over the CUDA sources the config's dominant kernel is built from (all sources of the library without a config):
+    ties an ncu capture (profiles/traffic.json) to a build of that kernel"""
     import hashlib
     h = hashlib.sha256()
-    for f in sorted((ROOT / "spg_b200" / "csrc").glob("*")):
-        if f.suffix in (".cu", ".cuh", ".h"):
+    names = KERNEL_SOURCES.get(cfg_id)
+    files = sorted((ROOT / "spg_b200" / "csrc").glob("*")) if names is None else [ROOT / "spg_b200" / "csrc" / n for n in sorted(names)]
+    for f in files:
+        if f.suffix in (".cu", ".cuh", ".h", ".def"):
             h.update(f.name.encode())
             h.update(f.read_bytes())
     return h.hexdigest()[:16]
@@ -352,16 +364,18 @@ def ncu_traffic(cfg_id):
     """(traffic bytes per launch, FP64 pipe %, provenance) of the dominant kernel from the committed ncu capture -- only
     when that capture was taken on THIS build of the kernels (same source hash); otherwise null with the reason."""
     prof = ROOT / "profiles" / "traffic.json"
-    here = kernel_source_hash()
+    here = kernel_source_hash(cfg_id)
     if not prof.exists():
         return None, None, {"csrc_sha256": here, "note": "no ncu capture committed"}
     try:
         tj = json.loads(prof.read_text())
     except Exception as e:
         return None, None, {"csrc_sha256": here, "note": f"profiles/traffic.json unreadable: {e}"}
-    src = {"csrc_sha256": here, "ncu_csrc_sha256": tj.get("_csrc_sha256"), "ncu_capture": tj.get(f"_source_{cfg_id}", tj.get("_source"))}
-    if tj.get("_csrc_sha256") != here:
-        src["note"] = "the committed ncu capture is of another build of the kernels: traffic omitted"
+    there = tj.get(f"_csrc_sha256_{cfg_id}")
+    src = {"csrc_sha256": here, "ncu_csrc_sha256": there, "hashed_sources": KERNEL_SOURCES.get(cfg_id, "all of spg_b200/csrc"),
+           "ncu_capture": tj.get(f"_source_{cfg_id}", tj.get("_source"))}
+    if there != here:
+        src["note"] = "the committed ncu capture is of another build of this kernel: traffic omitted"
         return None, None, src
     return tj.get(str(cfg_id)), tj.get(f"fp64_pipe_pct_{cfg_id}"), src
 

@@ -35,7 +35,8 @@ tj[f"fp64_pipe_pct_{cfg}"] = sum(fp64[i] for i in full) / len(full)
 tj[f"_source_{cfg}"] = (f"{what}: (dram__bytes_read.sum + dram__bytes_write.sum) summed over the {n} launches captured / {n}; "
                         f"FP64 pipe averaged over the {len(full)} full launches; launches under ncu are isolated and cache-cold "
                         "(the positions are re-read from DRAM by every launch, which they are not back to back)")
-tj["_csrc_sha256"] = bench.kernel_source_hash()
+tj[f"_csrc_sha256_{cfg}"] = bench.kernel_source_hash(int(cfg))
+tj.pop("_csrc_sha256", None)
 tj.pop("_source", None)
 tj.pop("_fp64_source", None)
 prof.write_text(json.dumps(tj, indent=1) + "\n")
