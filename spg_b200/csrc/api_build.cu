@@ -375,7 +375,7 @@ static void patchStreamRecords(spgx_group &grp, const EnergyState &edited, int s
         for (int l = 0; l < local; ++l) earlier |= edited.stencils[static_cast<size_t>(stencil) * edited.S + l] == v;
         const int slot = grp.vert2slot[v];
         if (earlier || slot < 0 || slot >= grp.nOwned) continue;  // a halo copy: its owner patches it
-        // incidence lists of v alone, addressed as "vertex 0" of a one-row CSR per energy
+        // incidence lists of v alone: a one-row CSR per energy (appendSlotRecords uses its vertex argument as the row only)
         std::vector<std::vector<int64_t>> flat(grp.energies.size());
         std::vector<std::array<int64_t, 2>> rowptr(grp.energies.size());
         std::vector<StreamEnergyView> views(grp.energies.size());
@@ -385,13 +385,12 @@ static void patchStreamRecords(spgx_group &grp, const EnergyState &edited, int s
                 for (size_t q = 0; q < e.stencils.size(); ++q)
                     if (e.stencils[q] == v) flat[ei].push_back(static_cast<int64_t>(q));
             rowptr[ei] = {0, static_cast<int64_t>(flat[ei].size())};
-            // (rows are looked up at index v: shift the base pointers so that row v is the one row there is)
-            views[ei] = {e.kind, e.S, e.NP, e.stencils.data(), e.records.data(), rowptr[ei].data() - v, flat[ei].data()};
+            views[ei] = {e.kind, e.S, e.NP, e.stencils.data(), e.records.data(), rowptr[ei].data(), flat[ei].data()};
         }
         SlotScratch sc;
         std::vector<uint32_t> idx[ST_COUNT];
         std::vector<double> q[ST_COUNT];
-        appendSlotRecords(views.data(), static_cast<int>(views.size()), v, wedgeB, wedgeM, sc, idx, q);
+        appendSlotRecords(views.data(), static_cast<int>(views.size()), /*row*/ 0, wedgeB, wedgeM, sc, idx, q);
         int colour = 0;
         while (grp.colorOffsets[colour + 1] <= slot) ++colour;
         const int inColour = slot - static_cast<int>(grp.colorOffsets[colour]);
