@@ -134,11 +134,16 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
     const bool viaNccl = grp->partitioned && !p2p && !grp->peers.empty();
     VbdHaloDev halo = p2p ? grp->p2p.dev : VbdHaloDev{};
     const bool signalling = p2p && halo.nPeers > 0;
-    // (measured and removed: the velocity update of a substep fused with the prediction of the next into one launch on the
-    // programmatic-dependent-launch chain of the passes -- 1.63 vs 1.375 ms per frame at config 2)
+    // The velocity update of a substep and the prediction of the next are one launch (plain: on the programmatic-dependent-
+    // launch chain of the passes it measured SLOWER, 1.63 vs 1.375 ms per frame at config 2, and so did predict / finalize as
+    // separate launches on that chain); the phase timer keeps them apart.  SPGX_XPBD_FUSE_STATE=0: two launches.
+    const bool fuseStateEnv = !(getenv("SPGX_XPBD_FUSE_STATE") && atoi(getenv("SPGX_XPBD_FUSE_STATE")) == 0);  // read when the graph is captured
+    const bool fuseState = fuseStateEnv && !timePhases;
     for (int s = 0; s < nsub; ++s) {
-        launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nLocal, dt, grp->graphKey.g, st);
-        grp->launchCounter++;
+        if (s == 0 || !fuseState) {
+            launchPredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, nullptr, grp->nLocal, dt, grp->graphKey.g, st);
+            grp->launchCounter++;
+        }
         if (timePhases) grp->markPhase(st);
         if (signalling) {
             // event 0: this rank's halo copies have been predicted; neighbours may store into them from now on
@@ -180,7 +185,10 @@ void enqueueXpbdFrame(spgx_group *grp, double dtStep, int nsub, int iters, cudaS
             grp->launchCounter++;
         }
         if (timePhases) grp->markPhase(st);
-        launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
+        if (fuseState && s + 1 < nsub)
+            launchFinalizePredict(grp->d_x.ptr, grp->d_v.ptr, grp->d_xOld.ptr, grp->nLocal, dt, invdt, grp->graphKey.g, st);
+        else
+            launchFinalize(grp->d_x.ptr, grp->d_xOld.ptr, grp->d_v.ptr, grp->nLocal, invdt, st);
         grp->launchCounter++;
         if (timePhases) grp->markPhase(st);
     }

@@ -94,6 +94,9 @@ void launchPredict(double *x, double *v, double *xOld, double *xInertial, int nV
                    cudaStream_t stream);
 // particleGroup.cpp:65-72: v <- (x - xOld) * invdt
 void launchFinalize(const double *x, const double *xOld, double *v, int nVerts, double invdt, cudaStream_t stream);
+// launchFinalize of one substep and launchPredict (xInertial == nullptr) of the next in one launch, same roundings
+void launchFinalizePredict(double *x, double *v, double *xOld, int nVerts, double dt, double invdt, const double *g3,
+                           cudaStream_t stream);
 // peer-memory halo exchange outside the colour passes (comm.cu): raise event `event` / wait for it and advance the epoch
 void launchHaloSignal(const VbdHaloDev &h, int event, cudaStream_t stream);
 void launchHaloWaitAdvance(const VbdHaloDev &h, int event, uint32_t *epochBase, cudaStream_t stream);

@@ -33,6 +33,26 @@ __global__ void finalizeKernel(const double *__restrict__ x, const double *__res
     v[i] = (x[i] - xOld[i]) * invdt;
 }
 
+// finalize of one substep + predict of the next in one launch (XPBD runs 20 substeps a frame: one kernel boundary less per
+// substep).  The same roundings as the two kernels above: the velocity is rounded where finalizeKernel stores it (no
+// contraction of its multiplication into the gravity add), the position update is the expression predictKernel uses.
+__global__ void finalizePredictKernel(double *__restrict__ x, double *__restrict__ v, double *__restrict__ xOld, long long n3,
+                                      double dt, double invdt, double gx, double gy, double gz)
+{
+    const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n3) return;
+    const int c = static_cast<int>(i % 3);
+    const double dtg = dt * (c == 0 ? gx : (c == 1 ? gy : gz));
+    const double xo = x[i];
+    const double vf = __dmul_rn(__dsub_rn(xo, xOld[i]), invdt);  // finalizeKernel: rounded here, as where it is stored
+    const double vn = vf + dtg;                                  // predictKernel from here on (the same expressions, so the
+                                                                 // same contractions: dt g + v is one fused multiply-add there)
+    const double xn = xo + vn * dt;
+    xOld[i] = xo;
+    v[i] = vn;
+    x[i] = xn;
+}
+
 __global__ void permute3Kernel(const double *__restrict__ src, double *__restrict__ dst,
                                const int32_t *__restrict__ perm, int n, bool gather)
 {
@@ -97,6 +117,16 @@ void launchFinalize(const double *x, const double *xOld, double *v, int nVerts, 
     if (n3 == 0) return;
     const int threads = 256;
     finalizeKernel<<<static_cast<unsigned>((n3 + threads - 1) / threads), threads, 0, stream>>>(x, xOld, v, n3, invdt);
+}
+
+void launchFinalizePredict(double *x, double *v, double *xOld, int nVerts, double dt, double invdt, const double *g3,
+                           cudaStream_t stream)
+{
+    const long long n3 = 3LL * nVerts;
+    if (n3 == 0) return;
+    const int threads = 256;
+    finalizePredictKernel<<<static_cast<unsigned>((n3 + threads - 1) / threads), threads, 0, stream>>>(x, v, xOld, n3, dt, invdt, g3[0],
+                                                                                                       g3[1], g3[2]);
 }
 
 void launchPermute3(const double *src, double *dst, const int32_t *perm, int n, bool gather, cudaStream_t stream)

@@ -92,6 +92,29 @@ def test_vbd_graph_and_plain_launch_agree(ctx):
     assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
 
 
+@pytest.mark.parametrize("iters", [1, 3])
+def test_xpbd_graph_and_plain_launch_agree(ctx, iters, monkeypatch):
+    """XPBD frames as a replayed CUDA graph (the velocity update of a substep and the prediction of the next in one launch),
+    as plain launches with the phase timer (two launches), and with the fusion switched off: bit-identical state over
+    consecutive frames, and the launch count that goes with each form."""
+    sc = S.cloth(24, 19, S.K_SPRING, S.K_QUADRATIC_BENDING)
+    out = {}
+    for name, graph, fuse in (("graph", True, "1"), ("plain", False, "1"), ("graph_unfused", True, "0")):
+        monkeypatch.setenv("SPGX_XPBD_FUSE_STATE", fuse)
+        g = api.Group.from_scene(ctx, sc)
+        g.finalize(api.SPGX_XPBD)
+        g.set_graph_mode(graph)
+        g.xpbd_step(0.01, 5, iters, frames=3)
+        out[name] = g.download()
+        passes = sum(g.num_colors(e) for e in range(len(sc.energies)))
+        n_state = 5 + 1 if name == "graph" else 10   # predict + 4 fused + finalize, or predict and finalize per substep
+        assert g.timings().kernel_launches == 3 * (5 * iters * passes + n_state), name
+        g.close()
+    monkeypatch.delenv("SPGX_XPBD_FUSE_STATE", raising=False)
+    for name in ("plain", "graph_unfused"):
+        assert np.array_equal(out["graph"][0], out[name][0]) and np.array_equal(out["graph"][1], out[name][1]), name
+
+
 def test_vbd_reset_upload_roundtrip(ctx):
     sc = S.cloth(9, 9)
     g = api.Group.from_scene(ctx, sc)
